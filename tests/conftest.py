@@ -1,0 +1,53 @@
+import json
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(ROOT, "vllm-production-stack_b200")
+for p in (ROOT, PKG):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+def pytest_collection_modifyitems(config, items):
+    # Without a device the gpu-marked tests cannot run; the driver selects them
+    # with -m gpu on the B200 box and with -m "not gpu" here.
+    try:
+        import torch
+        have = torch.cuda.is_available()
+    except Exception:
+        have = False
+    if have:
+        return
+    skip = pytest.mark.skip(reason="no CUDA device")
+    for it in items:
+        if "gpu" in it.keywords:
+            it.add_marker(skip)
+
+
+def load_golden(name):
+    with open(os.path.join(GOLDEN, name)) as f:
+        return json.load(f)
+
+
+@pytest.fixture(scope="session")
+def golden_prefix():
+    return load_golden("prefix_traces.json")
+
+
+@pytest.fixture(scope="session")
+def golden_xxh():
+    return load_golden("xxh64_kat.json")
+
+
+@pytest.fixture(scope="session")
+def golden_md5():
+    return load_golden("md5_ring_kat.json")
