@@ -1,0 +1,178 @@
+/*
+ * b200_router.h -- C ABI of libb200router.so (hand-written sm_100a CUDA).
+ *
+ * Drop-in boundary for the routing decision of vllm_router (reference paths are
+ * relative to the reference repository root):
+ *
+ *   prefix-aware routing   src/vllm_router/prefix/hashtrie.py:24-103
+ *                          src/vllm_router/routers/routing_logic.py:347-423
+ *   session routing        src/vllm_router/routers/routing_logic.py:84-103,170-219
+ *                          (+ third-party uhashring==2.3 HashRing it calls)
+ *
+ * Conventions
+ *   - Every pointer named d_* is DEVICE memory owned by the caller (e.g. a torch
+ *     tensor's data_ptr()).  Nothing here takes or returns torch types.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = default stream).  The
+ *     batch entry points only enqueue work: no host synchronisation, no
+ *     allocation.  Object create/destroy/dump/status calls do synchronise.
+ *   - Return value: 0 on success, a negative B200R_E_* code otherwise;
+ *     b200r_last_error() returns a thread-local message for the last failure.
+ *   - Errors detected on the device (table full, chunk capacity exceeded) are
+ *     latched in the object and reported by b200r_trie_status().
+ *   - There is no CPU fallback: without a CUDA device every compute entry point
+ *     fails with B200R_E_CUDA.
+ *
+ * Packed prompt layout ("prompt bytes plus offsets"): request i occupies
+ * d_bytes[d_starts[i] .. d_starts[i] + d_lens[i]) as UTF-8.  Requests whose
+ * start address is 16-byte aligned and that are pure ASCII take the fast path
+ * (cp.async staging, 16-byte vector loads); anything else is still hashed
+ * bit-exactly by a slower generic path.  d_nchars[i] is the number of Unicode
+ * code points of request i (Python's len(str)); chunking is by code points,
+ * hashing over the UTF-8 bytes, exactly like hashtrie.py:55-56.
+ */
+#ifndef B200_ROUTER_H
+#define B200_ROUTER_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default) /* the library is built with -fvisibility=hidden */
+#endif
+
+#define B200R_ABI_VERSION 1
+
+#define B200R_OK 0
+#define B200R_E_INVALID (-1)  /* bad argument                                  */
+#define B200R_E_CUDA (-2)     /* CUDA runtime error (message has the detail)    */
+#define B200R_E_NOMEM (-3)    /* device allocation failed                       */
+#define B200R_E_SCRATCH (-4)  /* scratch buffer too small                       */
+#define B200R_E_CAPACITY (-5) /* latched: table full / chunk capacity exceeded  */
+
+/* flags for the prompt entry points */
+#define B200R_F_ALL_ASCII 1u /* caller guarantees nchars[i] == lens[i] for all i */
+
+/* latched device status bits (b200r_trie_status) */
+#define B200R_S_TABLE_FULL 1u
+#define B200R_S_CHUNK_CAP 2u
+
+typedef struct b200r_trie b200r_trie; /* GPU-resident HashTrie replacement     */
+typedef struct b200r_ring b200r_ring; /* GPU-resident consistent-hash ring     */
+
+int b200r_abi_version(void);
+const char *b200r_last_error(void);
+
+/* ------------------------------------------------------------------------
+ * a1  HashTrie._chunk_and_hash                      hashtrie.py:45-56
+ * For every request: split into chunks of `chunk_chars` code points, XXH64
+ * (seed 0) each chunk.  Output is CSR: d_chunk_base[n+1] (int32, exclusive
+ * prefix sum of per-request chunk counts) and d_hashes[d_chunk_base[n]].
+ * max_chunks = capacity of d_hashes (host upper bound: sum ceil(len_i/chunk)).
+ * d_nchars may be NULL: the library then counts code points on the device.
+ * ---------------------------------------------------------------------- */
+size_t b200r_xxh64_chunks_scratch_bytes(int64_t n, int64_t max_chunks);
+int b200r_xxh64_chunks(const uint8_t *d_bytes, const int64_t *d_starts, const int32_t *d_lens,
+                       const int32_t *d_nchars, int64_t n, int32_t chunk_chars, uint32_t flags,
+                       int32_t *d_chunk_base, uint64_t *d_hashes, int64_t max_chunks,
+                       void *d_scratch, size_t scratch_bytes, void *stream);
+
+/* ------------------------------------------------------------------------
+ * a4/a6  TrieNode / HashTrie.__init__               hashtrie.py:24-43
+ * The pointer trie becomes an open-addressing table of 32-byte entries
+ * {path key (128 bit), chunk hash, endpoint bitmask}; capacity = 2^cap_log2
+ * entries (plus 8 bytes per entry of batch bookkeeping).  Endpoints are bit
+ * indices 0..63.  The reference never evicts, neither does the table: size it
+ * for the expected node count at load factor <= 0.5 (b200r_trie_status reports
+ * the node count; a full table latches B200R_S_TABLE_FULL).
+ * ---------------------------------------------------------------------- */
+int b200r_trie_create(int32_t cap_log2, int32_t chunk_chars, b200r_trie **out);
+int b200r_trie_destroy(b200r_trie *t);
+int b200r_trie_clear(b200r_trie *t, void *stream);
+/* synchronises `stream`; any of the outputs may be NULL */
+int b200r_trie_status(b200r_trie *t, void *stream, uint32_t *status_bits, int64_t *num_nodes,
+                      uint64_t *root_mask, int64_t *capacity);
+
+/* ------------------------------------------------------------------------
+ * a2  HashTrie.longest_prefix_match                 hashtrie.py:76-103
+ * Frozen-table lookup from chunk hashes (CSR as produced by a1).  Outputs per
+ * request: d_match_depth = matched chunks (reference match_length / chunk_size),
+ * d_matched_mask = selected endpoint set (avail_mask itself when depth is 0).
+ * ---------------------------------------------------------------------- */
+int b200r_trie_lookup_batch(b200r_trie *t, const uint64_t *d_hashes, const int32_t *d_chunk_base,
+                            int64_t n, uint64_t avail_mask, int32_t *d_match_depth,
+                            uint64_t *d_matched_mask, void *stream);
+
+/* ------------------------------------------------------------------------
+ * a3  HashTrie.insert                               hashtrie.py:58-74
+ * Adds d_endpoint[i] to the root and to every node on request i's path,
+ * creating missing nodes.  Order-independent (set union), so equal to the
+ * reference's sequential inserts.  Entries with d_endpoint[i] < 0 are skipped.
+ * ---------------------------------------------------------------------- */
+int b200r_trie_insert_batch(b200r_trie *t, const uint64_t *d_hashes, const int32_t *d_chunk_base,
+                            int64_t n, const int32_t *d_endpoint, void *stream);
+
+/* ------------------------------------------------------------------------
+ * a5  PrefixAwareRouter.route_request               routing_logic.py:414-423
+ * Fused batch: hash, lookup, tie-break, insert, with results equal to routing
+ * the n requests one after another in index order against the same table
+ * (SURVEY.md 7.3 H1).  avail_mask must be constant for the batch.  Tie-break:
+ * candidates in endpoint-index order, draw = b200r_pick(seed, seq0 + i, count).
+ * Outputs per request: d_endpoint (chosen bit index), d_match_depth,
+ * d_matched_mask (the candidate set the request drew from).
+ * ---------------------------------------------------------------------- */
+size_t b200r_prefix_route_scratch_bytes(int64_t n, int64_t max_chunks, uint32_t flags);
+int b200r_prefix_route_batch(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
+                             const int32_t *d_lens, const int32_t *d_nchars, int64_t n,
+                             int64_t max_chunks, uint32_t flags, uint64_t avail_mask,
+                             uint64_t seed, uint64_t seq0, int32_t *d_endpoint,
+                             int32_t *d_match_depth, uint64_t *d_matched_mask, void *d_scratch,
+                             size_t scratch_bytes, void *stream);
+/* the canonical draw, on the host (same arithmetic as the kernels) */
+uint32_t b200r_pick(uint64_t seed, uint64_t seq, uint32_t n);
+
+/* ------------------------------------------------------------------------
+ * Trie state export (parity / checkpoint; the reference has no counterpart
+ * beyond walking TrieNode.children, hashtrie.py:24-32).  Writes up to
+ * max_nodes entries {key_lo, key_hi, chunk_hash, mask} (4 x u64 each) to
+ * d_out and the number of occupied entries to *count (may exceed max_nodes).
+ * Synchronises.  Path keys are invertible: see DESIGN.md "Path keys".
+ * ---------------------------------------------------------------------- */
+int b200r_trie_dump(b200r_trie *t, uint64_t *d_out, int64_t max_nodes, int64_t *count,
+                    uint64_t *root_mask, void *stream);
+/* Re-insert dumped entries (checkpoint restore / multi-GPU merge of nodes
+ * created on other ranks): ORs mask into the entry with that key, creating it. */
+int b200r_trie_apply_remote(b200r_trie *t, const uint64_t *d_entries, int64_t count,
+                            uint64_t root_mask_or, void *stream);
+/* constants of the path-key recurrence, for host-side decoding of dumps:
+ * out[0..5] = {A1, A2, ROOT1, ROOT2, A1^-1, A2^-1} */
+void b200r_trie_key_constants(uint64_t out[6]);
+
+/* ------------------------------------------------------------------------
+ * a9  uhashring.HashRing (md5 points, bisect_right + wrap), a7 SessionRouter
+ *                                                   routing_logic.py:84-103,217
+ * b200r_md5_batch: 128-bit digests as the big-endian integer uhashring uses,
+ * d_out[2*i] = high 64 bits, d_out[2*i+1] = low 64 bits.
+ * b200r_ring_build: upload `npoints` ring points sorted ascending with their
+ * owner endpoint indices (HOST pointers; the ring is small).
+ * b200r_ring_lookup_batch: owner of the first point strictly greater than
+ * md5(key), wrapping to point 0; -1 when the ring is empty.
+ * ---------------------------------------------------------------------- */
+int b200r_md5_batch(const uint8_t *d_bytes, const int64_t *d_starts, const int32_t *d_lens,
+                    int64_t n, uint64_t *d_out, void *stream);
+int b200r_ring_create(b200r_ring **out);
+int b200r_ring_destroy(b200r_ring *r);
+int b200r_ring_build(b200r_ring *r, const uint64_t *h_points_hi, const uint64_t *h_points_lo,
+                     const int32_t *h_owner, int32_t npoints, void *stream);
+int b200r_ring_lookup_batch(b200r_ring *r, const uint8_t *d_bytes, const int64_t *d_starts,
+                            const int32_t *d_lens, int64_t n, int32_t *d_endpoint, void *stream);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_ROUTER_H */

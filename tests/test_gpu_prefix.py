@@ -1,0 +1,272 @@
+"""Parity of the CUDA prefix-routing path (through the C ABI) with the oracle
+and with the golden fixtures generated from the unmodified reference."""
+import asyncio
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import coracle, prefix_ref
+from b200_router import traces
+from b200_router.packing import pack_arrays, pack_prompts
+
+from helpers import bits, tight_pack, trie_as_sorted_list, u64
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture()
+def trie():
+    from b200_router.trie import GpuHashTrie
+    t = GpuHashTrie(cap_log2=18)
+    yield t
+    t.close()
+
+
+def _oracle_hashes(prompts):
+    return [coracle.xxh64_chunks(p.encode("utf-8"), 128) for p in prompts]
+
+
+def _check_hashes(trie, packed, prompts):
+    base, hs = trie.hash_chunks(packed)
+    base = base.cpu().numpy()
+    hs = u64(hs)
+    want = _oracle_hashes(prompts)
+    assert base[0] == 0
+    for i, w in enumerate(want):
+        assert base[i + 1] - base[i] == len(w), (i, len(prompts[i]))
+        assert (hs[base[i]:base[i + 1]] == w).all(), i
+
+
+def test_xxh64_known_answers(trie):
+    kat = {"": None, "a": 0xd24ec4f1a98c6e5b, "abc": 0x44bc2cf5ad770999,
+           "1" * 128: 0x2ceab0ab9ef63228, "a" * 128: 0x6550288941193272,
+           "hi " * 42 + "hi": 0x380de794396a43ea, "é" * 128: 0x9b2210ff98cf44b0}
+    prompts = list(kat)
+    base, hs = trie.hash_chunks(pack_prompts(prompts))
+    base, hs = base.cpu().numpy(), u64(hs)
+    for i, p in enumerate(prompts):
+        if kat[p] is None:
+            assert base[i + 1] == base[i]
+        else:
+            assert base[i + 1] - base[i] == 1 and int(hs[base[i]]) == kat[p], p
+
+
+def test_xxh64_golden_chunking(trie, golden_xxh):
+    texts = [c["text"] for c in golden_xxh["chunked"]]
+    base, hs = trie.hash_chunks(pack_prompts(texts))
+    base, hs = base.cpu().numpy(), u64(hs)
+    for i, c in enumerate(golden_xxh["chunked"]):
+        assert ["%016x" % int(h) for h in hs[base[i]:base[i + 1]]] == c["hashes"], i
+
+
+def test_xxh64_all_lengths_ascii_aligned(trie):
+    rng = np.random.default_rng(0)
+    prompts = ["".join(map(chr, rng.integers(32, 127, size=n))) for n in range(0, 520)]
+    prompts += ["".join(map(chr, rng.integers(32, 127, size=n))) for n in (1000, 4096, 4097, 33000)]
+    _check_hashes(trie, pack_prompts(prompts), prompts)
+
+
+def test_xxh64_unaligned_and_utf8(trie):
+    rng = np.random.default_rng(1)
+    alphabet = list("abcXYZ 01") + ["é", "ü", "日", "本", "🙂", "߿", "ࠀ", "\U00010000"]
+    prompts = ["".join(rng.choice(alphabet, size=n)) for n in list(range(0, 300, 7)) + [128, 129, 1000]]
+    prompts += ["", "x" * 5, ""]
+    _check_hashes(trie, pack_prompts(prompts), prompts)        # aligned, mixed ascii / utf-8
+    _check_hashes(trie, tight_pack(prompts), prompts)          # CSR-tight: unaligned starts
+
+
+def test_xxh64_device_counts_chars_when_nchars_missing(trie):
+    prompts = ["é" * 300, "abc", "日本語" * 100, ""]
+    p = pack_prompts(prompts)
+    p.nchars = None          # all_ascii stays False -> library must count code points itself
+    _check_hashes(trie, p, prompts)
+
+
+def _replay_golden(trie, tr):
+    seq = 0
+    dec, looks = [], []
+    for b in tr["batches"]:
+        if tr["json_inputs"] is not None:
+            prompts = [prefix_ref.flatten_prompt(tr["json_inputs"][i]) for i in b["prompts"]]
+        else:
+            prompts = b["prompts"]
+        avail = sum(1 << i for i in b["avail"])
+        ep, depth, matched = trie.route(pack_prompts(prompts), avail, tr["seed"], seq)
+        seq += len(prompts)
+        dec += ep.cpu().tolist()
+        looks += [[int(d), bits(m)] for d, m in zip(depth.cpu().tolist(), u64(matched))]
+    return dec, looks
+
+
+def test_route_golden_traces(golden_prefix):
+    """Decisions, per-request lookup results and final trie state equal the
+    unmodified reference's on every golden trace (batched per availability set)."""
+    from b200_router.trie import GpuHashTrie
+    for tr in golden_prefix["traces"]:
+        t = GpuHashTrie(cap_log2=14)
+        dec, looks = _replay_golden(t, tr)
+        assert dec == tr["decisions"], tr["name"]
+        if tr["lookups"] is not None:
+            assert looks == tr["lookups"], tr["name"]
+        st = t.check_status()
+        assert trie_as_sorted_list(t.dump()) == tr["trie"], tr["name"]
+        assert st["num_nodes"] == len(tr["trie"]) - 1
+        t.close()
+
+
+def test_route_golden_traces_one_request_per_batch(golden_prefix):
+    """Same traces with batch size 1: the degenerate sequential schedule."""
+    from b200_router.trie import GpuHashTrie
+    tr = golden_prefix["traces"][1]
+    t = GpuHashTrie(cap_log2=14)
+    seq, dec = 0, []
+    for b in tr["batches"]:
+        avail = sum(1 << i for i in b["avail"])
+        for p in b["prompts"]:
+            ep, _, _ = t.route(pack_prompts([p]), avail, tr["seed"], seq)
+            seq += 1
+            dec.append(int(ep.cpu()[0]))
+    assert dec == tr["decisions"]
+    assert trie_as_sorted_list(t.dump()) == tr["trie"]
+    t.close()
+
+
+def _route_vs_oracle(trie, batches, seed, chunk=128):
+    """batches: [(avail_mask, buf, starts, lens)] -> compares everything."""
+    orc = coracle.TrieOracle(chunk)
+    seq = 0
+    for avail, buf, starts, lens in batches:
+        ep, depth, matched = trie.route(pack_arrays(buf, starts, lens, pin=False), avail, seed, seq)
+        oep, odepth, omatched = orc.route_batch(buf, starts, lens, avail, seed, seq)
+        seq += len(starts)
+        assert (ep.cpu().numpy() == oep).all()
+        assert (depth.cpu().numpy() == odepth).all()
+        assert (u64(matched) == omatched).all()
+    trie.check_status()
+    assert trie.dump() == orc.dump()
+    return orc
+
+
+def test_route_shared_prefix_with_churn_vs_oracle():
+    """C3-shaped trace, scaled down: shared system prompts + unique suffixes,
+    one endpoint dropped for two batches and restored (multi-bit masks)."""
+    from b200_router.trie import GpuHashTrie
+    tr = traces.SharedPrefixTrace(n_total=24000, batch=4096, n_sys=16, sys_chars=512,
+                                  suffix_lo=100, suffix_hi=400, seed=3)
+    full = 0xFF
+    batches = []
+    for b in range(tr.num_batches()):
+        avail = full & ~(1 << 2) if b in (2, 3) else full
+        batches.append((avail,) + tr.batch_arrays(b))
+    t = GpuHashTrie(cap_log2=19)
+    _route_vs_oracle(t, batches, seed=42)
+    t.close()
+
+
+def test_route_heavy_sharing_random_vs_oracle():
+    """Many small random traces with tiny alphabets: long leader chains, every
+    availability subset, empty prompts, partial last chunks."""
+    from b200_router.trie import GpuHashTrie
+    for s in range(12):
+        t = GpuHashTrie(cap_log2=12)
+        batches = []
+        for avail_idx, prompts in traces.sharing_stress(n_batches=5, batch=150, n_endpoints=7,
+                                                        max_depth=6, alphabet=2, seed=1000 + s):
+            buf, starts, lens, _ = traces.pack_strings(prompts)
+            batches.append((sum(1 << i for i in avail_idx), buf, starts, lens))
+        _route_vs_oracle(t, batches, seed=s)
+        t.close()
+
+
+def test_route_long_prompts_many_blocks_vs_oracle():
+    """Prompts of more than 32 chunks (several warp iterations, carried path key)."""
+    from b200_router.trie import GpuHashTrie
+    buf, starts, lens = traces.long_context_batch(n=96, chars=128 * 70 + 5, group=8,
+                                                  shared_frac=0.6, seed=5)
+    t = GpuHashTrie(cap_log2=15)
+    half = len(starts) // 2
+    _route_vs_oracle(t, [((1 << 64) - 1, buf, starts[:half], lens[:half]),
+                         (0x0F0F, buf, starts[half:], lens[half:]),
+                         ((1 << 64) - 1, buf, starts, lens)], seed=9)
+    t.close()
+
+
+def test_lookup_and_insert_batches_vs_oracle(trie):
+    """a2 / a3 entry points on their own: externally chosen endpoints."""
+    rng = np.random.default_rng(7)
+    orc = coracle.TrieOracle()
+    for rnd in range(4):
+        _, prompts = traces.sharing_stress(n_batches=1, batch=300, max_depth=5, alphabet=3,
+                                           seed=50 + rnd)[0]
+        buf, starts, lens, _ = traces.pack_strings(prompts)
+        p = pack_arrays(buf, starts, lens, pin=False)
+        ep = rng.integers(0, 9, size=len(prompts)).astype(np.int32)
+        trie.insert(p, torch.from_numpy(ep))
+        orc.insert_batch(buf, starts, lens, ep)
+        for avail in (0x1FF, 0x5, 0x100, 0x0):
+            d, m = trie.longest_prefix_match(p, avail)
+            od, om = orc.lookup_batch(buf, starts, lens, avail)
+            assert (d.cpu().numpy() == od).all()
+            assert (u64(m) == om).all()
+    assert trie.dump() == orc.dump()
+
+
+def test_dump_restore_roundtrip(trie):
+    from b200_router.trie import GpuHashTrie
+    _, prompts = traces.sharing_stress(n_batches=1, batch=200, seed=77)[0]
+    p = pack_prompts(prompts)
+    trie.route(p, 0x3F, 1, 0)
+    arr, root = trie.dump_raw()
+    t2 = GpuHashTrie(cap_log2=13)
+    t2.apply_entries(torch.from_numpy(arr.view(np.int64).copy()), root)
+    assert t2.dump() == trie.dump()
+    assert t2.status()["num_nodes"] == trie.status()["num_nodes"]
+    d1, m1 = trie.longest_prefix_match(p, 0x3F)
+    d2, m2 = t2.longest_prefix_match(p, 0x3F)
+    assert torch.equal(d1, d2) and torch.equal(m1, m2)
+    t2.close()
+
+
+def test_table_full_is_reported():
+    from b200_router import B200RouterError
+    from b200_router.trie import GpuHashTrie
+    t = GpuHashTrie(cap_log2=4)          # 16 entries
+    prompts = ["%03d" % i * 100 for i in range(40)]
+    t.route(pack_prompts(prompts), 0x3, 0, 0)
+    with pytest.raises(B200RouterError):
+        t.check_status()
+    t.close()
+
+
+def test_router_e2e_prefix_families():
+    """The reference's e2e assertion (tests/e2e/test-routing.py:299-418): every
+    nested-prompt family lands on one endpoint."""
+    from b200_router import routers
+    routers._reset_singletons_for_tests()
+    r = routers.initialize_routing_logic("prefixaware")
+    assert routers.get_routing_logic() is r and isinstance(r, routers.PrefixAwareRouter)
+
+    class Ep:
+        def __init__(self, url): self.url = url
+    eps = [Ep("http://localhost:8001"), Ep("http://localhost:8002")]
+    c = 128
+    fams = [["1" * c, "1" * c + "2" * c, "1" * c + "2" * c + "3" * c],
+            ["2" * c + "3" * c + "4" * c, "2" * c + "3" * c, "2" * c],
+            ["5" * c, "5" * c + "6" * c, "5" * c + "6" * c + "7" * c]]
+
+    async def go():
+        seen = []
+        for fam in fams:
+            urls = set()
+            for sample in fam:
+                for _ in range(5):
+                    urls.add(await r.route_request(eps, None, None, None,
+                                                   {"messages": [{"role": "user", "content": sample}]}))
+            seen.append(urls)
+        return seen
+    for urls in asyncio.run(go()):
+        assert len(urls) == 1
+    with pytest.raises(KeyError):
+        asyncio.run(r.route_request(eps, None, None, None, {"nothing": 1}))
+    routers._reset_singletons_for_tests()

@@ -1,0 +1,221 @@
+"""GPU-resident replacement of the reference HashTrie.
+
+Mirrors src/vllm_router/prefix/hashtrie.py (HashTrie: _chunk_and_hash, insert,
+longest_prefix_match) with batch methods over packed prompts; every method calls
+the C ABI (include/b200_router.h) on the current CUDA stream.  No CPU fallback.
+"""
+import ctypes as C
+from typing import Dict, Optional, Tuple
+
+import numpy as np
+import torch
+
+from . import _lib
+from .packing import PackedPrompts
+
+M64 = (1 << 64) - 1
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class GpuHashTrie:
+    """Open-addressing table of trie nodes on one GPU.
+
+    capacity = 2**cap_log2 entries of 32 bytes (+8 bytes bookkeeping each).  The
+    reference never evicts (routing_logic.py:352) and neither does the table;
+    `status()` reports the node count, a full table raises."""
+
+    def __init__(self, cap_log2: int = 22, chunk_chars: int = 128, device=None):
+        torch_ = _lib.require_cuda()
+        self.device = torch_.device("cuda", torch_.cuda.current_device()) if device is None \
+            else torch_.device(device)
+        self.cap_log2 = cap_log2
+        self.chunk_chars = chunk_chars
+        self._h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().b200r_trie_create(cap_log2, chunk_chars, C.byref(self._h)))
+        self._scratch = None
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            _lib.lib().b200r_trie_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------ utils
+    def _scratch_for(self, nbytes: int) -> torch.Tensor:
+        if self._scratch is None or self._scratch.numel() < nbytes:
+            self._scratch = torch.empty(int(nbytes * 1.25) + 4096, dtype=torch.uint8,
+                                        device=self.device)
+        return self._scratch
+
+    def reserve(self, n: int, max_chunks: int, all_ascii: bool = True):
+        """Pre-size the scratch buffer (so the hot loop never allocates)."""
+        flags = _lib.F_ALL_ASCII if all_ascii else 0
+        self._scratch_for(_lib.lib().b200r_prefix_route_scratch_bytes(n, max_chunks, flags))
+
+    def _dev(self, p: PackedPrompts) -> PackedPrompts:
+        return p if p.bytes.device == self.device else p.to(self.device)
+
+    def clear(self):
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().b200r_trie_clear(self._h, _stream()))
+
+    def status(self) -> Dict[str, int]:
+        st, nn, rm, cap = C.c_uint32(), C.c_int64(), C.c_uint64(), C.c_int64()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().b200r_trie_status(self._h, _stream(), C.byref(st), C.byref(nn),
+                                                    C.byref(rm), C.byref(cap)))
+        return {"status": st.value, "num_nodes": nn.value, "root_mask": rm.value,
+                "capacity": cap.value}
+
+    def check_status(self):
+        s = self.status()
+        if s["status"] & _lib.S_TABLE_FULL:
+            raise _lib.B200RouterError("GPU trie table is full (%d nodes, capacity %d): create it "
+                                       "with a larger cap_log2" % (s["num_nodes"], s["capacity"]))
+        if s["status"] & _lib.S_CHUNK_CAP:
+            raise _lib.B200RouterError("chunk capacity exceeded: max_chunks was too small")
+        return s
+
+    # -------------------------------------------------------------------- a1
+    def hash_chunks(self, p: PackedPrompts) -> Tuple[torch.Tensor, torch.Tensor]:
+        """HashTrie._chunk_and_hash for a batch: (chunk_base int32[n+1], hashes int64[...])."""
+        p = self._dev(p)
+        L = _lib.lib()
+        chunk_base = torch.empty(p.n + 1, dtype=torch.int32, device=self.device)
+        hashes = torch.empty(max(p.max_chunks, 1), dtype=torch.int64, device=self.device)
+        need = L.b200r_xxh64_chunks_scratch_bytes(p.n, p.max_chunks)
+        sc = self._scratch_for(need)
+        flags = _lib.F_ALL_ASCII if p.all_ascii else 0
+        with torch.cuda.device(self.device):
+            _lib.check(L.b200r_xxh64_chunks(_ptr(p.bytes), _ptr(p.starts), _ptr(p.lens),
+                                            _ptr(p.nchars), p.n, self.chunk_chars, flags,
+                                            _ptr(chunk_base), _ptr(hashes), p.max_chunks,
+                                            _ptr(sc), sc.numel(), _stream()))
+        return chunk_base, hashes
+
+    # -------------------------------------------------------------------- a2
+    def longest_prefix_match(self, p: PackedPrompts, avail_mask: int):
+        """Batch of HashTrie.longest_prefix_match: (depth int32[n], matched int64[n])."""
+        chunk_base, hashes = self.hash_chunks(p)
+        return self.lookup_hashes(hashes, chunk_base, p.n, avail_mask)
+
+    def lookup_hashes(self, hashes, chunk_base, n: int, avail_mask: int):
+        depth = torch.empty(max(n, 1), dtype=torch.int32, device=self.device)
+        matched = torch.empty(max(n, 1), dtype=torch.int64, device=self.device)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().b200r_trie_lookup_batch(self._h, _ptr(hashes), _ptr(chunk_base), n,
+                                                          avail_mask & M64, _ptr(depth),
+                                                          _ptr(matched), _stream()))
+        return depth[:n], matched[:n]
+
+    # -------------------------------------------------------------------- a3
+    def insert(self, p: PackedPrompts, endpoint_idx: torch.Tensor):
+        """Batch of HashTrie.insert (endpoint given as bit index per request)."""
+        chunk_base, hashes = self.hash_chunks(p)
+        self.insert_hashes(hashes, chunk_base, p.n, endpoint_idx)
+
+    def insert_hashes(self, hashes, chunk_base, n: int, endpoint_idx: torch.Tensor):
+        ep = endpoint_idx.to(device=self.device, dtype=torch.int32).contiguous()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().b200r_trie_insert_batch(self._h, _ptr(hashes), _ptr(chunk_base), n,
+                                                          _ptr(ep), _stream()))
+
+    # -------------------------------------------------------------------- a5
+    def route(self, p: PackedPrompts, avail_mask: int, seed: int, seq0: int, out=None):
+        """Fused lookup + tie-break + insert for a batch, equal to routing the
+        requests sequentially in index order.  Returns device tensors
+        (endpoint int32[n], depth int32[n], matched int64[n])."""
+        p = self._dev(p)
+        L = _lib.lib()
+        n = p.n
+        if out is None:
+            out = (torch.empty(max(n, 1), dtype=torch.int32, device=self.device),
+                   torch.empty(max(n, 1), dtype=torch.int32, device=self.device),
+                   torch.empty(max(n, 1), dtype=torch.int64, device=self.device))
+        ep, depth, matched = out
+        flags = _lib.F_ALL_ASCII if p.all_ascii else 0
+        sc = self._scratch_for(L.b200r_prefix_route_scratch_bytes(n, p.max_chunks, flags))
+        with torch.cuda.device(self.device):
+            _lib.check(L.b200r_prefix_route_batch(
+                self._h, _ptr(p.bytes), _ptr(p.starts), _ptr(p.lens), _ptr(p.nchars), n,
+                p.max_chunks, flags, avail_mask & M64, seed & M64, seq0 & M64, _ptr(ep), _ptr(depth),
+                _ptr(matched), _ptr(sc), sc.numel(), _stream()))
+        return ep[:n], depth[:n], matched[:n]
+
+    # --------------------------------------------------------------- dump etc
+    def dump_raw(self):
+        """(entries uint64[count,4] = key_lo,key_hi,chunk_hash,mask ; root_mask)."""
+        s = self.status()
+        cap = max(int(s["num_nodes"]), 1)
+        out = torch.empty(cap * 4, dtype=torch.int64, device=self.device)
+        cnt, rm = C.c_int64(), C.c_uint64()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().b200r_trie_dump(self._h, _ptr(out), cap, C.byref(cnt), C.byref(rm),
+                                                  _stream()))
+        if cnt.value > cap:
+            raise _lib.B200RouterError("dump overflow: %d > %d" % (cnt.value, cap))
+        arr = out.cpu().numpy().view(np.uint64).reshape(-1, 4)[:cnt.value]
+        return arr, rm.value
+
+    def apply_entries(self, entries: torch.Tensor, root_mask_or: int = 0):
+        """Merge dumped entries (restore / nodes created on another GPU)."""
+        ent = entries.to(self.device).contiguous()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().b200r_trie_apply_remote(self._h, _ptr(ent), ent.numel() // 4,
+                                                          root_mask_or & M64, _stream()))
+
+    def dump(self) -> Dict[tuple, int]:
+        """Decode the table back into the reference's shape:
+        {tuple(chunk hashes from the root): mask}; () is the root."""
+        arr, root = self.dump_raw()
+        return decode_dump(arr, root)
+
+
+def key_constants():
+    out = (C.c_uint64 * 6)()
+    _lib.lib().b200r_trie_key_constants(out)
+    return [int(x) for x in out]
+
+
+def _rotl32of64(h: int) -> int:
+    return ((h << 32) | (h >> 32)) & M64
+
+
+def decode_dump(arr: np.ndarray, root_mask: int) -> Dict[tuple, int]:
+    """Invert the path-key recurrence (csrc/common.cuh): parent key =
+    ((k1 - h) * A1^-1, (k2 - rotl(h,32)) * A2^-1); walk up to the root key."""
+    a1, a2, r1, r2, i1, i2 = key_constants()
+    nodes = {(int(k1), int(k2)): (int(h), int(m)) for k1, k2, h, m in arr}
+    paths: Dict[Tuple[int, int], tuple] = {(r1, r2): ()}
+
+    def path_of(key):
+        chain = []
+        while key not in paths:
+            if key not in nodes:
+                raise ValueError("dump is not prefix-closed: missing parent of a node")
+            h, _ = nodes[key]
+            chain.append((key, h))
+            key = (((key[0] - h) * i1) & M64, ((key[1] - _rotl32of64(h)) * i2) & M64)
+        base = paths[key]
+        for k, h in reversed(chain):
+            base = base + (h,)
+            paths[k] = base
+        return base
+
+    out = {(): int(root_mask)}
+    for key, (h, m) in nodes.items():
+        out[path_of(key)] = m
+    return out

@@ -1,0 +1,881 @@
+// prefix.cu -- batched prefix-aware routing on sm_100a.
+//
+// Replaces, behind the C ABI of include/b200_router.h, the reference's
+//   HashTrie._chunk_and_hash / longest_prefix_match / insert
+//       (src/vllm_router/prefix/hashtrie.py:45-103)
+//   PrefixAwareRouter.route_request lookup -> choice -> insert
+//       (src/vllm_router/routers/routing_logic.py:414-423)
+//
+// Kernel pipeline of one routed batch (all on one stream, no host sync):
+//   k_prep_sums / k_prep_scan   chunk counts -> CSR chunk_base, tile map
+//   [k_count_chars, k_utf8_bounds   only for batches that are not pure ASCII]
+//   k_hash_chunks               XXH64 of every chunk, one thread per chunk,
+//                               bytes staged by cp.async into swizzled smem
+//   k_claim                     path keys (warp scan) + find-or-create in the
+//                               open-addressing table + "first toucher" atomicMin
+//   k_select                    per request: deepest usable node, root draw or leader
+//   k_commit                    resolve leader chains, OR the endpoint into new nodes
+#include <cstdarg>
+
+#include "common.cuh"
+
+namespace b200r {
+
+// ------------------------------------------------------------------- errors
+static thread_local char g_err[512] = "";
+
+void set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char *what)
+{
+    set_error("%s: %s", what, cudaGetErrorString(e));
+    return e == cudaErrorMemoryAllocation ? B200R_E_NOMEM : B200R_E_CUDA;
+}
+
+constexpr int TILE = 256;          // chunks per CTA of k_hash_chunks
+constexpr int PREP_BLOCK = 1024;   // requests per CTA of the prep kernels
+constexpr int WARPS_PER_CTA = 8;   // per-request kernels: one warp per request
+
+// =========================================================================
+// Prep: per-request chunk counts -> exclusive scan (CSR) + tile -> request map
+// =========================================================================
+__device__ __forceinline__ int chunks_of(const int32_t *lens, const int32_t *nchars, int i, int cc)
+{
+    int nc = nchars ? nchars[i] : lens[i];
+    return (nc + cc - 1) / cc;
+}
+
+__device__ __forceinline__ int block_sum_1024(int v, int *s_red)
+{   // all 1024 threads get the block total
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) s_red[w] = v;
+    __syncthreads();
+    int t = s_red[lane];
+    for (int o = 16; o; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    __syncthreads();
+    return t;
+}
+
+__global__ void __launch_bounds__(PREP_BLOCK)
+k_prep_sums(const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars, int n, int cc,
+            int32_t *__restrict__ block_sums)
+{
+    __shared__ int s_red[32];
+    int i = blockIdx.x * PREP_BLOCK + threadIdx.x;
+    int c = (i < n) ? chunks_of(lens, nchars, i, cc) : 0;
+    int tot = block_sum_1024(c, s_red);
+    if (threadIdx.x == 0) block_sums[blockIdx.x] = tot;
+}
+
+__global__ void __launch_bounds__(PREP_BLOCK)
+k_prep_scan(const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars, int n, int cc,
+            const int32_t *__restrict__ block_sums, int32_t *__restrict__ chunk_base,
+            int32_t *__restrict__ tile_first, int64_t max_chunks, TrieDev *dev)
+{
+    __shared__ int s_red[32];
+    __shared__ int s_wsum[32];
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    // offset of this block = sum of the sums of all earlier blocks
+    int part = 0;
+    for (int b = tid; b < (int)blockIdx.x; b += PREP_BLOCK) part += block_sums[b];
+    const int offset = block_sum_1024(part, s_red);
+
+    const int i = blockIdx.x * PREP_BLOCK + tid;
+    const int c = (i < n) ? chunks_of(lens, nchars, i, cc) : 0;
+    int inc = c;                                    // inclusive warp scan
+    for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) s_wsum[w] = inc;
+    __syncthreads();
+    int wbase = 0;
+    for (int k = 0; k < w; k++) wbase += s_wsum[k];
+    const int base = offset + wbase + inc - c;      // exclusive prefix
+    if (i < n) {
+        chunk_base[i] = base;
+        if (i == n - 1) {
+            chunk_base[n] = base + c;
+            if (dev && (int64_t)(base + c) > max_chunks) atomicOr(&dev->status, B200R_S_CHUNK_CAP);
+        }
+        // tiles whose first chunk belongs to this request
+        if (c > 0) {
+            int t0 = (base + TILE - 1) / TILE;
+            int64_t lim = (int64_t)base + c;
+            if (lim > max_chunks) lim = max_chunks;
+            for (int t = t0; (int64_t)t * TILE < lim; t++) tile_first[t] = i;
+        }
+    }
+}
+
+// code points of each request (only when the caller did not supply nchars)
+__global__ void k_count_chars(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ starts,
+                              const int32_t *__restrict__ lens, int n, int32_t *__restrict__ nchars)
+{
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= n) return;
+    const uint8_t *p = bytes + starts[warp];
+    const int len = lens[warp];
+    int cnt = 0;
+    for (int o = lane; o < len; o += 32) cnt += ((p[o] & 0xC0) != 0x80);
+    for (int o = 16; o; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    if (lane == 0) nchars[warp] = cnt;
+}
+
+// byte offset (inside the request) of every chunk start, for non-ASCII requests
+__global__ void k_utf8_bounds(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ starts,
+                              const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars,
+                              const int32_t *__restrict__ chunk_base, int n, int cc,
+                              int64_t max_chunks, int32_t *__restrict__ chunk_off)
+{
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= n) return;
+    const int len = lens[warp];
+    if (nchars[warp] == len) return;             // ASCII: offsets are arithmetic
+    const uint8_t *p = bytes + starts[warp];
+    const int b0 = chunk_base[warp];
+    int run = 0;                                  // code points before this block
+    for (int o = 0; o < len; o += 32) {
+        int pos = o + lane;
+        bool lead = pos < len && ((p[pos] & 0xC0) != 0x80);
+        unsigned bal = __ballot_sync(0xffffffffu, lead);
+        int idx = run + __popc(bal & ((1u << lane) - 1));
+        if (lead && idx % cc == 0) {
+            int64_t g = (int64_t)b0 + idx / cc;
+            if (g < max_chunks) chunk_off[g] = pos;
+        }
+        run += __popc(bal);
+    }
+}
+
+// =========================================================================
+// Chunk hashing
+// =========================================================================
+__device__ __forceinline__ void cp_async16(uint32_t smem_dst, const void *src, int src_bytes)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(smem_dst), "l"(src),
+                 "r"(src_bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all()
+{
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
+}
+
+// XXH64 of one staged chunk.  `row` = the chunk's 128-byte row in shared
+// memory, whose 16-byte units are XOR-swizzled by `sw` (= row index & 7) so
+// that the 8 lanes of an LDS.128 phase hit 8 different bank groups.
+__device__ __forceinline__ uint64_t xxh64_staged(const uint8_t *row, int sw, int len)
+{
+#define UNIT(u) (*(const uint4 *)(row + ((((u)) ^ sw) << 4)))
+#define BYTE_AT(o) (row[((((o) >> 4) ^ sw) << 4) | ((o)&15)])
+    uint64_t h;
+    const int nst = len >> 5;
+    if (nst) {
+        uint64_t v1 = XP1 + XP2, v2 = XP2, v3 = 0, v4 = 0 - XP1;
+#pragma unroll
+        for (int s = 0; s < 4; s++) {
+            if (s < nst) {
+                uint4 a = UNIT(2 * s), b = UNIT(2 * s + 1);
+                v1 = xround(v1, u64_of(a.x, a.y));
+                v2 = xround(v2, u64_of(a.z, a.w));
+                v3 = xround(v3, u64_of(b.x, b.y));
+                v4 = xround(v4, u64_of(b.z, b.w));
+            }
+        }
+        h = rotl64(v1, 1) + rotl64(v2, 7) + rotl64(v3, 12) + rotl64(v4, 18);
+        h = xmerge(h, v1); h = xmerge(h, v2); h = xmerge(h, v3); h = xmerge(h, v4);
+    } else {
+        h = XP5;
+    }
+    h += (uint64_t)len;
+    int o = nst << 5;
+    // 8- and 4-byte steps never straddle a 16-byte unit (o is a multiple of 4/8)
+    while (o + 8 <= len) {
+        uint64_t w = *(const uint64_t *)(row + ((((o >> 4) ^ sw) << 4) | (o & 15)));
+        h ^= xround(0, w);
+        h = rotl64(h, 27) * XP1 + XP4;
+        o += 8;
+    }
+    if (o + 4 <= len) {
+        uint32_t w = *(const uint32_t *)(row + ((((o >> 4) ^ sw) << 4) | (o & 15)));
+        h ^= (uint64_t)w * XP1;
+        h = rotl64(h, 23) * XP2 + XP3;
+        o += 4;
+    }
+    while (o < len) {
+        h ^= (uint64_t)BYTE_AT(o) * XP5;
+        h = rotl64(h, 11) * XP1;
+        o++;
+    }
+    return xavalanche(h);
+#undef UNIT
+#undef BYTE_AT
+}
+
+__global__ void __launch_bounds__(TILE)
+k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ starts,
+              const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars,
+              const int32_t *__restrict__ chunk_base, const int32_t *__restrict__ tile_first,
+              const int32_t *__restrict__ chunk_off, int n, int cc, int64_t max_chunks,
+              uint64_t *__restrict__ hashes)
+{
+    __shared__ __align__(128) uint8_t s_tile[TILE * 128];
+    __shared__ int s_req[TILE];
+    __shared__ int s_wmax[TILE / 32];
+    __shared__ unsigned long long s_src[TILE];
+    __shared__ int s_len[TILE];
+
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const int64_t G0 = (int64_t)blockIdx.x * TILE;
+    int64_t total = chunk_base[n];
+    if (total > max_chunks) total = max_chunks;
+    if (G0 >= total) return;
+
+    // ---- which request does each chunk of the tile belong to?
+    const int r0 = tile_first[blockIdx.x];
+    s_req[tid] = (tid == 0) ? r0 : 0;
+    __syncthreads();
+    for (int r = r0 + 1 + tid; r < n; r += TILE) {
+        int64_t b = chunk_base[r];
+        if (b >= G0 + TILE) break;
+        if (chunk_base[r + 1] > b) s_req[(int)(b - G0)] = r;    // head of a non-empty request
+    }
+    __syncthreads();
+    int r = s_req[tid];
+    for (int o = 1; o < 32; o <<= 1) {                          // inclusive max-scan
+        int t = __shfl_up_sync(0xffffffffu, r, o);
+        if (lane >= o) r = max(r, t);
+    }
+    if (lane == 31) s_wmax[w] = r;
+    __syncthreads();
+    for (int k = 0; k < w; k++) r = max(r, s_wmax[k]);
+
+    // ---- chunk descriptor
+    const int64_t g = G0 + tid;
+    const bool valid = g < total;
+    const uint8_t *p = nullptr;
+    int clen = 0;
+    bool fast = false;
+    if (valid) {
+        const int d = (int)(g - chunk_base[r]);
+        const int ln = lens[r];
+        const int nc = nchars ? nchars[r] : ln;
+        int off;
+        if (nc == ln) {                          // ASCII: chunk = cc bytes
+            off = d * cc;
+            clen = min(cc, ln - off);
+        } else {                                 // code-point boundaries from k_utf8_bounds
+            off = chunk_off[g];
+            int end = (g + 1 < (int64_t)chunk_base[r + 1] && g + 1 < max_chunks) ? chunk_off[g + 1] : ln;
+            clen = end - off;
+        }
+        p = bytes + starts[r] + off;
+        fast = (clen <= 128) && (((uintptr_t)p & 15) == 0);
+    }
+    s_src[tid] = fast ? (unsigned long long)(uintptr_t)p : 0ULL;
+    s_len[tid] = fast ? clen : 0;
+    __syncthreads();
+
+    // ---- stage: 8 x 16-byte units per chunk, coalesced over the tile
+    const uint32_t tile_s = (uint32_t)__cvta_generic_to_shared(s_tile);
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        int item = k * TILE + tid;
+        int c = item >> 3, u = item & 7;
+        int rem = s_len[c] - (u << 4);
+        if (rem > 0) {
+            const uint8_t *src = (const uint8_t *)(uintptr_t)s_src[c] + (u << 4);
+            cp_async16(tile_s + c * 128 + ((u ^ (c & 7)) << 4), src, rem < 16 ? rem : 16);
+        }
+    }
+    cp_async_wait_all();
+    __syncthreads();
+
+    if (!valid) return;
+    uint64_t h = fast ? xxh64_staged(s_tile + tid * 128, tid & 7, clen) : xxh64_global(p, clen);
+    hashes[g] = h;
+}
+
+// =========================================================================
+// Table kernels (one warp per request, lanes = chunk depths)
+// =========================================================================
+struct ReqSpan { int b0, C; };
+
+__device__ __forceinline__ ReqSpan req_span(const int32_t *chunk_base, int i, int64_t max_chunks)
+{
+    ReqSpan s;
+    s.b0 = chunk_base[i];
+    int64_t e = chunk_base[i + 1];
+    if (e > max_chunks) e = max_chunks;
+    s.C = (e > s.b0) ? (int)(e - s.b0) : 0;
+    return s;
+}
+
+// a2: frozen-table longest prefix match.  All depths of a 32-chunk block are
+// probed in parallel; the first miss is located with __ballot_sync/__ffs.
+// Relies on the trie invariant child.endpoints subset-of parent.endpoints
+// (inserts add the endpoint to every node of a path), so the reference's
+// running intersection equals mask(node) & avail.
+__global__ void __launch_bounds__(WARPS_PER_CTA * 32)
+k_lookup(const Entry *__restrict__ tab, int cap_log2, const uint64_t *__restrict__ hashes,
+         const int32_t *__restrict__ chunk_base, int n, uint64_t avail,
+         int32_t *__restrict__ depth_out, uint64_t *__restrict__ matched_out)
+{
+    const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (i >= n) return;
+    const ReqSpan sp = req_span(chunk_base, i, INT64_MAX);
+    Key carry = { KROOT1, KROOT2 };
+    int depth = 0;
+    uint64_t sel = avail;
+    for (int blk = 0; blk * 32 < sp.C; blk++) {
+        const int d = blk * 32 + lane;
+        const bool valid = d < sp.C;
+        const uint64_t h = valid ? hashes[sp.b0 + d] : 0;
+        const Key k = key_scan_warp(h, carry, lane);
+        carry.k1 = __shfl_sync(0xffffffffu, k.k1, 31);
+        carry.k2 = __shfl_sync(0xffffffffu, k.k2, 31);
+        uint64_t m = 0;
+        if (valid) {
+            uint32_t s = table_find(tab, cap_log2, k.k1, k.k2);
+            if (s != SLOT_NONE) m = tab[s].mask & avail;
+        }
+        const unsigned bal = __ballot_sync(0xffffffffu, m != 0);
+        const int nok = (bal == 0xffffffffu) ? 32 : (__ffs(~bal) - 1);
+        if (nok > 0) {
+            sel = __shfl_sync(0xffffffffu, m, nok - 1);
+            depth += nok;
+        }
+        if (nok < 32) break;
+    }
+    if (lane == 0) {
+        depth_out[i] = depth;
+        matched_out[i] = sel;
+    }
+}
+
+__device__ __forceinline__ void count_created(TrieDev *dev, bool created)
+{
+    unsigned bal = __ballot_sync(0xffffffffu, created);
+    if (bal && (threadIdx.x & 31) == (__ffs(bal) - 1))
+        atomicAdd(&dev->num_nodes, (unsigned long long)__popc(bal));
+}
+
+// a3: order-independent batched insert.
+__global__ void __launch_bounds__(WARPS_PER_CTA * 32)
+k_insert(Entry *__restrict__ tab, int cap_log2, TrieDev *dev, const uint64_t *__restrict__ hashes,
+         const int32_t *__restrict__ chunk_base, int n, const int32_t *__restrict__ endpoint)
+{
+    const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (i >= n) return;
+    const int e = endpoint[i];
+    if (e < 0 || e > 63) return;
+    const uint64_t bit = 1ULL << e;
+    if (lane == 0 && !(dev->root_mask & bit)) atomicOr((unsigned long long *)&dev->root_mask, bit);
+    const ReqSpan sp = req_span(chunk_base, i, INT64_MAX);
+    Key carry = { KROOT1, KROOT2 };
+    for (int blk = 0; blk * 32 < sp.C; blk++) {
+        const int d = blk * 32 + lane;
+        const bool valid = d < sp.C;
+        const uint64_t h = valid ? hashes[sp.b0 + d] : 0;
+        const Key k = key_scan_warp(h, carry, lane);
+        carry.k1 = __shfl_sync(0xffffffffu, k.k1, 31);
+        carry.k2 = __shfl_sync(0xffffffffu, k.k2, 31);
+        bool created = false;
+        if (valid) {
+            uint32_t s = table_claim(tab, cap_log2, k.k1, k.k2, h, &created);
+            if (s == SLOT_NONE) atomicOr(&dev->status, B200R_S_TABLE_FULL);
+            else if (created || !(tab[s].mask & bit))
+                atomicOr((unsigned long long *)&tab[s].mask, bit);
+        }
+        count_created(dev, created);
+    }
+}
+
+// a5 step 1: claim every node of every path; classify against the pre-batch
+// masks; record who touches a not-yet-usable node first.
+//   slots[g] = slot | PREOK_BIT   node usable before the batch (mask & avail != 0)
+//   slots[g] = slot               otherwise; first[slot] = min request index (epoch-tagged)
+constexpr uint32_t PREOK_BIT = 0x80000000u;
+
+__global__ void __launch_bounds__(WARPS_PER_CTA * 32)
+k_claim(Entry *__restrict__ tab, int cap_log2, unsigned long long *__restrict__ first, TrieDev *dev,
+        const uint64_t *__restrict__ hashes, const int32_t *__restrict__ chunk_base, int n,
+        int64_t max_chunks, uint64_t avail, unsigned long long tag, uint32_t *__restrict__ slots)
+{
+    const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (i >= n) return;
+    const ReqSpan sp = req_span(chunk_base, i, max_chunks);
+    Key carry = { KROOT1, KROOT2 };
+    for (int blk = 0; blk * 32 < sp.C; blk++) {
+        const int d = blk * 32 + lane;
+        const bool valid = d < sp.C;
+        const uint64_t h = valid ? hashes[sp.b0 + d] : 0;
+        const Key k = key_scan_warp(h, carry, lane);
+        carry.k1 = __shfl_sync(0xffffffffu, k.k1, 31);
+        carry.k2 = __shfl_sync(0xffffffffu, k.k2, 31);
+        bool created = false;
+        if (valid) {
+            uint32_t s = table_claim(tab, cap_log2, k.k1, k.k2, h, &created);
+            if (s == SLOT_NONE) {
+                atomicOr(&dev->status, B200R_S_TABLE_FULL);
+                slots[sp.b0 + d] = SLOT_NONE;
+            } else {
+                const uint64_t m = created ? 0 : tab[s].mask;
+                if (m & avail) {
+                    slots[sp.b0 + d] = s | PREOK_BIT;
+                } else {
+                    slots[sp.b0 + d] = s;
+                    atomicMin(first + s, tag | (unsigned long long)(unsigned)i);
+                }
+            }
+        }
+        count_created(dev, created);
+    }
+}
+
+// a5 step 2: deepest node usable by request i = last depth d with
+//   PREOK(node) or first(node) < i      (monotone in d)
+// If that node was usable before the batch (or depth 0) the request is a root
+// and draws from its candidate set; else it follows the request that touched
+// the node first.
+__global__ void __launch_bounds__(WARPS_PER_CTA * 32)
+k_select(const Entry *__restrict__ tab, const unsigned long long *__restrict__ first,
+         const int32_t *__restrict__ chunk_base, int n, int64_t max_chunks,
+         const uint32_t *__restrict__ slots, uint64_t avail, unsigned long long tag, uint64_t seed,
+         uint64_t seq0, int32_t *__restrict__ leader, int32_t *__restrict__ choice,
+         int32_t *__restrict__ depth_out, uint64_t *__restrict__ matched_out)
+{
+    const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (i >= n) return;
+    const ReqSpan sp = req_span(chunk_base, i, max_chunks);
+    int dstar = 0;
+    uint32_t star_slot = SLOT_NONE;       // slot word of the node at depth dstar
+    uint32_t star_first = 0;
+    for (int blk = 0; blk * 32 < sp.C; blk++) {
+        const int d = blk * 32 + lane;
+        const uint32_t sl = (d < sp.C) ? slots[sp.b0 + d] : SLOT_NONE;
+        bool ok = false;
+        uint32_t f = 0;
+        if (sl != SLOT_NONE) {
+            if (sl & PREOK_BIT) ok = true;
+            else {
+                unsigned long long fv = first[sl];
+                f = (uint32_t)fv;
+                ok = ((fv >> 32) == (tag >> 32)) && f < (uint32_t)i;
+            }
+        }
+        const unsigned bal = __ballot_sync(0xffffffffu, ok);
+        const int nok = (bal == 0xffffffffu) ? 32 : (__ffs(~bal) - 1);
+        if (nok > 0) {
+            star_slot = __shfl_sync(0xffffffffu, sl, nok - 1);
+            star_first = __shfl_sync(0xffffffffu, f, nok - 1);
+            dstar += nok;
+        }
+        if (nok < 32) break;
+    }
+    if (lane != 0) return;
+    depth_out[i] = dstar;
+    if (dstar == 0 || (star_slot & PREOK_BIT)) {
+        const uint64_t cand = (dstar == 0) ? avail : (tab[star_slot & ~PREOK_BIT].mask & avail);
+        const int cnt = __popcll(cand);
+        leader[i] = -1;
+        choice[i] = cnt ? nth_set_bit(cand, pick(seed, seq0 + (uint64_t)i, (uint32_t)cnt)) : -1;
+        matched_out[i] = cand;
+    } else {
+        leader[i] = (int32_t)star_first;
+        choice[i] = -1;
+    }
+}
+
+// a5 step 3: followers take their (transitive) leader's endpoint; every
+// request ORs its endpoint into the nodes below its match depth -- exactly the
+// nodes it was the first to touch, so no other request writes them.
+__global__ void __launch_bounds__(WARPS_PER_CTA * 32)
+k_commit(Entry *__restrict__ tab, TrieDev *dev, const int32_t *__restrict__ chunk_base, int n,
+         int64_t max_chunks, const uint32_t *__restrict__ slots, const int32_t *__restrict__ leader,
+         const int32_t *__restrict__ choice, const int32_t *__restrict__ depth,
+         int32_t *__restrict__ endpoint, uint64_t *__restrict__ matched_out)
+{
+    const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (i >= n) return;
+    int j = i, l;
+    while ((l = leader[j]) >= 0) j = l;          // chains strictly decrease in index
+    const int e = choice[j];
+    if (lane == 0) {
+        endpoint[i] = e;
+        if (j != i) matched_out[i] = (e >= 0) ? (1ULL << e) : 0;
+    }
+    if (e < 0) return;
+    const uint64_t bit = 1ULL << e;
+    if (lane == 0 && !(dev->root_mask & bit)) atomicOr((unsigned long long *)&dev->root_mask, bit);
+    const ReqSpan sp = req_span(chunk_base, i, max_chunks);
+    for (int d = depth[i] + lane; d < sp.C; d += 32) {
+        const uint32_t sl = slots[sp.b0 + d];
+        if (sl != SLOT_NONE) atomicOr((unsigned long long *)&tab[sl & ~PREOK_BIT].mask, bit);
+    }
+}
+
+// ------------------------------------------------------------ dump / restore
+__global__ void k_dump(const Entry *__restrict__ tab, int64_t cap, TrieDev *dev,
+                       uint64_t *__restrict__ out, int64_t max_nodes)
+{
+    for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < cap;
+         s += (int64_t)gridDim.x * blockDim.x) {
+        const Entry e = tab[s];
+        if (e.k1 | e.k2) {
+            unsigned long long idx = atomicAdd(&dev->dump_count, 1ULL);
+            if ((int64_t)idx < max_nodes) {
+                out[4 * idx + 0] = e.k1;
+                out[4 * idx + 1] = e.k2;
+                out[4 * idx + 2] = e.h;
+                out[4 * idx + 3] = e.mask;
+            }
+        }
+    }
+}
+
+__global__ void k_apply_remote(Entry *__restrict__ tab, int cap_log2, TrieDev *dev,
+                               const uint64_t *__restrict__ ent, int64_t count, uint64_t root_or)
+{
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx == 0 && root_or) atomicOr((unsigned long long *)&dev->root_mask, root_or);
+    bool created = false;
+    if (idx < count) {
+        const uint64_t k1 = ent[4 * idx], k2 = ent[4 * idx + 1], h = ent[4 * idx + 2],
+                       m = ent[4 * idx + 3];
+        uint32_t s = table_claim(tab, cap_log2, k1, k2, h, &created);
+        if (s == SLOT_NONE) atomicOr(&dev->status, B200R_S_TABLE_FULL);
+        else if (m) atomicOr((unsigned long long *)&tab[s].mask, m);
+    }
+    count_created(dev, created);
+}
+
+}  // namespace b200r
+
+// =========================================================================
+// C ABI
+// =========================================================================
+using namespace b200r;
+
+struct b200r_trie {
+    int device;
+    int cap_log2;
+    int chunk_chars;
+    Entry *tab;
+    unsigned long long *first;
+    TrieDev *dev;
+    uint32_t epoch;
+};
+
+static inline size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
+
+struct Plan {           // carve-up of the caller's scratch buffer
+    size_t off_tile_first, off_block_sums, off_nchars, off_chunk_off, off_chunk_base, off_hashes,
+        off_slots, off_leader, off_choice, total;
+};
+
+static Plan make_plan(int64_t n, int64_t max_chunks, uint32_t flags, bool routing)
+{
+    Plan p;
+    size_t o = 0;
+    const int64_t ntiles = (max_chunks + TILE - 1) / TILE + 1;
+    const int64_t nblk = (n + PREP_BLOCK - 1) / PREP_BLOCK + 1;
+    const bool ascii = flags & B200R_F_ALL_ASCII;
+    p.off_tile_first = o; o += align_up(ntiles * 4);
+    p.off_block_sums = o; o += align_up(nblk * 4);
+    p.off_nchars = o;     o += ascii ? 0 : align_up((n + 1) * 4);
+    p.off_chunk_off = o;  o += ascii ? 0 : align_up((max_chunks + 1) * 4);
+    p.off_chunk_base = o; o += routing ? align_up((n + 1) * 4) : 0;
+    p.off_hashes = o;     o += routing ? align_up((max_chunks + 1) * 8) : 0;
+    p.off_slots = o;      o += routing ? align_up((max_chunks + 1) * 4) : 0;
+    p.off_leader = o;     o += routing ? align_up((n + 1) * 4) : 0;
+    p.off_choice = o;     o += routing ? align_up((n + 1) * 4) : 0;
+    p.total = o + 256;
+    return p;
+}
+
+static int check_prompt_args(const void *bytes, const void *starts, const void *lens, int64_t n,
+                             int64_t max_chunks, int32_t cc)
+{
+    if (n < 0 || max_chunks < 0 || cc <= 0 || n > 0x7fffffff - 2048 || max_chunks > 0x7fffffff - 2048) {
+        set_error("invalid sizes: n=%lld max_chunks=%lld chunk_chars=%d", (long long)n,
+                  (long long)max_chunks, cc);
+        return B200R_E_INVALID;
+    }
+    if (n > 0 && (!bytes || !starts || !lens)) {
+        set_error("null prompt pointer");
+        return B200R_E_INVALID;
+    }
+    return B200R_OK;
+}
+
+// prep + (utf8) + hash; shared by b200r_xxh64_chunks and b200r_prefix_route_batch
+static int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const int32_t *d_lens,
+                       const int32_t *d_nchars, int64_t n, int32_t cc, uint32_t flags,
+                       int32_t *d_chunk_base, uint64_t *d_hashes, int64_t max_chunks,
+                       uint8_t *scratch, const Plan &p, TrieDev *dev, cudaStream_t st)
+{
+    int32_t *tile_first = (int32_t *)(scratch + p.off_tile_first);
+    int32_t *block_sums = (int32_t *)(scratch + p.off_block_sums);
+    int32_t *chunk_off = nullptr;
+    const bool ascii = flags & B200R_F_ALL_ASCII;
+    const int nwarp_blocks = (int)((n + WARPS_PER_CTA - 1) / WARPS_PER_CTA);
+    if (ascii) {
+        d_nchars = nullptr;                     // nchars == lens by contract
+    } else {
+        chunk_off = (int32_t *)(scratch + p.off_chunk_off);
+        if (!d_nchars) {
+            int32_t *tmp = (int32_t *)(scratch + p.off_nchars);
+            k_count_chars<<<nwarp_blocks, WARPS_PER_CTA * 32, 0, st>>>(d_bytes, d_starts, d_lens,
+                                                                      (int)n, tmp);
+            B200R_LAUNCH_CHECK("k_count_chars");
+            d_nchars = tmp;
+        }
+    }
+    const int nblk = (int)((n + PREP_BLOCK - 1) / PREP_BLOCK);
+    k_prep_sums<<<nblk, PREP_BLOCK, 0, st>>>(d_lens, d_nchars, (int)n, cc, block_sums);
+    B200R_LAUNCH_CHECK("k_prep_sums");
+    k_prep_scan<<<nblk, PREP_BLOCK, 0, st>>>(d_lens, d_nchars, (int)n, cc, block_sums, d_chunk_base,
+                                             tile_first, max_chunks, dev);
+    B200R_LAUNCH_CHECK("k_prep_scan");
+    if (!ascii) {
+        k_utf8_bounds<<<nwarp_blocks, WARPS_PER_CTA * 32, 0, st>>>(
+            d_bytes, d_starts, d_lens, d_nchars, d_chunk_base, (int)n, cc, max_chunks, chunk_off);
+        B200R_LAUNCH_CHECK("k_utf8_bounds");
+    }
+    const int ntiles = (int)((max_chunks + TILE - 1) / TILE);
+    if (ntiles > 0) {
+        k_hash_chunks<<<ntiles, TILE, 0, st>>>(d_bytes, d_starts, d_lens, d_nchars, d_chunk_base,
+                                               tile_first, chunk_off, (int)n, cc, max_chunks,
+                                               d_hashes);
+        B200R_LAUNCH_CHECK("k_hash_chunks");
+    }
+    return B200R_OK;
+}
+
+extern "C" {
+
+int b200r_abi_version(void) { return B200R_ABI_VERSION; }
+const char *b200r_last_error(void) { return g_err; }
+uint32_t b200r_pick(uint64_t seed, uint64_t seq, uint32_t n) { return pick(seed, seq, n); }
+
+void b200r_trie_key_constants(uint64_t out[6])
+{
+    out[0] = KA1; out[1] = KA2; out[2] = KROOT1; out[3] = KROOT2;
+    out[4] = cinv(KA1); out[5] = cinv(KA2);
+}
+
+size_t b200r_xxh64_chunks_scratch_bytes(int64_t n, int64_t max_chunks)
+{
+    return make_plan(n, max_chunks, 0, false).total;
+}
+
+int b200r_xxh64_chunks(const uint8_t *d_bytes, const int64_t *d_starts, const int32_t *d_lens,
+                       const int32_t *d_nchars, int64_t n, int32_t chunk_chars, uint32_t flags,
+                       int32_t *d_chunk_base, uint64_t *d_hashes, int64_t max_chunks,
+                       void *d_scratch, size_t scratch_bytes, void *stream)
+{
+    int rc = check_prompt_args(d_bytes, d_starts, d_lens, n, max_chunks, chunk_chars);
+    if (rc) return rc;
+    if (!d_chunk_base || (max_chunks > 0 && !d_hashes)) { set_error("null output pointer"); return B200R_E_INVALID; }
+    const Plan p = make_plan(n, max_chunks, flags, false);
+    if (!d_scratch || scratch_bytes < p.total) {
+        set_error("scratch too small: need %zu bytes, got %zu", p.total, scratch_bytes);
+        return B200R_E_SCRATCH;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n == 0) {
+        B200R_CUDA(cudaMemsetAsync(d_chunk_base, 0, 4, st));
+        return B200R_OK;
+    }
+    return launch_hash(d_bytes, d_starts, d_lens, d_nchars, n, chunk_chars, flags, d_chunk_base,
+                       d_hashes, max_chunks, (uint8_t *)d_scratch, p, nullptr, st);
+}
+
+int b200r_trie_create(int32_t cap_log2, int32_t chunk_chars, b200r_trie **out)
+{
+    if (!out || cap_log2 < 4 || cap_log2 > 30 || chunk_chars <= 0) {
+        set_error("b200r_trie_create: cap_log2 must be 4..30, chunk_chars > 0");
+        return B200R_E_INVALID;
+    }
+    b200r_trie *t = new b200r_trie();
+    B200R_CUDA(cudaGetDevice(&t->device));
+    t->cap_log2 = cap_log2;
+    t->chunk_chars = chunk_chars;
+    t->epoch = 0;
+    const size_t cap = (size_t)1 << cap_log2;
+    cudaError_t e;
+    if ((e = cudaMalloc(&t->tab, cap * sizeof(Entry))) != cudaSuccess ||
+        (e = cudaMalloc(&t->first, cap * 8)) != cudaSuccess ||
+        (e = cudaMalloc(&t->dev, sizeof(TrieDev))) != cudaSuccess) {
+        cudaFree(t->tab); cudaFree(t->first); cudaFree(t->dev);
+        delete t;
+        return cuda_fail(e, "cudaMalloc(trie)");
+    }
+    int rc = b200r_trie_clear(t, nullptr);
+    if (rc) { b200r_trie_destroy(t); return rc; }
+    B200R_CUDA(cudaStreamSynchronize(nullptr));
+    *out = t;
+    return B200R_OK;
+}
+
+int b200r_trie_destroy(b200r_trie *t)
+{
+    if (!t) return B200R_OK;
+    cudaFree(t->tab); cudaFree(t->first); cudaFree(t->dev);
+    delete t;
+    return B200R_OK;
+}
+
+int b200r_trie_clear(b200r_trie *t, void *stream)
+{
+    if (!t) { set_error("null trie"); return B200R_E_INVALID; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t cap = (size_t)1 << t->cap_log2;
+    B200R_CUDA(cudaMemsetAsync(t->tab, 0, cap * sizeof(Entry), st));
+    B200R_CUDA(cudaMemsetAsync(t->first, 0xFF, cap * 8, st));
+    B200R_CUDA(cudaMemsetAsync(t->dev, 0, sizeof(TrieDev), st));
+    t->epoch = 0;
+    return B200R_OK;
+}
+
+int b200r_trie_status(b200r_trie *t, void *stream, uint32_t *status_bits, int64_t *num_nodes,
+                      uint64_t *root_mask, int64_t *capacity)
+{
+    if (!t) { set_error("null trie"); return B200R_E_INVALID; }
+    cudaStream_t st = (cudaStream_t)stream;
+    TrieDev h;
+    B200R_CUDA(cudaMemcpyAsync(&h, t->dev, sizeof h, cudaMemcpyDeviceToHost, st));
+    B200R_CUDA(cudaStreamSynchronize(st));
+    if (status_bits) *status_bits = h.status;
+    if (num_nodes) *num_nodes = (int64_t)h.num_nodes;
+    if (root_mask) *root_mask = h.root_mask;
+    if (capacity) *capacity = (int64_t)1 << t->cap_log2;
+    return B200R_OK;
+}
+
+int b200r_trie_lookup_batch(b200r_trie *t, const uint64_t *d_hashes, const int32_t *d_chunk_base,
+                            int64_t n, uint64_t avail_mask, int32_t *d_match_depth,
+                            uint64_t *d_matched_mask, void *stream)
+{
+    if (!t || n < 0 || n > 0x7fffffff - 2048) { set_error("b200r_trie_lookup_batch: bad trie or n"); return B200R_E_INVALID; }
+    if (n == 0) return B200R_OK;
+    if (!d_hashes || !d_chunk_base || !d_match_depth || !d_matched_mask) { set_error("null pointer"); return B200R_E_INVALID; }
+    const int blocks = (int)((n + WARPS_PER_CTA - 1) / WARPS_PER_CTA);
+    k_lookup<<<blocks, WARPS_PER_CTA * 32, 0, (cudaStream_t)stream>>>(
+        t->tab, t->cap_log2, d_hashes, d_chunk_base, (int)n, avail_mask, d_match_depth,
+        d_matched_mask);
+    B200R_LAUNCH_CHECK("k_lookup");
+    return B200R_OK;
+}
+
+int b200r_trie_insert_batch(b200r_trie *t, const uint64_t *d_hashes, const int32_t *d_chunk_base,
+                            int64_t n, const int32_t *d_endpoint, void *stream)
+{
+    if (!t || n < 0 || n > 0x7fffffff - 2048) { set_error("b200r_trie_insert_batch: bad trie or n"); return B200R_E_INVALID; }
+    if (n == 0) return B200R_OK;
+    if (!d_hashes || !d_chunk_base || !d_endpoint) { set_error("null pointer"); return B200R_E_INVALID; }
+    const int blocks = (int)((n + WARPS_PER_CTA - 1) / WARPS_PER_CTA);
+    k_insert<<<blocks, WARPS_PER_CTA * 32, 0, (cudaStream_t)stream>>>(
+        t->tab, t->cap_log2, t->dev, d_hashes, d_chunk_base, (int)n, d_endpoint);
+    B200R_LAUNCH_CHECK("k_insert");
+    return B200R_OK;
+}
+
+size_t b200r_prefix_route_scratch_bytes(int64_t n, int64_t max_chunks, uint32_t flags)
+{
+    return make_plan(n, max_chunks, flags, true).total;
+}
+
+int b200r_prefix_route_batch(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
+                             const int32_t *d_lens, const int32_t *d_nchars, int64_t n,
+                             int64_t max_chunks, uint32_t flags, uint64_t avail_mask,
+                             uint64_t seed, uint64_t seq0, int32_t *d_endpoint,
+                             int32_t *d_match_depth, uint64_t *d_matched_mask, void *d_scratch,
+                             size_t scratch_bytes, void *stream)
+{
+    if (!t) { set_error("null trie"); return B200R_E_INVALID; }
+    int rc = check_prompt_args(d_bytes, d_starts, d_lens, n, max_chunks, t->chunk_chars);
+    if (rc) return rc;
+    if (n == 0) return B200R_OK;
+    if (!d_endpoint || !d_match_depth || !d_matched_mask) { set_error("null output pointer"); return B200R_E_INVALID; }
+    const Plan p = make_plan(n, max_chunks, flags, true);
+    if (!d_scratch || scratch_bytes < p.total) {
+        set_error("scratch too small: need %zu bytes, got %zu", p.total, scratch_bytes);
+        return B200R_E_SCRATCH;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    uint8_t *sc = (uint8_t *)d_scratch;
+    int32_t *chunk_base = (int32_t *)(sc + p.off_chunk_base);
+    uint64_t *hashes = (uint64_t *)(sc + p.off_hashes);
+    uint32_t *slots = (uint32_t *)(sc + p.off_slots);
+    int32_t *leader = (int32_t *)(sc + p.off_leader);
+    int32_t *choice = (int32_t *)(sc + p.off_choice);
+
+    // batch epoch for the "first toucher" words: newer batches carry a smaller
+    // high half, so atomicMin overrides anything left from older batches.
+    if (t->epoch >= 0xFFFFFFF0u) {
+        B200R_CUDA(cudaMemsetAsync(t->first, 0xFF, ((size_t)8) << t->cap_log2, st));
+        t->epoch = 0;
+    }
+    t->epoch++;
+    const unsigned long long tag = (unsigned long long)(0xFFFFFFFFu - t->epoch) << 32;
+
+    rc = launch_hash(d_bytes, d_starts, d_lens, d_nchars, n, t->chunk_chars, flags, chunk_base,
+                     hashes, max_chunks, sc, p, t->dev, st);
+    if (rc) return rc;
+    const int blocks = (int)((n + WARPS_PER_CTA - 1) / WARPS_PER_CTA);
+    const int thr = WARPS_PER_CTA * 32;
+    k_claim<<<blocks, thr, 0, st>>>(t->tab, t->cap_log2, t->first, t->dev, hashes, chunk_base,
+                                    (int)n, max_chunks, avail_mask, tag, slots);
+    B200R_LAUNCH_CHECK("k_claim");
+    k_select<<<blocks, thr, 0, st>>>(t->tab, t->first, chunk_base, (int)n, max_chunks, slots,
+                                     avail_mask, tag, seed, seq0, leader, choice, d_match_depth,
+                                     d_matched_mask);
+    B200R_LAUNCH_CHECK("k_select");
+    k_commit<<<blocks, thr, 0, st>>>(t->tab, t->dev, chunk_base, (int)n, max_chunks, slots, leader,
+                                     choice, d_match_depth, d_endpoint, d_matched_mask);
+    B200R_LAUNCH_CHECK("k_commit");
+    return B200R_OK;
+}
+
+int b200r_trie_dump(b200r_trie *t, uint64_t *d_out, int64_t max_nodes, int64_t *count,
+                    uint64_t *root_mask, void *stream)
+{
+    if (!t || max_nodes < 0 || (max_nodes > 0 && !d_out)) { set_error("b200r_trie_dump: bad argument"); return B200R_E_INVALID; }
+    cudaStream_t st = (cudaStream_t)stream;
+    B200R_CUDA(cudaMemsetAsync(&t->dev->dump_count, 0, 8, st));
+    const int64_t cap = (int64_t)1 << t->cap_log2;
+    int blocks = (int)((cap + 255) / 256);
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    k_dump<<<blocks, 256, 0, st>>>(t->tab, cap, t->dev, d_out, max_nodes);
+    B200R_LAUNCH_CHECK("k_dump");
+    TrieDev h;
+    B200R_CUDA(cudaMemcpyAsync(&h, t->dev, sizeof h, cudaMemcpyDeviceToHost, st));
+    B200R_CUDA(cudaStreamSynchronize(st));
+    if (count) *count = (int64_t)h.dump_count;
+    if (root_mask) *root_mask = h.root_mask;
+    return B200R_OK;
+}
+
+int b200r_trie_apply_remote(b200r_trie *t, const uint64_t *d_entries, int64_t count,
+                            uint64_t root_mask_or, void *stream)
+{
+    if (!t || count < 0 || (count > 0 && !d_entries)) { set_error("b200r_trie_apply_remote: bad argument"); return B200R_E_INVALID; }
+    const int64_t work = count > 0 ? count : 1;
+    const int blocks = (int)((work + 255) / 256);
+    k_apply_remote<<<blocks, 256, 0, (cudaStream_t)stream>>>(t->tab, t->cap_log2, t->dev, d_entries,
+                                                           count, root_mask_or);
+    B200R_LAUNCH_CHECK("k_apply_remote");
+    return B200R_OK;
+}
+
+}  // extern "C"
