@@ -1,0 +1,403 @@
+#!/usr/bin/env python
+"""bench.py -- prefix-route decisions/s (and prompt GB/s vs the HBM roofline).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+
+Workload (BASELINE.json configs[2], SURVEY.md 8d "C3"): prompts = one of 64
+shared 2048-char system prompts + a unique 256..1024-char suffix, 8 endpoints,
+batches of 65536 requests, one endpoint dropped for two batches (availability
+churn).  A step = one batch through the whole routing path (hash, lookup,
+tie-break, insert; results equal to the reference's sequential order).  Every
+step routes a batch the table has not seen; batches (~177 MB of prompt bytes)
+are larger than L2 (126 MB) and distinct, so no flush is needed between steps.
+
+  value      whole-job decisions/s, batches resident in HBM, CUDA events
+  e2e        same through the public Python API from pinned HOST buffers:
+             H2D of the packed batch + route + D2H of the decisions, per step
+  roofline   k_hash_chunks (the dominant kernel): prompt bytes per launch /
+             its CUDA-event duration (second pass with per-kernel events)
+  cpu_baseline  oracle/prefix_ref.py (Python restatement of the reference,
+             asyncio structure included) on a bounded sample, 1 core
+
+--impl reference times that restatement alone (the reference is pure Python
+and is not installable on the GPU box).  Under torchrun every
+rank runs the b200 arm on its shard; for --impl reference only rank 0 works.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "vllm-production-stack_b200"))
+
+import numpy as np  # noqa: E402
+
+BATCH = 1 << 16
+N_ENDPOINTS = 8
+N_SYS = 64
+SYS_CHARS = 2048
+SUFFIX = (256, 1024)
+SEED = 20240607
+METRIC = "prefix_route_decisions_per_sec"
+UNIT = "decisions/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=16)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=BATCH, help=argparse.SUPPRESS)
+    ap.add_argument("--cpu-sample", type=int, default=BATCH, help=argparse.SUPPRESS)
+    ap.add_argument("--no-cpu", action="store_true", help=argparse.SUPPRESS)
+    return ap.parse_args()
+
+
+def workload_config(args, n_gpus):
+    return {"workload": "C3: 64 shared 2048-char system prompts + unique 256-1024-char suffix, "
+                        "%d endpoints, batch %d per GPU, endpoint 3 unavailable in batches 5-6"
+                        % (N_ENDPOINTS, args.batch),
+            "batch_per_gpu": args.batch, "global_batch": args.batch * n_gpus,
+            "chunk_chars": 128, "endpoints": N_ENDPOINTS,
+            "l2": "inputs larger than L2: each step reads a distinct ~%d MB batch"
+                  % (args.batch * 2700 // 1000000),
+            "tie_break": "canonical (endpoint-index order, counter-based draw)"}
+
+
+def avail_mask(step_index):
+    full = (1 << N_ENDPOINTS) - 1
+    return full & ~(1 << 3) if step_index in (5, 6) else full
+
+
+def make_trace(args, n_batches):
+    from b200_router import traces
+    return traces.SharedPrefixTrace(n_total=n_batches * args.batch, batch=args.batch, n_sys=N_SYS,
+                                    sys_chars=SYS_CHARS, suffix_lo=SUFFIX[0], suffix_hi=SUFFIX[1],
+                                    seed=SEED)
+
+
+# ---------------------------------------------------------------- clocks
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.proc = None
+        self.path = "/tmp/b200r_clocks_%d_%d.csv" % (os.getpid(), gpu_index)
+
+    def start(self):
+        try:
+            self.f = open(self.path, "w")
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.f.close()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        try:
+            for line in open(self.path):
+                p = [x.strip() for x in line.split(",")]
+                if len(p) < 9:
+                    continue
+                try:
+                    sm.append(float(p[1])); mx.append(float(p[2]))
+                except ValueError:
+                    continue
+                for nm, v in zip(names, p[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            os.unlink(self.path)
+        except Exception:
+            pass
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), samples=len(sm))
+        out["reasons"] = sorted(reasons)
+        return out
+
+
+# ------------------------------------------------------- CPU (oracle) legs
+def prompts_of(buf, starts, lens, count):
+    out = []
+    for i in range(min(count, len(starts))):
+        s = int(starts[i])
+        out.append(buf[s:s + int(lens[i])].tobytes().decode("ascii"))
+    return out
+
+
+def cpu_port_rate(prompts, avail, seed=SEED):
+    """Python restatement of the reference router, one asyncio loop, 1 core.
+    Returns (decisions/s, decisions as endpoint indices)."""
+    from oracle import prefix_ref
+    from oracle.chooser import ChoiceShim
+    from b200_router import traces
+    urls = traces.endpoint_urls(N_ENDPOINTS)
+    index_of = {u: i for i, u in enumerate(urls)}
+    router = prefix_ref.PrefixRouterRef(ChoiceShim(index_of, seed))
+    eps = [urls[i] for i in range(N_ENDPOINTS) if (avail >> i) & 1]
+    t0 = time.perf_counter()
+    got = router.route_many(eps, prompts)
+    dt = time.perf_counter() - t0
+    return len(prompts) / dt, [index_of[u] for u in got]
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import asyncio
+    from oracle import prefix_ref
+    from oracle.chooser import ChoiceShim
+    from b200_router import traces
+    sample = 8192                      # requests per step: bounded sample of a batch
+    nb = args.warmup + args.steps
+    tr = make_trace(args, nb)
+    urls = traces.endpoint_urls(N_ENDPOINTS)
+    index_of = {u: i for i, u in enumerate(urls)}
+    router = prefix_ref.PrefixRouterRef(ChoiceShim(index_of, SEED))
+    steps = []
+    for b in range(nb):
+        buf, starts, lens = tr.batch_arrays(b) if args.batch <= 8192 else \
+            _first_requests(tr, b, sample)
+        steps.append((avail_mask(b), prompts_of(buf, starts, lens, sample)))
+
+    async def one(avail, prompts):
+        aset = set(urls[i] for i in range(N_ENDPOINTS) if (avail >> i) & 1)
+        for p in prompts:
+            await router.route_prompt(aset, p)
+
+    for b in range(args.warmup):
+        asyncio.run(one(*steps[b]))
+    t0 = time.perf_counter()
+    nreq = nbytes = 0
+    for b in range(args.warmup, nb):
+        asyncio.run(one(*steps[b]))
+        nreq += len(steps[b][1])
+        nbytes += sum(len(p) for p in steps[b][1])
+    dt = time.perf_counter() - t0
+    value = nreq / dt
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT,
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+            "config": workload_config(args, args.gpus),
+            "prompt_gbs": nbytes / dt / 1e9,
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "port",
+                             "sample": "first %d requests of each of %d batches; Python "
+                                       "restatement of the reference (oracle/prefix_ref.py), one "
+                                       "asyncio loop; host has %d cpus" % (sample, args.steps,
+                                                                           os.cpu_count())},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0,
+                    "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def _first_requests(tr, b, count):
+    """First `count` requests of batch b without materialising the whole batch."""
+    from b200_router import traces
+    small = traces.SharedPrefixTrace(n_total=tr.n_total, batch=tr.batch, n_sys=tr.n_sys,
+                                     sys_chars=tr.sys_chars, suffix_lo=tr.suffix_lo,
+                                     suffix_hi=tr.suffix_hi, seed=tr.seed)
+    buf, starts, lens = small.batch_arrays(b)
+    return buf, starts[:count], lens[:count]
+
+
+# ------------------------------------------------------------- B200 arm
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from b200_router import _lib
+    from b200_router.packing import pack_arrays
+    from b200_router.trie import GpuHashTrie
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the B200 path has no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    W, K = args.warmup, args.steps
+    nb = W + K
+
+    # ---- synthetic batches (host, pinned), this rank's shard of every global batch
+    tr = make_trace(args, nb * world)
+    host = []
+    for b in range(nb):
+        buf, starts, lens = tr.batch_arrays(b * world + rank)
+        host.append(pack_arrays(buf, starts, lens, pin=True))
+    max_chunks = max(p.max_chunks for p in host)
+
+    nodes_est = nb * world * args.batch * 8
+    cap_log2 = max(16, min(28, int(np.ceil(np.log2(nodes_est * 2.2)))))
+
+    def new_router():
+        if world == 1:
+            t = GpuHashTrie(cap_log2=cap_log2, device=dev)
+            t.reserve(args.batch, max_chunks)
+            return t
+        from b200_router.distributed import ShardedPrefixRouter
+        return ShardedPrefixRouter(cap_log2=cap_log2, device=dev, max_requests=args.batch,
+                                   max_chunks=max_chunks)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    out = (torch.empty(args.batch, dtype=torch.int32, device=dev),
+           torch.empty(args.batch, dtype=torch.int32, device=dev),
+           torch.empty(args.batch, dtype=torch.int64, device=dev))
+
+    # ---- pass 1: device-resident batches, whole timed region bracketed by events
+    resident = [p.to(dev, non_blocking=False) for p in host]
+    router = new_router()
+    seq = 0
+    for b in range(W):
+        router.route(resident[b], avail_mask(b), SEED, seq, out=out)
+        seq += args.batch * world
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    launches0 = _lib.launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for b in range(W, nb):
+        router.route(resident[b], avail_mask(b), SEED, seq, out=out)
+        seq += args.batch * world
+    ev1.record()
+    barrier()
+    clocks = sampler.stop()
+    launches = _lib.launch_count() - launches0
+    ms = ev0.elapsed_time(ev1)
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    st = router.check_status()
+    n_dec = K * args.batch * world
+    payload = sum(p.payload_bytes for p in host[W:])
+    if world > 1:
+        t = torch.tensor([payload], device=dev, dtype=torch.int64)
+        dist.all_reduce(t)
+        payload = int(t.item())
+    value = n_dec / (ms * 1e-3)
+
+    # ---- pass 2: same batches again with per-kernel events (roofline of k_hash_chunks)
+    _lib.prof_enable(True)
+    for b in range(W, nb):
+        router.route(resident[b], avail_mask(b), SEED, seq, out=out)
+        seq += args.batch * world
+    torch.cuda.synchronize()
+    prof = _lib.prof_read()
+    _lib.prof_enable(False)
+    my_payload = sum(p.payload_bytes for p in host[W:])
+    hash_ms, hash_n = prof["hash"]
+    peaks, peak_src = load_peaks()
+    achieved = my_payload / (hash_ms * 1e-3) / 1e9 if hash_ms > 0 else 0.0
+    prof_total = sum(v[0] for v in prof.values())
+    del router
+    resident = None
+    torch.cuda.empty_cache()
+
+    # ---- pass 3: end to end from pinned host buffers through the public API
+    router = new_router()
+    seq = 0
+    for b in range(W):
+        ep, _, _ = router.route(host[b].to(dev, non_blocking=True), avail_mask(b), SEED, seq, out=out)
+        ep.cpu()
+        seq += args.batch * world
+    barrier()
+    t0 = time.perf_counter()
+    for b in range(W, nb):
+        ep, _, _ = router.route(host[b].to(dev, non_blocking=True), avail_mask(b), SEED, seq, out=out)
+        decisions = ep.cpu()                  # D2H read of the step's result (synchronises)
+        seq += args.batch * world
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    h2d = int(np.mean([p.h2d_bytes() for p in host[W:]]))
+    e2e = {"value": n_dec / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
+           "d2h_bytes_per_step": args.batch * 4, "ms_per_step": e2e_s / K * 1e3}
+
+    # ---- CPU baseline (rank 0, N=1 only) + parity of the same sample on a fresh table
+    cpu = None
+    parity = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        b = W
+        cnt = min(args.cpu_sample, args.batch)
+        buf, starts, lens = tr.batch_arrays(b)
+        prompts = prompts_of(buf, starts, lens, cnt)
+        rate, want = cpu_port_rate(prompts, avail_mask(b))
+        t2 = GpuHashTrie(cap_log2=max(16, int(np.ceil(np.log2(cnt * 24 * 2.2)))), device=dev)
+        ep, _, _ = t2.route(pack_arrays(buf, starts[:cnt], lens[:cnt], pin=False),
+                            avail_mask(b), SEED, 0)
+        parity = bool(ep.cpu().tolist() == want)
+        t2.close()
+        cpu = {"value": rate, "unit": UNIT, "cores": 1, "kind": "port",
+               "sample": "first %d requests of timed batch 0 on an empty table; Python "
+                         "restatement of the reference (oracle/prefix_ref.py), one asyncio loop, "
+                         "host has %d cpus" % (cnt, os.cpu_count())}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K,
+                "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+                "config": workload_config(args, world),
+                "prompt_gbs": payload / (ms * 1e-3) / 1e9,
+                "prompt_frac_of_hbm": payload / (ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
+                "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
+                "roofline": {"bound": "hbm", "kernel": "k_hash_chunks", "achieved": achieved,
+                             "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                             "frac": achieved / peaks["hbm_gbs"], "traffic": None,
+                             "peak_source": peak_src, "launches": hash_n,
+                             "ms_per_launch": hash_ms / max(hash_n, 1),
+                             "share_of_step": hash_ms / prof_total if prof_total else None,
+                             "kernel_ms_per_step": {k: v[0] / K for k, v in prof.items() if v[1]}},
+                "cpu_baseline": cpu, "parity_sample_ok": parity,
+                "table": {"nodes": st["num_nodes"], "capacity": st["capacity"]}}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            return json.load(f), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return {"hbm_gbs": 6650.0}, "fallback (B200_PROFILING.md)"
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

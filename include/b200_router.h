@@ -169,6 +169,20 @@ int b200r_ring_build(b200r_ring *r, const uint64_t *h_points_hi, const uint64_t 
 int b200r_ring_lookup_batch(b200r_ring *r, const uint8_t *d_bytes, const int64_t *d_starts,
                             const int32_t *d_lens, int64_t n, int32_t *d_endpoint, void *stream);
 
+/* ------------------------------------------------------------------------
+ * Measurement hooks (bench.py; no counterpart in the reference).
+ * b200r_prof_enable(1): every pipeline kernel is bracketed by CUDA events on
+ * its launch stream.  b200r_prof_read synchronises those events and returns,
+ * per kernel class, the summed milliseconds and the number of launches since
+ * the last read; slots: 0 prep, 1 utf8, 2 hash, 3 claim, 4 select, 5 commit,
+ * 6 lookup, 7 insert.  b200r_launch_count: kernels enqueued by this library
+ * since load (process-wide).
+ * ---------------------------------------------------------------------- */
+#define B200R_PROF_SLOTS 8
+int b200r_prof_enable(int on);
+int b200r_prof_read(float *ms_out, long long *count_out, int nslots);
+long long b200r_launch_count(void);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

@@ -37,6 +37,9 @@ SIGNATURES = {
     "b200r_trie_dump": (C.c_int, [_vp, _vp, _i64, C.POINTER(_i64), C.POINTER(_u64), _vp]),
     "b200r_trie_apply_remote": (C.c_int, [_vp, _vp, _i64, _u64, _vp]),
     "b200r_trie_key_constants": (None, [C.POINTER(_u64)]),
+    "b200r_prof_enable": (C.c_int, [C.c_int]),
+    "b200r_prof_read": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_longlong), C.c_int]),
+    "b200r_launch_count": (C.c_longlong, []),
     "b200r_md5_batch": (C.c_int, [_vp, _vp, _vp, _i64, _vp, _vp]),
     "b200r_ring_create": (C.c_int, [C.POINTER(_vp)]),
     "b200r_ring_destroy": (C.c_int, [_vp]),
@@ -81,3 +84,22 @@ def require_cuda():
     if not torch.cuda.is_available():
         raise B200RouterError("no CUDA device: the B200 router has no CPU fallback")
     return torch
+
+
+PROF_SLOTS = ("prep", "utf8", "hash", "claim", "select", "commit", "lookup", "insert")
+
+
+def prof_enable(on: bool):
+    check(lib().b200r_prof_enable(1 if on else 0))
+
+
+def prof_read():
+    """{kernel class: (ms, launches)} since the last read (synchronises)."""
+    ms = (C.c_float * 8)()
+    cnt = (C.c_longlong * 8)()
+    check(lib().b200r_prof_read(ms, cnt, 8))
+    return {k: (float(ms[i]), int(cnt[i])) for i, k in enumerate(PROF_SLOTS)}
+
+
+def launch_count() -> int:
+    return int(lib().b200r_launch_count())

@@ -16,6 +16,7 @@
 //   k_select                    per request: deepest usable node, root draw or leader
 //   k_commit                    resolve leader chains, OR the endpoint into new nodes
 #include <cstdarg>
+#include <vector>
 
 #include "common.cuh"
 
@@ -37,6 +38,33 @@ int cuda_fail(cudaError_t e, const char *what)
     set_error("%s: %s", what, cudaGetErrorString(e));
     return e == cudaErrorMemoryAllocation ? B200R_E_NOMEM : B200R_E_CUDA;
 }
+
+// ------------------------------------------------------------- profiling
+// Optional per-kernel timing with CUDA events on the launching stream
+// (b200r_prof_enable / b200r_prof_read).  Off by default: the hot path then
+// records nothing.  g_launches counts every kernel this library enqueues.
+enum { PK_PREP = 0, PK_UTF8, PK_HASH, PK_CLAIM, PK_SELECT, PK_COMMIT, PK_LOOKUP, PK_INSERT, PK_COUNT };
+struct ProfSpan { int kid; cudaEvent_t a, b; };
+static bool g_prof_on = false;
+static std::vector<ProfSpan> g_spans;
+static long long g_launches = 0;
+
+struct ProfScope {
+    bool on; cudaStream_t st; ProfSpan sp;
+    ProfScope(int kid, cudaStream_t s) : on(g_prof_on), st(s)
+    {
+        if (!on) return;
+        sp.kid = kid;
+        cudaEventCreate(&sp.a); cudaEventCreate(&sp.b);
+        cudaEventRecord(sp.a, st);
+    }
+    ~ProfScope()
+    {
+        if (!on) return;
+        cudaEventRecord(sp.b, st);
+        g_spans.push_back(sp);
+    }
+};
 
 constexpr int TILE = 256;          // chunks per CTA of k_hash_chunks
 constexpr int PREP_BLOCK = 1024;   // requests per CTA of the prep kernels
@@ -634,29 +662,39 @@ static int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const in
         chunk_off = (int32_t *)(scratch + p.off_chunk_off);
         if (!d_nchars) {
             int32_t *tmp = (int32_t *)(scratch + p.off_nchars);
+            { ProfScope ps__(PK_UTF8, st); g_launches += 1;
             k_count_chars<<<nwarp_blocks, WARPS_PER_CTA * 32, 0, st>>>(d_bytes, d_starts, d_lens,
                                                                       (int)n, tmp);
             B200R_LAUNCH_CHECK("k_count_chars");
+            }
             d_nchars = tmp;
         }
     }
     const int nblk = (int)((n + PREP_BLOCK - 1) / PREP_BLOCK);
+    { ProfScope ps__(PK_PREP, st); g_launches += 1;
     k_prep_sums<<<nblk, PREP_BLOCK, 0, st>>>(d_lens, d_nchars, (int)n, cc, block_sums);
     B200R_LAUNCH_CHECK("k_prep_sums");
+    }
+    { ProfScope ps__(PK_PREP, st); g_launches += 1;
     k_prep_scan<<<nblk, PREP_BLOCK, 0, st>>>(d_lens, d_nchars, (int)n, cc, block_sums, d_chunk_base,
                                              tile_first, max_chunks, dev);
     B200R_LAUNCH_CHECK("k_prep_scan");
+    }
     if (!ascii) {
+        { ProfScope ps__(PK_UTF8, st); g_launches += 1;
         k_utf8_bounds<<<nwarp_blocks, WARPS_PER_CTA * 32, 0, st>>>(
             d_bytes, d_starts, d_lens, d_nchars, d_chunk_base, (int)n, cc, max_chunks, chunk_off);
         B200R_LAUNCH_CHECK("k_utf8_bounds");
+        }
     }
     const int ntiles = (int)((max_chunks + TILE - 1) / TILE);
     if (ntiles > 0) {
+        { ProfScope ps__(PK_HASH, st); g_launches += 1;
         k_hash_chunks<<<ntiles, TILE, 0, st>>>(d_bytes, d_starts, d_lens, d_nchars, d_chunk_base,
                                                tile_first, chunk_off, (int)n, cc, max_chunks,
                                                d_hashes);
         B200R_LAUNCH_CHECK("k_hash_chunks");
+        }
     }
     return B200R_OK;
 }
@@ -666,6 +704,33 @@ extern "C" {
 int b200r_abi_version(void) { return B200R_ABI_VERSION; }
 const char *b200r_last_error(void) { return g_err; }
 uint32_t b200r_pick(uint64_t seed, uint64_t seq, uint32_t n) { return pick(seed, seq, n); }
+
+int b200r_prof_enable(int on)
+{
+    g_prof_on = on != 0;
+    return B200R_OK;
+}
+
+long long b200r_launch_count(void) { return g_launches; }
+
+int b200r_prof_read(float *ms_out, long long *count_out, int nslots)
+{
+    float ms[PK_COUNT] = { 0 };
+    long long cnt[PK_COUNT] = { 0 };
+    for (auto &sp : g_spans) {
+        B200R_CUDA(cudaEventSynchronize(sp.b));
+        float t = 0;
+        B200R_CUDA(cudaEventElapsedTime(&t, sp.a, sp.b));
+        ms[sp.kid] += t; cnt[sp.kid]++;
+        cudaEventDestroy(sp.a); cudaEventDestroy(sp.b);
+    }
+    g_spans.clear();
+    for (int k = 0; k < nslots && k < PK_COUNT; k++) {
+        if (ms_out) ms_out[k] = ms[k];
+        if (count_out) count_out[k] = cnt[k];
+    }
+    return B200R_OK;
+}
 
 void b200r_trie_key_constants(uint64_t out[6])
 {
@@ -770,10 +835,12 @@ int b200r_trie_lookup_batch(b200r_trie *t, const uint64_t *d_hashes, const int32
     if (n == 0) return B200R_OK;
     if (!d_hashes || !d_chunk_base || !d_match_depth || !d_matched_mask) { set_error("null pointer"); return B200R_E_INVALID; }
     const int blocks = (int)((n + WARPS_PER_CTA - 1) / WARPS_PER_CTA);
+    { ProfScope ps__(PK_LOOKUP, (cudaStream_t)stream); g_launches += 1;
     k_lookup<<<blocks, WARPS_PER_CTA * 32, 0, (cudaStream_t)stream>>>(
         t->tab, t->cap_log2, d_hashes, d_chunk_base, (int)n, avail_mask, d_match_depth,
         d_matched_mask);
     B200R_LAUNCH_CHECK("k_lookup");
+    }
     return B200R_OK;
 }
 
@@ -784,9 +851,11 @@ int b200r_trie_insert_batch(b200r_trie *t, const uint64_t *d_hashes, const int32
     if (n == 0) return B200R_OK;
     if (!d_hashes || !d_chunk_base || !d_endpoint) { set_error("null pointer"); return B200R_E_INVALID; }
     const int blocks = (int)((n + WARPS_PER_CTA - 1) / WARPS_PER_CTA);
+    { ProfScope ps__(PK_INSERT, (cudaStream_t)stream); g_launches += 1;
     k_insert<<<blocks, WARPS_PER_CTA * 32, 0, (cudaStream_t)stream>>>(
         t->tab, t->cap_log2, t->dev, d_hashes, d_chunk_base, (int)n, d_endpoint);
     B200R_LAUNCH_CHECK("k_insert");
+    }
     return B200R_OK;
 }
 
@@ -834,16 +903,22 @@ int b200r_prefix_route_batch(b200r_trie *t, const uint8_t *d_bytes, const int64_
     if (rc) return rc;
     const int blocks = (int)((n + WARPS_PER_CTA - 1) / WARPS_PER_CTA);
     const int thr = WARPS_PER_CTA * 32;
+    { ProfScope ps__(PK_CLAIM, st); g_launches += 1;
     k_claim<<<blocks, thr, 0, st>>>(t->tab, t->cap_log2, t->first, t->dev, hashes, chunk_base,
                                     (int)n, max_chunks, avail_mask, tag, slots);
     B200R_LAUNCH_CHECK("k_claim");
+    }
+    { ProfScope ps__(PK_SELECT, st); g_launches += 1;
     k_select<<<blocks, thr, 0, st>>>(t->tab, t->first, chunk_base, (int)n, max_chunks, slots,
                                      avail_mask, tag, seed, seq0, leader, choice, d_match_depth,
                                      d_matched_mask);
     B200R_LAUNCH_CHECK("k_select");
+    }
+    { ProfScope ps__(PK_COMMIT, st); g_launches += 1;
     k_commit<<<blocks, thr, 0, st>>>(t->tab, t->dev, chunk_base, (int)n, max_chunks, slots, leader,
                                      choice, d_match_depth, d_endpoint, d_matched_mask);
     B200R_LAUNCH_CHECK("k_commit");
+    }
     return B200R_OK;
 }
 
