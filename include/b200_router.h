@@ -80,6 +80,37 @@ int b200r_xxh64_chunks(const uint8_t *d_bytes, const int64_t *d_starts, const in
                        void *d_scratch, size_t scratch_bytes, void *stream);
 
 /* ------------------------------------------------------------------------
+ * b200r_xxh64_chunks_noalloc -- the same chunk hashing for callers that cannot
+ * allocate.  (No counterpart in the reference; added for embedders.)
+ *
+ * Who needs it: code that is only ever given input and output buffers -- a
+ * plugin inside a serving process whose engine has already claimed almost all
+ * device memory (a cudaMalloc for work space would fail), or a request-path
+ * thread that must avoid cudaMalloc/cudaFree because they stall the device.
+ * The work space is a fixed B200R_NOALLOC_SCRATCH_BYTES area compiled into
+ * the library (each GPU that loads the library holds it until exit); the call
+ * itself performs no cudaMalloc/cudaFree and uses no allocating routine.
+ *
+ * Same arguments and results as b200r_xxh64_chunks minus the scratch pair.
+ * Limits and rules:
+ *   - the batch must fit the built-in area: roughly 4*n + 4*max_chunks bytes
+ *     for non-ASCII batches (about 900k chunks = 115 MB of prompt text), far
+ *     more with B200R_F_ALL_ASCII; larger batches fail with B200R_E_SCRATCH
+ *     and a message giving the required size;
+ *   - the first call on each device looks up the area's address (with that
+ *     device current); make that first call before starting any stream capture;
+ *   - all calls on a device share the one area, which keeps whatever the last
+ *     call left in it (nothing needs to be cleared between calls); two calls
+ *     whose kernels may overlap on the GPU -- different streams without an
+ *     ordering between them -- race on it and must be serialised by the caller.
+ * ---------------------------------------------------------------------- */
+#define B200R_NOALLOC_SCRATCH_BYTES (4 * 1024 * 1024)
+int b200r_xxh64_chunks_noalloc(const uint8_t *d_bytes, const int64_t *d_starts,
+                               const int32_t *d_lens, const int32_t *d_nchars, int64_t n,
+                               int32_t chunk_chars, uint32_t flags, int32_t *d_chunk_base,
+                               uint64_t *d_hashes, int64_t max_chunks, void *stream);
+
+/* ------------------------------------------------------------------------
  * a4/a6  TrieNode / HashTrie.__init__               hashtrie.py:24-43
  * The pointer trie becomes an open-addressing table of 32-byte entries
  * {path key (128 bit), chunk hash, endpoint bitmask}; capacity = 2^cap_log2

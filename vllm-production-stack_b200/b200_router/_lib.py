@@ -14,6 +14,7 @@ OK = 0
 F_ALL_ASCII = 1
 S_TABLE_FULL = 1
 S_CHUNK_CAP = 2
+NOALLOC_SCRATCH_BYTES = 4 * 1024 * 1024
 
 _vp, _i64, _i32, _u32, _u64, _sz = C.c_void_p, C.c_int64, C.c_int32, C.c_uint32, C.c_uint64, C.c_size_t
 
@@ -23,6 +24,7 @@ SIGNATURES = {
     "b200r_last_error": (C.c_char_p, []),
     "b200r_xxh64_chunks_scratch_bytes": (_sz, [_i64, _i64]),
     "b200r_xxh64_chunks": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i32, _u32, _vp, _vp, _i64, _vp, _sz, _vp]),
+    "b200r_xxh64_chunks_noalloc": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i32, _u32, _vp, _vp, _i64, _vp]),
     "b200r_trie_create": (C.c_int, [_i32, _i32, C.POINTER(_vp)]),
     "b200r_trie_destroy": (C.c_int, [_vp]),
     "b200r_trie_clear": (C.c_int, [_vp, _vp]),

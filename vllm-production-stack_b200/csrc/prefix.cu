@@ -16,6 +16,7 @@
 //   k_select                    per request: deepest usable node, root draw or leader
 //   k_commit                    resolve leader chains, OR the endpoint into new nodes
 #include <cstdarg>
+#include <mutex>
 #include <vector>
 
 #include "common.cuh"
@@ -763,6 +764,79 @@ int b200r_xxh64_chunks(const uint8_t *d_bytes, const int64_t *d_starts, const in
     }
     return launch_hash(d_bytes, d_starts, d_lens, d_nchars, n, chunk_chars, flags, d_chunk_base,
                        d_hashes, max_chunks, (uint8_t *)d_scratch, p, nullptr, st);
+}
+
+// ---------------------------------------------------------------------------
+// Chunk hashing for callers that cannot allocate device memory.
+//
+// Some users of this library only ever hold the input and output buffers their
+// host framework hands them: a router plugin living inside a serving process
+// whose engine has already reserved (nearly) all of HBM, so that a cudaMalloc
+// for a few MB of work space fails; or a request-path thread that must not call
+// cudaMalloc/cudaFree because those calls synchronise the whole device.  For
+// them the work space of the hashing pipeline (tile map, block sums, code-point
+// counts, UTF-8 chunk offsets) lives in the fixed array below, which is part of
+// the library image: every GPU that loads libb200router.so carries these
+// B200R_NOALLOC_SCRATCH_BYTES until the process exits.
+//
+// In host code `g_noalloc_scratch` is only a handle for the symbol, not a device
+// address, so the address is looked up with cudaGetSymbolAddress -- once per
+// device, with that device current -- and handed to the kernels like any other
+// scratch pointer.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[B200R_NOALLOC_SCRATCH_BYTES];
+
+static std::mutex g_noalloc_mu;
+static uint8_t *g_noalloc_ptr[64] = { nullptr };   // resolved address, per device ordinal
+
+static int noalloc_scratch_for_current_device(uint8_t **out)
+{
+    int devid = -1;
+    B200R_CUDA(cudaGetDevice(&devid));
+    if (devid < 0 || devid >= 64) {
+        set_error("b200r_xxh64_chunks_noalloc: device ordinal %d out of range", devid);
+        return B200R_E_INVALID;
+    }
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_ptr[devid]) {
+        void *ptr = nullptr;
+        B200R_CUDA(cudaGetSymbolAddress(&ptr, g_noalloc_scratch));
+        if (!ptr) { set_error("cudaGetSymbolAddress returned a null address"); return B200R_E_CUDA; }
+        g_noalloc_ptr[devid] = (uint8_t *)ptr;
+    }
+    *out = g_noalloc_ptr[devid];
+    return B200R_OK;
+}
+
+int b200r_xxh64_chunks_noalloc(const uint8_t *d_bytes, const int64_t *d_starts,
+                               const int32_t *d_lens, const int32_t *d_nchars, int64_t n,
+                               int32_t chunk_chars, uint32_t flags, int32_t *d_chunk_base,
+                               uint64_t *d_hashes, int64_t max_chunks, void *stream)
+{
+    int rc = check_prompt_args(d_bytes, d_starts, d_lens, n, max_chunks, chunk_chars);
+    if (rc) return rc;
+    if (!d_chunk_base || (max_chunks > 0 && !d_hashes)) { set_error("null output pointer"); return B200R_E_INVALID; }
+    const Plan p = make_plan(n, max_chunks, flags, false);
+    if (p.total > (size_t)B200R_NOALLOC_SCRATCH_BYTES) {
+        set_error("b200r_xxh64_chunks_noalloc: a batch of n=%lld requests / max_chunks=%lld chunks "
+                  "needs %zu bytes of work space, the built-in area holds %d; split the batch or "
+                  "use b200r_xxh64_chunks with a caller-provided scratch buffer",
+                  (long long)n, (long long)max_chunks, p.total, B200R_NOALLOC_SCRATCH_BYTES);
+        return B200R_E_SCRATCH;
+    }
+    uint8_t *scratch = nullptr;
+    rc = noalloc_scratch_for_current_device(&scratch);   // first call on a device resolves the symbol
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n == 0) {
+        B200R_CUDA(cudaMemsetAsync(d_chunk_base, 0, 4, st));
+        return B200R_OK;
+    }
+    // Nothing in the work space has to start at zero: every word the kernels
+    // read in this call was written earlier in this call (tile map and block
+    // sums by the prep kernels, counts/offsets by the UTF-8 kernels), so stale
+    // contents of the previous call are never observed.
+    return launch_hash(d_bytes, d_starts, d_lens, d_nchars, n, chunk_chars, flags, d_chunk_base,
+                       d_hashes, max_chunks, scratch, p, nullptr, st);
 }
 
 int b200r_trie_create(int32_t cap_log2, int32_t chunk_chars, b200r_trie **out)
