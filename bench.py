@@ -83,55 +83,59 @@ def make_trace(args, n_batches):
 
 # ---------------------------------------------------------------- clocks
 class ClockSampler:
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
-         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """Samples SM clock and throttle reasons with NVML from a background thread
+    while the timed region runs (nvidia-smi's own loop is too slow to start for
+    a region of a few milliseconds)."""
 
     def __init__(self, gpu_index):
         self.gpu = gpu_index
-        self.proc = None
-        self.path = "/tmp/b200r_clocks_%d_%d.csv" % (os.getpid(), gpu_index)
+        self.samples, self.reasons = [], set()
+        self.stop_flag = False
+        self.thread = None
+        self.max_mhz = None
+
+    def _run(self):
+        import pynvml as nv
+        names = {nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+                 nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, nm in names.items():
+                    if r & bit:
+                        self.reasons.add(nm)
+            except Exception:
+                break
+            time.sleep(0.0005)
 
     def start(self):
         try:
-            self.f = open(self.path, "w")
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
-                 "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
-                stderr=subprocess.DEVNULL)
+            import threading
+            import pynvml as nv
+            nv.nvmlInit()
+            # NVML enumerates physical GPUs; honour CUDA_VISIBLE_DEVICES when it lists indices
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            idx = self.gpu
+            if vis and all(x.strip().isdigit() for x in vis.split(",")):
+                idx = int(vis.split(",")[self.gpu])
+            self.h = nv.nvmlDeviceGetHandleByIndex(idx)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)
+            self.thread = threading.Thread(target=self._run, daemon=True)
+            self.thread.start()
         except Exception:
-            self.proc = None
+            self.thread = None
 
     def stop(self):
-        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        if self.proc is None:
-            return out
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except Exception:
-            self.proc.kill()
-        self.f.close()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        try:
-            for line in open(self.path):
-                p = [x.strip() for x in line.split(",")]
-                if len(p) < 9:
-                    continue
-                try:
-                    sm.append(float(p[1])); mx.append(float(p[2]))
-                except ValueError:
-                    continue
-                for nm, v in zip(names, p[5:9]):
-                    if v.lower().startswith("active"):
-                        reasons.add(nm)
-            os.unlink(self.path)
-        except Exception:
-            pass
-        if sm:
-            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), samples=len(sm))
-        out["reasons"] = sorted(reasons)
+        self.stop_flag = True
+        if self.thread is not None:
+            self.thread.join(timeout=2)
+        out = {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+               "samples": len(self.samples)}
+        if self.samples:
+            out["sm_mhz"] = float(np.median(self.samples))
         return out
 
 
@@ -284,9 +288,11 @@ def run_b200(args):
     launches0 = _lib.launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
+    th0 = time.perf_counter()
     for b in range(W, nb):
         router.route(resident[b], avail_mask(b), SEED, seq, out=out)
         seq += args.batch * world
+    host_submit_ms = (time.perf_counter() - th0) * 1e3 / K
     ev1.record()
     barrier()
     clocks = sampler.stop()
@@ -296,7 +302,7 @@ def run_b200(args):
         t = torch.tensor([ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
-    st = router.check_status()
+    st = router.check_status(count_nodes=True)
     n_dec = K * args.batch * world
     payload = sum(p.payload_bytes for p in host[W:])
     if world > 1:
@@ -305,7 +311,15 @@ def run_b200(args):
         payload = int(t.item())
     value = n_dec / (ms * 1e-3)
 
-    # ---- pass 2: same batches again with per-kernel events (roofline of k_hash_chunks)
+    # ---- pass 2: the same W+K batches on a fresh table, with per-kernel CUDA events
+    # around every launch of the K timed steps (roofline of k_hash_chunks, kernel shares)
+    del router
+    router = new_router()
+    seq = 0
+    for b in range(W):
+        router.route(resident[b], avail_mask(b), SEED, seq, out=out)
+        seq += args.batch * world
+    barrier()
     _lib.prof_enable(True)
     for b in range(W, nb):
         router.route(resident[b], avail_mask(b), SEED, seq, out=out)
@@ -371,7 +385,7 @@ def run_b200(args):
                 "config": workload_config(args, world),
                 "prompt_gbs": payload / (ms * 1e-3) / 1e9,
                 "prompt_frac_of_hbm": payload / (ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
-                "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
+                "clocks": clocks, "host_submit_ms_per_step": host_submit_ms, "e2e": e2e, "gpu_launches": int(launches),
                 "roofline": {"bound": "hbm", "kernel": "k_hash_chunks", "achieved": achieved,
                              "peak": peaks["hbm_gbs"], "unit": "GB/s",
                              "frac": achieved / peaks["hbm_gbs"], "traffic": None,

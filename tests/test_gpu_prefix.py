@@ -109,7 +109,7 @@ def test_route_golden_traces(golden_prefix):
         assert dec == tr["decisions"], tr["name"]
         if tr["lookups"] is not None:
             assert looks == tr["lookups"], tr["name"]
-        st = t.check_status()
+        st = t.check_status(count_nodes=True)
         assert trie_as_sorted_list(t.dump()) == tr["trie"], tr["name"]
         assert st["num_nodes"] == len(tr["trie"]) - 1
         t.close()

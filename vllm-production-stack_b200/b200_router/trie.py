@@ -72,19 +72,22 @@ class GpuHashTrie:
         with torch.cuda.device(self.device):
             _lib.check(_lib.lib().b200r_trie_clear(self._h, _stream()))
 
-    def status(self) -> Dict[str, int]:
-        st, nn, rm, cap = C.c_uint32(), C.c_int64(), C.c_uint64(), C.c_int64()
+    def status(self, count_nodes: bool = True) -> Dict[str, int]:
+        """Latched status bits, root mask, capacity; the node count is a table
+        scan on the device and only done when asked for."""
+        st, nn, rm, cap = C.c_uint32(), C.c_int64(-1), C.c_uint64(), C.c_int64()
         with torch.cuda.device(self.device):
-            _lib.check(_lib.lib().b200r_trie_status(self._h, _stream(), C.byref(st), C.byref(nn),
+            _lib.check(_lib.lib().b200r_trie_status(self._h, _stream(), C.byref(st),
+                                                    C.byref(nn) if count_nodes else None,
                                                     C.byref(rm), C.byref(cap)))
         return {"status": st.value, "num_nodes": nn.value, "root_mask": rm.value,
                 "capacity": cap.value}
 
-    def check_status(self):
-        s = self.status()
+    def check_status(self, count_nodes: bool = False):
+        s = self.status(count_nodes)
         if s["status"] & _lib.S_TABLE_FULL:
-            raise _lib.B200RouterError("GPU trie table is full (%d nodes, capacity %d): create it "
-                                       "with a larger cap_log2" % (s["num_nodes"], s["capacity"]))
+            raise _lib.B200RouterError("GPU trie table is full (capacity %d entries): create it "
+                                       "with a larger cap_log2" % s["capacity"])
         if s["status"] & _lib.S_CHUNK_CAP:
             raise _lib.B200RouterError("chunk capacity exceeded: max_chunks was too small")
         return s

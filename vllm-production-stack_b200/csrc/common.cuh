@@ -34,18 +34,52 @@ constexpr uint64_t XP3 = 0x165667B19E3779F9ULL;
 constexpr uint64_t XP4 = 0x85EBCA77C2B2AE63ULL;
 constexpr uint64_t XP5 = 0x27D4EB2F165667C5ULL;
 
+// 64-bit helpers written against the 32-bit integer pipes of sm_100a: a 64x64->64
+// multiply by a constant is IMAD.WIDE + 2 IMAD, a 64-bit rotate is two funnel shifts.
+__device__ __forceinline__ void split64(uint64_t x, uint32_t &lo, uint32_t &hi)
+{
+    asm("mov.b64 {%0,%1}, %2;" : "=r"(lo), "=r"(hi) : "l"(x));
+}
+__device__ __forceinline__ uint64_t join64(uint32_t lo, uint32_t hi)
+{
+    uint64_t x;
+    asm("mov.b64 %0, {%1,%2};" : "=l"(x) : "r"(lo), "r"(hi));
+    return x;
+}
+template <int R>
+__device__ __forceinline__ uint64_t rotl(uint64_t x)
+{
+    uint32_t lo, hi;
+    split64(x, lo, hi);
+    if (R >= 32) { uint32_t t = lo; lo = hi; hi = t; }
+    constexpr int r = R & 31;
+    if (r == 0) return join64(lo, hi);
+    return join64(__funnelshift_l(hi, lo, r), __funnelshift_l(lo, hi, r));
+}
 __device__ __forceinline__ uint64_t rotl64(uint64_t x, int r) { return (x << r) | (x >> (64 - r)); }
+template <uint64_t C>
+__device__ __forceinline__ uint64_t mulc(uint64_t x)
+{
+    uint32_t xl, xh, wl, wh;
+    split64(x, xl, xh);
+    uint64_t w;
+    asm("mul.wide.u32 %0, %1, %2;" : "=l"(w) : "r"(xl), "r"((uint32_t)C));
+    split64(w, wl, wh);
+    asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(wh) : "r"(xh), "r"((uint32_t)C));
+    asm("mad.lo.u32 %0, %1, %2, %0;" : "+r"(wh) : "r"(xl), "r"((uint32_t)(C >> 32)));
+    return join64(wl, wh);
+}
 __device__ __forceinline__ uint64_t xround(uint64_t acc, uint64_t in)
 {
-    return rotl64(acc + in * XP2, 31) * XP1;
+    return mulc<XP1>(rotl<31>(acc + mulc<XP2>(in)));
 }
 __device__ __forceinline__ uint64_t xmerge(uint64_t h, uint64_t v)
 {
-    return (h ^ xround(0, v)) * XP1 + XP4;
+    return mulc<XP1>(h ^ xround(0, v)) + XP4;
 }
 __device__ __forceinline__ uint64_t xavalanche(uint64_t h)
 {
-    h ^= h >> 33; h *= XP2; h ^= h >> 29; h *= XP3; h ^= h >> 32;
+    h ^= h >> 33; h = mulc<XP2>(h); h ^= h >> 29; h = mulc<XP3>(h); h ^= h >> 32;
     return h;
 }
 __device__ __forceinline__ uint64_t u64_of(uint32_t lo, uint32_t hi)
@@ -85,15 +119,15 @@ __device__ inline uint64_t xxh64_global(const uint8_t *p, int len)
             v4 = xround(v4, ldg64_any(p + 24));
             p += 32;
         } while (p <= lim);
-        h = rotl64(v1, 1) + rotl64(v2, 7) + rotl64(v3, 12) + rotl64(v4, 18);
+        h = rotl<1>(v1) + rotl<7>(v2) + rotl<12>(v3) + rotl<18>(v4);
         h = xmerge(h, v1); h = xmerge(h, v2); h = xmerge(h, v3); h = xmerge(h, v4);
     } else {
         h = XP5;
     }
     h += (uint64_t)len;
-    while (p + 8 <= end) { h ^= xround(0, ldg64_any(p)); h = rotl64(h, 27) * XP1 + XP4; p += 8; }
-    if (p + 4 <= end) { h ^= (uint64_t)ldg32_any(p) * XP1; h = rotl64(h, 23) * XP2 + XP3; p += 4; }
-    while (p < end) { h ^= (uint64_t)(*p) * XP5; h = rotl64(h, 11) * XP1; p++; }
+    while (p + 8 <= end) { h ^= xround(0, ldg64_any(p)); h = mulc<XP1>(rotl<27>(h)) + XP4; p += 8; }
+    if (p + 4 <= end) { h ^= mulc<XP1>((uint64_t)ldg32_any(p)); h = mulc<XP2>(rotl<23>(h)) + XP3; p += 4; }
+    while (p < end) { h ^= mulc<XP5>((uint64_t)(*p)); h = mulc<XP1>(rotl<11>(h)); p++; }
     return xavalanche(h);
 }
 
@@ -132,7 +166,7 @@ struct Key { uint64_t k1, k2; };
 // node just before lane 0.  Out: key of this lane's node.
 __device__ __forceinline__ Key key_scan_warp(uint64_t h, Key carry, int lane)
 {
-    uint64_t p1 = h, p2 = rotl64(h, 32);
+    uint64_t p1 = h, p2 = rotl<32>(h);
     if (lane == 0) { p1 += KA1 * carry.k1; p2 += KA2 * carry.k2; }
 #define B200R_KS_STEP(S)                                           \
     {                                                              \
@@ -150,13 +184,17 @@ __device__ __forceinline__ Key key_scan_warp(uint64_t h, Key carry, int lane)
 // -------------------------------------------------------------- table entries
 struct __align__(32) Entry {
     uint64_t k1, k2;   // path key; (0,0) = empty.  Stored keys have k1,k2 != 0.
-    uint64_t h;        // chunk hash of the edge parent -> node (for dumps)
     uint64_t mask;     // endpoint set
+    unsigned long long first;   // batch bookkeeping: (epoch << 32) | ~request of the first
+                                // request of batch `epoch` that touched the node (atomicMax)
 };
+// The chunk hash of the edge parent -> node is kept in a side array hs[slot]:
+// written once at creation, read only by dumps, so it stays out of the 32-byte
+// sector every probe touches.
 
 struct TrieDev {             // device-resident control block
     uint64_t root_mask;
-    unsigned long long num_nodes;
+    unsigned long long num_nodes;    // filled by k_count_nodes (status / dump), not on the hot path
     unsigned int status;
     unsigned int dump_count_lo;
     unsigned long long dump_count;
@@ -209,8 +247,8 @@ __device__ __forceinline__ uint32_t table_find(const Entry *tab, int cap_log2, u
 
 // Find or create the entry for (k1,k2).  Returns the slot, SLOT_NONE if the
 // table is full.  *created is set when this call made the entry.
-__device__ __forceinline__ uint32_t table_claim(Entry *tab, int cap_log2, uint64_t k1, uint64_t k2,
-                                                uint64_t h, bool *created)
+__device__ __forceinline__ uint32_t table_claim(Entry *tab, uint64_t *hs, int cap_log2, uint64_t k1,
+                                                uint64_t k2, uint64_t h, bool *created)
 {
     if (k1 == 0) k1 = 1;
     if (k2 == 0) k2 = 1;
@@ -226,7 +264,7 @@ __device__ __forceinline__ uint32_t table_claim(Entry *tab, int cap_log2, uint64
             if (a == 0 && b == 0) {
                 cas128(e, k1, k2, a, b);
                 if (a == 0 && b == 0) {
-                    e->h = h;
+                    hs[s] = h;
                     *created = true;
                     return s;
                 }

@@ -12,7 +12,7 @@
 //   k_hash_chunks               XXH64 of every chunk, one thread per chunk,
 //                               bytes staged by cp.async into swizzled smem
 //   k_claim                     path keys (warp scan) + find-or-create in the
-//                               open-addressing table + "first toucher" atomicMin
+//                               open-addressing table + "first toucher" atomicMax
 //   k_select                    per request: deepest usable node, root draw or leader
 //   k_commit                    resolve leader chains, OR the endpoint into new nodes
 #include <cstdarg>
@@ -198,57 +198,92 @@ __device__ __forceinline__ void cp_async_wait_all()
     asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
 }
 
-// XXH64 of one staged chunk.  `row` = the chunk's 128-byte row in shared
-// memory, whose 16-byte units are XOR-swizzled by `sw` (= row index & 7) so
-// that the 8 lanes of an LDS.128 phase hit 8 different bank groups.
-__device__ __forceinline__ uint64_t xxh64_staged(const uint8_t *row, int sw, int len)
+__device__ __forceinline__ uint4 lds128(uint32_t saddr)
 {
-#define UNIT(u) (*(const uint4 *)(row + ((((u)) ^ sw) << 4)))
-#define BYTE_AT(o) (row[((((o) >> 4) ^ sw) << 4) | ((o)&15)])
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(saddr));
+    return v;
+}
+
+// Staged chunk rows: row c of the tile is 128 bytes at tile + 128*c whose eight
+// 16-byte units are XOR-swizzled by (c & 7), so the LDS.128 reads of the 8
+// threads of one shared-memory phase (stride 128 B) hit 8 different bank groups.
+//
+// XXH64 of a full 128-byte chunk: straight-line, all eight LDS.128 up front.
+__device__ __forceinline__ uint64_t xxh64_row128(uint32_t row, int sw)
+{
+    uint4 q[8];
+#pragma unroll
+    for (int u = 0; u < 8; u++) q[u] = lds128(row + ((u ^ sw) << 4));
+    uint64_t v1 = XP1 + XP2, v2 = XP2, v3 = 0, v4 = 0 - XP1;
+#pragma unroll
+    for (int s = 0; s < 4; s++) {
+        v1 = xround(v1, join64(q[2 * s].x, q[2 * s].y));
+        v2 = xround(v2, join64(q[2 * s].z, q[2 * s].w));
+        v3 = xround(v3, join64(q[2 * s + 1].x, q[2 * s + 1].y));
+        v4 = xround(v4, join64(q[2 * s + 1].z, q[2 * s + 1].w));
+    }
+    uint64_t h = rotl<1>(v1) + rotl<7>(v2) + rotl<12>(v3) + rotl<18>(v4);
+    h = xmerge(h, v1); h = xmerge(h, v2); h = xmerge(h, v3); h = xmerge(h, v4);
+    h += 128;
+    return xavalanche(h);
+}
+
+// XXH64 of a staged chunk of any length 1..128 (ragged last chunk of a request).
+__device__ __noinline__ uint64_t xxh64_row_any(const uint8_t *row, int sw, int len)
+{
+#define ROW_OFF(o) (((((o) >> 4) ^ sw) << 4) | ((o)&15))
     uint64_t h;
     const int nst = len >> 5;
     if (nst) {
         uint64_t v1 = XP1 + XP2, v2 = XP2, v3 = 0, v4 = 0 - XP1;
-#pragma unroll
-        for (int s = 0; s < 4; s++) {
-            if (s < nst) {
-                uint4 a = UNIT(2 * s), b = UNIT(2 * s + 1);
-                v1 = xround(v1, u64_of(a.x, a.y));
-                v2 = xround(v2, u64_of(a.z, a.w));
-                v3 = xround(v3, u64_of(b.x, b.y));
-                v4 = xround(v4, u64_of(b.z, b.w));
-            }
+        for (int s = 0; s < nst; s++) {
+            const uint4 a = *(const uint4 *)(row + (((2 * s) ^ sw) << 4));
+            const uint4 b = *(const uint4 *)(row + (((2 * s + 1) ^ sw) << 4));
+            v1 = xround(v1, join64(a.x, a.y));
+            v2 = xround(v2, join64(a.z, a.w));
+            v3 = xround(v3, join64(b.x, b.y));
+            v4 = xround(v4, join64(b.z, b.w));
         }
-        h = rotl64(v1, 1) + rotl64(v2, 7) + rotl64(v3, 12) + rotl64(v4, 18);
+        h = rotl<1>(v1) + rotl<7>(v2) + rotl<12>(v3) + rotl<18>(v4);
         h = xmerge(h, v1); h = xmerge(h, v2); h = xmerge(h, v3); h = xmerge(h, v4);
     } else {
         h = XP5;
     }
     h += (uint64_t)len;
     int o = nst << 5;
-    // 8- and 4-byte steps never straddle a 16-byte unit (o is a multiple of 4/8)
+    // 8- and 4-byte steps never straddle a 16-byte unit (o is a multiple of 8 / 4)
     while (o + 8 <= len) {
-        uint64_t w = *(const uint64_t *)(row + ((((o >> 4) ^ sw) << 4) | (o & 15)));
+        const uint64_t w = *(const uint64_t *)(row + ROW_OFF(o));
         h ^= xround(0, w);
-        h = rotl64(h, 27) * XP1 + XP4;
+        h = mulc<XP1>(rotl<27>(h)) + XP4;
         o += 8;
     }
     if (o + 4 <= len) {
-        uint32_t w = *(const uint32_t *)(row + ((((o >> 4) ^ sw) << 4) | (o & 15)));
-        h ^= (uint64_t)w * XP1;
-        h = rotl64(h, 23) * XP2 + XP3;
+        const uint32_t w = *(const uint32_t *)(row + ROW_OFF(o));
+        h ^= mulc<XP1>((uint64_t)w);
+        h = mulc<XP2>(rotl<23>(h)) + XP3;
         o += 4;
     }
     while (o < len) {
-        h ^= (uint64_t)BYTE_AT(o) * XP5;
-        h = rotl64(h, 11) * XP1;
+        h ^= mulc<XP5>((uint64_t)row[ROW_OFF(o)]);
+        h = mulc<XP1>(rotl<11>(h));
         o++;
     }
     return xavalanche(h);
-#undef UNIT
-#undef BYTE_AT
+#undef ROW_OFF
 }
 
+// One thread per chunk, 256-chunk tiles.
+//   1. tile -> request map: head flags in shared memory + max-scan
+//   2. each warp stages its own 32 chunks with cp.async (coalesced: one
+//      instruction moves 4 chunks x 128 B), descriptors exchanged by shuffles,
+//      so staging needs no block-wide barrier
+//   3. full 128-byte chunks: straight-line XXH64 from swizzled shared memory;
+//      ragged last chunks are compacted per tile and finished in a second pass
+//      (so their longer code path runs once per tile, not once per warp);
+//      unaligned / multi-byte-UTF-8 chunks go through the generic global path.
 __global__ void __launch_bounds__(TILE)
 k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ starts,
               const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars,
@@ -256,11 +291,11 @@ k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ sta
               const int32_t *__restrict__ chunk_off, int n, int cc, int64_t max_chunks,
               uint64_t *__restrict__ hashes)
 {
-    __shared__ __align__(128) uint8_t s_tile[TILE * 128];
+    __shared__ __align__(1024) uint8_t s_tile[TILE * 128];
     __shared__ int s_req[TILE];
     __shared__ int s_wmax[TILE / 32];
-    __shared__ unsigned long long s_src[TILE];
-    __shared__ int s_len[TILE];
+    __shared__ int s_part[TILE];
+    __shared__ int s_npart;
 
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const int64_t G0 = (int64_t)blockIdx.x * TILE;
@@ -268,9 +303,10 @@ k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ sta
     if (total > max_chunks) total = max_chunks;
     if (G0 >= total) return;
 
-    // ---- which request does each chunk of the tile belong to?
+    // ---- 1. which request does each chunk of the tile belong to?
     const int r0 = tile_first[blockIdx.x];
     s_req[tid] = (tid == 0) ? r0 : 0;
+    if (tid == 0) s_npart = 0;
     __syncthreads();
     for (int r = r0 + 1 + tid; r < n; r += TILE) {
         int64_t b = chunk_base[r];
@@ -309,28 +345,49 @@ k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ sta
         p = bytes + starts[r] + off;
         fast = (clen <= 128) && (((uintptr_t)p & 15) == 0);
     }
-    s_src[tid] = fast ? (unsigned long long)(uintptr_t)p : 0ULL;
-    s_len[tid] = fast ? clen : 0;
-    __syncthreads();
 
-    // ---- stage: 8 x 16-byte units per chunk, coalesced over the tile
+    // ---- 2. stage this warp's 32 chunks
     const uint32_t tile_s = (uint32_t)__cvta_generic_to_shared(s_tile);
+    const uint32_t wrow = tile_s + (uint32_t)(w * 32) * 128;
+    const unsigned long long my_src = fast ? (unsigned long long)(uintptr_t)p : 0ULL;
+    const int my_units = fast ? ((clen + 15) >> 4) : 0;
+    {
+        // lane copies unit u of chunk c = 4k + sub; (c & 7) = sub ^ 4(k&1), so the swizzled
+        // destination is one of two per-lane bases plus k * 512
+        const int u = lane & 7, sub = lane >> 3;
+        uint32_t d_even = wrow + sub * 128 + ((u ^ sub) << 4);
+        asm volatile("" : "+r"(d_even));                 // keep it in a register
+        const uint32_t d_odd = d_even ^ 64u;
 #pragma unroll
-    for (int k = 0; k < 8; k++) {
-        int item = k * TILE + tid;
-        int c = item >> 3, u = item & 7;
-        int rem = s_len[c] - (u << 4);
-        if (rem > 0) {
-            const uint8_t *src = (const uint8_t *)(uintptr_t)s_src[c] + (u << 4);
-            cp_async16(tile_s + c * 128 + ((u ^ (c & 7)) << 4), src, rem < 16 ? rem : 16);
+        for (int k = 0; k < 8; k++) {
+            const int c = 4 * k + sub;                       // chunk (lane) inside the warp
+            const unsigned long long src = __shfl_sync(0xffffffffu, my_src, c);
+            const int nu = __shfl_sync(0xffffffffu, my_units, c);
+            // a whole 16-byte unit is copied when it holds at least one byte of the
+            // chunk: the unit is 16-byte aligned, so it lies inside the buffer's granule
+            if (u < nu)
+                cp_async16(((k & 1) ? d_odd : d_even) + k * 512,
+                           (const uint8_t *)(uintptr_t)src + (u << 4), 16);
         }
     }
     cp_async_wait_all();
-    __syncthreads();
+    __syncwarp();
 
-    if (!valid) return;
-    uint64_t h = fast ? xxh64_staged(s_tile + tid * 128, tid & 7, clen) : xxh64_global(p, clen);
-    hashes[g] = h;
+    // ---- 3. hash
+    if (valid) {
+        if (fast && clen == 128) {
+            hashes[g] = xxh64_row128(wrow + lane * 128, lane & 7);
+        } else if (fast) {
+            s_part[atomicAdd(&s_npart, 1)] = (tid << 8) | clen;
+        } else {
+            hashes[g] = xxh64_global(p, clen);
+        }
+    }
+    __syncthreads();
+    if (tid < s_npart) {
+        const int e = s_part[tid], c = e >> 8;
+        hashes[G0 + c] = xxh64_row_any(s_tile + c * 128, c & 7, e & 0xFF);
+    }
 }
 
 // =========================================================================
@@ -390,16 +447,10 @@ k_lookup(const Entry *__restrict__ tab, int cap_log2, const uint64_t *__restrict
     }
 }
 
-__device__ __forceinline__ void count_created(TrieDev *dev, bool created)
-{
-    unsigned bal = __ballot_sync(0xffffffffu, created);
-    if (bal && (threadIdx.x & 31) == (__ffs(bal) - 1))
-        atomicAdd(&dev->num_nodes, (unsigned long long)__popc(bal));
-}
-
 // a3: order-independent batched insert.
 __global__ void __launch_bounds__(WARPS_PER_CTA * 32)
-k_insert(Entry *__restrict__ tab, int cap_log2, TrieDev *dev, const uint64_t *__restrict__ hashes,
+k_insert(Entry *__restrict__ tab, uint64_t *__restrict__ hs, int cap_log2, TrieDev *dev,
+         const uint64_t *__restrict__ hashes,
          const int32_t *__restrict__ chunk_base, int n, const int32_t *__restrict__ endpoint)
 {
     const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
@@ -419,23 +470,22 @@ k_insert(Entry *__restrict__ tab, int cap_log2, TrieDev *dev, const uint64_t *__
         carry.k2 = __shfl_sync(0xffffffffu, k.k2, 31);
         bool created = false;
         if (valid) {
-            uint32_t s = table_claim(tab, cap_log2, k.k1, k.k2, h, &created);
+            uint32_t s = table_claim(tab, hs, cap_log2, k.k1, k.k2, h, &created);
             if (s == SLOT_NONE) atomicOr(&dev->status, B200R_S_TABLE_FULL);
             else if (created || !(tab[s].mask & bit))
                 atomicOr((unsigned long long *)&tab[s].mask, bit);
         }
-        count_created(dev, created);
     }
 }
 
 // a5 step 1: claim every node of every path; classify against the pre-batch
 // masks; record who touches a not-yet-usable node first.
 //   slots[g] = slot | PREOK_BIT   node usable before the batch (mask & avail != 0)
-//   slots[g] = slot               otherwise; first[slot] = min request index (epoch-tagged)
+//   slots[g] = slot               otherwise; entry.first = (epoch, ~min request index)
 constexpr uint32_t PREOK_BIT = 0x80000000u;
 
 __global__ void __launch_bounds__(WARPS_PER_CTA * 32)
-k_claim(Entry *__restrict__ tab, int cap_log2, unsigned long long *__restrict__ first, TrieDev *dev,
+k_claim(Entry *__restrict__ tab, uint64_t *__restrict__ hs, int cap_log2, TrieDev *dev,
         const uint64_t *__restrict__ hashes, const int32_t *__restrict__ chunk_base, int n,
         int64_t max_chunks, uint64_t avail, unsigned long long tag, uint32_t *__restrict__ slots)
 {
@@ -452,21 +502,25 @@ k_claim(Entry *__restrict__ tab, int cap_log2, unsigned long long *__restrict__ 
         carry.k2 = __shfl_sync(0xffffffffu, k.k2, 31);
         bool created = false;
         if (valid) {
-            uint32_t s = table_claim(tab, cap_log2, k.k1, k.k2, h, &created);
+            uint32_t s = table_claim(tab, hs, cap_log2, k.k1, k.k2, h, &created);
             if (s == SLOT_NONE) {
                 atomicOr(&dev->status, B200R_S_TABLE_FULL);
                 slots[sp.b0 + d] = SLOT_NONE;
             } else {
-                const uint64_t m = created ? 0 : tab[s].mask;
+                uint64_t m = 0, cur = 0;
+                if (!created) ld_key((const Entry *)&tab[s].mask, m, cur);   // (mask, first): same sector
                 if (m & avail) {
                     slots[sp.b0 + d] = s | PREOK_BIT;
                 } else {
                     slots[sp.b0 + d] = s;
-                    atomicMin(first + s, tag | (unsigned long long)(unsigned)i);
+                    // hot nodes are touched by many requests of a batch: skip the atomic when
+                    // an earlier request of this batch is already recorded (a stale read only
+                    // costs a redundant atomicMax)
+                    const unsigned long long mine = tag | (unsigned long long)(~(unsigned)i);
+                    if (cur < mine) atomicMax(&tab[s].first, mine);
                 }
             }
         }
-        count_created(dev, created);
     }
 }
 
@@ -475,42 +529,42 @@ k_claim(Entry *__restrict__ tab, int cap_log2, unsigned long long *__restrict__ 
 // If that node was usable before the batch (or depth 0) the request is a root
 // and draws from its candidate set; else it follows the request that touched
 // the node first.
-__global__ void __launch_bounds__(WARPS_PER_CTA * 32)
-k_select(const Entry *__restrict__ tab, const unsigned long long *__restrict__ first,
-         const int32_t *__restrict__ chunk_base, int n, int64_t max_chunks,
+__global__ void __launch_bounds__(256)
+k_select(const Entry *__restrict__ tab, const int32_t *__restrict__ chunk_base, int n, int64_t max_chunks,
          const uint32_t *__restrict__ slots, uint64_t avail, unsigned long long tag, uint64_t seed,
          uint64_t seq0, int32_t *__restrict__ leader, int32_t *__restrict__ choice,
          int32_t *__restrict__ depth_out, uint64_t *__restrict__ matched_out)
 {
-    const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    // one thread per request: independent dependent-load chains, 32 per warp in flight
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const ReqSpan sp = req_span(chunk_base, i, max_chunks);
+    const uint32_t *sl = slots + sp.b0;
     int dstar = 0;
-    uint32_t star_slot = SLOT_NONE;       // slot word of the node at depth dstar
-    uint32_t star_first = 0;
-    for (int blk = 0; blk * 32 < sp.C; blk++) {
-        const int d = blk * 32 + lane;
-        const uint32_t sl = (d < sp.C) ? slots[sp.b0 + d] : SLOT_NONE;
-        bool ok = false;
-        uint32_t f = 0;
-        if (sl != SLOT_NONE) {
-            if (sl & PREOK_BIT) ok = true;
-            else {
-                unsigned long long fv = first[sl];
-                f = (uint32_t)fv;
-                ok = ((fv >> 32) == (tag >> 32)) && f < (uint32_t)i;
+    uint32_t star_slot = SLOT_NONE, star_first = 0;
+    bool go = true;
+    for (int d0 = 0; d0 < sp.C && go; d0 += 4) {
+        uint32_t v[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) v[k] = (d0 + k < sp.C) ? sl[d0 + k] : SLOT_NONE;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            if (!go) break;
+            const uint32_t x = v[k];
+            bool ok = false;
+            uint32_t f = 0;
+            if (x != SLOT_NONE) {
+                if (x & PREOK_BIT) ok = true;
+                else {
+                    const unsigned long long fv = tab[x].first;
+                    f = ~(uint32_t)fv;
+                    ok = ((fv >> 32) == (tag >> 32)) && f < (uint32_t)i;
+                }
             }
+            if (ok) { dstar = d0 + k + 1; star_slot = x; star_first = f; }
+            else go = false;
         }
-        const unsigned bal = __ballot_sync(0xffffffffu, ok);
-        const int nok = (bal == 0xffffffffu) ? 32 : (__ffs(~bal) - 1);
-        if (nok > 0) {
-            star_slot = __shfl_sync(0xffffffffu, sl, nok - 1);
-            star_first = __shfl_sync(0xffffffffu, f, nok - 1);
-            dstar += nok;
-        }
-        if (nok < 32) break;
     }
-    if (lane != 0) return;
     depth_out[i] = dstar;
     if (dstar == 0 || (star_slot & PREOK_BIT)) {
         const uint64_t cand = (dstar == 0) ? avail : (tab[star_slot & ~PREOK_BIT].mask & avail);
@@ -527,33 +581,44 @@ k_select(const Entry *__restrict__ tab, const unsigned long long *__restrict__ f
 // a5 step 3: followers take their (transitive) leader's endpoint; every
 // request ORs its endpoint into the nodes below its match depth -- exactly the
 // nodes it was the first to touch, so no other request writes them.
-__global__ void __launch_bounds__(WARPS_PER_CTA * 32)
+__global__ void __launch_bounds__(256)
 k_commit(Entry *__restrict__ tab, TrieDev *dev, const int32_t *__restrict__ chunk_base, int n,
          int64_t max_chunks, const uint32_t *__restrict__ slots, const int32_t *__restrict__ leader,
          const int32_t *__restrict__ choice, const int32_t *__restrict__ depth,
          int32_t *__restrict__ endpoint, uint64_t *__restrict__ matched_out)
 {
-    const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     int j = i, l;
     while ((l = leader[j]) >= 0) j = l;          // chains strictly decrease in index
     const int e = choice[j];
-    if (lane == 0) {
-        endpoint[i] = e;
-        if (j != i) matched_out[i] = (e >= 0) ? (1ULL << e) : 0;
-    }
+    endpoint[i] = e;
+    if (j != i) matched_out[i] = (e >= 0) ? (1ULL << e) : 0;
     if (e < 0) return;
     const uint64_t bit = 1ULL << e;
-    if (lane == 0 && !(dev->root_mask & bit)) atomicOr((unsigned long long *)&dev->root_mask, bit);
+    if (!(dev->root_mask & bit)) atomicOr((unsigned long long *)&dev->root_mask, bit);
     const ReqSpan sp = req_span(chunk_base, i, max_chunks);
-    for (int d = depth[i] + lane; d < sp.C; d += 32) {
-        const uint32_t sl = slots[sp.b0 + d];
-        if (sl != SLOT_NONE) atomicOr((unsigned long long *)&tab[sl & ~PREOK_BIT].mask, bit);
+    for (int d = depth[i]; d < sp.C; d++) {
+        const uint32_t x = slots[sp.b0 + d];
+        if (x != SLOT_NONE) atomicOr((unsigned long long *)&tab[x & ~PREOK_BIT].mask, bit);
     }
 }
 
 // ------------------------------------------------------------ dump / restore
-__global__ void k_dump(const Entry *__restrict__ tab, int64_t cap, TrieDev *dev,
+__global__ void k_count_nodes(const Entry *__restrict__ tab, int64_t cap, TrieDev *dev)
+{
+    unsigned long long mine = 0;
+    for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < cap;
+         s += (int64_t)gridDim.x * blockDim.x) {
+        uint64_t a, b;
+        ld_key(tab + s, a, b);
+        mine += (a | b) ? 1 : 0;
+    }
+    for (int o = 16; o; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
+    if ((threadIdx.x & 31) == 0 && mine) atomicAdd(&dev->num_nodes, mine);
+}
+
+__global__ void k_dump(const Entry *__restrict__ tab, const uint64_t *__restrict__ hs, int64_t cap, TrieDev *dev,
                        uint64_t *__restrict__ out, int64_t max_nodes)
 {
     for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < cap;
@@ -564,14 +629,14 @@ __global__ void k_dump(const Entry *__restrict__ tab, int64_t cap, TrieDev *dev,
             if ((int64_t)idx < max_nodes) {
                 out[4 * idx + 0] = e.k1;
                 out[4 * idx + 1] = e.k2;
-                out[4 * idx + 2] = e.h;
+                out[4 * idx + 2] = hs[s];
                 out[4 * idx + 3] = e.mask;
             }
         }
     }
 }
 
-__global__ void k_apply_remote(Entry *__restrict__ tab, int cap_log2, TrieDev *dev,
+__global__ void k_apply_remote(Entry *__restrict__ tab, uint64_t *__restrict__ hs, int cap_log2, TrieDev *dev,
                                const uint64_t *__restrict__ ent, int64_t count, uint64_t root_or)
 {
     const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -580,11 +645,10 @@ __global__ void k_apply_remote(Entry *__restrict__ tab, int cap_log2, TrieDev *d
     if (idx < count) {
         const uint64_t k1 = ent[4 * idx], k2 = ent[4 * idx + 1], h = ent[4 * idx + 2],
                        m = ent[4 * idx + 3];
-        uint32_t s = table_claim(tab, cap_log2, k1, k2, h, &created);
+        uint32_t s = table_claim(tab, hs, cap_log2, k1, k2, h, &created);
         if (s == SLOT_NONE) atomicOr(&dev->status, B200R_S_TABLE_FULL);
         else if (m) atomicOr((unsigned long long *)&tab[s].mask, m);
     }
-    count_created(dev, created);
 }
 
 }  // namespace b200r
@@ -599,7 +663,7 @@ struct b200r_trie {
     int cap_log2;
     int chunk_chars;
     Entry *tab;
-    unsigned long long *first;
+    uint64_t *hs;
     TrieDev *dev;
     uint32_t epoch;
 };
@@ -853,9 +917,9 @@ int b200r_trie_create(int32_t cap_log2, int32_t chunk_chars, b200r_trie **out)
     const size_t cap = (size_t)1 << cap_log2;
     cudaError_t e;
     if ((e = cudaMalloc(&t->tab, cap * sizeof(Entry))) != cudaSuccess ||
-        (e = cudaMalloc(&t->first, cap * 8)) != cudaSuccess ||
+        (e = cudaMalloc(&t->hs, cap * 8)) != cudaSuccess ||
         (e = cudaMalloc(&t->dev, sizeof(TrieDev))) != cudaSuccess) {
-        cudaFree(t->tab); cudaFree(t->first); cudaFree(t->dev);
+        cudaFree(t->tab); cudaFree(t->hs); cudaFree(t->dev);
         delete t;
         return cuda_fail(e, "cudaMalloc(trie)");
     }
@@ -869,7 +933,7 @@ int b200r_trie_create(int32_t cap_log2, int32_t chunk_chars, b200r_trie **out)
 int b200r_trie_destroy(b200r_trie *t)
 {
     if (!t) return B200R_OK;
-    cudaFree(t->tab); cudaFree(t->first); cudaFree(t->dev);
+    cudaFree(t->tab); cudaFree(t->hs); cudaFree(t->dev);
     delete t;
     return B200R_OK;
 }
@@ -880,7 +944,6 @@ int b200r_trie_clear(b200r_trie *t, void *stream)
     cudaStream_t st = (cudaStream_t)stream;
     const size_t cap = (size_t)1 << t->cap_log2;
     B200R_CUDA(cudaMemsetAsync(t->tab, 0, cap * sizeof(Entry), st));
-    B200R_CUDA(cudaMemsetAsync(t->first, 0xFF, cap * 8, st));
     B200R_CUDA(cudaMemsetAsync(t->dev, 0, sizeof(TrieDev), st));
     t->epoch = 0;
     return B200R_OK;
@@ -891,6 +954,14 @@ int b200r_trie_status(b200r_trie *t, void *stream, uint32_t *status_bits, int64_
 {
     if (!t) { set_error("null trie"); return B200R_E_INVALID; }
     cudaStream_t st = (cudaStream_t)stream;
+    if (num_nodes) {     // counted on demand: keeps a contended counter off the routing path
+        const int64_t cap = (int64_t)1 << t->cap_log2;
+        int blocks = (int)((cap + 255) / 256);
+        if (blocks > 148 * 16) blocks = 148 * 16;
+        B200R_CUDA(cudaMemsetAsync(&t->dev->num_nodes, 0, 8, st));
+        k_count_nodes<<<blocks, 256, 0, st>>>(t->tab, cap, t->dev);
+        B200R_LAUNCH_CHECK("k_count_nodes");
+    }
     TrieDev h;
     B200R_CUDA(cudaMemcpyAsync(&h, t->dev, sizeof h, cudaMemcpyDeviceToHost, st));
     B200R_CUDA(cudaStreamSynchronize(st));
@@ -927,7 +998,7 @@ int b200r_trie_insert_batch(b200r_trie *t, const uint64_t *d_hashes, const int32
     const int blocks = (int)((n + WARPS_PER_CTA - 1) / WARPS_PER_CTA);
     { ProfScope ps__(PK_INSERT, (cudaStream_t)stream); g_launches += 1;
     k_insert<<<blocks, WARPS_PER_CTA * 32, 0, (cudaStream_t)stream>>>(
-        t->tab, t->cap_log2, t->dev, d_hashes, d_chunk_base, (int)n, d_endpoint);
+        t->tab, t->hs, t->cap_log2, t->dev, d_hashes, d_chunk_base, (int)n, d_endpoint);
     B200R_LAUNCH_CHECK("k_insert");
     }
     return B200R_OK;
@@ -963,33 +1034,35 @@ int b200r_prefix_route_batch(b200r_trie *t, const uint8_t *d_bytes, const int64_
     int32_t *leader = (int32_t *)(sc + p.off_leader);
     int32_t *choice = (int32_t *)(sc + p.off_choice);
 
-    // batch epoch for the "first toucher" words: newer batches carry a smaller
-    // high half, so atomicMin overrides anything left from older batches.
+    // batch epoch of the "first toucher" words: value = (epoch << 32) | ~request, merged
+    // with atomicMax, so a newer batch overrides whatever older batches left and, inside
+    // a batch, the smallest request index wins.  Zero (fresh table) means "never".
     if (t->epoch >= 0xFFFFFFF0u) {
-        B200R_CUDA(cudaMemsetAsync(t->first, 0xFF, ((size_t)8) << t->cap_log2, st));
-        t->epoch = 0;
+        set_error("b200r_prefix_route_batch: batch epoch exhausted; b200r_trie_clear or re-create the table");
+        return B200R_E_INVALID;
     }
     t->epoch++;
-    const unsigned long long tag = (unsigned long long)(0xFFFFFFFFu - t->epoch) << 32;
+    const unsigned long long tag = (unsigned long long)t->epoch << 32;
 
     rc = launch_hash(d_bytes, d_starts, d_lens, d_nchars, n, t->chunk_chars, flags, chunk_base,
                      hashes, max_chunks, sc, p, t->dev, st);
     if (rc) return rc;
     const int blocks = (int)((n + WARPS_PER_CTA - 1) / WARPS_PER_CTA);
     const int thr = WARPS_PER_CTA * 32;
+    const int tblocks = (int)((n + 255) / 256);
     { ProfScope ps__(PK_CLAIM, st); g_launches += 1;
-    k_claim<<<blocks, thr, 0, st>>>(t->tab, t->cap_log2, t->first, t->dev, hashes, chunk_base,
+    k_claim<<<blocks, thr, 0, st>>>(t->tab, t->hs, t->cap_log2, t->dev, hashes, chunk_base,
                                     (int)n, max_chunks, avail_mask, tag, slots);
     B200R_LAUNCH_CHECK("k_claim");
     }
     { ProfScope ps__(PK_SELECT, st); g_launches += 1;
-    k_select<<<blocks, thr, 0, st>>>(t->tab, t->first, chunk_base, (int)n, max_chunks, slots,
+    k_select<<<tblocks, 256, 0, st>>>(t->tab, chunk_base, (int)n, max_chunks, slots,
                                      avail_mask, tag, seed, seq0, leader, choice, d_match_depth,
                                      d_matched_mask);
     B200R_LAUNCH_CHECK("k_select");
     }
     { ProfScope ps__(PK_COMMIT, st); g_launches += 1;
-    k_commit<<<blocks, thr, 0, st>>>(t->tab, t->dev, chunk_base, (int)n, max_chunks, slots, leader,
+    k_commit<<<tblocks, 256, 0, st>>>(t->tab, t->dev, chunk_base, (int)n, max_chunks, slots, leader,
                                      choice, d_match_depth, d_endpoint, d_matched_mask);
     B200R_LAUNCH_CHECK("k_commit");
     }
@@ -1005,7 +1078,7 @@ int b200r_trie_dump(b200r_trie *t, uint64_t *d_out, int64_t max_nodes, int64_t *
     const int64_t cap = (int64_t)1 << t->cap_log2;
     int blocks = (int)((cap + 255) / 256);
     if (blocks > 148 * 16) blocks = 148 * 16;
-    k_dump<<<blocks, 256, 0, st>>>(t->tab, cap, t->dev, d_out, max_nodes);
+    k_dump<<<blocks, 256, 0, st>>>(t->tab, t->hs, cap, t->dev, d_out, max_nodes);
     B200R_LAUNCH_CHECK("k_dump");
     TrieDev h;
     B200R_CUDA(cudaMemcpyAsync(&h, t->dev, sizeof h, cudaMemcpyDeviceToHost, st));
@@ -1021,7 +1094,7 @@ int b200r_trie_apply_remote(b200r_trie *t, const uint64_t *d_entries, int64_t co
     if (!t || count < 0 || (count > 0 && !d_entries)) { set_error("b200r_trie_apply_remote: bad argument"); return B200R_E_INVALID; }
     const int64_t work = count > 0 ? count : 1;
     const int blocks = (int)((work + 255) / 256);
-    k_apply_remote<<<blocks, 256, 0, (cudaStream_t)stream>>>(t->tab, t->cap_log2, t->dev, d_entries,
+    k_apply_remote<<<blocks, 256, 0, (cudaStream_t)stream>>>(t->tab, t->hs, t->cap_log2, t->dev, d_entries,
                                                            count, root_mask_or);
     B200R_LAUNCH_CHECK("k_apply_remote");
     return B200R_OK;
