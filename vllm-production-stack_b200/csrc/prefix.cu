@@ -67,7 +67,6 @@ struct ProfScope {
     }
 };
 
-constexpr int TILE = 256;          // chunks per CTA of k_hash_chunks
 constexpr int PREP_BLOCK = 1024;   // requests per CTA of the prep kernels
 constexpr int WARPS_PER_CTA = 8;   // per-request kernels: one warp per request
 
@@ -106,7 +105,9 @@ k_prep_sums(const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars
 __global__ void __launch_bounds__(PREP_BLOCK)
 k_prep_scan(const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars, int n, int cc,
             const int32_t *__restrict__ block_sums, int32_t *__restrict__ chunk_base,
-            int32_t *__restrict__ tile_first, int64_t max_chunks, TrieDev *dev)
+            int32_t *__restrict__ tile_first, int64_t max_chunks, TrieDev *dev,
+            const uint8_t *__restrict__ bytes, const int64_t *__restrict__ starts,
+            uint64_t *__restrict__ hashes)
 {
     __shared__ int s_red[32];
     __shared__ int s_wsum[32];
@@ -134,12 +135,22 @@ k_prep_scan(const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars
             chunk_base[n] = base + c;
             if (dev && (int64_t)(base + c) > max_chunks) atomicOr(&dev->status, B200R_S_CHUNK_CAP);
         }
-        // tiles whose first chunk belongs to this request
+        // warp tiles (32 chunks) whose first chunk belongs to this request
         if (c > 0) {
-            int t0 = (base + TILE - 1) / TILE;
+            int t0 = (base + 31) / 32;
             int64_t lim = (int64_t)base + c;
             if (lim > max_chunks) lim = max_chunks;
-            for (int t = t0; (int64_t)t * TILE < lim; t++) tile_first[t] = i;
+            for (int t = t0; (int64_t)t * 32 < lim; t++) tile_first[t] = i;
+            // The ragged last chunk of an ASCII request is hashed here, one thread per
+            // request, so that k_hash_chunks is left with full 128-byte chunks only.
+            const int ln = lens[i];
+            const int nc = nchars ? nchars[i] : ln;
+            const int tail = ln - (c - 1) * cc;
+            const int64_t gl = (int64_t)base + c - 1;
+            if (hashes && nc == ln && tail < cc && gl < max_chunks) {
+                const uint8_t *q = bytes + starts[i];
+                if ((((uintptr_t)q) & 15) == 0) hashes[gl] = xxh64_global(q + (ln - tail), tail);
+            }
         }
     }
 }
@@ -275,97 +286,112 @@ __device__ __noinline__ uint64_t xxh64_row_any(const uint8_t *row, int sw, int l
 #undef ROW_OFF
 }
 
-// One thread per chunk, 256-chunk tiles.
-//   1. tile -> request map: head flags in shared memory + max-scan
-//   2. each warp stages its own 32 chunks with cp.async (coalesced: one
-//      instruction moves 4 chunks x 128 B), descriptors exchanged by shuffles,
-//      so staging needs no block-wide barrier
-//   3. full 128-byte chunks: straight-line XXH64 from swizzled shared memory;
-//      ragged last chunks are compacted per tile and finished in a second pass
-//      (so their longer code path runs once per tile, not once per warp);
-//      unaligned / multi-byte-UTF-8 chunks go through the generic global path.
-__global__ void __launch_bounds__(TILE)
+// ---------------------------------------------------------------------------
+// k_hash_chunks: one thread per chunk, and every WARP is an independent worker
+// on its own tile of 32 consecutive chunks -- no block-wide barrier anywhere, so
+// the 48 resident warps of an SM (6 CTAs x 8 warps, 4 KB of staging each) are
+// 48 independent latency chains and ~190 KB of prompt bytes stay in flight.
+//   map     tile -> requests with two rounds of independent global loads:
+//           tile_first[tile], then lane j fetches everything about request
+//           r0 + j; head positions are combined with a warp OR-reduction and
+//           each chunk lane pulls its request's record by shuffle.
+//   stage   the warp copies its 32 chunks with cp.async (coalesced: one
+//           instruction moves 4 chunks x 128 B) into XOR-swizzled shared memory
+//   hash    full 128-byte chunks: straight-line XXH64, eight LDS.128 up front.
+// Ragged last chunks of ASCII requests are not touched here: k_prep_scan (one
+// thread per request) hashes them, so this kernel has a single code path.
+// Unaligned or multi-byte-UTF-8 chunks take the generic global-memory routine.
+constexpr int WTILE = 32;                 // chunks per warp tile
+constexpr int HASH_WARPS = 8;             // warps per CTA
+
+struct ReqRec { int b, b1, ln, nc; long long st; };
+
+__global__ void __launch_bounds__(HASH_WARPS * 32)
 k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ starts,
               const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars,
               const int32_t *__restrict__ chunk_base, const int32_t *__restrict__ tile_first,
               const int32_t *__restrict__ chunk_off, int n, int cc, int64_t max_chunks,
               uint64_t *__restrict__ hashes)
 {
-    __shared__ __align__(1024) uint8_t s_tile[TILE * 128];
-    __shared__ int s_req[TILE];
-    __shared__ int s_wmax[TILE / 32];
-    __shared__ int s_part[TILE];
-    __shared__ int s_npart;
-
-    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    const int64_t G0 = (int64_t)blockIdx.x * TILE;
+    __shared__ __align__(1024) uint8_t s_tile[HASH_WARPS * WTILE * 128];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int64_t tile = (int64_t)blockIdx.x * HASH_WARPS + w;
+    const int64_t G0 = tile * WTILE;
     int64_t total = chunk_base[n];
     if (total > max_chunks) total = max_chunks;
-    if (G0 >= total) return;
+    if (G0 >= total) return;                                   // whole warp
 
-    // ---- 1. which request does each chunk of the tile belong to?
-    const int r0 = tile_first[blockIdx.x];
-    s_req[tid] = (tid == 0) ? r0 : 0;
-    if (tid == 0) s_npart = 0;
-    __syncthreads();
-    for (int r = r0 + 1 + tid; r < n; r += TILE) {
-        int64_t b = chunk_base[r];
-        if (b >= G0 + TILE) break;
-        if (chunk_base[r + 1] > b) s_req[(int)(b - G0)] = r;    // head of a non-empty request
+    // ---- map: which request owns each of the 32 chunks?
+    const int r0 = tile_first[tile];
+    ReqRec mine = { 0, 0, 0, 0, 0 };      // record of the request that owns this lane's chunk
+    for (int jb = 0;; jb += 32) {
+        const int r = r0 + jb + lane;
+        ReqRec q = { 0, 0, 0, 0, 0 };
+        bool live = false;
+        if (r < n) {
+            q.b = chunk_base[r]; q.b1 = chunk_base[r + 1];
+            q.st = starts[r]; q.ln = lens[r];
+            q.nc = nchars ? nchars[r] : q.ln;
+            live = (int64_t)q.b < G0 + WTILE;
+        }
+        const bool nonempty = live && q.b1 > q.b;
+        const int pos = (int64_t)q.b > G0 ? (int)(q.b - G0) : 0;
+        const unsigned heads = __reduce_or_sync(0xffffffffu, nonempty ? (1u << pos) : 0u);
+        const unsigned ne = __ballot_sync(0xffffffffu, nonempty);
+        const unsigned below = heads & (0xffffffffu >> (31 - lane));   // heads at positions <= lane
+        // lanes with `below` != 0: a request of this block starts at or before my chunk
+        int src = 0;
+        if (below) {
+            const int hp = 31 - __clz(below);
+            const int k = __popc(heads & ((1u << hp) - 1));            // its rank among non-empty ones
+            src = (ne == (0xffffffffu >> (32 - __popc(ne)))) ? k : (int)__fns(ne, 0, k + 1);
+        }
+        const int tb = __shfl_sync(0xffffffffu, q.b, src), tb1 = __shfl_sync(0xffffffffu, q.b1, src);
+        const int tln = __shfl_sync(0xffffffffu, q.ln, src), tnc = __shfl_sync(0xffffffffu, q.nc, src);
+        const long long tst = __shfl_sync(0xffffffffu, q.st, src);
+        if (below) { mine.b = tb; mine.b1 = tb1; mine.ln = tln; mine.nc = tnc; mine.st = tst; }
+        // more requests can start inside the tile only if the last lane's request ends inside it
+        const int last_b1 = __shfl_sync(0xffffffffu, q.b1, 31);
+        const bool last_live = __shfl_sync(0xffffffffu, (int)live, 31);
+        if (!(last_live && (int64_t)last_b1 < G0 + WTILE && r0 + jb + 32 < n)) break;
     }
-    __syncthreads();
-    int r = s_req[tid];
-    for (int o = 1; o < 32; o <<= 1) {                          // inclusive max-scan
-        int t = __shfl_up_sync(0xffffffffu, r, o);
-        if (lane >= o) r = max(r, t);
-    }
-    if (lane == 31) s_wmax[w] = r;
-    __syncthreads();
-    for (int k = 0; k < w; k++) r = max(r, s_wmax[k]);
 
     // ---- chunk descriptor
-    const int64_t g = G0 + tid;
-    const bool valid = g < total;
+    const int64_t g = G0 + lane;
     const uint8_t *p = nullptr;
-    int clen = 0;
-    bool fast = false;
-    if (valid) {
-        const int d = (int)(g - chunk_base[r]);
-        const int ln = lens[r];
-        const int nc = nchars ? nchars[r] : ln;
+    int clen = 0, kind = 0;               // 0 none / done elsewhere, 1 full staged, 3 generic
+    if (g < total) {
+        const int d = (int)(g - mine.b);
         int off;
-        if (nc == ln) {                          // ASCII: chunk = cc bytes
+        if (mine.nc == mine.ln) {                        // ASCII: chunk = cc bytes
             off = d * cc;
-            clen = min(cc, ln - off);
-        } else {                                 // code-point boundaries from k_utf8_bounds
+            clen = min(cc, mine.ln - off);
+        } else {                                         // code-point boundaries (k_utf8_bounds)
             off = chunk_off[g];
-            int end = (g + 1 < (int64_t)chunk_base[r + 1] && g + 1 < max_chunks) ? chunk_off[g + 1] : ln;
+            const int end = (g + 1 < (int64_t)mine.b1 && g + 1 < max_chunks) ? chunk_off[g + 1] : mine.ln;
             clen = end - off;
         }
-        p = bytes + starts[r] + off;
-        fast = (clen <= 128) && (((uintptr_t)p & 15) == 0);
+        p = bytes + mine.st + off;
+        const bool aligned = (((uintptr_t)p & 15) == 0);
+        const bool tail_done_by_prep = (mine.nc == mine.ln) && g + 1 == (int64_t)mine.b1 &&
+                                       clen < cc && ((((uintptr_t)bytes + mine.st) & 15) == 0);
+        kind = tail_done_by_prep ? 0 : ((aligned && clen == 128) ? 1 : 3);
     }
 
-    // ---- 2. stage this warp's 32 chunks
-    const uint32_t tile_s = (uint32_t)__cvta_generic_to_shared(s_tile);
-    const uint32_t wrow = tile_s + (uint32_t)(w * 32) * 128;
-    const unsigned long long my_src = fast ? (unsigned long long)(uintptr_t)p : 0ULL;
-    const int my_units = fast ? ((clen + 15) >> 4) : 0;
+    // ---- stage this warp's full chunks
+    const uint32_t wrow = (uint32_t)__cvta_generic_to_shared(s_tile) + (uint32_t)(w * WTILE) * 128;
     {
+        const unsigned long long my_src = kind == 1 ? (unsigned long long)(uintptr_t)p : 0ULL;
         // lane copies unit u of chunk c = 4k + sub; (c & 7) = sub ^ 4(k&1), so the swizzled
         // destination is one of two per-lane bases plus k * 512
         const int u = lane & 7, sub = lane >> 3;
         uint32_t d_even = wrow + sub * 128 + ((u ^ sub) << 4);
-        asm volatile("" : "+r"(d_even));                 // keep it in a register
+        asm volatile("" : "+r"(d_even));
         const uint32_t d_odd = d_even ^ 64u;
 #pragma unroll
         for (int k = 0; k < 8; k++) {
-            const int c = 4 * k + sub;                       // chunk (lane) inside the warp
-            const unsigned long long src = __shfl_sync(0xffffffffu, my_src, c);
-            const int nu = __shfl_sync(0xffffffffu, my_units, c);
-            // a whole 16-byte unit is copied when it holds at least one byte of the
-            // chunk: the unit is 16-byte aligned, so it lies inside the buffer's granule
-            if (u < nu)
+            const unsigned long long src = __shfl_sync(0xffffffffu, my_src, 4 * k + sub);
+            if (src)
                 cp_async16(((k & 1) ? d_odd : d_even) + k * 512,
                            (const uint8_t *)(uintptr_t)src + (u << 4), 16);
         }
@@ -373,21 +399,9 @@ k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ sta
     cp_async_wait_all();
     __syncwarp();
 
-    // ---- 3. hash
-    if (valid) {
-        if (fast && clen == 128) {
-            hashes[g] = xxh64_row128(wrow + lane * 128, lane & 7);
-        } else if (fast) {
-            s_part[atomicAdd(&s_npart, 1)] = (tid << 8) | clen;
-        } else {
-            hashes[g] = xxh64_global(p, clen);
-        }
-    }
-    __syncthreads();
-    if (tid < s_npart) {
-        const int e = s_part[tid], c = e >> 8;
-        hashes[G0 + c] = xxh64_row_any(s_tile + c * 128, c & 7, e & 0xFF);
-    }
+    // ---- hash
+    if (kind == 1) hashes[g] = xxh64_row128(wrow + lane * 128, lane & 7);
+    else if (kind == 3) hashes[g] = xxh64_global(p, clen);
 }
 
 // =========================================================================
@@ -679,7 +693,7 @@ static Plan make_plan(int64_t n, int64_t max_chunks, uint32_t flags, bool routin
 {
     Plan p;
     size_t o = 0;
-    const int64_t ntiles = (max_chunks + TILE - 1) / TILE + 1;
+    const int64_t ntiles = (max_chunks + 31) / 32 + 1;
     const int64_t nblk = (n + PREP_BLOCK - 1) / PREP_BLOCK + 1;
     const bool ascii = flags & B200R_F_ALL_ASCII;
     p.off_tile_first = o; o += align_up(ntiles * 4);
@@ -742,7 +756,7 @@ static int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const in
     }
     { ProfScope ps__(PK_PREP, st); g_launches += 1;
     k_prep_scan<<<nblk, PREP_BLOCK, 0, st>>>(d_lens, d_nchars, (int)n, cc, block_sums, d_chunk_base,
-                                             tile_first, max_chunks, dev);
+                                             tile_first, max_chunks, dev, d_bytes, d_starts, d_hashes);
     B200R_LAUNCH_CHECK("k_prep_scan");
     }
     if (!ascii) {
@@ -752,12 +766,12 @@ static int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const in
         B200R_LAUNCH_CHECK("k_utf8_bounds");
         }
     }
-    const int ntiles = (int)((max_chunks + TILE - 1) / TILE);
+    const int ntiles = (int)((max_chunks + HASH_WARPS * WTILE - 1) / (HASH_WARPS * WTILE));
     if (ntiles > 0) {
         { ProfScope ps__(PK_HASH, st); g_launches += 1;
-        k_hash_chunks<<<ntiles, TILE, 0, st>>>(d_bytes, d_starts, d_lens, d_nchars, d_chunk_base,
-                                               tile_first, chunk_off, (int)n, cc, max_chunks,
-                                               d_hashes);
+        k_hash_chunks<<<ntiles, HASH_WARPS * 32, 0, st>>>(
+            d_bytes, d_starts, d_lens, d_nchars, d_chunk_base, tile_first, chunk_off, (int)n, cc,
+            max_chunks, d_hashes);
         B200R_LAUNCH_CHECK("k_hash_chunks");
         }
     }
