@@ -321,11 +321,21 @@ def run_b200(args):
         seq += args.batch * world
     barrier()
     _lib.prof_enable(True)
+    verbose = os.environ.get("BENCH_VERBOSE") == "1"
+    prof = None
     for b in range(W, nb):
         router.route(resident[b], avail_mask(b), SEED, seq, out=out)
         seq += args.batch * world
+        if verbose:                      # per-step kernel times (synchronises every step)
+            one = _lib.prof_read()
+            print("step %d avail=%x " % (b, avail_mask(b)) +
+                  " ".join("%s=%.1fus" % (k, v[0] * 1e3) for k, v in one.items() if v[1]),
+                  file=sys.stderr)
+            prof = one if prof is None else {k: (prof[k][0] + one[k][0], prof[k][1] + one[k][1])
+                                             for k in one}
     torch.cuda.synchronize()
-    prof = _lib.prof_read()
+    if not verbose:
+        prof = _lib.prof_read()
     _lib.prof_enable(False)
     my_payload = sum(p.payload_bytes for p in host[W:])
     hash_ms, hash_n = prof["hash"]

@@ -521,8 +521,8 @@ k_claim(Entry *__restrict__ tab, uint64_t *__restrict__ hs, int cap_log2, TrieDe
                 atomicOr(&dev->status, B200R_S_TABLE_FULL);
                 slots[sp.b0 + d] = SLOT_NONE;
             } else {
-                uint64_t m = 0, cur = 0;
-                if (!created) ld_key((const Entry *)&tab[s].mask, m, cur);   // (mask, first): same sector
+                // masks do not change during this kernel: L1 may serve them (hot nodes)
+                const uint64_t m = created ? 0 : tab[s].mask;
                 if (m & avail) {
                     slots[sp.b0 + d] = s | PREOK_BIT;
                 } else {
@@ -531,6 +531,8 @@ k_claim(Entry *__restrict__ tab, uint64_t *__restrict__ hs, int cap_log2, TrieDe
                     // an earlier request of this batch is already recorded (a stale read only
                     // costs a redundant atomicMax)
                     const unsigned long long mine = tag | (unsigned long long)(~(unsigned)i);
+                    unsigned long long cur = 0;
+                    if (!created) cur = *(volatile unsigned long long *)&tab[s].first;
                     if (cur < mine) atomicMax(&tab[s].first, mine);
                 }
             }
