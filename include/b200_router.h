@@ -182,6 +182,47 @@ int b200r_trie_apply_remote(b200r_trie *t, const uint64_t *d_entries, int64_t co
 void b200r_trie_key_constants(uint64_t out[6]);
 
 /* ------------------------------------------------------------------------
+ * Multi-GPU routing of one global batch (no counterpart in the reference, whose
+ * router replicas share nothing).  The global batch is the
+ * rank-major concatenation of the shards and is routed as if sequentially;
+ * every rank keeps a full replica of the table.  Call order per batch, on
+ * every rank (the all-gathers between the calls are the host's job, e.g.
+ * torch.distributed over NCCL):
+ *   b200r_shard_classify  hash + frozen lookup of the own shard; emits one
+ *        32-byte record {key_lo, key_hi, chunk_hash, u32 request index inside
+ *        the shard, u32 depth} per chunk whose node is not usable yet
+ *        -> all-gather record counts and records (rank q at q*stride)
+ *   b200r_shard_apply     applies all ranks' records to the local replica
+ *   b200r_shard_select    leaders / choices / match depths of the own shard
+ *        -> all-gather them (rank q at q*rstride)
+ *   b200r_shard_commit    resolves every request's endpoint, inserts it into
+ *        every replica, writes the own shard's results
+ * d_req_off = int32 [world+1] device array: global position of every shard's
+ * request 0 (exclusive prefix sum of the shard sizes); req_off = the own one.  The scratch buffer
+ * (b200r_prefix_route_scratch_bytes) must be the same for all four calls.
+ * ---------------------------------------------------------------------- */
+#define B200R_SHARD_RECORD_BYTES 32
+int b200r_shard_classify(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
+                         const int32_t *d_lens, const int32_t *d_nchars, int64_t n,
+                         int64_t max_chunks, uint32_t flags, uint64_t avail_mask,
+                         void *d_records, uint32_t *d_rec_count, void *d_scratch,
+                         size_t scratch_bytes, void *stream);
+int b200r_shard_apply(b200r_trie *t, const void *d_records_all, const int32_t *d_counts,
+                      int32_t world, int64_t stride, int32_t my_rank, const int32_t *d_req_off,
+                      int64_t n, int64_t max_chunks, uint32_t flags, uint32_t *d_rec_slot,
+                      void *d_scratch, void *stream);
+int b200r_shard_select(b200r_trie *t, int64_t n, int64_t max_chunks, uint32_t flags,
+                       uint64_t avail_mask, uint64_t seed, uint64_t seq0, uint32_t req_off,
+                       int32_t *d_leader, int32_t *d_choice, int32_t *d_depth,
+                       uint64_t *d_matched, void *d_scratch, void *stream);
+int b200r_shard_commit(b200r_trie *t, const void *d_records_all, const int32_t *d_counts,
+                       int32_t world, int64_t stride, const uint32_t *d_rec_slot,
+                       const int32_t *d_leader_all, const int32_t *d_choice_all,
+                       const int32_t *d_depth_all, const int32_t *d_req_off, int64_t rstride,
+                       int32_t my_rank, int64_t n, int32_t *d_endpoint_all, int32_t *d_endpoint,
+                       uint64_t *d_matched, void *stream);
+
+/* ------------------------------------------------------------------------
  * a9  uhashring.HashRing (md5 points, bisect_right + wrap), a7 SessionRouter
  *                                                   routing_logic.py:84-103,217
  * b200r_md5_batch: 128-bit digests as the big-endian integer uhashring uses,

@@ -1,0 +1,118 @@
+"""The multi-GPU path (b200r_shard_* entry points + ShardedPrefixRouter) on ONE
+device: the ranks are threads of this process, each with its own table replica,
+and the all-gathers are done through shared memory (the orchestration code is the
+product's; only the collective is swapped).  Results must equal routing the
+rank-major concatenation sequentially (C oracle); all replicas must be identical.
+The real NCCL path is exercised by `torchrun ... bench.py --gpus N`."""
+import threading
+
+import numpy as np
+import pytest
+import torch
+
+from b200_router import traces
+from b200_router.packing import pack_arrays, pack_prompts
+from oracle import coracle
+
+from helpers import u64
+
+pytestmark = pytest.mark.gpu
+
+
+class ThreadComm:
+    def __init__(self, world, rank, shared):
+        self.world, self.rank, self.sh = world, rank, shared
+
+    def all_gather(self, out_flat, inp_flat):
+        self.sh["slots"][self.rank] = inp_flat
+        self.sh["barrier"].wait()
+        out_flat.copy_(torch.cat([s.reshape(-1) for s in self.sh["slots"]]))
+        torch.cuda.synchronize()
+        self.sh["barrier"].wait()
+
+
+def _run_ranks(world, batches, seed, cap_log2=17):
+    """batches: [(avail, [per-rank packed prompts])] -> per-rank results and dumps."""
+    from b200_router.distributed import ShardedPrefixRouter
+    shared = {"barrier": threading.Barrier(world), "slots": [None] * world}
+    results = [[] for _ in range(world)]
+    dumps = [None] * world
+    errors = []
+
+    def work(rank):
+        try:
+            torch.cuda.set_device(0)
+            r = ShardedPrefixRouter(cap_log2=cap_log2, device="cuda:0",
+                                    comm=ThreadComm(world, rank, shared))
+            seq = 0
+            for avail, shards in batches:
+                ep, depth, matched = r.route(shards[rank], avail, seed, seq)
+                seq += sum(s.n for s in shards)
+                results[rank].append((ep.cpu().numpy().copy(), depth.cpu().numpy().copy(),
+                                      u64(matched).copy()))
+            r.check_status()
+            dumps[rank] = r.dump()
+        except Exception as e:          # pragma: no cover
+            errors.append(e)
+            shared["barrier"].abort()
+
+    ts = [threading.Thread(target=work, args=(k,)) for k in range(world)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    if errors:
+        raise errors[0]
+    return results, dumps
+
+
+def _check(world, batches_np, seed):
+    """batches_np: [(avail, [(buf, starts, lens) per rank])]"""
+    batches = [(a, [pack_arrays(*s, pin=False) for s in shards]) for a, shards in batches_np]
+    results, dumps = _run_ranks(world, batches, seed)
+    orc = coracle.TrieOracle()
+    seq = 0
+    for b, (avail, shards) in enumerate(batches_np):
+        # sequential over the concatenation: feed the shards one after another
+        off = 0
+        for r, (buf, st, ln) in enumerate(shards):
+            oep, odepth, omatched = orc.route_batch(buf, st, ln, avail, seed, seq + off)
+            off += len(st)
+            ep, depth, matched = results[r][b]
+            assert (ep == oep).all(), (b, r)
+            assert (depth == odepth).all(), (b, r)
+            assert (matched == omatched).all(), (b, r)
+        seq += off
+    for d in dumps:
+        assert d == orc.dump()
+
+
+def test_sharded_heavy_sharing_two_and_three_ranks():
+    for world in (2, 3):
+        batches = []
+        for avail_idx, prompts in traces.sharing_stress(n_batches=5, batch=90, n_endpoints=7,
+                                                        max_depth=6, alphabet=2, seed=40 + world):
+            cuts = np.linspace(0, len(prompts), world + 1).astype(int)
+            shards = []
+            for r in range(world):
+                buf, st, ln, _ = traces.pack_strings(prompts[cuts[r]:cuts[r + 1]])
+                shards.append((buf, st, ln))
+            batches.append((sum(1 << i for i in avail_idx), shards))
+        _check(world, batches, seed=5)
+
+
+def test_sharded_shared_prefix_trace_with_churn():
+    world = 4
+    tr = traces.SharedPrefixTrace(n_total=16000, batch=1000, n_sys=8, sys_chars=512,
+                                  suffix_lo=100, suffix_hi=300, seed=9)
+    batches = []
+    for g in range(4):
+        avail = 0xFF & ~(1 << 1) if g in (1, 2) else 0xFF
+        batches.append((avail, [tr.batch_arrays(g * world + r) for r in range(world)]))
+    _check(world, batches, seed=11)
+
+
+def test_sharded_uneven_and_empty_shards():
+    world = 2
+    _, prompts = traces.sharing_stress(n_batches=1, batch=50, seed=8)[0]
+    shards0 = [traces.pack_strings(prompts[:50])[:3], traces.pack_strings([])[:3]]
+    shards1 = [traces.pack_strings(prompts[:7])[:3], traces.pack_strings(prompts[7:])[:3]]
+    _check(world, [(0x3F, shards0), (0x15, shards1)], seed=2)

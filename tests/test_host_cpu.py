@@ -1,0 +1,142 @@
+"""CPU-only checks: the C ABI library loads and exports exactly what the header
+declares, and the host-side mirror of the reference interface behaves like the
+reference (no compute calls -- those need a GPU and are in test_gpu_*.py)."""
+import asyncio
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+import b200_router
+from b200_router import _lib, packing, traces
+from b200_router import routers
+from oracle import prefix_ref
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "b200_router.h")
+
+
+def _declared_symbols():
+    text = open(HEADER).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(b200r_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = _lib.lib()
+    declared = _declared_symbols()
+    assert len(declared) >= 20
+    for name in declared:
+        assert hasattr(lib, name), name
+    out = subprocess.check_output(["nm", "-D", "--defined-only", _lib.LIB_PATH], text=True)
+    exported = sorted(set(re.findall(r"\b(b200r_[a-z0-9_]+)\b", out)))
+    assert exported == declared
+    # and the ctypes table binds each of them
+    assert sorted(_lib.SIGNATURES) == declared
+
+
+def test_abi_version_and_host_side_pick():
+    from oracle.chooser import pick
+    lib = _lib.lib()
+    assert lib.b200r_abi_version() == 1
+    for seed, seq, n in [(0, 0, 1), (7, 123456789, 8), (2**63, 2**40 + 3, 64), (5, 9, 3)]:
+        assert lib.b200r_pick(seed, seq, n) == pick(seed, seq, n)
+
+
+def test_no_cuda_means_loud_failure():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("needs a machine without a GPU")
+    with pytest.raises(b200_router.B200RouterError):
+        routers._reset_singletons_for_tests()
+        routers.PrefixAwareRouter()
+    with pytest.raises(b200_router.B200RouterError):
+        routers.SessionRouter("x-user-id")
+
+
+def test_invalid_arguments_are_rejected_without_a_device():
+    lib = _lib.lib()
+    assert lib.b200r_trie_lookup_batch(None, None, None, 1, 0, None, None, None) == -1
+    assert b"trie" in lib.b200r_last_error()
+    assert lib.b200r_md5_batch(None, None, None, -1, None, None) == -1
+    assert lib.b200r_xxh64_chunks_noalloc(None, None, None, None, 1, 128, 0, None, None, 1, None) == -1
+
+
+def test_pack_prompts_layout():
+    prompts = ["abc", "é" * 200, "", "x" * 128, "日本語"]
+    p = packing.pack_prompts(prompts, pin=False)
+    assert p.n == 5 and not p.all_ascii
+    assert (p.starts.numpy() % 16 == 0).all()
+    assert p.lens.tolist() == [len(s.encode()) for s in prompts]
+    assert p.nchars.tolist() == [len(s) for s in prompts]
+    assert p.max_chunks == sum((len(s) + 127) // 128 for s in prompts)
+    buf = p.bytes.numpy()
+    for s, st, ln in zip(prompts, p.starts.tolist(), p.lens.tolist()):
+        assert bytes(buf[st:st + ln]) == s.encode()
+    q = packing.pack_prompts(["a" * 300, "b"], pin=False)
+    assert q.all_ascii and q.nchars is None and q.max_chunks == 4 and q.payload_bytes == 301
+
+
+def test_extract_prompt_matches_reference_shapes(golden_prefix):
+    tr = [t for t in golden_prefix["traces"] if t["name"] == "request_json_shapes"][0]
+    for js in tr["json_inputs"]:
+        assert routers.extract_prompt(js) == prefix_ref.flatten_prompt(js)
+    with pytest.raises(KeyError):
+        routers.extract_prompt({"neither": 1})
+
+
+def test_endpoint_registry_is_append_only():
+    reg = routers.EndpointRegistry()
+
+    class Ep:
+        def __init__(self, url): self.url = url
+    a = reg.mask([Ep("u1"), Ep("u2")])
+    b = reg.mask([Ep("u3"), Ep("u1")])
+    assert a == 0b011 and b == 0b101 and reg.urls == ["u1", "u2", "u3"]
+    small = routers.EndpointRegistry(limit=2)
+    small.mask(["a", "b"])
+    with pytest.raises(b200_router.B200RouterError):
+        small.bit("c")
+
+
+def test_qps_routing_rule():
+    class Ep:
+        def __init__(self, url): self.url = url
+
+    class St:
+        def __init__(self, qps): self.qps = qps
+
+    class Dummy(routers.RoutingInterface):
+        def route_request(self, *a):
+            return None
+    routers.SingletonABCMeta._instances.pop(Dummy, None)
+    d = Dummy()
+    eps = [Ep("a"), Ep("b"), Ep("c")]
+    assert d._qps_routing(eps, {"a": St(3), "b": St(1), "c": St(1)}) == "b"   # first minimum
+    assert d._qps_routing(eps, {"a": St(3), "c": St(1)}) == "b"               # unseen endpoint wins
+    routers.SingletonABCMeta._instances.pop(Dummy, None)
+
+
+def test_registry_names_and_errors():
+    assert routers.RoutingLogic("prefixaware") == routers.RoutingLogic.PREFIXAWARE
+    assert routers.RoutingLogic("session") == routers.RoutingLogic.SESSION_BASED
+    with pytest.raises(ValueError):
+        routers.initialize_routing_logic("nonsense")
+    routers._reset_singletons_for_tests()
+    with pytest.raises(ValueError):
+        routers.get_routing_logic()
+
+
+def test_trace_generators_are_deterministic():
+    a = traces.SharedPrefixTrace(n_total=300, batch=100, n_sys=4, sys_chars=256, seed=5)
+    b = traces.SharedPrefixTrace(n_total=300, batch=100, n_sys=4, sys_chars=256, seed=5)
+    for k in range(3):
+        x, y = a.batch_arrays(k), b.batch_arrays(k)
+        assert all((u == v).all() for u, v in zip(x, y))
+        assert (x[1] % 16 == 0).all()
+    p, u = traces.multi_round_qa(users=3, rounds=2, sys_len=5, hist_len=2, answer_len=1)
+    assert len(p) == 6 and p[3].startswith(p[0]) and u == [0, 1, 2, 0, 1, 2]
+    ids = traces.session_ids_uuid(5, 1)
+    assert ids == traces.session_ids_uuid(5, 1) and all(len(i) == 36 and i[14] == "4" for i in ids)

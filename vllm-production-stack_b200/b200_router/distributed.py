@@ -1,0 +1,198 @@
+"""Prefix-aware routing of one global batch sharded over the GPUs of a box.
+
+One process per GPU (torch.distributed, NCCL over NVLink / NVSwitch).  Every
+rank keeps a full replica of the trie table; the global batch is the rank-major
+concatenation of the ranks' shards and must be routed exactly as if the
+requests arrived one after another in that order.
+
+Per batch, on every rank:
+  classify   hash the own shard, look every chunk up in the (identical) local
+             replica; chunks whose node is not usable yet become 32-byte records
+  gather #1  shard sizes + record counts (one tiny all-gather, one host read)
+  gather #2  the records themselves
+  apply      all ranks' records -> find-or-create + global "first toucher"
+  select     own shard: deepest usable node, root draw or leader (global order)
+  gather #3  leaders / choices / match depths of all shards
+  commit     resolve every request's endpoint; OR it into the new nodes of
+             every replica; write the own shard's results
+
+`ops` does the arithmetic.  The product uses CudaShardOps (C ABI of
+libb200router.so, no CPU fallback); the gloo test in tests/ injects an
+emulation so that this orchestration is exercised with world_size 2 on CPUs.
+"""
+import ctypes as C
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+from .packing import PackedPrompts
+
+M64 = (1 << 64) - 1
+
+
+def _ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class CudaShardOps:
+    """The four per-batch device steps, through the C ABI (include/b200_router.h)."""
+
+    def __init__(self, cap_log2: int, device, chunk_chars: int = 128):
+        from .trie import GpuHashTrie
+        self.trie = GpuHashTrie(cap_log2=cap_log2, chunk_chars=chunk_chars, device=device)
+        self.device = self.trie.device
+        self._shape = None
+
+    def _scratch(self, p: PackedPrompts):
+        flags = _lib.F_ALL_ASCII if p.all_ascii else 0
+        need = _lib.lib().b200r_prefix_route_scratch_bytes(p.n, p.max_chunks, flags)
+        self._shape = (p.n, p.max_chunks, flags)
+        return self.trie._scratch_for(need), flags
+
+    def classify(self, p: PackedPrompts, avail_mask: int, recs: torch.Tensor, count: torch.Tensor):
+        sc, flags = self._scratch(p)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().b200r_shard_classify(
+                self.trie._h, _ptr(p.bytes), _ptr(p.starts), _ptr(p.lens), _ptr(p.nchars), p.n,
+                p.max_chunks, flags, avail_mask & M64, _ptr(recs), _ptr(count), _ptr(sc), sc.numel(),
+                _stream()))
+
+    def apply(self, recs_all, counts, world, stride, rank, req_off, rec_slot):
+        n, max_chunks, flags = self._shape
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().b200r_shard_apply(
+                self.trie._h, _ptr(recs_all), _ptr(counts), world, stride, rank, _ptr(req_off), n,
+                max_chunks, flags, _ptr(rec_slot), _ptr(self.trie._scratch), _stream()))
+
+    def select(self, avail_mask, seed, seq0, my_off, leader, choice, depth, matched):
+        n, max_chunks, flags = self._shape
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().b200r_shard_select(
+                self.trie._h, n, max_chunks, flags, avail_mask & M64, seed & M64, seq0 & M64, my_off,
+                _ptr(leader), _ptr(choice), _ptr(depth), _ptr(matched), _ptr(self.trie._scratch),
+                _stream()))
+
+    def commit(self, recs_all, counts, world, stride, rec_slot, leader_all, choice_all, depth_all,
+               req_off, rstride, rank, endpoint_all, endpoint, matched):
+        n = self._shape[0]
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().b200r_shard_commit(
+                self.trie._h, _ptr(recs_all), _ptr(counts), world, stride, _ptr(rec_slot),
+                _ptr(leader_all), _ptr(choice_all), _ptr(depth_all), _ptr(req_off), rstride, rank, n,
+                _ptr(endpoint_all), _ptr(endpoint), _ptr(matched), _stream()))
+
+    def check_status(self, count_nodes=False):
+        return self.trie.check_status(count_nodes)
+
+    def dump(self):
+        return self.trie.dump()
+
+
+class TorchComm:
+    """all-gather over a torch.distributed process group (NCCL on GPUs, gloo in CPU tests)."""
+
+    def __init__(self, group=None):
+        self.group = group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+
+    def all_gather(self, out_flat: torch.Tensor, inp_flat: torch.Tensor):
+        dist.all_gather_into_tensor(out_flat, inp_flat, group=self.group)
+
+
+class ShardedPrefixRouter:
+    """route(shard) on every rank == sequential routing of the concatenated batch."""
+
+    def __init__(self, cap_log2: int = 22, device=None, max_requests: int = 0, max_chunks: int = 0,
+                 group=None, ops=None, comm=None):
+        self.comm = comm if comm is not None else TorchComm(group)
+        self.world = self.comm.world
+        self.rank = self.comm.rank
+        self.ops = ops if ops is not None else CudaShardOps(cap_log2, device)
+        self.device = self.ops.device
+        self._recs = None          # int64 [cap, 4]: this rank's records
+        self._count = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._bufs = {}
+        if max_chunks:
+            self._ensure_recs(max_chunks)
+        self.last_exchange_bytes = 0
+
+    def _ensure_recs(self, cap):
+        if self._recs is None or self._recs.shape[0] < cap:
+            old = self._recs
+            self._recs = torch.empty((int(cap * 1.1) + 64, 4), dtype=torch.int64, device=self.device)
+            if old is not None:
+                self._recs[:old.shape[0]] = old
+        return self._recs
+
+    def _buf(self, name, shape, dtype):
+        t = self._bufs.get(name)
+        numel = 1
+        for s in shape:
+            numel *= s
+        if t is None or t.numel() < numel or t.dtype != dtype:
+            t = torch.empty(int(numel * 1.1) + 64, dtype=dtype, device=self.device)
+            self._bufs[name] = t
+        return t[:numel].view(*shape)
+
+    def route(self, p: PackedPrompts, avail_mask: int, seed: int, seq0: int, out=None):
+        """seq0 = global sequence number of the batch's first request (same on all ranks)."""
+        if p.bytes.device != self.device:
+            p = p.to(self.device)
+        W, rank, n = self.world, self.rank, p.n
+        recs = self._ensure_recs(max(p.max_chunks, 1))
+        self.ops.classify(p, avail_mask, recs, self._count)
+
+        # gather #1: shard sizes and record counts
+        meta = torch.stack([torch.full((), n, dtype=torch.int32, device=self.device),
+                            self._count[0]]).contiguous()
+        meta_all = self._buf("meta", (W, 2), torch.int32)
+        self.comm.all_gather(meta_all.view(-1), meta)
+        meta_host = meta_all.cpu()                       # the one host read of the batch
+        ns = meta_host[:, 0].tolist()
+        cnts = meta_host[:, 1].tolist()
+        stride = max(cnts)
+        rstride = max(max(ns), 1)
+        req_off = torch.zeros(W + 1, dtype=torch.int32)
+        req_off[1:] = torch.cumsum(meta_host[:, 0], 0)
+        req_off_dev = req_off.to(self.device, non_blocking=True)
+        counts_dev = meta_all[:, 1].contiguous()
+
+        # gather #2: records (rank q at q * stride)
+        recs_all = self._buf("recs_all", (W, max(stride, 1), 4), torch.int64)
+        rec_slot = self._buf("rec_slot", (W * max(stride, 1),), torch.int32)
+        if stride > 0:
+            recs = self._ensure_recs(stride)
+            self.comm.all_gather(recs_all.view(-1), recs[:stride].reshape(-1))
+            self.ops.apply(recs_all, counts_dev, W, stride, rank, req_off_dev, rec_slot)
+
+        # select on the own shard; gather #3: leaders, choices, match depths
+        lcd = self._buf("lcd", (3, rstride), torch.int32)
+        if out is None:
+            out = (torch.empty(max(n, 1), dtype=torch.int32, device=self.device),
+                   torch.empty(max(n, 1), dtype=torch.int32, device=self.device),
+                   torch.empty(max(n, 1), dtype=torch.int64, device=self.device))
+        ep, depth, matched = out
+        self.ops.select(avail_mask, seed, seq0, int(req_off[rank]), lcd[0], lcd[1], lcd[2], matched)
+        lcd_all = self._buf("lcd_all", (W, 3, rstride), torch.int32)
+        self.comm.all_gather(lcd_all.view(-1), lcd.reshape(-1))
+        by_kind = self._buf("lcd_kind", (3, W, rstride), torch.int32)
+        by_kind.copy_(lcd_all.permute(1, 0, 2))
+        endpoint_all = self._buf("ep_all", (W * rstride,), torch.int32)
+        self.ops.commit(recs_all, counts_dev, W, stride, rec_slot, by_kind[0], by_kind[1], by_kind[2],
+                        req_off_dev, rstride, rank, endpoint_all, ep, matched)
+        if n:
+            depth[:n].copy_(lcd[2][:n])
+        self.last_exchange_bytes = (W - 1) * (stride * 32 + rstride * 12 + 8)
+        return ep[:n], depth[:n], matched[:n]
+
+    def check_status(self, count_nodes=False):
+        return self.ops.check_status(count_nodes)
+
+    def dump(self):
+        return self.ops.dump()

@@ -549,9 +549,11 @@ __global__ void __launch_bounds__(256)
 k_select(const Entry *__restrict__ tab, const int32_t *__restrict__ chunk_base, int n, int64_t max_chunks,
          const uint32_t *__restrict__ slots, uint64_t avail, unsigned long long tag, uint64_t seed,
          uint64_t seq0, int32_t *__restrict__ leader, int32_t *__restrict__ choice,
-         int32_t *__restrict__ depth_out, uint64_t *__restrict__ matched_out)
+         int32_t *__restrict__ depth_out, uint64_t *__restrict__ matched_out, uint32_t req_off)
 {
-    // one thread per request: independent dependent-load chains, 32 per warp in flight
+    // one thread per request: independent dependent-load chains, 32 per warp in flight.
+    // req_off = position of request 0 of this shard in the global (rank-major) order;
+    // 0 on a single GPU.  `first` words, leaders and the tie-break counter are global.
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const ReqSpan sp = req_span(chunk_base, i, max_chunks);
@@ -574,7 +576,7 @@ k_select(const Entry *__restrict__ tab, const int32_t *__restrict__ chunk_base, 
                 else {
                     const unsigned long long fv = tab[x].first;
                     f = ~(uint32_t)fv;
-                    ok = ((fv >> 32) == (tag >> 32)) && f < (uint32_t)i;
+                    ok = ((fv >> 32) == (tag >> 32)) && f < req_off + (uint32_t)i;
                 }
             }
             if (ok) { dstar = d0 + k + 1; star_slot = x; star_first = f; }
@@ -586,7 +588,7 @@ k_select(const Entry *__restrict__ tab, const int32_t *__restrict__ chunk_base, 
         const uint64_t cand = (dstar == 0) ? avail : (tab[star_slot & ~PREOK_BIT].mask & avail);
         const int cnt = __popcll(cand);
         leader[i] = -1;
-        choice[i] = cnt ? nth_set_bit(cand, pick(seed, seq0 + (uint64_t)i, (uint32_t)cnt)) : -1;
+        choice[i] = cnt ? nth_set_bit(cand, pick(seed, seq0 + req_off + (uint64_t)i, (uint32_t)cnt)) : -1;
         matched_out[i] = cand;
     } else {
         leader[i] = (int32_t)star_first;
@@ -618,6 +620,149 @@ k_commit(Entry *__restrict__ tab, TrieDev *dev, const int32_t *__restrict__ chun
         const uint32_t x = slots[sp.b0 + d];
         if (x != SLOT_NONE) atomicOr((unsigned long long *)&tab[x & ~PREOK_BIT].mask, bit);
     }
+}
+
+// =========================================================================
+// Multi-GPU: request batches sharded across ranks, table replicated per GPU.
+// The global batch is the rank-major concatenation of the shards; results must
+// equal routing it sequentially.  Per batch every rank
+//   1. k_shard_classify  hashes its shard and looks every chunk up in its
+//      (identical) replica; chunks whose node is not usable yet become 32-byte
+//      records {path key, chunk hash, request index inside the shard, depth};
+//   2. the records are all-gathered (NCCL over NVLink; host side);
+//   3. k_shard_apply     applies ALL ranks' records to the local replica:
+//      find-or-create + atomicMax of the global "first toucher" -> replicas stay
+//      identical in content;
+//   4. k_select (global positions) on the own shard; leaders / choices / match
+//      depths of all ranks are all-gathered;
+//   5. k_shard_resolve + k_shard_commit: every rank resolves every request's
+//      endpoint and ORs it into the nodes of every record below its owner's
+//      match depth -> all replicas receive all inserts.
+// =========================================================================
+struct __align__(32) ShardRec { uint64_t k1, k2, h; uint32_t req, depth; };
+
+__global__ void __launch_bounds__(WARPS_PER_CTA * 32)
+k_shard_classify(const Entry *__restrict__ tab, int cap_log2, const uint64_t *__restrict__ hashes,
+                 const int32_t *__restrict__ chunk_base, int n, int64_t max_chunks, uint64_t avail,
+                 uint32_t *__restrict__ slots, ShardRec *__restrict__ recs,
+                 unsigned int *__restrict__ rec_count)
+{
+    const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (i >= n) return;
+    const ReqSpan sp = req_span(chunk_base, i, max_chunks);
+    Key carry = { KROOT1, KROOT2 };
+    for (int blk = 0; blk * 32 < sp.C; blk++) {
+        const int d = blk * 32 + lane;
+        const bool valid = d < sp.C;
+        const uint64_t h = valid ? hashes[sp.b0 + d] : 0;
+        const Key k = key_scan_warp(h, carry, lane);
+        carry.k1 = __shfl_sync(0xffffffffu, k.k1, 31);
+        carry.k2 = __shfl_sync(0xffffffffu, k.k2, 31);
+        bool emit = false;
+        if (valid) {
+            const uint32_t s = table_find(tab, cap_log2, k.k1, k.k2);
+            const uint64_t m = (s != SLOT_NONE) ? tab[s].mask : 0;
+            if (m & avail) slots[sp.b0 + d] = s | PREOK_BIT;
+            else { slots[sp.b0 + d] = SLOT_NONE; emit = true; }
+        }
+        const unsigned bal = __ballot_sync(0xffffffffu, emit);
+        if (bal) {
+            unsigned base = 0;
+            const int leader = __ffs(bal) - 1;
+            if (lane == leader) base = atomicAdd(rec_count, (unsigned)__popc(bal));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (emit) {
+                ShardRec r;
+                r.k1 = k.k1; r.k2 = k.k2; r.h = h; r.req = (uint32_t)i; r.depth = (uint32_t)d;
+                recs[base + __popc(bal & ((1u << lane) - 1))] = r;
+            }
+        }
+    }
+}
+
+// records of rank q live at recs_all[q * stride .. q * stride + counts[q])
+__global__ void k_shard_apply(Entry *__restrict__ tab, uint64_t *__restrict__ hs, int cap_log2,
+                              TrieDev *dev, const ShardRec *__restrict__ recs_all,
+                              const int32_t *__restrict__ counts, int world, int64_t stride,
+                              int my_rank, const int32_t *__restrict__ req_off,
+                              const int32_t *__restrict__ chunk_base, unsigned long long tag,
+                              uint32_t *__restrict__ slots,
+                              uint32_t *__restrict__ rec_slot)
+{
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (int64_t)world * stride) return;
+    const int q = (int)(idx / stride);
+    if (idx - (int64_t)q * stride >= counts[q]) return;
+    const ShardRec r = recs_all[idx];
+    bool created;
+    const uint32_t s = table_claim(tab, hs, cap_log2, r.k1, r.k2, r.h, &created);
+    rec_slot[idx] = s;
+    if (s == SLOT_NONE) { atomicOr(&dev->status, B200R_S_TABLE_FULL); return; }
+    // global position of the request = position of its shard + index inside the shard
+    const unsigned long long mine = tag | (unsigned long long)(~((uint32_t)req_off[q] + r.req));
+    unsigned long long cur = 0;
+    if (!created) cur = *(volatile unsigned long long *)&tab[s].first;
+    if (cur < mine) atomicMax(&tab[s].first, mine);
+    if (q == my_rank) slots[chunk_base[r.req] + r.depth] = s;
+}
+
+// position in the global order -> index into the rank-strided gathered arrays
+__device__ __forceinline__ int64_t shard_index(const int32_t *req_off, int world, int64_t rstride,
+                                               uint32_t pos)
+{
+    int q = 0;
+    while (q + 1 < world && pos >= (uint32_t)req_off[q + 1]) q++;
+    return (int64_t)q * rstride + (pos - (uint32_t)req_off[q]);
+}
+
+__global__ void k_shard_resolve(TrieDev *dev, const int32_t *__restrict__ leader_all,
+                                const int32_t *__restrict__ choice_all,
+                                const int32_t *__restrict__ req_off, int world, int64_t rstride,
+                                int32_t *__restrict__ endpoint_all)
+{
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (int64_t)world * rstride) return;
+    const int q = (int)(idx / rstride);
+    if (idx - (int64_t)q * rstride >= req_off[q + 1] - req_off[q]) return;
+    int64_t j = idx;
+    int l;
+    while ((l = leader_all[j]) >= 0) j = shard_index(req_off, world, rstride, (uint32_t)l);
+    const int e = choice_all[j];
+    endpoint_all[idx] = e;
+    if (e >= 0) {
+        const uint64_t bit = 1ULL << e;
+        if (!(dev->root_mask & bit)) atomicOr((unsigned long long *)&dev->root_mask, bit);
+    }
+}
+
+__global__ void k_shard_commit(Entry *__restrict__ tab, const ShardRec *__restrict__ recs_all,
+                               const int32_t *__restrict__ counts, int world, int64_t stride,
+                               const uint32_t *__restrict__ rec_slot,
+                               const int32_t *__restrict__ endpoint_all,
+                               const int32_t *__restrict__ depth_all, int64_t rstride)
+{
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (int64_t)world * stride) return;
+    const int q = (int)(idx / stride);
+    if (idx - (int64_t)q * stride >= counts[q]) return;
+    const uint32_t s = rec_slot[idx];
+    if (s == SLOT_NONE) return;
+    const uint32_t req = recs_all[idx].req, d = recs_all[idx].depth;
+    const int64_t ri = (int64_t)q * rstride + req;
+    const int e = endpoint_all[ri];
+    if (e >= 0 && (int)d >= depth_all[ri])
+        atomicOr((unsigned long long *)&tab[s].mask, 1ULL << e);
+}
+
+__global__ void k_shard_finish(const int32_t *__restrict__ endpoint_all,
+                               const int32_t *__restrict__ leader_all, int n, int64_t my_base,
+                               int32_t *__restrict__ endpoint, uint64_t *__restrict__ matched)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int e = endpoint_all[my_base + i];
+    endpoint[i] = e;
+    if (leader_all[my_base + i] >= 0) matched[i] = (e >= 0) ? (1ULL << e) : 0;
 }
 
 // ------------------------------------------------------------ dump / restore
@@ -1074,13 +1219,125 @@ int b200r_prefix_route_batch(b200r_trie *t, const uint8_t *d_bytes, const int64_
     { ProfScope ps__(PK_SELECT, st); g_launches += 1;
     k_select<<<tblocks, 256, 0, st>>>(t->tab, chunk_base, (int)n, max_chunks, slots,
                                      avail_mask, tag, seed, seq0, leader, choice, d_match_depth,
-                                     d_matched_mask);
+                                     d_matched_mask, 0u);
     B200R_LAUNCH_CHECK("k_select");
     }
     { ProfScope ps__(PK_COMMIT, st); g_launches += 1;
     k_commit<<<tblocks, 256, 0, st>>>(t->tab, t->dev, chunk_base, (int)n, max_chunks, slots, leader,
                                      choice, d_match_depth, d_endpoint, d_matched_mask);
     B200R_LAUNCH_CHECK("k_commit");
+    }
+    return B200R_OK;
+}
+
+// ---------------------------------------------------------------- multi-GPU
+int b200r_shard_classify(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
+                         const int32_t *d_lens, const int32_t *d_nchars, int64_t n,
+                         int64_t max_chunks, uint32_t flags, uint64_t avail_mask,
+                         void *d_records, uint32_t *d_rec_count, void *d_scratch,
+                         size_t scratch_bytes, void *stream)
+{
+    if (!t) { set_error("null trie"); return B200R_E_INVALID; }
+    int rc = check_prompt_args(d_bytes, d_starts, d_lens, n, max_chunks, t->chunk_chars);
+    if (rc) return rc;
+    if (!d_rec_count || (max_chunks > 0 && !d_records)) { set_error("null record buffer"); return B200R_E_INVALID; }
+    const Plan p = make_plan(n, max_chunks, flags, true);
+    if (!d_scratch || scratch_bytes < p.total) {
+        set_error("scratch too small: need %zu bytes, got %zu", p.total, scratch_bytes);
+        return B200R_E_SCRATCH;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    if (t->epoch >= 0xFFFFFFF0u) { set_error("batch epoch exhausted"); return B200R_E_INVALID; }
+    t->epoch++;
+    B200R_CUDA(cudaMemsetAsync(d_rec_count, 0, 4, st));
+    if (n == 0) return B200R_OK;
+    uint8_t *sc = (uint8_t *)d_scratch;
+    int32_t *chunk_base = (int32_t *)(sc + p.off_chunk_base);
+    uint64_t *hashes = (uint64_t *)(sc + p.off_hashes);
+    uint32_t *slots = (uint32_t *)(sc + p.off_slots);
+    rc = launch_hash(d_bytes, d_starts, d_lens, d_nchars, n, t->chunk_chars, flags, chunk_base,
+                     hashes, max_chunks, sc, p, t->dev, st);
+    if (rc) return rc;
+    const int blocks = (int)((n + WARPS_PER_CTA - 1) / WARPS_PER_CTA);
+    g_launches += 1;
+    k_shard_classify<<<blocks, WARPS_PER_CTA * 32, 0, st>>>(
+        t->tab, t->cap_log2, hashes, chunk_base, (int)n, max_chunks, avail_mask, slots,
+        (ShardRec *)d_records, d_rec_count);
+    B200R_LAUNCH_CHECK("k_shard_classify");
+    return B200R_OK;
+}
+
+int b200r_shard_apply(b200r_trie *t, const void *d_records_all, const int32_t *d_counts,
+                      int32_t world, int64_t stride, int32_t my_rank, const int32_t *d_req_off,
+                      int64_t n, int64_t max_chunks, uint32_t flags, uint32_t *d_rec_slot,
+                      void *d_scratch, void *stream)
+{
+    if (!t || world <= 0 || stride < 0 || my_rank < 0 || my_rank >= world) { set_error("b200r_shard_apply: bad argument"); return B200R_E_INVALID; }
+    if (stride == 0) return B200R_OK;
+    if (!d_records_all || !d_counts || !d_rec_slot || !d_scratch || !d_req_off) { set_error("null pointer"); return B200R_E_INVALID; }
+    const Plan p = make_plan(n, max_chunks, flags, true);
+    uint8_t *sc = (uint8_t *)d_scratch;
+    const int64_t work = (int64_t)world * stride;
+    const unsigned long long tag = (unsigned long long)t->epoch << 32;
+    g_launches += 1;
+    k_shard_apply<<<(int)((work + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        t->tab, t->hs, t->cap_log2, t->dev, (const ShardRec *)d_records_all, d_counts, world, stride,
+        my_rank, d_req_off, (const int32_t *)(sc + p.off_chunk_base), tag,
+        (uint32_t *)(sc + p.off_slots), d_rec_slot);
+    B200R_LAUNCH_CHECK("k_shard_apply");
+    return B200R_OK;
+}
+
+int b200r_shard_select(b200r_trie *t, int64_t n, int64_t max_chunks, uint32_t flags,
+                       uint64_t avail_mask, uint64_t seed, uint64_t seq0, uint32_t req_off,
+                       int32_t *d_leader, int32_t *d_choice, int32_t *d_depth,
+                       uint64_t *d_matched, void *d_scratch, void *stream)
+{
+    if (!t || n < 0) { set_error("b200r_shard_select: bad argument"); return B200R_E_INVALID; }
+    if (n == 0) return B200R_OK;
+    if (!d_leader || !d_choice || !d_depth || !d_matched || !d_scratch) { set_error("null pointer"); return B200R_E_INVALID; }
+    const Plan p = make_plan(n, max_chunks, flags, true);
+    uint8_t *sc = (uint8_t *)d_scratch;
+    const unsigned long long tag = (unsigned long long)t->epoch << 32;
+    g_launches += 1;
+    k_select<<<(int)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        t->tab, (const int32_t *)(sc + p.off_chunk_base), (int)n, max_chunks,
+        (const uint32_t *)(sc + p.off_slots), avail_mask, tag, seed, seq0, d_leader, d_choice,
+        d_depth, d_matched, req_off);
+    B200R_LAUNCH_CHECK("k_select");
+    return B200R_OK;
+}
+
+int b200r_shard_commit(b200r_trie *t, const void *d_records_all, const int32_t *d_counts,
+                       int32_t world, int64_t stride, const uint32_t *d_rec_slot,
+                       const int32_t *d_leader_all, const int32_t *d_choice_all,
+                       const int32_t *d_depth_all, const int32_t *d_req_off, int64_t rstride,
+                       int32_t my_rank, int64_t n, int32_t *d_endpoint_all, int32_t *d_endpoint,
+                       uint64_t *d_matched, void *stream)
+{
+    if (!t || world <= 0 || my_rank < 0 || my_rank >= world || rstride < 0 || stride < 0) { set_error("b200r_shard_commit: bad argument"); return B200R_E_INVALID; }
+    if (rstride == 0) return B200R_OK;
+    if (!d_leader_all || !d_choice_all || !d_depth_all || !d_req_off || !d_endpoint_all) { set_error("null pointer"); return B200R_E_INVALID; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t rwork = (int64_t)world * rstride;
+    g_launches += 1;
+    k_shard_resolve<<<(int)((rwork + 255) / 256), 256, 0, st>>>(t->dev, d_leader_all, d_choice_all,
+                                                              d_req_off, world, rstride,
+                                                              d_endpoint_all);
+    B200R_LAUNCH_CHECK("k_shard_resolve");
+    const int64_t work = (int64_t)world * stride;
+    if (work > 0) {
+        g_launches += 1;
+        k_shard_commit<<<(int)((work + 255) / 256), 256, 0, st>>>(
+            t->tab, (const ShardRec *)d_records_all, d_counts, world, stride, d_rec_slot,
+            d_endpoint_all, d_depth_all, rstride);
+        B200R_LAUNCH_CHECK("k_shard_commit");
+    }
+    if (n > 0) {
+        g_launches += 1;
+        k_shard_finish<<<(int)((n + 255) / 256), 256, 0, st>>>(
+            d_endpoint_all, d_leader_all, (int)n, (int64_t)my_rank * rstride, d_endpoint, d_matched);
+        B200R_LAUNCH_CHECK("k_shard_finish");
     }
     return B200R_OK;
 }
