@@ -259,9 +259,12 @@ def run_b200(args):
 
     def new_router():
         if world == 1:
-            t = GpuHashTrie(cap_log2=cap_log2, device=dev)
-            t.reserve(args.batch, max_chunks)
-            return t
+            # public single-GPU API: table + two-stream batch pipeline (hash stage of batch
+            # b+1 overlaps the route stage of batch b; results stay sequential)
+            from b200_router.trie import RoutePipeline
+            pipe = RoutePipeline(GpuHashTrie(cap_log2=cap_log2, device=dev))
+            pipe.reserve(args.batch, max_chunks)
+            return pipe
         from b200_router.distributed import ShardedPrefixRouter
         return ShardedPrefixRouter(cap_log2=cap_log2, device=dev, max_requests=args.batch,
                                    max_chunks=max_chunks)
@@ -275,12 +278,17 @@ def run_b200(args):
            torch.empty(args.batch, dtype=torch.int32, device=dev),
            torch.empty(args.batch, dtype=torch.int64, device=dev))
 
+    def route_resident(router, b, seq):
+        if world == 1:
+            return router.route(resident[b], avail_mask(b), SEED, seq, inputs_ready=True)
+        return router.route(resident[b], avail_mask(b), SEED, seq, out=out)
+
     # ---- pass 1: device-resident batches, whole timed region bracketed by events
     resident = [p.to(dev, non_blocking=False) for p in host]
     router = new_router()
     seq = 0
     for b in range(W):
-        router.route(resident[b], avail_mask(b), SEED, seq, out=out)
+        route_resident(router, b, seq)
         seq += args.batch * world
     barrier()
     sampler = ClockSampler(local)
@@ -290,7 +298,7 @@ def run_b200(args):
     ev0.record()
     th0 = time.perf_counter()
     for b in range(W, nb):
-        router.route(resident[b], avail_mask(b), SEED, seq, out=out)
+        route_resident(router, b, seq)
         seq += args.batch * world
     host_submit_ms = (time.perf_counter() - th0) * 1e3 / K
     ev1.record()
@@ -317,14 +325,14 @@ def run_b200(args):
     router = new_router()
     seq = 0
     for b in range(W):
-        router.route(resident[b], avail_mask(b), SEED, seq, out=out)
+        route_resident(router, b, seq)
         seq += args.batch * world
     barrier()
     _lib.prof_enable(True)
     verbose = os.environ.get("BENCH_VERBOSE") == "1"
     prof = None
     for b in range(W, nb):
-        router.route(resident[b], avail_mask(b), SEED, seq, out=out)
+        route_resident(router, b, seq)
         seq += args.batch * world
         if verbose:                      # per-step kernel times (synchronises every step)
             one = _lib.prof_read()
@@ -346,19 +354,41 @@ def run_b200(args):
     resident = None
     torch.cuda.empty_cache()
 
-    # ---- pass 3: end to end from pinned host buffers through the public API
+    # ---- pass 3: end to end from pinned host buffers through the public API.  Every step
+    # copies its packed batch host->device and its decisions device->host inside the timed
+    # region; the host reads step b's decisions after submitting step b+1 (the pipeline
+    # overlaps the copy of the next batch with the routing of the current one).
     router = new_router()
     seq = 0
+    res_host = [torch.empty(args.batch, dtype=torch.int32).pin_memory() for _ in range(3)]
+    res_ev = [torch.cuda.Event() for _ in range(3)]
+
+    def submit(b, seq, j):
+        if world == 1:
+            ep, _, _ = router.route(host[b], avail_mask(b), SEED, seq)
+        else:
+            ep, _, _ = router.route(host[b].to(dev, non_blocking=True), avail_mask(b), SEED, seq,
+                                    out=out)
+        res_host[j][:ep.numel()].copy_(ep, non_blocking=True)
+        res_ev[j].record()
+
+    checksum = 0
     for b in range(W):
-        ep, _, _ = router.route(host[b].to(dev, non_blocking=True), avail_mask(b), SEED, seq, out=out)
-        ep.cpu()
+        submit(b, seq, b % 3)
         seq += args.batch * world
     barrier()
     t0 = time.perf_counter()
+    prev = None
     for b in range(W, nb):
-        ep, _, _ = router.route(host[b].to(dev, non_blocking=True), avail_mask(b), SEED, seq, out=out)
-        decisions = ep.cpu()                  # D2H read of the step's result (synchronises)
+        j = b % 3
+        submit(b, seq, j)
         seq += args.batch * world
+        if prev is not None:
+            res_ev[prev].synchronize()
+            checksum += int(res_host[prev][0]) + int(res_host[prev][-1])   # host reads the result
+        prev = j
+    res_ev[prev].synchronize()
+    checksum += int(res_host[prev][0]) + int(res_host[prev][-1])
     barrier()
     e2e_s = time.perf_counter() - t0
     if world > 1:
@@ -378,6 +408,8 @@ def run_b200(args):
         buf, starts, lens = tr.batch_arrays(b)
         prompts = prompts_of(buf, starts, lens, cnt)
         rate, want = cpu_port_rate(prompts, avail_mask(b))
+        router = None
+        torch.cuda.empty_cache()
         t2 = GpuHashTrie(cap_log2=max(16, int(np.ceil(np.log2(cnt * 24 * 2.2)))), device=dev)
         ep, _, _ = t2.route(pack_arrays(buf, starts[:cnt], lens[:cnt], pin=False),
                             avail_mask(b), SEED, 0)

@@ -161,6 +161,21 @@ int b200r_prefix_route_batch(b200r_trie *t, const uint8_t *d_bytes, const int64_
                              uint64_t seed, uint64_t seq0, int32_t *d_endpoint,
                              int32_t *d_match_depth, uint64_t *d_matched_mask, void *d_scratch,
                              size_t scratch_bytes, void *stream);
+/* The same batch as two stages that meet only in the scratch buffer, for callers
+ * that overlap batches: the hash stage (prep + chunk hashing; never touches the
+ * table) of batch b+1 can run on another stream while the route stage (claim /
+ * select / commit) of batch b runs; one scratch buffer per batch in flight.
+ * Route stages must be issued in batch order.  b200r_prefix_route_batch is
+ * exactly hash stage + route stage on one stream. */
+int b200r_prefix_hash_stage(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
+                            const int32_t *d_lens, const int32_t *d_nchars, int64_t n,
+                            int64_t max_chunks, uint32_t flags, void *d_scratch,
+                            size_t scratch_bytes, void *stream);
+int b200r_prefix_route_stage(b200r_trie *t, int64_t n, int64_t max_chunks, uint32_t flags,
+                             uint64_t avail_mask, uint64_t seed, uint64_t seq0,
+                             int32_t *d_endpoint, int32_t *d_match_depth,
+                             uint64_t *d_matched_mask, void *d_scratch, size_t scratch_bytes,
+                             void *stream);
 /* the canonical draw, on the host (same arithmetic as the kernels) */
 uint32_t b200r_pick(uint64_t seed, uint64_t seq, uint32_t n);
 

@@ -179,6 +179,38 @@ def test_route_heavy_sharing_random_vs_oracle():
         t.close()
 
 
+def test_route_pipeline_overlapped_batches_vs_oracle():
+    """RoutePipeline (hash stage of batch b+1 overlapping the route stage of batch b,
+    host inputs copied on the hash stream) gives the sequential results."""
+    from b200_router.trie import GpuHashTrie, RoutePipeline
+    tr = traces.SharedPrefixTrace(n_total=30000, batch=3000, n_sys=16, sys_chars=512,
+                                  suffix_lo=100, suffix_hi=400, seed=21)
+    for host_inputs in (False, True):
+        t = GpuHashTrie(cap_log2=19)
+        pipe = RoutePipeline(t)
+        orc = coracle.TrieOracle()
+        seq, pending = 0, []
+        for b in range(tr.num_batches()):
+            avail = 0xFF & ~(1 << 5) if b in (3, 4, 5) else 0xFF
+            buf, starts, lens = tr.batch_arrays(b)
+            p = pack_arrays(buf, starts, lens, pin=host_inputs)
+            if not host_inputs:
+                p = p.to(t.device)
+                torch.cuda.synchronize()
+            ep, depth, matched = pipe.route(p, avail, 3, seq, inputs_ready=not host_inputs)
+            want = orc.route_batch(buf, starts, lens, avail, 3, seq)
+            seq += len(starts)
+            pending.append((ep.clone(), depth.clone(), matched.clone(), want))
+        torch.cuda.synchronize()
+        for ep, depth, matched, (oep, odepth, omatched) in pending:
+            assert (ep.cpu().numpy() == oep).all()
+            assert (depth.cpu().numpy() == odepth).all()
+            assert (u64(matched) == omatched).all()
+        t.check_status()
+        assert t.dump() == orc.dump()
+        t.close()
+
+
 def test_route_long_prompts_many_blocks_vs_oracle():
     """Prompts of more than 32 chunks (several warp iterations, carried path key)."""
     from b200_router.trie import GpuHashTrie

@@ -222,3 +222,96 @@ def decode_dump(arr: np.ndarray, root_mask: int) -> Dict[tuple, int]:
     for key, (h, m) in nodes.items():
         out[path_of(key)] = m
     return out
+
+
+class RoutePipeline:
+    """Overlaps consecutive batches on one GPU.
+
+    A routed batch is a hash stage (prep + chunk hashing: streams the prompt bytes,
+    never touches the table) and a route stage (claim / select / commit: table
+    probes, latency bound).  The pipeline runs the hash stage of batch b+1 on its
+    own stream while the route stage of batch b runs on the caller's stream; the
+    stages meet in one scratch buffer per batch in flight.  Route stages stay in
+    submission order, so results are still those of sequential routing.
+
+    Host (pinned) inputs are copied to the device on the hash stream, so the H2D
+    copy of batch b+1 also overlaps the routing of batch b.  For inputs that are
+    already on the device pass inputs_ready=True when they are complete (e.g.
+    produced and synchronised earlier); otherwise the hash stage waits for the
+    caller's stream, which is safe but serialises the two stages."""
+
+    def __init__(self, trie: GpuHashTrie, depth: int = 2):
+        self.trie = trie
+        self.depth = depth
+        self.device = trie.device
+        self.hash_stream = torch.cuda.Stream(device=self.device)
+        self._scratch = [None] * depth
+        self._done = [None] * depth
+        self._hashed = [torch.cuda.Event() for _ in range(depth)]
+        self._outs = [None] * (depth + 1)
+        self._i = 0
+
+    def _scratch_for(self, k, nbytes):
+        t = self._scratch[k]
+        if t is None or t.numel() < nbytes:
+            t = self._scratch[k] = torch.empty(int(nbytes * 1.25) + 4096, dtype=torch.uint8,
+                                               device=self.device)
+        return t
+
+    def reserve(self, n: int, max_chunks: int, all_ascii: bool = True):
+        flags = _lib.F_ALL_ASCII if all_ascii else 0
+        need = _lib.lib().b200r_prefix_route_scratch_bytes(n, max_chunks, flags)
+        for k in range(self.depth):
+            self._scratch_for(k, need)
+        for j in range(self.depth + 1):
+            self._out_for(j, n)
+
+    def _out_for(self, j, n):
+        o = self._outs[j]
+        if o is None or o[0].numel() < n:
+            o = self._outs[j] = (torch.empty(max(n, 1), dtype=torch.int32, device=self.device),
+                                 torch.empty(max(n, 1), dtype=torch.int32, device=self.device),
+                                 torch.empty(max(n, 1), dtype=torch.int64, device=self.device))
+        return o
+
+    def route(self, p: PackedPrompts, avail_mask: int, seed: int, seq0: int, out=None,
+              inputs_ready: bool = False):
+        """Returns device tensors (endpoint, depth, matched), valid in stream order on
+        the caller's current stream.  Unless `out` is given they live in a ring of
+        depth+1 buffers: consume them before depth+1 further batches are submitted."""
+        L = _lib.lib()
+        k = self._i % self.depth
+        o = out if out is not None else self._out_for(self._i % (self.depth + 1), p.n)
+        self._i += 1
+        n = p.n
+        cur = torch.cuda.current_stream(self.device)
+        hs = self.hash_stream
+        flags = _lib.F_ALL_ASCII if p.all_ascii else 0
+        need = L.b200r_prefix_route_scratch_bytes(n, p.max_chunks, flags)
+        sc = self._scratch_for(k, need)
+        on_host = p.bytes.device.type == "cpu"
+        if self._done[k] is not None:
+            hs.wait_event(self._done[k])          # scratch k is free again
+        if not on_host and not inputs_ready:
+            hs.wait_stream(cur)
+        with torch.cuda.device(self.device), torch.cuda.stream(hs):
+            if on_host:
+                p = p.to(self.device, non_blocking=True)
+            _lib.check(L.b200r_prefix_hash_stage(
+                self.trie._h, _ptr(p.bytes), _ptr(p.starts), _ptr(p.lens), _ptr(p.nchars), n,
+                p.max_chunks, flags, _ptr(sc), sc.numel(), C.c_void_p(hs.cuda_stream)))
+            self._hashed[k].record(hs)
+        cur.wait_event(self._hashed[k])
+        ep, depth, matched = o
+        with torch.cuda.device(self.device):
+            _lib.check(L.b200r_prefix_route_stage(
+                self.trie._h, n, p.max_chunks, flags, avail_mask & M64, seed & M64, seq0 & M64,
+                _ptr(ep), _ptr(depth), _ptr(matched), _ptr(sc), sc.numel(),
+                C.c_void_p(cur.cuda_stream)))
+        done = torch.cuda.Event()
+        done.record(cur)
+        self._done[k] = done
+        return ep[:n], depth[:n], matched[:n]
+
+    def check_status(self, count_nodes: bool = False):
+        return self.trie.check_status(count_nodes)

@@ -67,7 +67,7 @@ struct ProfScope {
     }
 };
 
-constexpr int PREP_BLOCK = 1024;   // requests per CTA of the prep kernels
+constexpr int PREP_BLOCK = 256;    // requests per CTA of the prep kernels
 constexpr int WARPS_PER_CTA = 8;   // per-request kernels: one warp per request
 
 // =========================================================================
@@ -80,12 +80,12 @@ __device__ __forceinline__ int chunks_of(const int32_t *lens, const int32_t *nch
 }
 
 __device__ __forceinline__ int block_sum_1024(int v, int *s_red)
-{   // all 1024 threads get the block total
+{   // all PREP_BLOCK threads get the block total
     int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     if (lane == 0) s_red[w] = v;
     __syncthreads();
-    int t = s_red[lane];
+    int t = lane < PREP_BLOCK / 32 ? s_red[lane] : 0;
     for (int o = 16; o; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
     __syncthreads();
     return t;
@@ -149,7 +149,20 @@ k_prep_scan(const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars
             const int64_t gl = (int64_t)base + c - 1;
             if (hashes && nc == ln && tail < cc && gl < max_chunks) {
                 const uint8_t *q = bytes + starts[i];
-                if ((((uintptr_t)q) & 15) == 0) hashes[gl] = xxh64_global(q + (ln - tail), tail);
+                if ((((uintptr_t)q) & 15) == 0) {
+                    const uint8_t *tp = q + (ln - tail);
+                    if (tail <= 128 && (((uintptr_t)tp) & 15) == 0) {
+                        // fetch the whole tail with independent 16-byte loads first (one DRAM
+                        // round trip instead of one per stripe), then hash it out of local memory
+                        uint4 loc[8];
+#pragma unroll
+                        for (int u = 0; u < 8; u++)
+                            loc[u] = (u * 16 < tail) ? __ldg((const uint4 *)tp + u) : make_uint4(0, 0, 0, 0);
+                        hashes[gl] = xxh64_global((const uint8_t *)loc, tail);
+                    } else {
+                        hashes[gl] = xxh64_global(tp, tail);
+                    }
+                }
             }
         }
     }
@@ -1170,16 +1183,39 @@ size_t b200r_prefix_route_scratch_bytes(int64_t n, int64_t max_chunks, uint32_t 
     return make_plan(n, max_chunks, flags, true).total;
 }
 
-int b200r_prefix_route_batch(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
-                             const int32_t *d_lens, const int32_t *d_nchars, int64_t n,
-                             int64_t max_chunks, uint32_t flags, uint64_t avail_mask,
-                             uint64_t seed, uint64_t seq0, int32_t *d_endpoint,
-                             int32_t *d_match_depth, uint64_t *d_matched_mask, void *d_scratch,
-                             size_t scratch_bytes, void *stream)
+// The routed batch is two stages that only meet in the scratch buffer:
+//   hash stage   prep + chunk hashing: reads the prompt bytes, does NOT touch the table
+//   route stage  claim / select / commit: reads the hashes, updates the table
+// so a caller may run the hash stage of batch b+1 (HBM-bandwidth bound) on one stream
+// while the route stage of batch b (latency bound) runs on another, with one scratch
+// buffer per batch in flight.  Route stages must be issued in batch order.
+int b200r_prefix_hash_stage(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
+                            const int32_t *d_lens, const int32_t *d_nchars, int64_t n,
+                            int64_t max_chunks, uint32_t flags, void *d_scratch,
+                            size_t scratch_bytes, void *stream)
 {
     if (!t) { set_error("null trie"); return B200R_E_INVALID; }
     int rc = check_prompt_args(d_bytes, d_starts, d_lens, n, max_chunks, t->chunk_chars);
     if (rc) return rc;
+    if (n == 0) return B200R_OK;
+    const Plan p = make_plan(n, max_chunks, flags, true);
+    if (!d_scratch || scratch_bytes < p.total) {
+        set_error("scratch too small: need %zu bytes, got %zu", p.total, scratch_bytes);
+        return B200R_E_SCRATCH;
+    }
+    uint8_t *sc = (uint8_t *)d_scratch;
+    return launch_hash(d_bytes, d_starts, d_lens, d_nchars, n, t->chunk_chars, flags,
+                       (int32_t *)(sc + p.off_chunk_base), (uint64_t *)(sc + p.off_hashes),
+                       max_chunks, sc, p, t->dev, (cudaStream_t)stream);
+}
+
+int b200r_prefix_route_stage(b200r_trie *t, int64_t n, int64_t max_chunks, uint32_t flags,
+                             uint64_t avail_mask, uint64_t seed, uint64_t seq0,
+                             int32_t *d_endpoint, int32_t *d_match_depth,
+                             uint64_t *d_matched_mask, void *d_scratch, size_t scratch_bytes,
+                             void *stream)
+{
+    if (!t || n < 0 || max_chunks < 0) { set_error("b200r_prefix_route_stage: bad argument"); return B200R_E_INVALID; }
     if (n == 0) return B200R_OK;
     if (!d_endpoint || !d_match_depth || !d_matched_mask) { set_error("null output pointer"); return B200R_E_INVALID; }
     const Plan p = make_plan(n, max_chunks, flags, true);
@@ -1199,15 +1235,12 @@ int b200r_prefix_route_batch(b200r_trie *t, const uint8_t *d_bytes, const int64_
     // with atomicMax, so a newer batch overrides whatever older batches left and, inside
     // a batch, the smallest request index wins.  Zero (fresh table) means "never".
     if (t->epoch >= 0xFFFFFFF0u) {
-        set_error("b200r_prefix_route_batch: batch epoch exhausted; b200r_trie_clear or re-create the table");
+        set_error("batch epoch exhausted; b200r_trie_clear or re-create the table");
         return B200R_E_INVALID;
     }
     t->epoch++;
     const unsigned long long tag = (unsigned long long)t->epoch << 32;
 
-    rc = launch_hash(d_bytes, d_starts, d_lens, d_nchars, n, t->chunk_chars, flags, chunk_base,
-                     hashes, max_chunks, sc, p, t->dev, st);
-    if (rc) return rc;
     const int blocks = (int)((n + WARPS_PER_CTA - 1) / WARPS_PER_CTA);
     const int thr = WARPS_PER_CTA * 32;
     const int tblocks = (int)((n + 255) / 256);
@@ -1228,6 +1261,20 @@ int b200r_prefix_route_batch(b200r_trie *t, const uint8_t *d_bytes, const int64_
     B200R_LAUNCH_CHECK("k_commit");
     }
     return B200R_OK;
+}
+
+int b200r_prefix_route_batch(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
+                             const int32_t *d_lens, const int32_t *d_nchars, int64_t n,
+                             int64_t max_chunks, uint32_t flags, uint64_t avail_mask,
+                             uint64_t seed, uint64_t seq0, int32_t *d_endpoint,
+                             int32_t *d_match_depth, uint64_t *d_matched_mask, void *d_scratch,
+                             size_t scratch_bytes, void *stream)
+{
+    int rc = b200r_prefix_hash_stage(t, d_bytes, d_starts, d_lens, d_nchars, n, max_chunks, flags,
+                                     d_scratch, scratch_bytes, stream);
+    if (rc) return rc;
+    return b200r_prefix_route_stage(t, n, max_chunks, flags, avail_mask, seed, seq0, d_endpoint,
+                                    d_match_depth, d_matched_mask, d_scratch, scratch_bytes, stream);
 }
 
 // ---------------------------------------------------------------- multi-GPU
