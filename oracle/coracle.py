@@ -113,9 +113,12 @@ class TrieOracle:
         self.chunk_chars = chunk_chars
 
     def __del__(self):
-        if getattr(self, "h", None):
-            lib().orc_trie_free(self.h)
-            self.h = None
+        try:
+            if getattr(self, "h", None):
+                lib().orc_trie_free(self.h)
+                self.h = None
+        except Exception:      # interpreter shutdown
+            pass
 
     def route_batch(self, byts, starts, lens, avail, seed, seq0):
         n = len(starts)

@@ -302,3 +302,21 @@ def test_router_e2e_prefix_families():
     with pytest.raises(KeyError):
         asyncio.run(r.route_request(eps, None, None, None, {"nothing": 1}))
     routers._reset_singletons_for_tests()
+
+
+def test_checkpoint_save_load(tmp_path):
+    from b200_router.trie import GpuHashTrie
+    _, prompts = traces.sharing_stress(n_batches=1, batch=300, max_depth=6, seed=123)[0]
+    t = GpuHashTrie(cap_log2=13)
+    p = pack_prompts(prompts)
+    t.route(p, 0x3F, 9, 0)
+    path = str(tmp_path / "trie.npz")
+    t.save(path)
+    t2 = GpuHashTrie.load(path)
+    assert t2.dump() == t.dump()
+    # both continue identically
+    a = t.route(p, 0x15, 9, 300)
+    b = t2.route(p, 0x15, 9, 300)
+    assert all(torch.equal(x, y) for x, y in zip(a, b))
+    assert t2.dump() == t.dump()
+    t.close(); t2.close()

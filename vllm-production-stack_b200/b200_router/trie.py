@@ -180,6 +180,29 @@ class GpuHashTrie:
             _lib.check(_lib.lib().b200r_trie_apply_remote(self._h, _ptr(ent), ent.numel() // 4,
                                                           root_mask_or & M64, _stream()))
 
+    # ------------------------------------------------------- checkpoint (f4)
+    def save(self, path: str):
+        """Write the table to disk (the reference has no checkpoint; its trie dies
+        with the process).  Format: npz with entries uint64[count,4] =
+        {key_lo, key_hi, chunk_hash, mask}, root mask, chunk size, format version."""
+        arr, root = self.dump_raw()
+        np.savez(path, entries=arr, root_mask=np.uint64(root),
+                 chunk_chars=np.int32(self.chunk_chars), version=np.int32(1))
+
+    @classmethod
+    def load(cls, path: str, cap_log2: Optional[int] = None, device=None) -> "GpuHashTrie":
+        z = np.load(path)
+        if int(z["version"]) != 1:
+            raise _lib.B200RouterError("unknown trie checkpoint version %d" % int(z["version"]))
+        arr = z["entries"]
+        if cap_log2 is None:
+            cap_log2 = max(12, int(np.ceil(np.log2(max(len(arr), 1) * 2.5))))
+        t = cls(cap_log2=cap_log2, chunk_chars=int(z["chunk_chars"]), device=device)
+        if len(arr):
+            t.apply_entries(torch.from_numpy(arr.view(np.int64).copy()), int(z["root_mask"]))
+        t.check_status()
+        return t
+
     def dump(self) -> Dict[tuple, int]:
         """Decode the table back into the reference's shape:
         {tuple(chunk hashes from the root): mask}; () is the root."""
