@@ -52,6 +52,8 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=16)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="prefix", choices=["prefix", "session"],
+                    help="prefix = BASELINE metric (default); session = configs[1], 1M session ids")
     ap.add_argument("--batch", type=int, default=BATCH, help=argparse.SUPPRESS)
     ap.add_argument("--cpu-sample", type=int, default=BATCH, help=argparse.SUPPRESS)
     ap.add_argument("--no-cpu", action="store_true", help=argparse.SUPPRESS)
@@ -430,7 +432,8 @@ def run_b200(args):
                 "clocks": clocks, "host_submit_ms_per_step": host_submit_ms, "e2e": e2e, "gpu_launches": int(launches),
                 "roofline": {"bound": "hbm", "kernel": "k_hash_chunks", "achieved": achieved,
                              "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                             "frac": achieved / peaks["hbm_gbs"], "traffic": None,
+                             "frac": achieved / peaks["hbm_gbs"],
+                             "traffic": load_ncu_traffic("k_hash_chunks"),
                              "peak_source": peak_src, "launches": hash_n,
                              "ms_per_launch": hash_ms / max(hash_n, 1),
                              "share_of_step": hash_ms / prof_total if prof_total else None,
@@ -440,6 +443,72 @@ def run_b200(args):
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def load_ncu_traffic(kernel):
+    """DRAM bytes per launch of `kernel` from the committed ncu --set full capture."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            return json.load(f)[kernel]["dram_bytes_per_launch"]
+    except Exception:
+        return None
+
+
+def run_session(args):
+    """configs[1]: 1M synthetic session ids over 16 endpoints, batched ring lookup on 1 GPU.
+    ALU-bound (one MD5 block per key); the HBM fraction is informational."""
+    import torch
+    from b200_router import traces
+    from b200_router.packing import pack_arrays
+    from b200_router.ring import GpuHashRing
+    n = 1 << 20
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(0)
+    nodes = traces.endpoint_urls(16)
+    ring = GpuHashRing(nodes)
+    buf, starts, lens = traces.session_ids_packed(n, seed=0)
+    host = pack_arrays(buf, starts, lens, pin=True)
+    res = host.to(dev, non_blocking=False)
+    W, K = args.warmup, args.steps
+    for _ in range(W):
+        out = ring.lookup_packed(res)
+    torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(K):
+        out = ring.lookup_packed(res)
+    ev1.record()
+    torch.cuda.synchronize()
+    ms = ev0.elapsed_time(ev1)
+    t0 = time.perf_counter()
+    for _ in range(K):
+        got = ring.lookup_packed(host.to(dev, non_blocking=True)).cpu()
+    e2e_s = time.perf_counter() - t0
+    cpu = None
+    if not args.no_cpu:
+        from oracle import ring_ref
+        ref = ring_ref.RingRef(nodes)
+        ids = traces.session_ids_uuid(200000, 0)
+        t0 = time.perf_counter()
+        want = [ref.get_node(k) for k in ids]
+        dt = time.perf_counter() - t0
+        cpu = {"value": len(ids) / dt, "unit": "lookups/s", "cores": 1, "kind": "port",
+               "sample": "200000 uuid ids through oracle/ring_ref.py (restated uhashring ring)"}
+        assert ring.get_node_batch(ids[:5000]) == want[:5000]
+    peaks, src = load_peaks()
+    algo = n * (36 + 8 + 4 + 4)
+    print(json.dumps({
+        "metric": "session_route_lookups_per_sec", "value": n * K / (ms * 1e-3), "unit": "lookups/s",
+        "n_gpus": 1, "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+        "config": {"workload": "C2: 1M uuid-shaped session ids, 16 endpoints, ring of 2560 points"},
+        "e2e": {"value": n * K / e2e_s, "unit": "lookups/s", "h2d_bytes_per_step": host.h2d_bytes(),
+                "d2h_bytes_per_step": n * 4},
+        "roofline": {"bound": "hbm", "kernel": "k_ring_lookup", "achieved": algo / (ms / K * 1e-3) / 1e9,
+                     "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                     "frac": algo / (ms / K * 1e-3) / 1e9 / peaks["hbm_gbs"], "traffic": None,
+                     "note": "ALU-bound by construction: one 64-step MD5 block per 36-byte key"},
+        "md5_blocks_per_sec": n * K / (ms * 1e-3), "cpu_baseline": cpu, "gpu_launches": K}))
 
 
 def load_peaks():
@@ -455,5 +524,7 @@ if __name__ == "__main__":
     a = parse_args()
     if a.impl == "reference":
         run_reference(a)
+    elif a.workload == "session":
+        run_session(a)
     else:
         run_b200(a)

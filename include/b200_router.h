@@ -212,8 +212,10 @@ void b200r_trie_key_constants(uint64_t out[6]);
  *        -> all-gather them (rank q at q*rstride)
  *   b200r_shard_commit    resolves every request's endpoint, inserts it into
  *        every replica, writes the own shard's results
- * d_req_off = int32 [world+1] device array: global position of every shard's
- * request 0 (exclusive prefix sum of the shard sizes); req_off = the own one.  The scratch buffer
+ * d_rec_count = u32[2], written by classify as {record count, shard size n}; the
+ * all-gather of it is d_meta = int32 [world][2].  req_off (select) = global
+ * position of the own shard's request 0 = sum of the earlier shards' sizes.
+ * d_lcd_all = int32 [world][3][rstride]: every rank's leaders, choices, depths.  The scratch buffer
  * (b200r_prefix_route_scratch_bytes) must be the same for all four calls.
  * ---------------------------------------------------------------------- */
 #define B200R_SHARD_RECORD_BYTES 32
@@ -222,19 +224,18 @@ int b200r_shard_classify(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d
                          int64_t max_chunks, uint32_t flags, uint64_t avail_mask,
                          void *d_records, uint32_t *d_rec_count, void *d_scratch,
                          size_t scratch_bytes, void *stream);
-int b200r_shard_apply(b200r_trie *t, const void *d_records_all, const int32_t *d_counts,
-                      int32_t world, int64_t stride, int32_t my_rank, const int32_t *d_req_off,
-                      int64_t n, int64_t max_chunks, uint32_t flags, uint32_t *d_rec_slot,
-                      void *d_scratch, void *stream);
+int b200r_shard_apply(b200r_trie *t, const void *d_records_all, const int32_t *d_meta,
+                      int32_t world, int64_t stride, int32_t my_rank, int64_t n,
+                      int64_t max_chunks, uint32_t flags, uint32_t *d_rec_slot, void *d_scratch,
+                      void *stream);
 int b200r_shard_select(b200r_trie *t, int64_t n, int64_t max_chunks, uint32_t flags,
                        uint64_t avail_mask, uint64_t seed, uint64_t seq0, uint32_t req_off,
                        int32_t *d_leader, int32_t *d_choice, int32_t *d_depth,
                        uint64_t *d_matched, void *d_scratch, void *stream);
-int b200r_shard_commit(b200r_trie *t, const void *d_records_all, const int32_t *d_counts,
+int b200r_shard_commit(b200r_trie *t, const void *d_records_all, const int32_t *d_meta,
                        int32_t world, int64_t stride, const uint32_t *d_rec_slot,
-                       const int32_t *d_leader_all, const int32_t *d_choice_all,
-                       const int32_t *d_depth_all, const int32_t *d_req_off, int64_t rstride,
-                       int32_t my_rank, int64_t n, int32_t *d_endpoint_all, int32_t *d_endpoint,
+                       const int32_t *d_lcd_all, int64_t rstride, int32_t my_rank, int64_t n,
+                       int32_t *d_endpoint_all, int32_t *d_endpoint, int32_t *d_match_depth,
                        uint64_t *d_matched, void *stream);
 
 /* ------------------------------------------------------------------------

@@ -65,13 +65,15 @@ class FakeShardOps:
         if rows:
             recs[:len(rows)] = torch.tensor(rows, dtype=torch.int64)
         count[0] = len(rows)
+        count[1] = p.n
 
-    def apply(self, recs_all, counts, world, stride, rank, req_off, rec_slot):
+    def apply(self, recs_all, meta_all, world, stride, rank, rec_slot):
         ra = recs_all.numpy()
+        offs = np.concatenate([[0], np.cumsum(meta_all[:, 1].numpy())])
         for q in range(world):
-            for j in range(int(counts[q])):
+            for j in range(int(meta_all[q, 0])):
                 k1, k2, h, rd = (_u64(x) for x in ra[q, j])
-                req = (rd & 0xFFFFFFFF) + int(req_off[q])
+                req = (rd & 0xFFFFFFFF) + int(offs[q])
                 ent = self.table.setdefault((k1, k2), [0, 0, 0, h])
                 if ent[1] != self.epoch or req < ent[2]:
                     ent[1], ent[2] = self.epoch, req
@@ -99,9 +101,13 @@ class FakeShardOps:
                 leader[i] = self.table[star[0]][2]
                 choice[i] = -1
 
-    def commit(self, recs_all, counts, world, stride, rec_slot, leader_all, choice_all, depth_all,
-               req_off, rstride, rank, endpoint_all, endpoint, matched):
-        offs = [int(x) for x in req_off]
+    def commit(self, recs_all, meta_all, world, stride, rec_slot, lcd_all, rstride, rank,
+               endpoint_all, endpoint, depth, matched):
+        offs = [0] + [int(x) for x in np.cumsum(meta_all[:, 1].numpy())]
+        counts = meta_all[:, 0]
+        leader_all = lcd_all[:, 0, :].contiguous()
+        choice_all = lcd_all[:, 1, :].contiguous()
+        depth_all = lcd_all[:, 2, :].contiguous()
 
         def index_of(pos):
             q = 0
@@ -131,6 +137,7 @@ class FakeShardOps:
         for i in range(n):
             e = ep_all[rank * rstride + i]
             endpoint[i] = e
+            depth[i] = int(da[rank * rstride + i])
             if int(la[rank * rstride + i]) >= 0:
                 matched[i] = _s64(1 << e) if e >= 0 else 0
 

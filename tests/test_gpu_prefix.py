@@ -320,3 +320,26 @@ def test_checkpoint_save_load(tmp_path):
     assert all(torch.equal(x, y) for x, y in zip(a, b))
     assert t2.dump() == t.dump()
     t.close(); t2.close()
+
+
+def test_router_micro_batched_concurrent_requests_equal_reference(golden_prefix):
+    """f1: concurrent route_request coroutines are micro-batched; the outcome equals the
+    reference's one-by-one routing of the same arrival order (golden decisions)."""
+    from b200_router import routers
+    tr = [t for t in golden_prefix["traces"] if t["name"] == "e2e_families"][0]
+    routers._reset_singletons_for_tests()
+    r = routers.PrefixAwareRouter(cap_log2=14, seed=tr["seed"], micro_batch_ms=20, micro_batch_max=64)
+
+    class Ep:
+        def __init__(self, url): self.url = url
+    eps = [Ep(u) for u in tr["urls"]]
+    prompts = tr["batches"][0]["prompts"]
+
+    async def go():
+        tasks = [asyncio.ensure_future(r.route_request(eps, None, None, None, {"prompt": p}))
+                 for p in prompts]
+        return await asyncio.gather(*tasks)
+    urls = asyncio.run(go())
+    assert [tr["urls"].index(u) for u in urls] == tr["decisions"]
+    assert 1 < r.batcher.batches_routed <= (len(prompts) + 63) // 64 + 1
+    routers._reset_singletons_for_tests()

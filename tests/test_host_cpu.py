@@ -140,3 +140,33 @@ def test_trace_generators_are_deterministic():
     assert len(p) == 6 and p[3].startswith(p[0]) and u == [0, 1, 2, 0, 1, 2]
     ids = traces.session_ids_uuid(5, 1)
     assert ids == traces.session_ids_uuid(5, 1) and all(len(i) == 36 and i[14] == "4" for i in ids)
+
+
+def test_micro_batcher_keeps_arrival_order_and_splits_on_endpoint_change():
+    from b200_router.batching import MicroBatcher
+    calls = []
+
+    def fake_route_batch(endpoints, prompts):
+        calls.append((tuple(endpoints), list(prompts)))
+        return ["%s@%s" % (p, endpoints[len(p) % len(endpoints)]) for p in prompts]
+
+    async def go():
+        mb = MicroBatcher(fake_route_batch, max_batch=4, max_delay_ms=20)
+        eps_a, eps_b = ["u1", "u2"], ["u1", "u3"]
+        tasks = [asyncio.ensure_future(mb.route(eps_a, "p%d" % i)) for i in range(6)]      # 4 + 2
+        tasks += [asyncio.ensure_future(mb.route(eps_b, "q%d" % i)) for i in range(3)]     # new set
+        tasks += [asyncio.ensure_future(mb.route(eps_a, "r0"))]
+        return await asyncio.gather(*tasks), mb
+    got, mb = asyncio.run(go())
+    assert [c[1] for c in calls] == [["p0", "p1", "p2", "p3"], ["p4", "p5"], ["q0", "q1", "q2"], ["r0"]]
+    assert [c[0] for c in calls] == [("u1", "u2")] * 2 + [("u1", "u3")] + [("u1", "u2")]
+    assert got[0] == "p0@u1" and got[6] == "q0@u1" and got[-1] == "r0@u1"
+    assert mb.batches_routed == 4 and mb.requests_routed == 10
+
+    def failing(endpoints, prompts):
+        raise KeyError("prompt")
+
+    async def go2():
+        mb = MicroBatcher(failing, max_batch=2, max_delay_ms=5)
+        return await asyncio.gather(mb.route(["u"], "a"), mb.route(["u"], "b"), return_exceptions=True)
+    assert all(isinstance(e, KeyError) for e in asyncio.run(go2()))

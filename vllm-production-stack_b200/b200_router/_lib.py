@@ -44,12 +44,11 @@ SIGNATURES = {
     "b200r_trie_key_constants": (None, [C.POINTER(_u64)]),
     "b200r_shard_classify": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _u32, _u64, _vp, _vp,
                                        _vp, _sz, _vp]),
-    "b200r_shard_apply": (C.c_int, [_vp, _vp, _vp, _i32, _i64, _i32, _vp, _i64, _i64, _u32, _vp, _vp,
-                                    _vp]),
+    "b200r_shard_apply": (C.c_int, [_vp, _vp, _vp, _i32, _i64, _i32, _i64, _i64, _u32, _vp, _vp, _vp]),
     "b200r_shard_select": (C.c_int, [_vp, _i64, _i64, _u32, _u64, _u64, _u64, _u32, _vp, _vp, _vp, _vp,
                                      _vp, _vp]),
-    "b200r_shard_commit": (C.c_int, [_vp, _vp, _vp, _i32, _i64, _vp, _vp, _vp, _vp, _vp, _i64, _i32,
-                                     _i64, _vp, _vp, _vp, _vp]),
+    "b200r_shard_commit": (C.c_int, [_vp, _vp, _vp, _i32, _i64, _vp, _vp, _i64, _i32, _i64, _vp, _vp,
+                                     _vp, _vp, _vp]),
     "b200r_prof_enable": (C.c_int, [C.c_int]),
     "b200r_prof_read": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_longlong), C.c_int]),
     "b200r_launch_count": (C.c_longlong, []),

@@ -62,12 +62,12 @@ class CudaShardOps:
                 p.max_chunks, flags, avail_mask & M64, _ptr(recs), _ptr(count), _ptr(sc), sc.numel(),
                 _stream()))
 
-    def apply(self, recs_all, counts, world, stride, rank, req_off, rec_slot):
+    def apply(self, recs_all, meta_all, world, stride, rank, rec_slot):
         n, max_chunks, flags = self._shape
         with torch.cuda.device(self.device):
             _lib.check(_lib.lib().b200r_shard_apply(
-                self.trie._h, _ptr(recs_all), _ptr(counts), world, stride, rank, _ptr(req_off), n,
-                max_chunks, flags, _ptr(rec_slot), _ptr(self.trie._scratch), _stream()))
+                self.trie._h, _ptr(recs_all), _ptr(meta_all), world, stride, rank, n, max_chunks,
+                flags, _ptr(rec_slot), _ptr(self.trie._scratch), _stream()))
 
     def select(self, avail_mask, seed, seq0, my_off, leader, choice, depth, matched):
         n, max_chunks, flags = self._shape
@@ -77,14 +77,14 @@ class CudaShardOps:
                 _ptr(leader), _ptr(choice), _ptr(depth), _ptr(matched), _ptr(self.trie._scratch),
                 _stream()))
 
-    def commit(self, recs_all, counts, world, stride, rec_slot, leader_all, choice_all, depth_all,
-               req_off, rstride, rank, endpoint_all, endpoint, matched):
+    def commit(self, recs_all, meta_all, world, stride, rec_slot, lcd_all, rstride, rank,
+               endpoint_all, endpoint, depth, matched):
         n = self._shape[0]
         with torch.cuda.device(self.device):
             _lib.check(_lib.lib().b200r_shard_commit(
-                self.trie._h, _ptr(recs_all), _ptr(counts), world, stride, _ptr(rec_slot),
-                _ptr(leader_all), _ptr(choice_all), _ptr(depth_all), _ptr(req_off), rstride, rank, n,
-                _ptr(endpoint_all), _ptr(endpoint), _ptr(matched), _stream()))
+                self.trie._h, _ptr(recs_all), _ptr(meta_all), world, stride, _ptr(rec_slot),
+                _ptr(lcd_all), rstride, rank, n, _ptr(endpoint_all), _ptr(endpoint), _ptr(depth),
+                _ptr(matched), _stream()))
 
     def check_status(self, count_nodes=False):
         return self.trie.check_status(count_nodes)
@@ -116,7 +116,7 @@ class ShardedPrefixRouter:
         self.ops = ops if ops is not None else CudaShardOps(cap_log2, device)
         self.device = self.ops.device
         self._recs = None          # int64 [cap, 4]: this rank's records
-        self._count = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._count = torch.zeros(2, dtype=torch.int32, device=self.device)   # {records, n}
         self._bufs = {}
         if max_chunks:
             self._ensure_recs(max_chunks)
@@ -148,20 +148,15 @@ class ShardedPrefixRouter:
         recs = self._ensure_recs(max(p.max_chunks, 1))
         self.ops.classify(p, avail_mask, recs, self._count)
 
-        # gather #1: shard sizes and record counts
-        meta = torch.stack([torch.full((), n, dtype=torch.int32, device=self.device),
-                            self._count[0]]).contiguous()
+        # gather #1: record counts and shard sizes ({count, n} per rank, written by classify)
         meta_all = self._buf("meta", (W, 2), torch.int32)
-        self.comm.all_gather(meta_all.view(-1), meta)
+        self.comm.all_gather(meta_all.view(-1), self._count)
         meta_host = meta_all.cpu()                       # the one host read of the batch
-        ns = meta_host[:, 0].tolist()
-        cnts = meta_host[:, 1].tolist()
+        cnts = meta_host[:, 0].tolist()
+        ns = meta_host[:, 1].tolist()
         stride = max(cnts)
         rstride = max(max(ns), 1)
-        req_off = torch.zeros(W + 1, dtype=torch.int32)
-        req_off[1:] = torch.cumsum(meta_host[:, 0], 0)
-        req_off_dev = req_off.to(self.device, non_blocking=True)
-        counts_dev = meta_all[:, 1].contiguous()
+        my_off = sum(ns[:rank])
 
         # gather #2: records (rank q at q * stride)
         recs_all = self._buf("recs_all", (W, max(stride, 1), 4), torch.int64)
@@ -169,7 +164,7 @@ class ShardedPrefixRouter:
         if stride > 0:
             recs = self._ensure_recs(stride)
             self.comm.all_gather(recs_all.view(-1), recs[:stride].reshape(-1))
-            self.ops.apply(recs_all, counts_dev, W, stride, rank, req_off_dev, rec_slot)
+            self.ops.apply(recs_all, meta_all, W, stride, rank, rec_slot)
 
         # select on the own shard; gather #3: leaders, choices, match depths
         lcd = self._buf("lcd", (3, rstride), torch.int32)
@@ -178,16 +173,12 @@ class ShardedPrefixRouter:
                    torch.empty(max(n, 1), dtype=torch.int32, device=self.device),
                    torch.empty(max(n, 1), dtype=torch.int64, device=self.device))
         ep, depth, matched = out
-        self.ops.select(avail_mask, seed, seq0, int(req_off[rank]), lcd[0], lcd[1], lcd[2], matched)
+        self.ops.select(avail_mask, seed, seq0, my_off, lcd[0], lcd[1], lcd[2], matched)
         lcd_all = self._buf("lcd_all", (W, 3, rstride), torch.int32)
         self.comm.all_gather(lcd_all.view(-1), lcd.reshape(-1))
-        by_kind = self._buf("lcd_kind", (3, W, rstride), torch.int32)
-        by_kind.copy_(lcd_all.permute(1, 0, 2))
         endpoint_all = self._buf("ep_all", (W * rstride,), torch.int32)
-        self.ops.commit(recs_all, counts_dev, W, stride, rec_slot, by_kind[0], by_kind[1], by_kind[2],
-                        req_off_dev, rstride, rank, endpoint_all, ep, matched)
-        if n:
-            depth[:n].copy_(lcd[2][:n])
+        self.ops.commit(recs_all, meta_all, W, stride, rec_slot, lcd_all, rstride, rank,
+                        endpoint_all, ep, depth, matched)
         self.last_exchange_bytes = (W - 1) * (stride * 32 + rstride * 12 + 8)
         return ep[:n], depth[:n], matched[:n]
 

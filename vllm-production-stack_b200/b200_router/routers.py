@@ -141,13 +141,20 @@ def extract_prompt(request_json: Dict) -> str:
 class PrefixAwareRouter(_RefPrefix):
     """GPU-backed `prefixaware` routing logic (drop-in for routing_logic.py:347-423)."""
 
-    def __init__(self, cap_log2: int = 22, seed: int = 0, device=None):
+    def __init__(self, cap_log2: int = 22, seed: int = 0, device=None,
+                 micro_batch_ms: float = 0.0, micro_batch_max: int = 4096):
+        """micro_batch_ms > 0: concurrent route_request calls arriving within that window
+        are routed as one GPU batch, in arrival order (b200_router.batching.MicroBatcher)."""
         if hasattr(self, "_initialized"):
             return
         self.hashtrie = GpuHashTrie(cap_log2=cap_log2, chunk_chars=128, device=device)
         self.registry = EndpointRegistry()
         self.seed = seed
         self.seq = 0                      # global request sequence number (tie-break counter)
+        self.batcher = None
+        if micro_batch_ms > 0:
+            from .batching import MicroBatcher
+            self.batcher = MicroBatcher(self.route_batch, micro_batch_max, micro_batch_ms)
         self._initialized = True
 
     # ---- batch API
@@ -173,6 +180,8 @@ class PrefixAwareRouter(_RefPrefix):
     async def route_request(self, endpoints, engine_stats, request_stats, request,
                             request_json) -> str:
         prompt = extract_prompt(request_json)
+        if self.batcher is not None:
+            return await self.batcher.route(endpoints, prompt)
         return self.route_batch(endpoints, [prompt])[0]
 
 

@@ -693,54 +693,59 @@ k_shard_classify(const Entry *__restrict__ tab, int cap_log2, const uint64_t *__
     }
 }
 
-// records of rank q live at recs_all[q * stride .. q * stride + counts[q])
+// Gathered layouts (rank q):
+//   meta[2q] = number of records of rank q, meta[2q+1] = number of requests of rank q
+//   records  at recs_all[q * stride ...]
+//   leaders / choices / match depths at lcd[(3q + 0|1|2) * rstride ...]
+// The global position of request i of rank q is req_off(q) + i, req_off = prefix sum of
+// the shard sizes (world is small: computed on the fly).
+__device__ __forceinline__ uint32_t shard_req_off(const int32_t *meta, int q)
+{
+    uint32_t o = 0;
+    for (int p = 0; p < q; p++) o += (uint32_t)meta[2 * p + 1];
+    return o;
+}
+
 __global__ void k_shard_apply(Entry *__restrict__ tab, uint64_t *__restrict__ hs, int cap_log2,
                               TrieDev *dev, const ShardRec *__restrict__ recs_all,
-                              const int32_t *__restrict__ counts, int world, int64_t stride,
-                              int my_rank, const int32_t *__restrict__ req_off,
-                              const int32_t *__restrict__ chunk_base, unsigned long long tag,
-                              uint32_t *__restrict__ slots,
+                              const int32_t *__restrict__ meta, int world, int64_t stride,
+                              int my_rank, const int32_t *__restrict__ chunk_base,
+                              unsigned long long tag, uint32_t *__restrict__ slots,
                               uint32_t *__restrict__ rec_slot)
 {
     const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= (int64_t)world * stride) return;
     const int q = (int)(idx / stride);
-    if (idx - (int64_t)q * stride >= counts[q]) return;
+    if (idx - (int64_t)q * stride >= meta[2 * q]) return;
     const ShardRec r = recs_all[idx];
     bool created;
     const uint32_t s = table_claim(tab, hs, cap_log2, r.k1, r.k2, r.h, &created);
     rec_slot[idx] = s;
     if (s == SLOT_NONE) { atomicOr(&dev->status, B200R_S_TABLE_FULL); return; }
-    // global position of the request = position of its shard + index inside the shard
-    const unsigned long long mine = tag | (unsigned long long)(~((uint32_t)req_off[q] + r.req));
+    const unsigned long long mine = tag | (unsigned long long)(~(shard_req_off(meta, q) + r.req));
     unsigned long long cur = 0;
     if (!created) cur = *(volatile unsigned long long *)&tab[s].first;
     if (cur < mine) atomicMax(&tab[s].first, mine);
     if (q == my_rank) slots[chunk_base[r.req] + r.depth] = s;
 }
 
-// position in the global order -> index into the rank-strided gathered arrays
-__device__ __forceinline__ int64_t shard_index(const int32_t *req_off, int world, int64_t rstride,
-                                               uint32_t pos)
-{
-    int q = 0;
-    while (q + 1 < world && pos >= (uint32_t)req_off[q + 1]) q++;
-    return (int64_t)q * rstride + (pos - (uint32_t)req_off[q]);
-}
-
-__global__ void k_shard_resolve(TrieDev *dev, const int32_t *__restrict__ leader_all,
-                                const int32_t *__restrict__ choice_all,
-                                const int32_t *__restrict__ req_off, int world, int64_t rstride,
+__global__ void k_shard_resolve(TrieDev *dev, const int32_t *__restrict__ lcd,
+                                const int32_t *__restrict__ meta, int world, int64_t rstride,
                                 int32_t *__restrict__ endpoint_all)
 {
     const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= (int64_t)world * rstride) return;
-    const int q = (int)(idx / rstride);
-    if (idx - (int64_t)q * rstride >= req_off[q + 1] - req_off[q]) return;
-    int64_t j = idx;
+    int q = (int)(idx / rstride);
+    int64_t i = idx - (int64_t)q * rstride;
+    if (i >= meta[2 * q + 1]) return;
     int l;
-    while ((l = leader_all[j]) >= 0) j = shard_index(req_off, world, rstride, (uint32_t)l);
-    const int e = choice_all[j];
+    while ((l = lcd[(3 * (int64_t)q) * rstride + i]) >= 0) {   // leader = global position
+        uint32_t pos = (uint32_t)l, o = 0;
+        q = 0;
+        while (q + 1 < world && pos >= o + (uint32_t)meta[2 * q + 1]) { o += (uint32_t)meta[2 * q + 1]; q++; }
+        i = pos - o;
+    }
+    const int e = lcd[(3 * (int64_t)q + 1) * rstride + i];
     endpoint_all[idx] = e;
     if (e >= 0) {
         const uint64_t bit = 1ULL << e;
@@ -749,33 +754,34 @@ __global__ void k_shard_resolve(TrieDev *dev, const int32_t *__restrict__ leader
 }
 
 __global__ void k_shard_commit(Entry *__restrict__ tab, const ShardRec *__restrict__ recs_all,
-                               const int32_t *__restrict__ counts, int world, int64_t stride,
+                               const int32_t *__restrict__ meta, int world, int64_t stride,
                                const uint32_t *__restrict__ rec_slot,
                                const int32_t *__restrict__ endpoint_all,
-                               const int32_t *__restrict__ depth_all, int64_t rstride)
+                               const int32_t *__restrict__ lcd, int64_t rstride)
 {
     const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= (int64_t)world * stride) return;
     const int q = (int)(idx / stride);
-    if (idx - (int64_t)q * stride >= counts[q]) return;
+    if (idx - (int64_t)q * stride >= meta[2 * q]) return;
     const uint32_t s = rec_slot[idx];
     if (s == SLOT_NONE) return;
     const uint32_t req = recs_all[idx].req, d = recs_all[idx].depth;
-    const int64_t ri = (int64_t)q * rstride + req;
-    const int e = endpoint_all[ri];
-    if (e >= 0 && (int)d >= depth_all[ri])
+    const int e = endpoint_all[(int64_t)q * rstride + req];
+    if (e >= 0 && (int)d >= lcd[(3 * (int64_t)q + 2) * rstride + req])
         atomicOr((unsigned long long *)&tab[s].mask, 1ULL << e);
 }
 
 __global__ void k_shard_finish(const int32_t *__restrict__ endpoint_all,
-                               const int32_t *__restrict__ leader_all, int n, int64_t my_base,
-                               int32_t *__restrict__ endpoint, uint64_t *__restrict__ matched)
+                               const int32_t *__restrict__ lcd, int n, int my_rank, int64_t rstride,
+                               int32_t *__restrict__ endpoint, int32_t *__restrict__ depth,
+                               uint64_t *__restrict__ matched)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const int e = endpoint_all[my_base + i];
+    const int e = endpoint_all[(int64_t)my_rank * rstride + i];
     endpoint[i] = e;
-    if (leader_all[my_base + i] >= 0) matched[i] = (e >= 0) ? (1ULL << e) : 0;
+    depth[i] = lcd[(3 * (int64_t)my_rank + 2) * rstride + i];
+    if (lcd[(3 * (int64_t)my_rank) * rstride + i] >= 0) matched[i] = (e >= 0) ? (1ULL << e) : 0;
 }
 
 // ------------------------------------------------------------ dump / restore
@@ -1296,7 +1302,8 @@ int b200r_shard_classify(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d
     cudaStream_t st = (cudaStream_t)stream;
     if (t->epoch >= 0xFFFFFFF0u) { set_error("batch epoch exhausted"); return B200R_E_INVALID; }
     t->epoch++;
-    B200R_CUDA(cudaMemsetAsync(d_rec_count, 0, 4, st));
+    const uint32_t init[2] = { 0u, (uint32_t)n };       // {record count, shard size}
+    B200R_CUDA(cudaMemcpyAsync(d_rec_count, init, 8, cudaMemcpyHostToDevice, st));
     if (n == 0) return B200R_OK;
     uint8_t *sc = (uint8_t *)d_scratch;
     int32_t *chunk_base = (int32_t *)(sc + p.off_chunk_base);
@@ -1314,23 +1321,23 @@ int b200r_shard_classify(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d
     return B200R_OK;
 }
 
-int b200r_shard_apply(b200r_trie *t, const void *d_records_all, const int32_t *d_counts,
-                      int32_t world, int64_t stride, int32_t my_rank, const int32_t *d_req_off,
-                      int64_t n, int64_t max_chunks, uint32_t flags, uint32_t *d_rec_slot,
-                      void *d_scratch, void *stream)
+int b200r_shard_apply(b200r_trie *t, const void *d_records_all, const int32_t *d_meta,
+                      int32_t world, int64_t stride, int32_t my_rank, int64_t n,
+                      int64_t max_chunks, uint32_t flags, uint32_t *d_rec_slot, void *d_scratch,
+                      void *stream)
 {
     if (!t || world <= 0 || stride < 0 || my_rank < 0 || my_rank >= world) { set_error("b200r_shard_apply: bad argument"); return B200R_E_INVALID; }
     if (stride == 0) return B200R_OK;
-    if (!d_records_all || !d_counts || !d_rec_slot || !d_scratch || !d_req_off) { set_error("null pointer"); return B200R_E_INVALID; }
+    if (!d_records_all || !d_meta || !d_rec_slot || !d_scratch) { set_error("null pointer"); return B200R_E_INVALID; }
     const Plan p = make_plan(n, max_chunks, flags, true);
     uint8_t *sc = (uint8_t *)d_scratch;
     const int64_t work = (int64_t)world * stride;
     const unsigned long long tag = (unsigned long long)t->epoch << 32;
     g_launches += 1;
     k_shard_apply<<<(int)((work + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-        t->tab, t->hs, t->cap_log2, t->dev, (const ShardRec *)d_records_all, d_counts, world, stride,
-        my_rank, d_req_off, (const int32_t *)(sc + p.off_chunk_base), tag,
-        (uint32_t *)(sc + p.off_slots), d_rec_slot);
+        t->tab, t->hs, t->cap_log2, t->dev, (const ShardRec *)d_records_all, d_meta, world, stride,
+        my_rank, (const int32_t *)(sc + p.off_chunk_base), tag, (uint32_t *)(sc + p.off_slots),
+        d_rec_slot);
     B200R_LAUNCH_CHECK("k_shard_apply");
     return B200R_OK;
 }
@@ -1355,35 +1362,35 @@ int b200r_shard_select(b200r_trie *t, int64_t n, int64_t max_chunks, uint32_t fl
     return B200R_OK;
 }
 
-int b200r_shard_commit(b200r_trie *t, const void *d_records_all, const int32_t *d_counts,
+int b200r_shard_commit(b200r_trie *t, const void *d_records_all, const int32_t *d_meta,
                        int32_t world, int64_t stride, const uint32_t *d_rec_slot,
-                       const int32_t *d_leader_all, const int32_t *d_choice_all,
-                       const int32_t *d_depth_all, const int32_t *d_req_off, int64_t rstride,
-                       int32_t my_rank, int64_t n, int32_t *d_endpoint_all, int32_t *d_endpoint,
+                       const int32_t *d_lcd_all, int64_t rstride, int32_t my_rank, int64_t n,
+                       int32_t *d_endpoint_all, int32_t *d_endpoint, int32_t *d_match_depth,
                        uint64_t *d_matched, void *stream)
 {
     if (!t || world <= 0 || my_rank < 0 || my_rank >= world || rstride < 0 || stride < 0) { set_error("b200r_shard_commit: bad argument"); return B200R_E_INVALID; }
     if (rstride == 0) return B200R_OK;
-    if (!d_leader_all || !d_choice_all || !d_depth_all || !d_req_off || !d_endpoint_all) { set_error("null pointer"); return B200R_E_INVALID; }
+    if (!d_lcd_all || !d_meta || !d_endpoint_all) { set_error("null pointer"); return B200R_E_INVALID; }
     cudaStream_t st = (cudaStream_t)stream;
     const int64_t rwork = (int64_t)world * rstride;
     g_launches += 1;
-    k_shard_resolve<<<(int)((rwork + 255) / 256), 256, 0, st>>>(t->dev, d_leader_all, d_choice_all,
-                                                              d_req_off, world, rstride,
-                                                              d_endpoint_all);
+    k_shard_resolve<<<(int)((rwork + 255) / 256), 256, 0, st>>>(t->dev, d_lcd_all, d_meta, world,
+                                                              rstride, d_endpoint_all);
     B200R_LAUNCH_CHECK("k_shard_resolve");
     const int64_t work = (int64_t)world * stride;
     if (work > 0) {
         g_launches += 1;
         k_shard_commit<<<(int)((work + 255) / 256), 256, 0, st>>>(
-            t->tab, (const ShardRec *)d_records_all, d_counts, world, stride, d_rec_slot,
-            d_endpoint_all, d_depth_all, rstride);
+            t->tab, (const ShardRec *)d_records_all, d_meta, world, stride, d_rec_slot,
+            d_endpoint_all, d_lcd_all, rstride);
         B200R_LAUNCH_CHECK("k_shard_commit");
     }
     if (n > 0) {
+        if (!d_endpoint || !d_match_depth || !d_matched) { set_error("null output pointer"); return B200R_E_INVALID; }
         g_launches += 1;
-        k_shard_finish<<<(int)((n + 255) / 256), 256, 0, st>>>(
-            d_endpoint_all, d_leader_all, (int)n, (int64_t)my_rank * rstride, d_endpoint, d_matched);
+        k_shard_finish<<<(int)((n + 255) / 256), 256, 0, st>>>(d_endpoint_all, d_lcd_all, (int)n, my_rank,
+                                                             rstride, d_endpoint, d_match_depth,
+                                                             d_matched);
         B200R_LAUNCH_CHECK("k_shard_finish");
     }
     return B200R_OK;
