@@ -267,9 +267,11 @@ def run_b200(args):
             pipe = RoutePipeline(GpuHashTrie(cap_log2=cap_log2, device=dev))
             pipe.reserve(args.batch, max_chunks)
             return pipe
-        from b200_router.distributed import ShardedPrefixRouter
-        return ShardedPrefixRouter(cap_log2=cap_log2, device=dev, max_requests=args.batch,
-                                   max_chunks=max_chunks)
+        # multi-GPU: exchange over NVLink peer memory by the library's own kernels;
+        # BENCH_EXCHANGE=nccl selects the NCCL all-gather variant for comparison
+        from b200_router.distributed import P2PShardedRouter, ShardedPrefixRouter
+        cls = ShardedPrefixRouter if os.environ.get("BENCH_EXCHANGE") == "nccl" else P2PShardedRouter
+        return cls(cap_log2=cap_log2, device=dev, max_requests=args.batch, max_chunks=max_chunks)
 
     def barrier():
         if world > 1:

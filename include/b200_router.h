@@ -58,6 +58,7 @@ extern "C" {
 /* latched device status bits (b200r_trie_status) */
 #define B200R_S_TABLE_FULL 1u
 #define B200R_S_CHUNK_CAP 2u
+#define B200R_S_PEER_TIMEOUT 4u /* multi-GPU: a peer's data did not arrive within ~3 s */
 
 typedef struct b200r_trie b200r_trie; /* GPU-resident HashTrie replacement     */
 typedef struct b200r_ring b200r_ring; /* GPU-resident consistent-hash ring     */
@@ -237,6 +238,40 @@ int b200r_shard_commit(b200r_trie *t, const void *d_records_all, const int32_t *
                        const int32_t *d_lcd_all, int64_t rstride, int32_t my_rank, int64_t n,
                        int32_t *d_endpoint_all, int32_t *d_endpoint, int32_t *d_match_depth,
                        uint64_t *d_matched, void *stream);
+
+/* ------------------------------------------------------------------------
+ * The same multi-GPU batch with the exchange done by this library's own kernels
+ * over NVLink peer memory instead of NCCL all-gathers (no host round trip at
+ * all).  Every rank allocates one buffer of b200r_p2p_layout(...)[0] bytes that
+ * all peers can address (e.g. torch.distributed._symmetric_memory) and passes
+ * the table of all ranks' base addresses (d_peer_bases, u64[world], device).
+ * cap = record capacity per rank and batch (>= max_chunks of any shard), rcap =
+ * request capacity per rank (multiple of 4); epoch = batch number, 1, 2, 3, ...,
+ * the same on all ranks.  The global tie-break sequence number is kept on the
+ * device (d_dyn, 1 KB, zero-initialised by the caller).  Per batch, per rank:
+ *   b200r_p2p_classify  hash + lookup; pushes the records into every peer
+ *   b200r_p2p_route     waits for all peers' records, applies them, selects,
+ *                       pushes leaders / choices / depths into every peer
+ *   b200r_p2p_commit    waits for those, resolves and inserts; own results
+ * A peer that does not deliver within ~3 s latches B200R_S_PEER_TIMEOUT.
+ * ---------------------------------------------------------------------- */
+#define B200R_P2P_DYN_BYTES 1024
+int b200r_p2p_layout(int32_t world, int64_t cap, int64_t rcap, size_t out[3]);
+int b200r_p2p_classify(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
+                       const int32_t *d_lens, const int32_t *d_nchars, int64_t n,
+                       int64_t max_chunks, uint32_t flags, uint64_t avail_mask,
+                       const uint64_t *d_peer_bases, int32_t world, int32_t rank, int64_t cap,
+                       int64_t rcap, uint32_t epoch, void *d_recs_local, uint32_t *d_rec_count,
+                       void *d_scratch, size_t scratch_bytes, void *stream);
+int b200r_p2p_route(b200r_trie *t, int64_t n, int64_t max_chunks, uint32_t flags,
+                    uint64_t avail_mask, uint64_t seed, const uint64_t *d_peer_bases,
+                    void *d_my_base, int32_t world, int32_t rank, int64_t cap, int64_t rcap,
+                    uint32_t epoch, void *d_dyn, uint32_t *d_rec_slot, int32_t *d_lcd_local,
+                    uint64_t *d_matched, void *d_scratch, void *stream);
+int b200r_p2p_commit(b200r_trie *t, int64_t n, void *d_my_base, int32_t world, int32_t rank,
+                     int64_t cap, int64_t rcap, uint32_t epoch, void *d_dyn,
+                     const uint32_t *d_rec_slot, int32_t *d_endpoint_all, int32_t *d_endpoint,
+                     int32_t *d_match_depth, uint64_t *d_matched, void *stream);
 
 /* ------------------------------------------------------------------------
  * a9  uhashring.HashRing (md5 points, bisect_right + wrap), a7 SessionRouter

@@ -14,6 +14,7 @@ OK = 0
 F_ALL_ASCII = 1
 S_TABLE_FULL = 1
 S_CHUNK_CAP = 2
+S_PEER_TIMEOUT = 4
 NOALLOC_SCRATCH_BYTES = 4 * 1024 * 1024
 
 _vp, _i64, _i32, _u32, _u64, _sz = C.c_void_p, C.c_int64, C.c_int32, C.c_uint32, C.c_uint64, C.c_size_t
@@ -49,6 +50,13 @@ SIGNATURES = {
                                      _vp, _vp]),
     "b200r_shard_commit": (C.c_int, [_vp, _vp, _vp, _i32, _i64, _vp, _vp, _i64, _i32, _i64, _vp, _vp,
                                      _vp, _vp, _vp]),
+    "b200r_p2p_layout": (C.c_int, [_i32, _i64, _i64, C.POINTER(_sz)]),
+    "b200r_p2p_classify": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _u32, _u64, _vp, _i32, _i32, _i64,
+                                     _i64, _u32, _vp, _vp, _vp, _sz, _vp]),
+    "b200r_p2p_route": (C.c_int, [_vp, _i64, _i64, _u32, _u64, _u64, _vp, _vp, _i32, _i32, _i64, _i64, _u32,
+                                  _vp, _vp, _vp, _vp, _vp, _vp]),
+    "b200r_p2p_commit": (C.c_int, [_vp, _i64, _vp, _i32, _i32, _i64, _i64, _u32, _vp, _vp, _vp, _vp, _vp,
+                                   _vp, _vp]),
     "b200r_prof_enable": (C.c_int, [C.c_int]),
     "b200r_prof_read": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_longlong), C.c_int]),
     "b200r_launch_count": (C.c_longlong, []),

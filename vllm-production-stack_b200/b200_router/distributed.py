@@ -187,3 +187,118 @@ class ShardedPrefixRouter:
 
     def dump(self):
         return self.ops.dump()
+
+
+class P2PShardedRouter:
+    """Same global-batch semantics as ShardedPrefixRouter, but the exchange is done by
+    the library's own kernels over NVLink peer memory: every rank pushes its records
+    (and later its leaders / choices / match depths) straight into buffers of all its
+    peers and publishes arrival flags; consumers spin on the device.  No NCCL call and
+    no host read per batch -- the host only enqueues kernels.
+
+    The peer-addressable buffer comes from torch.distributed._symmetric_memory.  The
+    global tie-break sequence number lives on the device (it starts at 0 and advances
+    by the global batch size), so `seq0` of route() is only checked on the first batch.
+    """
+
+    def __init__(self, cap_log2: int = 22, device=None, max_requests: int = 0, max_chunks: int = 0,
+                 group=None, _sim=None):
+        from .trie import GpuHashTrie
+        L = _lib.lib()
+        if _sim is None:
+            self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        else:
+            self.world, self.rank = _sim["world"], _sim["rank"]
+        self.trie = GpuHashTrie(cap_log2=cap_log2, device=device)
+        self.device = self.trie.device
+        self.cap = max(int(max_chunks), 64)
+        self.rcap = (max(int(max_requests), 4) + 3) // 4 * 4
+        lay = (C.c_size_t * 3)()
+        _lib.check(L.b200r_p2p_layout(self.world, self.cap, self.rcap, lay))
+        self.symm_bytes = int(lay[0])
+        if _sim is None:
+            import torch.distributed._symmetric_memory as symm_mem
+            self.symm = symm_mem.empty(self.symm_bytes, dtype=torch.uint8, device=self.device)
+            self.symm.zero_()
+            torch.cuda.synchronize(self.device)
+            g = group if group is not None else dist.group.WORLD
+            self._hdl = symm_mem.rendezvous(self.symm, g.group_name)
+            bases = list(self._hdl.buffer_ptrs)
+            self._hdl.barrier()                       # every peer's flag block is zeroed
+        else:                                         # single-device lock-step emulation (tests)
+            self.symm = _sim["buffers"][self.rank]
+            bases = [b.data_ptr() for b in _sim["buffers"]]
+        self.peer_bases = torch.tensor(bases, dtype=torch.int64, device=self.device)
+        self.dyn = torch.zeros(1024, dtype=torch.uint8, device=self.device)
+        self.recs_local = torch.empty((self.cap, 4), dtype=torch.int64, device=self.device)
+        self.rec_count = torch.zeros(2, dtype=torch.int32, device=self.device)
+        self.rec_slot = torch.empty(self.world * self.cap, dtype=torch.int32, device=self.device)
+        self.lcd_local = torch.zeros(3 * self.rcap, dtype=torch.int32, device=self.device)
+        self.endpoint_all = torch.empty(self.world * self.rcap, dtype=torch.int32, device=self.device)
+        self.epoch = 0
+        self._shape = None
+        self._out = None
+
+    @staticmethod
+    def symm_bytes_for(world: int, max_requests: int, max_chunks: int) -> int:
+        lay = (C.c_size_t * 3)()
+        _lib.check(_lib.lib().b200r_p2p_layout(world, max(int(max_chunks), 64),
+                                               (max(int(max_requests), 4) + 3) // 4 * 4, lay))
+        return int(lay[0])
+
+    # the three phases of a batch (route() runs them back to back)
+    def phase_classify(self, p: PackedPrompts, avail_mask: int):
+        if p.bytes.device != self.device:
+            p = p.to(self.device)
+        self.epoch += 1
+        flags = _lib.F_ALL_ASCII if p.all_ascii else 0
+        need = _lib.lib().b200r_prefix_route_scratch_bytes(p.n, p.max_chunks, flags)
+        sc = self.trie._scratch_for(need)
+        self._shape = (p.n, p.max_chunks, flags, avail_mask & M64)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().b200r_p2p_classify(
+                self.trie._h, _ptr(p.bytes), _ptr(p.starts), _ptr(p.lens), _ptr(p.nchars), p.n,
+                p.max_chunks, flags, avail_mask & M64, _ptr(self.peer_bases), self.world, self.rank,
+                self.cap, self.rcap, self.epoch, _ptr(self.recs_local), _ptr(self.rec_count),
+                _ptr(sc), sc.numel(), _stream()))
+
+    def phase_route(self, seed: int, out=None):
+        n, max_chunks, flags, avail = self._shape
+        if out is None:
+            out = (torch.empty(max(n, 1), dtype=torch.int32, device=self.device),
+                   torch.empty(max(n, 1), dtype=torch.int32, device=self.device),
+                   torch.empty(max(n, 1), dtype=torch.int64, device=self.device))
+        self._out = out
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().b200r_p2p_route(
+                self.trie._h, n, max_chunks, flags, avail, seed & M64, _ptr(self.peer_bases),
+                _ptr(self.symm), self.world, self.rank, self.cap, self.rcap, self.epoch,
+                _ptr(self.dyn), _ptr(self.rec_slot), _ptr(self.lcd_local), _ptr(out[2]),
+                _ptr(self.trie._scratch), _stream()))
+
+    def phase_commit(self):
+        n = self._shape[0]
+        ep, depth, matched = self._out
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().b200r_p2p_commit(
+                self.trie._h, n, _ptr(self.symm), self.world, self.rank, self.cap, self.rcap,
+                self.epoch, _ptr(self.dyn), _ptr(self.rec_slot), _ptr(self.endpoint_all), _ptr(ep),
+                _ptr(depth), _ptr(matched), _stream()))
+        return ep[:n], depth[:n], matched[:n]
+
+    def route(self, p: PackedPrompts, avail_mask: int, seed: int, seq0: int = 0, out=None):
+        if self.epoch == 0 and seq0 != 0:
+            raise _lib.B200RouterError("P2PShardedRouter keeps the sequence number on the device; "
+                                       "it starts at 0")
+        self.phase_classify(p, avail_mask)
+        self.phase_route(seed, out)
+        return self.phase_commit()
+
+    def check_status(self, count_nodes=False):
+        s = self.trie.check_status(count_nodes)
+        if s["status"] & _lib.S_PEER_TIMEOUT:
+            raise _lib.B200RouterError("a peer GPU did not deliver its part of a batch in time")
+        return s
+
+    def dump(self):
+        return self.trie.dump()

@@ -511,6 +511,14 @@ k_insert(Entry *__restrict__ tab, uint64_t *__restrict__ hs, int cap_log2, TrieD
 //   slots[g] = slot               otherwise; entry.first = (epoch, ~min request index)
 constexpr uint32_t PREOK_BIT = 0x80000000u;
 
+// Per-rank device-resident bookkeeping of the peer-exchange (P2P) multi-GPU path.
+constexpr int P2P_MAX_WORLD = 64;
+struct P2PDyn {
+    unsigned long long seq_base;     // global sequence number of the next batch's request 0
+    uint32_t my_off, total_n;        // position of this shard / size of the current global batch
+    int32_t meta[2 * P2P_MAX_WORLD]; // {record count, shard size} of every rank, current batch
+};
+
 __global__ void __launch_bounds__(WARPS_PER_CTA * 32)
 k_claim(Entry *__restrict__ tab, uint64_t *__restrict__ hs, int cap_log2, TrieDev *dev,
         const uint64_t *__restrict__ hashes, const int32_t *__restrict__ chunk_base, int n,
@@ -562,8 +570,10 @@ __global__ void __launch_bounds__(256)
 k_select(const Entry *__restrict__ tab, const int32_t *__restrict__ chunk_base, int n, int64_t max_chunks,
          const uint32_t *__restrict__ slots, uint64_t avail, unsigned long long tag, uint64_t seed,
          uint64_t seq0, int32_t *__restrict__ leader, int32_t *__restrict__ choice,
-         int32_t *__restrict__ depth_out, uint64_t *__restrict__ matched_out, uint32_t req_off)
+         int32_t *__restrict__ depth_out, uint64_t *__restrict__ matched_out, uint32_t req_off,
+         const P2PDyn *__restrict__ dyn)
 {
+    if (dyn) { req_off = dyn->my_off; seq0 = dyn->seq_base; }   // peer-exchange path: values live on the device
     // one thread per request: independent dependent-load chains, 32 per warp in flight.
     // req_off = position of request 0 of this shard in the global (rank-major) order;
     // 0 on a single GPU.  `first` words, leaders and the tie-break counter are global.
@@ -783,6 +793,107 @@ __global__ void k_shard_finish(const int32_t *__restrict__ endpoint_all,
     depth[i] = lcd[(3 * (int64_t)my_rank + 2) * rstride + i];
     if (lcd[(3 * (int64_t)my_rank) * rstride + i] >= 0) matched[i] = (e >= 0) ? (1ULL << e) : 0;
 }
+
+// =========================================================================
+// Multi-GPU exchange over NVLink peer memory (no NCCL, no host round trip).
+// Every rank owns one "symmetric" buffer that all peers can address:
+//   P2PFlags                      arrival flags, one set per batch parity
+//   recs  [2][world][cap]         32-byte records, region q written by rank q
+//   lcd   [2][world][3][rcap]     leaders / choices / depths, region q by rank q
+// A rank PUSHES its records (and later its leaders/choices/depths) into the
+// region it owns in every peer's buffer with coalesced 16-byte stores, then
+// publishes (epoch << 32 | count) flags; consumers spin on their own flags.  Two
+// buffer sets (batch parity) suffice: a rank can run at most one batch ahead of
+// a peer, because its next classify needs that peer's leaders of this batch.
+// =========================================================================
+struct P2PFlags {
+    unsigned long long rec_cnt[2][P2P_MAX_WORLD], rec_n[2][P2P_MAX_WORLD], lcd[2][P2P_MAX_WORLD];
+};
+constexpr size_t P2P_FLAGS_BYTES = 4096;
+static_assert(sizeof(P2PFlags) <= P2P_FLAGS_BYTES, "flag block");
+
+__global__ void k_p2p_push(const uint4 *__restrict__ src, const unsigned int *__restrict__ count_ptr,
+                           long long fixed_items, int units_per_item,
+                           const unsigned long long *__restrict__ peer_bases, int world,
+                           size_t dst_off)
+{
+    const long long items = count_ptr ? (long long)*count_ptr : fixed_items;
+    const long long units = items * units_per_item;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < units;
+         i += (long long)gridDim.x * blockDim.x) {
+        const uint4 v = src[i];
+        for (int p = 0; p < world; p++)
+            ((uint4 *)(uintptr_t)(peer_bases[p] + dst_off))[i] = v;
+    }
+    __threadfence_system();
+}
+
+__global__ void k_p2p_publish(const unsigned long long *__restrict__ peer_bases, int world,
+                              int my_rank, int set, unsigned long long epoch, int kind,
+                              const unsigned int *__restrict__ count_ptr, unsigned int n)
+{
+    const int p = threadIdx.x;
+    if (p >= world) return;
+    P2PFlags *f = (P2PFlags *)(uintptr_t)peer_bases[p];
+    __threadfence_system();
+    if (kind == 0) {
+        *(volatile unsigned long long *)&f->rec_n[set][my_rank] = (epoch << 32) | n;
+        *(volatile unsigned long long *)&f->rec_cnt[set][my_rank] = (epoch << 32) | *count_ptr;
+    } else {
+        *(volatile unsigned long long *)&f->lcd[set][my_rank] = (epoch << 32) | n;
+    }
+    __threadfence_system();
+}
+
+__device__ __forceinline__ bool p2p_spin(const volatile unsigned long long *flag,
+                                         unsigned long long epoch, unsigned long long *val)
+{
+    const long long t0 = clock64();
+    for (;;) {
+        const unsigned long long v = *flag;
+        if ((v >> 32) == epoch) { *val = v; return true; }
+        if (clock64() - t0 > 6000000000LL) return false;     // ~3 s: a peer is gone
+        __nanosleep(200);
+    }
+}
+
+__global__ void k_p2p_wait_meta(const P2PFlags *__restrict__ mine, int set, unsigned long long epoch,
+                                int world, int my_rank, P2PDyn *dyn, TrieDev *dev)
+{
+    const int q = threadIdx.x;
+    if (q < world) {
+        unsigned long long c = 0, m = 0;
+        const bool ok = p2p_spin(&mine->rec_cnt[set][q], epoch, &c) &&
+                        p2p_spin(&mine->rec_n[set][q], epoch, &m);
+        if (!ok) atomicOr(&dev->status, B200R_S_PEER_TIMEOUT);
+        dyn->meta[2 * q] = ok ? (int32_t)(uint32_t)c : 0;
+        dyn->meta[2 * q + 1] = ok ? (int32_t)(uint32_t)m : 0;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t off = 0, tot = 0;
+        for (int r = 0; r < world; r++) {
+            if (r == my_rank) off = tot;
+            tot += (uint32_t)dyn->meta[2 * r + 1];
+        }
+        dyn->my_off = off;
+        dyn->total_n = tot;
+    }
+    __threadfence_system();
+}
+
+__global__ void k_p2p_wait_lcd(const P2PFlags *__restrict__ mine, int set, unsigned long long epoch,
+                               int world, TrieDev *dev)
+{
+    const int q = threadIdx.x;
+    if (q < world) {
+        unsigned long long v;
+        if (!p2p_spin(&mine->lcd[set][q], epoch, &v)) atomicOr(&dev->status, B200R_S_PEER_TIMEOUT);
+    }
+    __threadfence_system();
+}
+
+__global__ void k_p2p_advance(P2PDyn *dyn) { dyn->seq_base += dyn->total_n; }
 
 // ------------------------------------------------------------ dump / restore
 __global__ void k_count_nodes(const Entry *__restrict__ tab, int64_t cap, TrieDev *dev)
@@ -1258,7 +1369,7 @@ int b200r_prefix_route_stage(b200r_trie *t, int64_t n, int64_t max_chunks, uint3
     { ProfScope ps__(PK_SELECT, st); g_launches += 1;
     k_select<<<tblocks, 256, 0, st>>>(t->tab, chunk_base, (int)n, max_chunks, slots,
                                      avail_mask, tag, seed, seq0, leader, choice, d_match_depth,
-                                     d_matched_mask, 0u);
+                                     d_matched_mask, 0u, nullptr);
     B200R_LAUNCH_CHECK("k_select");
     }
     { ProfScope ps__(PK_COMMIT, st); g_launches += 1;
@@ -1357,7 +1468,7 @@ int b200r_shard_select(b200r_trie *t, int64_t n, int64_t max_chunks, uint32_t fl
     k_select<<<(int)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
         t->tab, (const int32_t *)(sc + p.off_chunk_base), (int)n, max_chunks,
         (const uint32_t *)(sc + p.off_slots), avail_mask, tag, seed, seq0, d_leader, d_choice,
-        d_depth, d_matched, req_off);
+        d_depth, d_matched, req_off, nullptr);
     B200R_LAUNCH_CHECK("k_select");
     return B200R_OK;
 }
@@ -1393,6 +1504,139 @@ int b200r_shard_commit(b200r_trie *t, const void *d_records_all, const int32_t *
                                                              d_matched);
         B200R_LAUNCH_CHECK("k_shard_finish");
     }
+    return B200R_OK;
+}
+
+// --------------------------------------------------- multi-GPU over peer memory
+struct P2PLayout { size_t total, recs_off, lcd_off, rec_set, lcd_set; };
+
+static P2PLayout p2p_layout(int world, int64_t cap, int64_t rcap)
+{
+    P2PLayout L;
+    L.recs_off = P2P_FLAGS_BYTES;
+    L.rec_set = (size_t)world * (size_t)cap * sizeof(ShardRec);
+    L.lcd_off = L.recs_off + 2 * L.rec_set;
+    L.lcd_set = (size_t)world * 3 * (size_t)rcap * 4;
+    L.total = align_up(L.lcd_off + 2 * L.lcd_set);
+    return L;
+}
+
+static int p2p_check(int world, int rank, int64_t cap, int64_t rcap, const void *bases)
+{
+    if (world <= 0 || world > P2P_MAX_WORLD || rank < 0 || rank >= world || cap <= 0 || rcap <= 0 ||
+        (rcap & 3) || !bases) {
+        set_error("p2p: need 1 <= world <= %d, 0 <= rank < world, cap > 0, rcap > 0 and a multiple "
+                  "of 4, peer base table", P2P_MAX_WORLD);
+        return B200R_E_INVALID;
+    }
+    return B200R_OK;
+}
+
+int b200r_p2p_layout(int32_t world, int64_t cap, int64_t rcap, size_t out[3])
+{
+    if (world <= 0 || world > P2P_MAX_WORLD || cap <= 0 || rcap <= 0 || !out) { set_error("b200r_p2p_layout: bad argument"); return B200R_E_INVALID; }
+    const P2PLayout L = p2p_layout(world, cap, rcap);
+    out[0] = L.total; out[1] = L.recs_off; out[2] = L.lcd_off;
+    return B200R_OK;
+}
+
+int b200r_p2p_classify(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
+                       const int32_t *d_lens, const int32_t *d_nchars, int64_t n,
+                       int64_t max_chunks, uint32_t flags, uint64_t avail_mask,
+                       const uint64_t *d_peer_bases, int32_t world, int32_t rank, int64_t cap,
+                       int64_t rcap, uint32_t epoch, void *d_recs_local, uint32_t *d_rec_count,
+                       void *d_scratch, size_t scratch_bytes, void *stream)
+{
+    int rc = p2p_check(world, rank, cap, rcap, d_peer_bases);
+    if (rc) return rc;
+    if (max_chunks > cap || n > rcap) { set_error("p2p: batch (n=%lld, max_chunks=%lld) exceeds the exchange capacity (rcap=%lld, cap=%lld)", (long long)n, (long long)max_chunks, (long long)rcap, (long long)cap); return B200R_E_INVALID; }
+    rc = b200r_shard_classify(t, d_bytes, d_starts, d_lens, d_nchars, n, max_chunks, flags,
+                              avail_mask, d_recs_local, d_rec_count, d_scratch, scratch_bytes, stream);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const P2PLayout L = p2p_layout(world, cap, rcap);
+    const int set = (int)(epoch & 1);
+    const size_t dst = L.recs_off + (size_t)set * L.rec_set + (size_t)rank * (size_t)cap * sizeof(ShardRec);
+    g_launches += 2;
+    k_p2p_push<<<148 * 4, 256, 0, st>>>((const uint4 *)d_recs_local, d_rec_count, 0, 2,
+                                        (const unsigned long long *)d_peer_bases, world, dst);
+    B200R_LAUNCH_CHECK("k_p2p_push");
+    k_p2p_publish<<<1, P2P_MAX_WORLD, 0, st>>>((const unsigned long long *)d_peer_bases, world, rank,
+                                               set, epoch, 0, d_rec_count, (unsigned)n);
+    B200R_LAUNCH_CHECK("k_p2p_publish");
+    return B200R_OK;
+}
+
+int b200r_p2p_route(b200r_trie *t, int64_t n, int64_t max_chunks, uint32_t flags,
+                    uint64_t avail_mask, uint64_t seed, const uint64_t *d_peer_bases,
+                    void *d_my_base, int32_t world, int32_t rank, int64_t cap, int64_t rcap,
+                    uint32_t epoch, void *d_dyn, uint32_t *d_rec_slot, int32_t *d_lcd_local,
+                    uint64_t *d_matched, void *d_scratch, void *stream)
+{
+    int rc = p2p_check(world, rank, cap, rcap, d_peer_bases);
+    if (rc) return rc;
+    if (!t || !d_my_base || !d_dyn || !d_rec_slot || !d_lcd_local || !d_scratch || (n > 0 && !d_matched)) { set_error("b200r_p2p_route: null pointer"); return B200R_E_INVALID; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const P2PLayout L = p2p_layout(world, cap, rcap);
+    const int set = (int)(epoch & 1);
+    uint8_t *base = (uint8_t *)d_my_base;
+    P2PDyn *dyn = (P2PDyn *)d_dyn;
+    const ShardRec *recs_all = (const ShardRec *)(base + L.recs_off + (size_t)set * L.rec_set);
+    const Plan p = make_plan(n, max_chunks, flags, true);
+    uint8_t *sc = (uint8_t *)d_scratch;
+    const unsigned long long tag = (unsigned long long)t->epoch << 32;
+    g_launches += 1;
+    k_p2p_wait_meta<<<1, P2P_MAX_WORLD, 0, st>>>((const P2PFlags *)base, set, epoch, world, rank, dyn, t->dev);
+    B200R_LAUNCH_CHECK("k_p2p_wait_meta");
+    const int64_t work = (int64_t)world * cap;
+    g_launches += 1;
+    k_shard_apply<<<(int)((work + 255) / 256), 256, 0, st>>>(
+        t->tab, t->hs, t->cap_log2, t->dev, recs_all, dyn->meta, world, cap, rank,
+        (const int32_t *)(sc + p.off_chunk_base), tag, (uint32_t *)(sc + p.off_slots), d_rec_slot);
+    B200R_LAUNCH_CHECK("k_shard_apply");
+    if (n > 0) {
+        g_launches += 1;
+        k_select<<<(int)((n + 255) / 256), 256, 0, st>>>(
+            t->tab, (const int32_t *)(sc + p.off_chunk_base), (int)n, max_chunks,
+            (const uint32_t *)(sc + p.off_slots), avail_mask, tag, seed, 0, d_lcd_local,
+            d_lcd_local + rcap, d_lcd_local + 2 * rcap, d_matched, 0u, dyn);
+        B200R_LAUNCH_CHECK("k_select");
+    }
+    const size_t dst = L.lcd_off + (size_t)set * L.lcd_set + (size_t)rank * 3 * (size_t)rcap * 4;
+    g_launches += 2;
+    k_p2p_push<<<148, 256, 0, st>>>((const uint4 *)d_lcd_local, nullptr, 3 * rcap / 4, 1,
+                                    (const unsigned long long *)d_peer_bases, world, dst);
+    B200R_LAUNCH_CHECK("k_p2p_push(lcd)");
+    k_p2p_publish<<<1, P2P_MAX_WORLD, 0, st>>>((const unsigned long long *)d_peer_bases, world, rank,
+                                               set, epoch, 1, nullptr, (unsigned)n);
+    B200R_LAUNCH_CHECK("k_p2p_publish(lcd)");
+    return B200R_OK;
+}
+
+int b200r_p2p_commit(b200r_trie *t, int64_t n, void *d_my_base, int32_t world, int32_t rank,
+                     int64_t cap, int64_t rcap, uint32_t epoch, void *d_dyn,
+                     const uint32_t *d_rec_slot, int32_t *d_endpoint_all, int32_t *d_endpoint,
+                     int32_t *d_match_depth, uint64_t *d_matched, void *stream)
+{
+    int rc = p2p_check(world, rank, cap, rcap, d_my_base);
+    if (rc) return rc;
+    if (!t || !d_dyn || !d_rec_slot || !d_endpoint_all) { set_error("b200r_p2p_commit: null pointer"); return B200R_E_INVALID; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const P2PLayout L = p2p_layout(world, cap, rcap);
+    const int set = (int)(epoch & 1);
+    uint8_t *base = (uint8_t *)d_my_base;
+    P2PDyn *dyn = (P2PDyn *)d_dyn;
+    const int32_t *lcd_all = (const int32_t *)(base + L.lcd_off + (size_t)set * L.lcd_set);
+    g_launches += 1;
+    k_p2p_wait_lcd<<<1, P2P_MAX_WORLD, 0, st>>>((const P2PFlags *)base, set, epoch, world, t->dev);
+    B200R_LAUNCH_CHECK("k_p2p_wait_lcd");
+    rc = b200r_shard_commit(t, base + L.recs_off + (size_t)set * L.rec_set, dyn->meta, world, cap,
+                            d_rec_slot, lcd_all, rcap, rank, n, d_endpoint_all, d_endpoint,
+                            d_match_depth, d_matched, stream);
+    if (rc) return rc;
+    g_launches += 1;
+    k_p2p_advance<<<1, 1, 0, st>>>(dyn);
+    B200R_LAUNCH_CHECK("k_p2p_advance");
     return B200R_OK;
 }
 
