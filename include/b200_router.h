@@ -298,10 +298,11 @@ int b200r_ring_lookup_batch(b200r_ring *r, const uint8_t *d_bytes, const int64_t
  * its launch stream.  b200r_prof_read synchronises those events and returns,
  * per kernel class, the summed milliseconds and the number of launches since
  * the last read; slots: 0 prep, 1 utf8, 2 hash, 3 claim, 4 select, 5 commit,
- * 6 lookup, 7 insert.  b200r_launch_count: kernels enqueued by this library
+ * 6 lookup, 7 insert, 8 classify, 9 push, 10 wait, 11 apply, 12 resolve.
+ * b200r_launch_count: kernels enqueued by this library
  * since load (process-wide).
  * ---------------------------------------------------------------------- */
-#define B200R_PROF_SLOTS 8
+#define B200R_PROF_SLOTS 13
 int b200r_prof_enable(int on);
 int b200r_prof_read(float *ms_out, long long *count_out, int nslots);
 long long b200r_launch_count(void);

@@ -106,7 +106,8 @@ def require_cuda():
     return torch
 
 
-PROF_SLOTS = ("prep", "utf8", "hash", "claim", "select", "commit", "lookup", "insert")
+PROF_SLOTS = ("prep", "utf8", "hash", "claim", "select", "commit", "lookup", "insert",
+              "classify", "push", "wait", "apply", "resolve")
 
 
 def prof_enable(on: bool):
@@ -115,9 +116,9 @@ def prof_enable(on: bool):
 
 def prof_read():
     """{kernel class: (ms, launches)} since the last read (synchronises)."""
-    ms = (C.c_float * 8)()
-    cnt = (C.c_longlong * 8)()
-    check(lib().b200r_prof_read(ms, cnt, 8))
+    ms = (C.c_float * len(PROF_SLOTS))()
+    cnt = (C.c_longlong * len(PROF_SLOTS))()
+    check(lib().b200r_prof_read(ms, cnt, len(PROF_SLOTS)))
     return {k: (float(ms[i]), int(cnt[i])) for i, k in enumerate(PROF_SLOTS)}
 
 

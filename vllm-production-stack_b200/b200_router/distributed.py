@@ -211,6 +211,11 @@ class P2PShardedRouter:
             self.world, self.rank = _sim["world"], _sim["rank"]
         self.trie = GpuHashTrie(cap_log2=cap_log2, device=device)
         self.device = self.trie.device
+        if _sim is None and self.world > 1:           # capacities must agree on all ranks
+            caps = torch.tensor([int(max_requests), int(max_chunks)], dtype=torch.int64,
+                                device=self.device)
+            dist.all_reduce(caps, op=dist.ReduceOp.MAX, group=group)
+            max_requests, max_chunks = (int(x) for x in caps.tolist())
         self.cap = max(int(max_chunks), 64)
         self.rcap = (max(int(max_requests), 4) + 3) // 4 * 4
         lay = (C.c_size_t * 3)()

@@ -44,7 +44,8 @@ int cuda_fail(cudaError_t e, const char *what)
 // Optional per-kernel timing with CUDA events on the launching stream
 // (b200r_prof_enable / b200r_prof_read).  Off by default: the hot path then
 // records nothing.  g_launches counts every kernel this library enqueues.
-enum { PK_PREP = 0, PK_UTF8, PK_HASH, PK_CLAIM, PK_SELECT, PK_COMMIT, PK_LOOKUP, PK_INSERT, PK_COUNT };
+enum { PK_PREP = 0, PK_UTF8, PK_HASH, PK_CLAIM, PK_SELECT, PK_COMMIT, PK_LOOKUP, PK_INSERT,
+       PK_CLASSIFY, PK_PUSH, PK_WAIT, PK_APPLY, PK_RESOLVE, PK_COUNT };
 struct ProfSpan { int kid; cudaEvent_t a, b; };
 static bool g_prof_on = false;
 static std::vector<ProfSpan> g_spans;
@@ -1425,10 +1426,12 @@ int b200r_shard_classify(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d
     if (rc) return rc;
     const int blocks = (int)((n + WARPS_PER_CTA - 1) / WARPS_PER_CTA);
     g_launches += 1;
+    { ProfScope ps__(PK_CLASSIFY, st);
     k_shard_classify<<<blocks, WARPS_PER_CTA * 32, 0, st>>>(
         t->tab, t->cap_log2, hashes, chunk_base, (int)n, max_chunks, avail_mask, slots,
         (ShardRec *)d_records, d_rec_count);
     B200R_LAUNCH_CHECK("k_shard_classify");
+    }
     return B200R_OK;
 }
 
@@ -1485,24 +1488,30 @@ int b200r_shard_commit(b200r_trie *t, const void *d_records_all, const int32_t *
     cudaStream_t st = (cudaStream_t)stream;
     const int64_t rwork = (int64_t)world * rstride;
     g_launches += 1;
+    { ProfScope ps__(PK_RESOLVE, st);
     k_shard_resolve<<<(int)((rwork + 255) / 256), 256, 0, st>>>(t->dev, d_lcd_all, d_meta, world,
                                                               rstride, d_endpoint_all);
     B200R_LAUNCH_CHECK("k_shard_resolve");
+    }
     const int64_t work = (int64_t)world * stride;
     if (work > 0) {
         g_launches += 1;
+        { ProfScope ps__(PK_COMMIT, st);
         k_shard_commit<<<(int)((work + 255) / 256), 256, 0, st>>>(
             t->tab, (const ShardRec *)d_records_all, d_meta, world, stride, d_rec_slot,
             d_endpoint_all, d_lcd_all, rstride);
         B200R_LAUNCH_CHECK("k_shard_commit");
+        }
     }
     if (n > 0) {
         if (!d_endpoint || !d_match_depth || !d_matched) { set_error("null output pointer"); return B200R_E_INVALID; }
         g_launches += 1;
+        { ProfScope ps__(PK_RESOLVE, st);
         k_shard_finish<<<(int)((n + 255) / 256), 256, 0, st>>>(d_endpoint_all, d_lcd_all, (int)n, my_rank,
                                                              rstride, d_endpoint, d_match_depth,
                                                              d_matched);
         B200R_LAUNCH_CHECK("k_shard_finish");
+        }
     }
     return B200R_OK;
 }
@@ -1558,12 +1567,16 @@ int b200r_p2p_classify(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_s
     const int set = (int)(epoch & 1);
     const size_t dst = L.recs_off + (size_t)set * L.rec_set + (size_t)rank * (size_t)cap * sizeof(ShardRec);
     g_launches += 2;
+    { ProfScope ps__(PK_PUSH, st);
     k_p2p_push<<<148 * 4, 256, 0, st>>>((const uint4 *)d_recs_local, d_rec_count, 0, 2,
                                         (const unsigned long long *)d_peer_bases, world, dst);
     B200R_LAUNCH_CHECK("k_p2p_push");
+    }
+    { ProfScope ps__(PK_PUSH, st);
     k_p2p_publish<<<1, P2P_MAX_WORLD, 0, st>>>((const unsigned long long *)d_peer_bases, world, rank,
                                                set, epoch, 0, d_rec_count, (unsigned)n);
     B200R_LAUNCH_CHECK("k_p2p_publish");
+    }
     return B200R_OK;
 }
 
@@ -1586,30 +1599,40 @@ int b200r_p2p_route(b200r_trie *t, int64_t n, int64_t max_chunks, uint32_t flags
     uint8_t *sc = (uint8_t *)d_scratch;
     const unsigned long long tag = (unsigned long long)t->epoch << 32;
     g_launches += 1;
+    { ProfScope ps__(PK_WAIT, st);
     k_p2p_wait_meta<<<1, P2P_MAX_WORLD, 0, st>>>((const P2PFlags *)base, set, epoch, world, rank, dyn, t->dev);
     B200R_LAUNCH_CHECK("k_p2p_wait_meta");
+    }
     const int64_t work = (int64_t)world * cap;
     g_launches += 1;
+    { ProfScope ps__(PK_APPLY, st);
     k_shard_apply<<<(int)((work + 255) / 256), 256, 0, st>>>(
         t->tab, t->hs, t->cap_log2, t->dev, recs_all, dyn->meta, world, cap, rank,
         (const int32_t *)(sc + p.off_chunk_base), tag, (uint32_t *)(sc + p.off_slots), d_rec_slot);
     B200R_LAUNCH_CHECK("k_shard_apply");
+    }
     if (n > 0) {
         g_launches += 1;
+        { ProfScope ps__(PK_SELECT, st);
         k_select<<<(int)((n + 255) / 256), 256, 0, st>>>(
             t->tab, (const int32_t *)(sc + p.off_chunk_base), (int)n, max_chunks,
             (const uint32_t *)(sc + p.off_slots), avail_mask, tag, seed, 0, d_lcd_local,
             d_lcd_local + rcap, d_lcd_local + 2 * rcap, d_matched, 0u, dyn);
         B200R_LAUNCH_CHECK("k_select");
+        }
     }
     const size_t dst = L.lcd_off + (size_t)set * L.lcd_set + (size_t)rank * 3 * (size_t)rcap * 4;
     g_launches += 2;
+    { ProfScope ps__(PK_PUSH, st);
     k_p2p_push<<<148, 256, 0, st>>>((const uint4 *)d_lcd_local, nullptr, 3 * rcap / 4, 1,
                                     (const unsigned long long *)d_peer_bases, world, dst);
     B200R_LAUNCH_CHECK("k_p2p_push(lcd)");
+    }
+    { ProfScope ps__(PK_PUSH, st);
     k_p2p_publish<<<1, P2P_MAX_WORLD, 0, st>>>((const unsigned long long *)d_peer_bases, world, rank,
                                                set, epoch, 1, nullptr, (unsigned)n);
     B200R_LAUNCH_CHECK("k_p2p_publish(lcd)");
+    }
     return B200R_OK;
 }
 
@@ -1628,8 +1651,10 @@ int b200r_p2p_commit(b200r_trie *t, int64_t n, void *d_my_base, int32_t world, i
     P2PDyn *dyn = (P2PDyn *)d_dyn;
     const int32_t *lcd_all = (const int32_t *)(base + L.lcd_off + (size_t)set * L.lcd_set);
     g_launches += 1;
+    { ProfScope ps__(PK_WAIT, st);
     k_p2p_wait_lcd<<<1, P2P_MAX_WORLD, 0, st>>>((const P2PFlags *)base, set, epoch, world, t->dev);
     B200R_LAUNCH_CHECK("k_p2p_wait_lcd");
+    }
     rc = b200r_shard_commit(t, base + L.recs_off + (size_t)set * L.rec_set, dyn->meta, world, cap,
                             d_rec_slot, lcd_all, rcap, rank, n, d_endpoint_all, d_endpoint,
                             d_match_depth, d_matched, stream);
