@@ -324,19 +324,28 @@ def run_b200(args):
     value = n_dec / (ms * 1e-3)
 
     # ---- pass 2: the same W+K batches on a fresh table, with per-kernel CUDA events
-    # around every launch of the K timed steps (roofline of k_hash_chunks, kernel shares)
+    # around every launch of the K timed steps (roofline of k_hash_chunks, kernel shares).
+    # Single stream here (no batch overlap), so that every kernel is timed on its own and
+    # its share of the step is comparable with the serialised ncu launch list.
     del router
     router = new_router()
+    serial = router.trie if world == 1 else router
     seq = 0
     for b in range(W):
-        route_resident(router, b, seq)
+        if world == 1:
+            serial.route(resident[b], avail_mask(b), SEED, seq, out=out)
+        else:
+            route_resident(router, b, seq)
         seq += args.batch * world
     barrier()
     _lib.prof_enable(True)
     verbose = os.environ.get("BENCH_VERBOSE") == "1"
     prof = None
     for b in range(W, nb):
-        route_resident(router, b, seq)
+        if world == 1:
+            serial.route(resident[b], avail_mask(b), SEED, seq, out=out)
+        else:
+            route_resident(router, b, seq)
         seq += args.batch * world
         if verbose:                      # per-step kernel times (synchronises every step)
             one = _lib.prof_read()
