@@ -68,7 +68,12 @@ def workload_config(args, n_gpus):
             "chunk_chars": 128, "endpoints": N_ENDPOINTS,
             "l2": "inputs larger than L2: each step reads a distinct ~%d MB batch"
                   % (args.batch * 2700 // 1000000),
-            "tie_break": "canonical (endpoint-index order, counter-based draw)"}
+            "tie_break": "canonical (endpoint-index order, counter-based draw)",
+            "multi_gpu": None if n_gpus == 1 else
+            {"": "table partitioned by first-chunk hash, NVLink peer-memory exchange",
+             "replicated": "table replicated, NVLink peer-memory exchange of inserted nodes",
+             "nccl": "table replicated, NCCL all-gather of inserted nodes"}[
+                os.environ.get("BENCH_EXCHANGE", "")]}
 
 
 def avail_mask(step_index):
@@ -267,10 +272,14 @@ def run_b200(args):
             pipe = RoutePipeline(GpuHashTrie(cap_log2=cap_log2, device=dev))
             pipe.reserve(args.batch, max_chunks)
             return pipe
-        # multi-GPU: exchange over NVLink peer memory by the library's own kernels;
-        # BENCH_EXCHANGE=nccl selects the NCCL all-gather variant for comparison
-        from b200_router.distributed import P2PShardedRouter, ShardedPrefixRouter
-        cls = ShardedPrefixRouter if os.environ.get("BENCH_EXCHANGE") == "nccl" else P2PShardedRouter
+        # multi-GPU: table partitioned by first-chunk hash, chunk hashes and results shipped
+        # over NVLink peer memory by the library's own kernels (the variant that scales).
+        # BENCH_EXCHANGE=replicated / nccl select the replicated-table variants (peer-memory
+        # or NCCL all-gather exchange of inserted nodes) for comparison.
+        from b200_router.distributed import (P2PShardedRouter, PartitionedPrefixRouter,
+                                             ShardedPrefixRouter)
+        cls = {"nccl": ShardedPrefixRouter, "replicated": P2PShardedRouter}.get(
+            os.environ.get("BENCH_EXCHANGE", ""), PartitionedPrefixRouter)
         return cls(cap_log2=cap_log2, device=dev, max_requests=args.batch, max_chunks=max_chunks)
 
     def barrier():

@@ -274,6 +274,34 @@ int b200r_p2p_commit(b200r_trie *t, int64_t n, void *d_my_base, int32_t world, i
                      int32_t *d_match_depth, uint64_t *d_matched, void *stream);
 
 /* ------------------------------------------------------------------------
+ * Multi-GPU with a PARTITIONED table (scalable variant; no counterpart in the
+ * reference).  A request's whole path hangs under its first chunk, so the
+ * table is split by owner = f(first chunk hash) % world and nothing is
+ * replicated: every rank hashes its own shard, ships the chunk hashes (8 bytes
+ * per 128-byte chunk) of each request to the rank owning it, routes the
+ * requests it owns in global order against its partition and ships the results
+ * back -- all through NVLink peer memory by this library's kernels, no host
+ * round trip.  Results equal sequential routing of the rank-major global batch.
+ * Buffers: one peer-addressable buffer of b200r_part_layout(...)[0] bytes per
+ * rank (zeroed once, before the first batch) and a private work buffer of
+ * [1] bytes (zeroed once); d_peer_bases = u64[world] base addresses.  cap /
+ * rcap = per-rank chunk / request capacity of a batch; epoch = 1, 2, 3, ...
+ * Per batch and rank: b200r_part_send, b200r_part_route, b200r_part_finish.
+ * ---------------------------------------------------------------------- */
+int b200r_part_layout(int32_t world, int64_t cap, int64_t rcap, size_t out[2]);
+int b200r_part_send(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
+                    const int32_t *d_lens, const int32_t *d_nchars, int64_t n, int64_t max_chunks,
+                    uint32_t flags, const uint64_t *d_peer_bases, int32_t world, int32_t rank,
+                    int64_t cap, int64_t rcap, uint32_t epoch, void *d_work, void *d_scratch,
+                    size_t scratch_bytes, void *stream);
+int b200r_part_route(b200r_trie *t, uint64_t avail_mask, uint64_t seed,
+                     const uint64_t *d_peer_bases, void *d_my_base, int32_t world, int32_t rank,
+                     int64_t cap, int64_t rcap, uint32_t epoch, void *d_work, void *stream);
+int b200r_part_finish(b200r_trie *t, int64_t n, void *d_my_base, int32_t world, int32_t rank,
+                      int64_t cap, int64_t rcap, uint32_t epoch, void *d_work, int32_t *d_endpoint,
+                      int32_t *d_match_depth, uint64_t *d_matched, void *stream);
+
+/* ------------------------------------------------------------------------
  * a9  uhashring.HashRing (md5 points, bisect_right + wrap), a7 SessionRouter
  *                                                   routing_logic.py:84-103,217
  * b200r_md5_batch: 128-bit digests as the big-endian integer uhashring uses,

@@ -2,7 +2,7 @@
 """Multi-GPU parity check (test infrastructure; launch with torchrun, one rank per GPU):
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
-        --master-port 29520 scripts/check_multigpu.py [p2p|nccl]
+        --master-port 29520 scripts/check_multigpu.py [part|p2p|nccl]
 
 Routes a C3-shaped trace with availability churn through the sharded router (real NVLink
 peer-memory exchange or NCCL all-gathers) and compares every rank's decisions, and every
@@ -20,25 +20,29 @@ import torch
 import torch.distributed as dist
 
 from b200_router import traces
-from b200_router.distributed import P2PShardedRouter, ShardedPrefixRouter
+from b200_router.distributed import (P2PShardedRouter, PartitionedPrefixRouter,
+                                     ShardedPrefixRouter)
 from b200_router.packing import pack_arrays
 from oracle import coracle
 
 
 def main():
-    mode = sys.argv[1] if len(sys.argv) > 1 else "p2p"
+    mode = sys.argv[1] if len(sys.argv) > 1 else "part"
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
     nb, per = 6, 3000
-    tr = traces.SharedPrefixTrace(n_total=nb * world * per, batch=per, n_sys=8, sys_chars=512,
+    tr = traces.SharedPrefixTrace(n_total=nb * world * per, batch=per, n_sys=32, sys_chars=512,
                                   suffix_lo=100, suffix_hi=400, seed=31)
     shards = [[tr.batch_arrays(b * world + r) for r in range(world)] for b in range(nb)]
     max_chunks = max(int(((s[2] + 127) // 128).sum()) for row in shards for s in row)
     if mode == "p2p":
         router = P2PShardedRouter(cap_log2=20, device=dev, max_requests=per, max_chunks=max_chunks)
+    elif mode == "part":
+        router = PartitionedPrefixRouter(cap_log2=20, device=dev, max_requests=per,
+                                         max_chunks=max_chunks)
     else:
         router = ShardedPrefixRouter(cap_log2=20, device=dev, max_requests=per, max_chunks=max_chunks)
     orc = coracle.TrieOracle()
@@ -56,7 +60,20 @@ def main():
                            (mine[2] == omatched).all())
         seq += off
     router.check_status()
-    ok &= router.dump() == orc.dump()
+    if mode == "part":                      # union of the partitions == the reference trie
+        parts = [None] * world
+        dist.all_gather_object(parts, router.dump())
+        merged = {}
+        for d in parts:
+            for path, m in d.items():
+                if path == ():
+                    merged[path] = merged.get(path, 0) | m
+                else:
+                    ok &= path not in merged
+                    merged[path] = m
+        ok &= merged == orc.dump()
+    else:
+        ok &= router.dump() == orc.dump()
     flag = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if rank == 0:

@@ -179,3 +179,77 @@ def test_p2p_exchange_lockstep_shared_prefix_and_empty_shard():
             shards[1] = traces.pack_strings([])[:3]
         batches.append((avail, shards))
     _check_p2p_lockstep(world, batches, seed=13)
+
+
+def _merge_partitions(dumps):
+    out = {}
+    for d in dumps:
+        for path, m in d.items():
+            if path == ():
+                out[path] = out.get(path, 0) | m
+            else:
+                assert path not in out, "a node lives in two partitions"
+                out[path] = m
+    return out
+
+
+def _check_partitioned_lockstep(world, batches_np, seed):
+    """Partitioned-table path on ONE device, ranks in lock-step (nothing ever spins)."""
+    from b200_router.distributed import PartitionedPrefixRouter as R
+    max_req = max(len(s[1]) for _, shards in batches_np for s in shards)
+    batches = [(a, [pack_arrays(*s, pin=False) for s in shards]) for a, shards in batches_np]
+    max_chunks = max(p.max_chunks for _, shards in batches for p in shards)
+    nbytes = R.symm_bytes_for(world, max_req, max_chunks)
+    bufs = [torch.zeros(nbytes, dtype=torch.uint8, device="cuda:0") for _ in range(world)]
+    ranks = [R(cap_log2=17, device="cuda:0", max_requests=max_req, max_chunks=max_chunks,
+               _sim={"world": world, "rank": r, "buffers": bufs}) for r in range(world)]
+    orc = coracle.TrieOracle()
+    seq = 0
+    owned_total = np.zeros(world, dtype=np.int64)
+    for avail, shards in batches:
+        for r in range(world):
+            ranks[r].phase_send(shards[r])
+        for r in range(world):
+            ranks[r].phase_route(avail, seed)
+        outs = [ranks[r].phase_finish() for r in range(world)]
+        torch.cuda.synchronize()
+        off = 0
+        for r, p in enumerate(shards):
+            buf, st, ln = p.bytes.cpu().numpy(), p.starts.cpu().numpy(), p.lens.cpu().numpy()
+            oep, odepth, omatched = orc.route_batch(buf, st, ln, avail, seed, seq + off)
+            off += p.n
+            ep, depth, matched = outs[r]
+            assert (ep.cpu().numpy() == oep).all(), r
+            assert (depth.cpu().numpy() == odepth).all(), r
+            assert (u64(matched) == omatched).all(), r
+        seq += off
+    for rk in ranks:
+        rk.check_status()
+    assert _merge_partitions([rk.dump() for rk in ranks]) == orc.dump()
+    sizes = [len(rk.dump()) for rk in ranks]
+    assert sum(1 for s in sizes if s > 1) >= min(2, world)      # really spread over partitions
+
+
+def test_partitioned_lockstep_heavy_sharing():
+    for world in (2, 3):
+        batches = []
+        for avail_idx, prompts in traces.sharing_stress(n_batches=5, batch=90, n_endpoints=7,
+                                                        max_depth=6, alphabet=3, seed=90 + world):
+            cuts = np.linspace(0, len(prompts), world + 1).astype(int)
+            shards = [traces.pack_strings(prompts[cuts[r]:cuts[r + 1]])[:3] for r in range(world)]
+            batches.append((sum(1 << i for i in avail_idx), shards))
+        _check_partitioned_lockstep(world, batches, seed=8)
+
+
+def test_partitioned_lockstep_shared_prefix_and_empty_shard():
+    world = 4
+    tr = traces.SharedPrefixTrace(n_total=16000, batch=1000, n_sys=16, sys_chars=512,
+                                  suffix_lo=100, suffix_hi=300, seed=23)
+    batches = []
+    for g in range(4):
+        avail = 0xFF & ~(1 << 1) if g in (1, 2) else 0xFF
+        shards = [tr.batch_arrays(g * world + r) for r in range(world)]
+        if g == 2:
+            shards[1] = traces.pack_strings([])[:3]
+        batches.append((avail, shards))
+    _check_partitioned_lockstep(world, batches, seed=14)

@@ -57,6 +57,11 @@ SIGNATURES = {
                                   _vp, _vp, _vp, _vp, _vp, _vp]),
     "b200r_p2p_commit": (C.c_int, [_vp, _i64, _vp, _i32, _i32, _i64, _i64, _u32, _vp, _vp, _vp, _vp, _vp,
                                    _vp, _vp]),
+    "b200r_part_layout": (C.c_int, [_i32, _i64, _i64, C.POINTER(_sz)]),
+    "b200r_part_send": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _u32, _vp, _i32, _i32, _i64, _i64,
+                                  _u32, _vp, _vp, _sz, _vp]),
+    "b200r_part_route": (C.c_int, [_vp, _u64, _u64, _vp, _vp, _i32, _i32, _i64, _i64, _u32, _vp, _vp]),
+    "b200r_part_finish": (C.c_int, [_vp, _i64, _vp, _i32, _i32, _i64, _i64, _u32, _vp, _vp, _vp, _vp, _vp]),
     "b200r_prof_enable": (C.c_int, [C.c_int]),
     "b200r_prof_read": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_longlong), C.c_int]),
     "b200r_launch_count": (C.c_longlong, []),

@@ -307,3 +307,116 @@ class P2PShardedRouter:
 
     def dump(self):
         return self.trie.dump()
+
+
+class PartitionedPrefixRouter:
+    """Multi-GPU routing with a PARTITIONED table -- the variant that weak-scales.
+
+    A request's whole path hangs under its first chunk, so requests whose first chunk
+    hashes differ never meet in the trie.  Rank owner(first chunk hash) % world holds
+    that subtree; nothing is replicated.  Per batch every rank hashes its own shard,
+    pushes the chunk hashes of each request (8 bytes per 128-byte chunk) to the owning
+    rank over NVLink peer memory, routes the requests it owns -- in global order --
+    against its partition with the ordinary claim / select / commit kernels, and pushes
+    the results back.  No NCCL call and no host read per batch; the tie-break sequence
+    number lives on the device (starts at 0).  Same results as sequential routing of the
+    rank-major global batch; the union of the partitions is the reference trie.
+    (Deviation from north_star's "replicated table": see DESIGN.md 4.)"""
+
+    def __init__(self, cap_log2: int = 22, device=None, max_requests: int = 0, max_chunks: int = 0,
+                 group=None, _sim=None):
+        from .trie import GpuHashTrie
+        L = _lib.lib()
+        if _sim is None:
+            self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        else:
+            self.world, self.rank = _sim["world"], _sim["rank"]
+        self.trie = GpuHashTrie(cap_log2=cap_log2, device=device)
+        self.device = self.trie.device
+        if _sim is None and self.world > 1:
+            caps = torch.tensor([int(max_requests), int(max_chunks)], dtype=torch.int64,
+                                device=self.device)
+            dist.all_reduce(caps, op=dist.ReduceOp.MAX, group=group)
+            max_requests, max_chunks = (int(x) for x in caps.tolist())
+        self.cap, self.rcap = self.capacities(max_requests, max_chunks)
+        lay = (C.c_size_t * 2)()
+        _lib.check(L.b200r_part_layout(self.world, self.cap, self.rcap, lay))
+        self.symm_bytes, work_bytes = int(lay[0]), int(lay[1])
+        if _sim is None:
+            import torch.distributed._symmetric_memory as symm_mem
+            self.symm = symm_mem.empty(self.symm_bytes, dtype=torch.uint8, device=self.device)
+            self.symm.zero_()
+            torch.cuda.synchronize(self.device)
+            g = group if group is not None else dist.group.WORLD
+            self._hdl = symm_mem.rendezvous(self.symm, g.group_name)
+            bases = list(self._hdl.buffer_ptrs)
+            self._hdl.barrier()
+        else:
+            self.symm = _sim["buffers"][self.rank]
+            bases = [b.data_ptr() for b in _sim["buffers"]]
+        self.peer_bases = torch.tensor(bases, dtype=torch.int64, device=self.device)
+        self.work = torch.zeros(work_bytes, dtype=torch.uint8, device=self.device)
+        self.epoch = 0
+        self._shape = None
+
+    @staticmethod
+    def capacities(max_requests: int, max_chunks: int):
+        return max(int(max_chunks), 64), max(int(max_requests), 4)
+
+    @staticmethod
+    def symm_bytes_for(world: int, max_requests: int, max_chunks: int) -> int:
+        cap, rcap = PartitionedPrefixRouter.capacities(max_requests, max_chunks)
+        lay = (C.c_size_t * 2)()
+        _lib.check(_lib.lib().b200r_part_layout(world, cap, rcap, lay))
+        return int(lay[0])
+
+    def phase_send(self, p: PackedPrompts):
+        if p.bytes.device != self.device:
+            p = p.to(self.device)
+        self.epoch += 1
+        flags = _lib.F_ALL_ASCII if p.all_ascii else 0
+        need = _lib.lib().b200r_prefix_route_scratch_bytes(p.n, p.max_chunks, flags)
+        sc = self.trie._scratch_for(need)
+        self._shape = (p.n,)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().b200r_part_send(
+                self.trie._h, _ptr(p.bytes), _ptr(p.starts), _ptr(p.lens), _ptr(p.nchars), p.n,
+                p.max_chunks, flags, _ptr(self.peer_bases), self.world, self.rank, self.cap,
+                self.rcap, self.epoch, _ptr(self.work), _ptr(sc), sc.numel(), _stream()))
+
+    def phase_route(self, avail_mask: int, seed: int):
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().b200r_part_route(
+                self.trie._h, avail_mask & M64, seed & M64, _ptr(self.peer_bases), _ptr(self.symm),
+                self.world, self.rank, self.cap, self.rcap, self.epoch, _ptr(self.work), _stream()))
+
+    def phase_finish(self, out=None):
+        n = self._shape[0]
+        if out is None:
+            out = (torch.empty(max(n, 1), dtype=torch.int32, device=self.device),
+                   torch.empty(max(n, 1), dtype=torch.int32, device=self.device),
+                   torch.empty(max(n, 1), dtype=torch.int64, device=self.device))
+        ep, depth, matched = out
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().b200r_part_finish(
+                self.trie._h, n, _ptr(self.symm), self.world, self.rank, self.cap, self.rcap,
+                self.epoch, _ptr(self.work), _ptr(ep), _ptr(depth), _ptr(matched), _stream()))
+        return ep[:n], depth[:n], matched[:n]
+
+    def route(self, p: PackedPrompts, avail_mask: int, seed: int, seq0: int = 0, out=None):
+        if self.epoch == 0 and seq0 != 0:
+            raise _lib.B200RouterError("PartitionedPrefixRouter keeps the sequence number on the "
+                                       "device; it starts at 0")
+        self.phase_send(p)
+        self.phase_route(avail_mask, seed)
+        return self.phase_finish(out)
+
+    def check_status(self, count_nodes=False):
+        s = self.trie.check_status(count_nodes)
+        if s["status"] & _lib.S_PEER_TIMEOUT:
+            raise _lib.B200RouterError("a peer GPU did not deliver its part of a batch in time")
+        return s
+
+    def dump(self):
+        """This rank's partition; the union over ranks (root masks OR-ed) is the whole trie."""
+        return self.trie.dump()

@@ -94,9 +94,10 @@ __device__ __forceinline__ int block_sum_1024(int v, int *s_red)
 
 __global__ void __launch_bounds__(PREP_BLOCK)
 k_prep_sums(const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars, int n, int cc,
-            int32_t *__restrict__ block_sums)
+            int32_t *__restrict__ block_sums, const int32_t *__restrict__ n_dev)
 {
     __shared__ int s_red[32];
+    if (n_dev) n = *n_dev;          // batch size known only on the device (partitioned multi-GPU)
     int i = blockIdx.x * PREP_BLOCK + threadIdx.x;
     int c = (i < n) ? chunks_of(lens, nchars, i, cc) : 0;
     int tot = block_sum_1024(c, s_red);
@@ -108,10 +109,14 @@ k_prep_scan(const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars
             const int32_t *__restrict__ block_sums, int32_t *__restrict__ chunk_base,
             int32_t *__restrict__ tile_first, int64_t max_chunks, TrieDev *dev,
             const uint8_t *__restrict__ bytes, const int64_t *__restrict__ starts,
-            uint64_t *__restrict__ hashes)
+            uint64_t *__restrict__ hashes, const int32_t *__restrict__ n_dev)
 {
     __shared__ int s_red[32];
     __shared__ int s_wsum[32];
+    if (n_dev) {
+        n = *n_dev;
+        if (n == 0 && blockIdx.x == 0 && threadIdx.x == 0) chunk_base[0] = 0;
+    }
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     // offset of this block = sum of the sums of all earlier blocks
     int part = 0;
@@ -520,13 +525,12 @@ struct P2PDyn {
     int32_t meta[2 * P2P_MAX_WORLD]; // {record count, shard size} of every rank, current batch
 };
 
-__global__ void __launch_bounds__(WARPS_PER_CTA * 32)
-k_claim(Entry *__restrict__ tab, uint64_t *__restrict__ hs, int cap_log2, TrieDev *dev,
-        const uint64_t *__restrict__ hashes, const int32_t *__restrict__ chunk_base, int n,
-        int64_t max_chunks, uint64_t avail, unsigned long long tag, uint32_t *__restrict__ slots)
+__device__ __forceinline__ void
+claim_request(int i, int lane, Entry *__restrict__ tab, uint64_t *__restrict__ hs, int cap_log2,
+              TrieDev *dev, const uint64_t *__restrict__ hashes,
+              const int32_t *__restrict__ chunk_base, int64_t max_chunks, uint64_t avail,
+              unsigned long long tag, uint32_t *__restrict__ slots)
 {
-    const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    if (i >= n) return;
     const ReqSpan sp = req_span(chunk_base, i, max_chunks);
     Key carry = { KROOT1, KROOT2 };
     for (int blk = 0; blk * 32 < sp.C; blk++) {
@@ -562,24 +566,32 @@ k_claim(Entry *__restrict__ tab, uint64_t *__restrict__ hs, int cap_log2, TrieDe
     }
 }
 
+__global__ void __launch_bounds__(WARPS_PER_CTA * 32)
+k_claim(Entry *__restrict__ tab, uint64_t *__restrict__ hs, int cap_log2, TrieDev *dev,
+        const uint64_t *__restrict__ hashes, const int32_t *__restrict__ chunk_base, int n,
+        int64_t max_chunks, uint64_t avail, unsigned long long tag, uint32_t *__restrict__ slots,
+        const int32_t *__restrict__ n_dev)
+{
+    // grid-stride over requests: with n_dev the batch size is only known on the device and
+    // the grid is an estimate
+    const int lane = threadIdx.x & 31;
+    if (n_dev) n = *n_dev;
+    for (int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < n; i += (gridDim.x * blockDim.x) >> 5)
+        claim_request(i, lane, tab, hs, cap_log2, dev, hashes, chunk_base, max_chunks, avail, tag, slots);
+}
+
 // a5 step 2: deepest node usable by request i = last depth d with
 //   PREOK(node) or first(node) < i      (monotone in d)
 // If that node was usable before the batch (or depth 0) the request is a root
 // and draws from its candidate set; else it follows the request that touched
 // the node first.
-__global__ void __launch_bounds__(256)
-k_select(const Entry *__restrict__ tab, const int32_t *__restrict__ chunk_base, int n, int64_t max_chunks,
-         const uint32_t *__restrict__ slots, uint64_t avail, unsigned long long tag, uint64_t seed,
-         uint64_t seq0, int32_t *__restrict__ leader, int32_t *__restrict__ choice,
-         int32_t *__restrict__ depth_out, uint64_t *__restrict__ matched_out, uint32_t req_off,
-         const P2PDyn *__restrict__ dyn)
+__device__ __forceinline__ void
+select_request(int i, const Entry *__restrict__ tab, const int32_t *__restrict__ chunk_base,
+               int64_t max_chunks, const uint32_t *__restrict__ slots, uint64_t avail,
+               unsigned long long tag, uint64_t seed, uint64_t seq0, int32_t *__restrict__ leader,
+               int32_t *__restrict__ choice, int32_t *__restrict__ depth_out,
+               uint64_t *__restrict__ matched_out, uint32_t req_off, const uint32_t *__restrict__ pos)
 {
-    if (dyn) { req_off = dyn->my_off; seq0 = dyn->seq_base; }   // peer-exchange path: values live on the device
-    // one thread per request: independent dependent-load chains, 32 per warp in flight.
-    // req_off = position of request 0 of this shard in the global (rank-major) order;
-    // 0 on a single GPU.  `first` words, leaders and the tie-break counter are global.
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
     const ReqSpan sp = req_span(chunk_base, i, max_chunks);
     const uint32_t *sl = slots + sp.b0;
     int dstar = 0;
@@ -612,7 +624,7 @@ k_select(const Entry *__restrict__ tab, const int32_t *__restrict__ chunk_base, 
         const uint64_t cand = (dstar == 0) ? avail : (tab[star_slot & ~PREOK_BIT].mask & avail);
         const int cnt = __popcll(cand);
         leader[i] = -1;
-        choice[i] = cnt ? nth_set_bit(cand, pick(seed, seq0 + req_off + (uint64_t)i, (uint32_t)cnt)) : -1;
+        choice[i] = cnt ? nth_set_bit(cand, pick(seed, seq0 + (pos ? (uint64_t)pos[i] : req_off + (uint64_t)i), (uint32_t)cnt)) : -1;
         matched_out[i] = cand;
     } else {
         leader[i] = (int32_t)star_first;
@@ -620,17 +632,36 @@ k_select(const Entry *__restrict__ tab, const int32_t *__restrict__ chunk_base, 
     }
 }
 
+__global__ void __launch_bounds__(256)
+k_select(const Entry *__restrict__ tab, const int32_t *__restrict__ chunk_base, int n, int64_t max_chunks,
+         const uint32_t *__restrict__ slots, uint64_t avail, unsigned long long tag, uint64_t seed,
+         uint64_t seq0, int32_t *__restrict__ leader, int32_t *__restrict__ choice,
+         int32_t *__restrict__ depth_out, uint64_t *__restrict__ matched_out, uint32_t req_off,
+         const P2PDyn *__restrict__ dyn, const uint32_t *__restrict__ pos,
+         const int32_t *__restrict__ n_dev)
+{
+    // one thread per request: independent dependent-load chains, 32 per warp in flight.
+    // req_off = position of request 0 of this shard in the global (rank-major) order (0 on a
+    // single GPU); `first` words, leaders and the tie-break counter are global.  With `dyn`
+    // (peer-exchange paths) req_off and seq0 live on the device; with `pos` (partitioned
+    // path) pos[i] is the request's global position for the tie-break counter only.
+    if (n_dev) n = *n_dev;
+    if (dyn) { req_off = dyn->my_off; seq0 = dyn->seq_base; }
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        select_request(i, tab, chunk_base, max_chunks, slots, avail, tag, seed, seq0, leader, choice,
+                       depth_out, matched_out, req_off, pos);
+}
+
 // a5 step 3: followers take their (transitive) leader's endpoint; every
 // request ORs its endpoint into the nodes below its match depth -- exactly the
 // nodes it was the first to touch, so no other request writes them.
-__global__ void __launch_bounds__(256)
-k_commit(Entry *__restrict__ tab, TrieDev *dev, const int32_t *__restrict__ chunk_base, int n,
-         int64_t max_chunks, const uint32_t *__restrict__ slots, const int32_t *__restrict__ leader,
-         const int32_t *__restrict__ choice, const int32_t *__restrict__ depth,
-         int32_t *__restrict__ endpoint, uint64_t *__restrict__ matched_out)
+__device__ __forceinline__ void
+commit_request(int i, Entry *__restrict__ tab, TrieDev *dev, const int32_t *__restrict__ chunk_base,
+               int64_t max_chunks, const uint32_t *__restrict__ slots,
+               const int32_t *__restrict__ leader, const int32_t *__restrict__ choice,
+               const int32_t *__restrict__ depth, int32_t *__restrict__ endpoint,
+               uint64_t *__restrict__ matched_out)
 {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
     int j = i, l;
     while ((l = leader[j]) >= 0) j = l;          // chains strictly decrease in index
     const int e = choice[j];
@@ -644,6 +675,19 @@ k_commit(Entry *__restrict__ tab, TrieDev *dev, const int32_t *__restrict__ chun
         const uint32_t x = slots[sp.b0 + d];
         if (x != SLOT_NONE) atomicOr((unsigned long long *)&tab[x & ~PREOK_BIT].mask, bit);
     }
+}
+
+__global__ void __launch_bounds__(256)
+k_commit(Entry *__restrict__ tab, TrieDev *dev, const int32_t *__restrict__ chunk_base, int n,
+         int64_t max_chunks, const uint32_t *__restrict__ slots, const int32_t *__restrict__ leader,
+         const int32_t *__restrict__ choice, const int32_t *__restrict__ depth,
+         int32_t *__restrict__ endpoint, uint64_t *__restrict__ matched_out,
+         const int32_t *__restrict__ n_dev)
+{
+    if (n_dev) n = *n_dev;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        commit_request(i, tab, dev, chunk_base, max_chunks, slots, leader, choice, depth, endpoint,
+                       matched_out);
 }
 
 // =========================================================================
@@ -896,6 +940,251 @@ __global__ void k_p2p_wait_lcd(const P2PFlags *__restrict__ mine, int set, unsig
 
 __global__ void k_p2p_advance(P2PDyn *dyn) { dyn->seq_base += dyn->total_n; }
 
+// =========================================================================
+// Multi-GPU, PARTITIONED table (the scalable variant; SURVEY.md 8e fallback).
+// A request's whole path hangs under its first chunk, so requests with
+// different first-chunk hashes never meet in the trie.  The table is therefore
+// partitioned by owner(first chunk hash) = mix(h0) % world and nothing is
+// replicated: per batch every rank
+//   send    hashes its own shard (as before) and pushes, per owner, the chunk
+//           hashes + {local index, chunk count} of the requests that owner
+//           holds, order preserved, straight into the owner's buffer (NVLink
+//           peer stores, ~6 % of the prompt bytes), then publishes flags;
+//   route   waits for all sources, concatenates what it received in rank
+//           order (= global order of the requests it owns), runs the ordinary
+//           claim / select / commit on that batch against ITS partition, and
+//           pushes {endpoint, depth, candidates} back to the sources;
+//   finish  waits for all owners and scatters the results to request order.
+// Sequential equivalence holds per partition and partitions are independent;
+// the tie-break counter uses the request's position in the global order.
+// Per-GPU work no longer grows with the number of GPUs.
+// =========================================================================
+struct PartFlags {
+    unsigned long long in_req[2][P2P_MAX_WORLD], in_chunk[2][P2P_MAX_WORLD], in_n[2][P2P_MAX_WORLD],
+        res[2][P2P_MAX_WORLD];
+};
+static_assert(sizeof(PartFlags) <= 4096, "flag block");
+struct PartRes { int32_t ep, depth; uint64_t matched; };
+struct PartDyn {
+    P2PDyn base;                              // seq_base, total_n (my_off stays 0)
+    int32_t n_owned, c_owned;
+    uint32_t reqbase[P2P_MAX_WORLD + 1], chunkbase[P2P_MAX_WORLD + 1], off[P2P_MAX_WORLD + 1];
+};
+
+__device__ __forceinline__ int part_owner(const uint64_t *hashes, int b, int C, int world)
+{
+    if (C == 0) return 0;                     // empty prompt: touches only a root
+    uint64_t x = hashes[b] * 0x9E3779B97F4A7C15ULL;
+    return (int)((x >> 33) % (uint64_t)world);
+}
+
+constexpr int PART_BLOCK = 256;
+
+// per block of 256 requests: how many requests / chunks go to each owner
+__global__ void __launch_bounds__(PART_BLOCK)
+k_part_count(const int32_t *__restrict__ chunk_base, const uint64_t *__restrict__ hashes, int n,
+             int world, int32_t *__restrict__ blk_cnt)
+{
+    __shared__ int s_cnt[2 * P2P_MAX_WORLD];
+    for (int k = threadIdx.x; k < 2 * world; k += PART_BLOCK) s_cnt[k] = 0;
+    __syncthreads();
+    const int i = blockIdx.x * PART_BLOCK + threadIdx.x;
+    if (i < n) {
+        const int b = chunk_base[i], C = chunk_base[i + 1] - b;
+        const int o = part_owner(hashes, b, C, world);
+        atomicAdd(&s_cnt[2 * o], 1);
+        atomicAdd(&s_cnt[2 * o + 1], C);
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < 2 * world; k += PART_BLOCK)
+        blk_cnt[(size_t)blockIdx.x * 2 * world + k] = s_cnt[k];
+}
+
+// exclusive scan over the blocks, per owner (one thread per owner and kind)
+__global__ void k_part_scan(const int32_t *__restrict__ blk_cnt, int nblk, int world,
+                            int32_t *__restrict__ blk_off, int32_t *__restrict__ totals)
+{
+    const int k = threadIdx.x;
+    if (k >= 2 * world) return;
+    int run = 0;
+    for (int b = 0; b < nblk; b++) {
+        blk_off[(size_t)b * 2 * world + k] = run;
+        run += blk_cnt[(size_t)b * 2 * world + k];
+    }
+    totals[k] = run;
+}
+
+// order-preserving compaction per owner + push into the owners' buffers
+__global__ void __launch_bounds__(PART_BLOCK)
+k_part_push(const int32_t *__restrict__ chunk_base, const uint64_t *__restrict__ hashes, int n,
+            int world, int my_rank, const int32_t *__restrict__ blk_off,
+            const unsigned long long *__restrict__ peer_bases, size_t hash_off, size_t info_off,
+            int64_t cap, int64_t rcap, uint32_t *__restrict__ dest_slot)
+{
+    __shared__ int s_w[PART_BLOCK / 32][2 * P2P_MAX_WORLD];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int i = blockIdx.x * PART_BLOCK + threadIdx.x;
+    int b = 0, C = 0, o = -1;
+    if (i < n) {
+        b = chunk_base[i];
+        C = chunk_base[i + 1] - b;
+        o = part_owner(hashes, b, C, world);
+    }
+    // rank of this request / its chunks among the warp's earlier requests of the same owner
+    int rreq = 0, rchunk = 0;
+    for (int d = 0; d < world; d++) {
+        const unsigned m = __ballot_sync(0xffffffffu, o == d);
+        int v = (o == d) ? C : 0, inc = v;
+        for (int sft = 1; sft < 32; sft <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, sft);
+            if (lane >= sft) inc += t;
+        }
+        if (o == d) { rreq = __popc(m & ((1u << lane) - 1)); rchunk = inc - v; }
+        if (lane == 31) { s_w[w][2 * d] = __popc(m); s_w[w][2 * d + 1] = inc; }
+    }
+    __syncthreads();
+    if (o >= 0) {
+        int breq = blk_off[(size_t)blockIdx.x * 2 * world + 2 * o];
+        int bchunk = blk_off[(size_t)blockIdx.x * 2 * world + 2 * o + 1];
+        for (int k = 0; k < w; k++) { breq += s_w[k][2 * o]; bchunk += s_w[k][2 * o + 1]; }
+        rreq += breq;
+        rchunk += bchunk;
+        dest_slot[i] = ((uint32_t)o << 24) | (uint32_t)rreq;
+        unsigned long long *info = (unsigned long long *)(uintptr_t)(peer_bases[o] + info_off) +
+                                   (size_t)my_rank * rcap + rreq;
+        *info = (unsigned long long)(uint32_t)i | ((unsigned long long)(uint32_t)C << 32);
+    }
+    // hashes: the warp copies each lane's request cooperatively (coalesced 8-byte stores)
+    for (int src = 0; src < 32; src++) {
+        const int so = __shfl_sync(0xffffffffu, o, src);
+        if (so < 0) continue;
+        const int sb = __shfl_sync(0xffffffffu, b, src), sC = __shfl_sync(0xffffffffu, C, src);
+        const int sdst = __shfl_sync(0xffffffffu, rchunk, src);
+        uint64_t *dst = (uint64_t *)(uintptr_t)(peer_bases[so] + hash_off) + (size_t)my_rank * cap + sdst;
+        for (int c = lane; c < sC; c += 32) dst[c] = hashes[sb + c];
+    }
+    __threadfence_system();
+}
+
+__global__ void k_part_publish_in(const unsigned long long *__restrict__ peer_bases, int world,
+                                  int my_rank, int set, unsigned long long epoch,
+                                  const int32_t *__restrict__ totals, unsigned int n)
+{
+    const int d = threadIdx.x;
+    if (d >= world) return;
+    PartFlags *f = (PartFlags *)(uintptr_t)peer_bases[d];
+    __threadfence_system();
+    *(volatile unsigned long long *)&f->in_n[set][my_rank] = (epoch << 32) | n;
+    *(volatile unsigned long long *)&f->in_chunk[set][my_rank] = (epoch << 32) | (uint32_t)totals[2 * d + 1];
+    *(volatile unsigned long long *)&f->in_req[set][my_rank] = (epoch << 32) | (uint32_t)totals[2 * d];
+    __threadfence_system();
+}
+
+__global__ void k_part_wait_meta(const PartFlags *__restrict__ mine, int set, unsigned long long epoch,
+                                 int world, PartDyn *dyn, TrieDev *dev)
+{
+    __shared__ uint32_t s_req[P2P_MAX_WORLD], s_chunk[P2P_MAX_WORLD], s_n[P2P_MAX_WORLD];
+    const int q = threadIdx.x;
+    if (q < world) {
+        unsigned long long a = 0, b = 0, c = 0;
+        const bool ok = p2p_spin(&mine->in_req[set][q], epoch, &a) &&
+                        p2p_spin(&mine->in_chunk[set][q], epoch, &b) &&
+                        p2p_spin(&mine->in_n[set][q], epoch, &c);
+        if (!ok) atomicOr(&dev->status, B200R_S_PEER_TIMEOUT);
+        s_req[q] = ok ? (uint32_t)a : 0; s_chunk[q] = ok ? (uint32_t)b : 0; s_n[q] = ok ? (uint32_t)c : 0;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t r = 0, c = 0, o = 0;
+        for (int k = 0; k < world; k++) {
+            dyn->reqbase[k] = r; dyn->chunkbase[k] = c; dyn->off[k] = o;
+            r += s_req[k]; c += s_chunk[k]; o += s_n[k];
+        }
+        dyn->reqbase[world] = r; dyn->chunkbase[world] = c; dyn->off[world] = o;
+        dyn->n_owned = (int32_t)r; dyn->c_owned = (int32_t)c;
+        dyn->base.my_off = 0; dyn->base.total_n = o;
+    }
+    __threadfence_system();
+}
+
+// concatenate what the sources sent, in rank order
+__global__ void k_part_gather(const uint8_t *__restrict__ my_base, size_t hash_off, size_t info_off,
+                              int64_t cap, int64_t rcap, int world, const PartDyn *__restrict__ dyn,
+                              int32_t *__restrict__ c_owned, uint32_t *__restrict__ pos_owned,
+                              uint64_t *__restrict__ hashes_owned)
+{
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t step = (int64_t)gridDim.x * blockDim.x;
+    const unsigned long long *info = (const unsigned long long *)(my_base + info_off);
+    const uint64_t *hin = (const uint64_t *)(my_base + hash_off);
+    for (int64_t j = tid; j < dyn->n_owned; j += step) {
+        int q = 0;
+        while (q + 1 < world && j >= dyn->reqbase[q + 1]) q++;
+        const unsigned long long v = info[(size_t)q * rcap + (j - dyn->reqbase[q])];
+        c_owned[j] = (int32_t)(v >> 32);
+        pos_owned[j] = dyn->off[q] + (uint32_t)v;
+    }
+    for (int64_t x = tid; x < dyn->c_owned; x += step) {
+        int q = 0;
+        while (q + 1 < world && x >= dyn->chunkbase[q + 1]) q++;
+        hashes_owned[x] = hin[(size_t)q * cap + (x - dyn->chunkbase[q])];
+    }
+}
+
+__global__ void k_part_push_results(const PartDyn *__restrict__ dyn, int world, int my_rank,
+                                    const int32_t *__restrict__ ep, const int32_t *__restrict__ depth,
+                                    const uint64_t *__restrict__ matched,
+                                    const unsigned long long *__restrict__ peer_bases,
+                                    size_t res_off, int64_t rcap)
+{
+    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < dyn->n_owned;
+         j += (int64_t)gridDim.x * blockDim.x) {
+        int q = 0;
+        while (q + 1 < world && j >= dyn->reqbase[q + 1]) q++;
+        PartRes r;
+        r.ep = ep[j]; r.depth = depth[j]; r.matched = matched[j];
+        ((PartRes *)(uintptr_t)(peer_bases[q] + res_off))[(size_t)my_rank * rcap + (j - dyn->reqbase[q])] = r;
+    }
+    __threadfence_system();
+}
+
+__global__ void k_part_publish_res(const unsigned long long *__restrict__ peer_bases, int world,
+                                   int my_rank, int set, unsigned long long epoch,
+                                   const PartDyn *__restrict__ dyn)
+{
+    const int q = threadIdx.x;
+    if (q >= world) return;
+    PartFlags *f = (PartFlags *)(uintptr_t)peer_bases[q];
+    __threadfence_system();
+    *(volatile unsigned long long *)&f->res[set][my_rank] =
+        (epoch << 32) | (dyn->reqbase[q + 1] - dyn->reqbase[q]);
+    __threadfence_system();
+}
+
+__global__ void k_part_wait_res(const PartFlags *__restrict__ mine, int set, unsigned long long epoch,
+                                int world, TrieDev *dev, PartDyn *dyn)
+{
+    const int q = threadIdx.x;
+    if (q < world) {
+        unsigned long long v;
+        if (!p2p_spin(&mine->res[set][q], epoch, &v)) atomicOr(&dev->status, B200R_S_PEER_TIMEOUT);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) dyn->base.seq_base += dyn->base.total_n;   // next batch's request 0
+    __threadfence_system();
+}
+
+__global__ void k_part_scatter(const uint32_t *__restrict__ dest_slot, const uint8_t *__restrict__ my_base,
+                               size_t res_off, int64_t rcap, int n, int32_t *__restrict__ endpoint,
+                               int32_t *__restrict__ depth, uint64_t *__restrict__ matched)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t ds = dest_slot[i];
+    const PartRes r = ((const PartRes *)(my_base + res_off))[(size_t)(ds >> 24) * rcap + (ds & 0xFFFFFFu)];
+    endpoint[i] = r.ep; depth[i] = r.depth; matched[i] = r.matched;
+}
+
 // ------------------------------------------------------------ dump / restore
 __global__ void k_count_nodes(const Entry *__restrict__ tab, int64_t cap, TrieDev *dev)
 {
@@ -1029,12 +1318,12 @@ static int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const in
     }
     const int nblk = (int)((n + PREP_BLOCK - 1) / PREP_BLOCK);
     { ProfScope ps__(PK_PREP, st); g_launches += 1;
-    k_prep_sums<<<nblk, PREP_BLOCK, 0, st>>>(d_lens, d_nchars, (int)n, cc, block_sums);
+    k_prep_sums<<<nblk, PREP_BLOCK, 0, st>>>(d_lens, d_nchars, (int)n, cc, block_sums, nullptr);
     B200R_LAUNCH_CHECK("k_prep_sums");
     }
     { ProfScope ps__(PK_PREP, st); g_launches += 1;
     k_prep_scan<<<nblk, PREP_BLOCK, 0, st>>>(d_lens, d_nchars, (int)n, cc, block_sums, d_chunk_base,
-                                             tile_first, max_chunks, dev, d_bytes, d_starts, d_hashes);
+                                             tile_first, max_chunks, dev, d_bytes, d_starts, d_hashes, nullptr);
     B200R_LAUNCH_CHECK("k_prep_scan");
     }
     if (!ascii) {
@@ -1364,18 +1653,18 @@ int b200r_prefix_route_stage(b200r_trie *t, int64_t n, int64_t max_chunks, uint3
     const int tblocks = (int)((n + 255) / 256);
     { ProfScope ps__(PK_CLAIM, st); g_launches += 1;
     k_claim<<<blocks, thr, 0, st>>>(t->tab, t->hs, t->cap_log2, t->dev, hashes, chunk_base,
-                                    (int)n, max_chunks, avail_mask, tag, slots);
+                                    (int)n, max_chunks, avail_mask, tag, slots, nullptr);
     B200R_LAUNCH_CHECK("k_claim");
     }
     { ProfScope ps__(PK_SELECT, st); g_launches += 1;
     k_select<<<tblocks, 256, 0, st>>>(t->tab, chunk_base, (int)n, max_chunks, slots,
                                      avail_mask, tag, seed, seq0, leader, choice, d_match_depth,
-                                     d_matched_mask, 0u, nullptr);
+                                     d_matched_mask, 0u, nullptr, nullptr, nullptr);
     B200R_LAUNCH_CHECK("k_select");
     }
     { ProfScope ps__(PK_COMMIT, st); g_launches += 1;
     k_commit<<<tblocks, 256, 0, st>>>(t->tab, t->dev, chunk_base, (int)n, max_chunks, slots, leader,
-                                     choice, d_match_depth, d_endpoint, d_matched_mask);
+                                     choice, d_match_depth, d_endpoint, d_matched_mask, nullptr);
     B200R_LAUNCH_CHECK("k_commit");
     }
     return B200R_OK;
@@ -1471,7 +1760,7 @@ int b200r_shard_select(b200r_trie *t, int64_t n, int64_t max_chunks, uint32_t fl
     k_select<<<(int)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
         t->tab, (const int32_t *)(sc + p.off_chunk_base), (int)n, max_chunks,
         (const uint32_t *)(sc + p.off_slots), avail_mask, tag, seed, seq0, d_leader, d_choice,
-        d_depth, d_matched, req_off, nullptr);
+        d_depth, d_matched, req_off, nullptr, nullptr, nullptr);
     B200R_LAUNCH_CHECK("k_select");
     return B200R_OK;
 }
@@ -1617,7 +1906,7 @@ int b200r_p2p_route(b200r_trie *t, int64_t n, int64_t max_chunks, uint32_t flags
         k_select<<<(int)((n + 255) / 256), 256, 0, st>>>(
             t->tab, (const int32_t *)(sc + p.off_chunk_base), (int)n, max_chunks,
             (const uint32_t *)(sc + p.off_slots), avail_mask, tag, seed, 0, d_lcd_local,
-            d_lcd_local + rcap, d_lcd_local + 2 * rcap, d_matched, 0u, dyn);
+            d_lcd_local + rcap, d_lcd_local + 2 * rcap, d_matched, 0u, dyn, nullptr, nullptr);
         B200R_LAUNCH_CHECK("k_select");
         }
     }
@@ -1662,6 +1951,209 @@ int b200r_p2p_commit(b200r_trie *t, int64_t n, void *d_my_base, int32_t world, i
     g_launches += 1;
     k_p2p_advance<<<1, 1, 0, st>>>(dyn);
     B200R_LAUNCH_CHECK("k_p2p_advance");
+    return B200R_OK;
+}
+
+// ------------------------------------------------------ multi-GPU, partitioned
+struct PartLayout {
+    size_t symm_total, hash_off, info_off, res_off, hash_set, info_set, res_set;
+    // local work buffer
+    size_t work_total, w_dyn, w_blk_cnt, w_blk_off, w_totals, w_dest_slot, w_c_owned, w_pos_owned,
+        w_ep, w_depth, w_matched, w_plan;
+    int64_t n_max, c_max;
+    int nblk_max;
+};
+
+static PartLayout part_layout(int world, int64_t cap, int64_t rcap)
+{
+    PartLayout L;
+    L.hash_off = 4096;
+    L.hash_set = (size_t)world * cap * 8;
+    L.info_off = L.hash_off + 2 * L.hash_set;
+    L.info_set = (size_t)world * rcap * 8;
+    L.res_off = L.info_off + 2 * L.info_set;
+    L.res_set = (size_t)world * rcap * sizeof(PartRes);
+    L.symm_total = align_up(L.res_off + 2 * L.res_set);
+    L.n_max = (int64_t)world * rcap;
+    L.c_max = (int64_t)world * cap;
+    L.nblk_max = (int)((rcap + PART_BLOCK - 1) / PART_BLOCK);
+    size_t o = 0;
+    L.w_dyn = o;       o += align_up(sizeof(PartDyn));
+    L.w_blk_cnt = o;   o += align_up((size_t)L.nblk_max * 2 * world * 4);
+    L.w_blk_off = o;   o += align_up((size_t)L.nblk_max * 2 * world * 4);
+    L.w_totals = o;    o += align_up((size_t)2 * world * 4);
+    L.w_dest_slot = o; o += align_up((size_t)rcap * 4);
+    L.w_c_owned = o;   o += align_up((size_t)L.n_max * 4);
+    L.w_pos_owned = o; o += align_up((size_t)L.n_max * 4);
+    L.w_ep = o;        o += align_up((size_t)L.n_max * 4);
+    L.w_depth = o;     o += align_up((size_t)L.n_max * 4);
+    L.w_matched = o;   o += align_up((size_t)L.n_max * 8);
+    L.w_plan = o;      o += make_plan(L.n_max, L.c_max, B200R_F_ALL_ASCII, true).total;
+    L.work_total = o + 256;
+    return L;
+}
+
+static int part_check(int world, int rank, int64_t cap, int64_t rcap, const void *a, const void *b)
+{
+    if (world <= 0 || world > P2P_MAX_WORLD || rank < 0 || rank >= world || cap <= 0 || rcap <= 0 ||
+        rcap >= (1 << 24) || (int64_t)world * cap > 0x7fffffff - 4096 || !a || !b) {
+        set_error("partitioned routing: need 1 <= world <= %d, 0 <= rank < world, 0 < rcap < 2^24, "
+                  "world * cap < 2^31, non-null buffers", P2P_MAX_WORLD);
+        return B200R_E_INVALID;
+    }
+    return B200R_OK;
+}
+
+int b200r_part_layout(int32_t world, int64_t cap, int64_t rcap, size_t out[2])
+{
+    if (world <= 0 || world > P2P_MAX_WORLD || cap <= 0 || rcap <= 0 || !out) { set_error("b200r_part_layout: bad argument"); return B200R_E_INVALID; }
+    const PartLayout L = part_layout(world, cap, rcap);
+    out[0] = L.symm_total; out[1] = L.work_total;
+    return B200R_OK;
+}
+
+int b200r_part_send(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
+                    const int32_t *d_lens, const int32_t *d_nchars, int64_t n, int64_t max_chunks,
+                    uint32_t flags, const uint64_t *d_peer_bases, int32_t world, int32_t rank,
+                    int64_t cap, int64_t rcap, uint32_t epoch, void *d_work, void *d_scratch,
+                    size_t scratch_bytes, void *stream)
+{
+    int rc = part_check(world, rank, cap, rcap, d_peer_bases, d_work);
+    if (rc) return rc;
+    if (max_chunks > cap || n > rcap) { set_error("partitioned routing: batch (n=%lld, max_chunks=%lld) exceeds the exchange capacity (rcap=%lld, cap=%lld)", (long long)n, (long long)max_chunks, (long long)rcap, (long long)cap); return B200R_E_INVALID; }
+    rc = b200r_prefix_hash_stage(t, d_bytes, d_starts, d_lens, d_nchars, n, max_chunks, flags,
+                                 d_scratch, scratch_bytes, stream);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const PartLayout L = part_layout(world, cap, rcap);
+    const Plan p = make_plan(n, max_chunks, flags, true);
+    uint8_t *sc = (uint8_t *)d_scratch, *wk = (uint8_t *)d_work;
+    const int32_t *chunk_base = (const int32_t *)(sc + p.off_chunk_base);
+    const uint64_t *hashes = (const uint64_t *)(sc + p.off_hashes);
+    int32_t *blk_cnt = (int32_t *)(wk + L.w_blk_cnt), *blk_off = (int32_t *)(wk + L.w_blk_off);
+    int32_t *totals = (int32_t *)(wk + L.w_totals);
+    const int set = (int)(epoch & 1);
+    const int nblk = (int)((n + PART_BLOCK - 1) / PART_BLOCK);
+    ProfScope ps__(PK_PUSH, st);
+    if (nblk > 0) {
+        g_launches += 3;
+        k_part_count<<<nblk, PART_BLOCK, 0, st>>>(chunk_base, hashes, (int)n, world, blk_cnt);
+        B200R_LAUNCH_CHECK("k_part_count");
+        k_part_scan<<<1, 2 * P2P_MAX_WORLD, 0, st>>>(blk_cnt, nblk, world, blk_off, totals);
+        B200R_LAUNCH_CHECK("k_part_scan");
+        k_part_push<<<nblk, PART_BLOCK, 0, st>>>(
+            chunk_base, hashes, (int)n, world, rank, blk_off, (const unsigned long long *)d_peer_bases,
+            L.hash_off + (size_t)set * L.hash_set, L.info_off + (size_t)set * L.info_set, cap, rcap,
+            (uint32_t *)(wk + L.w_dest_slot));
+        B200R_LAUNCH_CHECK("k_part_push");
+    } else {
+        B200R_CUDA(cudaMemsetAsync(totals, 0, (size_t)2 * world * 4, st));
+    }
+    g_launches += 1;
+    k_part_publish_in<<<1, P2P_MAX_WORLD, 0, st>>>((const unsigned long long *)d_peer_bases, world, rank,
+                                                   set, epoch, totals, (unsigned)n);
+    B200R_LAUNCH_CHECK("k_part_publish_in");
+    return B200R_OK;
+}
+
+int b200r_part_route(b200r_trie *t, uint64_t avail_mask, uint64_t seed,
+                     const uint64_t *d_peer_bases, void *d_my_base, int32_t world, int32_t rank,
+                     int64_t cap, int64_t rcap, uint32_t epoch, void *d_work, void *stream)
+{
+    int rc = part_check(world, rank, cap, rcap, d_peer_bases, d_work);
+    if (rc) return rc;
+    if (!t || !d_my_base) { set_error("b200r_part_route: null pointer"); return B200R_E_INVALID; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const PartLayout L = part_layout(world, cap, rcap);
+    const Plan p = make_plan(L.n_max, L.c_max, B200R_F_ALL_ASCII, true);
+    const int set = (int)(epoch & 1);
+    uint8_t *base = (uint8_t *)d_my_base, *wk = (uint8_t *)d_work, *sc = wk + L.w_plan;
+    PartDyn *dyn = (PartDyn *)(wk + L.w_dyn);
+    int32_t *c_owned = (int32_t *)(wk + L.w_c_owned);
+    uint32_t *pos_owned = (uint32_t *)(wk + L.w_pos_owned);
+    int32_t *ep = (int32_t *)(wk + L.w_ep), *depth = (int32_t *)(wk + L.w_depth);
+    uint64_t *matched = (uint64_t *)(wk + L.w_matched);
+    int32_t *chunk_base = (int32_t *)(sc + p.off_chunk_base);
+    uint64_t *hashes = (uint64_t *)(sc + p.off_hashes);
+    uint32_t *slots = (uint32_t *)(sc + p.off_slots);
+    int32_t *leader = (int32_t *)(sc + p.off_leader), *choice = (int32_t *)(sc + p.off_choice);
+    int32_t *tile_first = (int32_t *)(sc + p.off_tile_first), *block_sums = (int32_t *)(sc + p.off_block_sums);
+
+    if (t->epoch >= 0xFFFFFFF0u) { set_error("batch epoch exhausted"); return B200R_E_INVALID; }
+    t->epoch++;
+    const unsigned long long tag = (unsigned long long)t->epoch << 32;
+    const int32_t *n_dev = &dyn->n_owned;
+
+    { ProfScope ps__(PK_WAIT, st); g_launches += 1;
+    k_part_wait_meta<<<1, P2P_MAX_WORLD, 0, st>>>((const PartFlags *)base, set, epoch, world, dyn, t->dev);
+    B200R_LAUNCH_CHECK("k_part_wait_meta");
+    }
+    { ProfScope ps__(PK_PREP, st); g_launches += 3;
+    k_part_gather<<<148 * 4, 256, 0, st>>>(base, L.hash_off + (size_t)set * L.hash_set,
+                                           L.info_off + (size_t)set * L.info_set, cap, rcap, world, dyn,
+                                           c_owned, pos_owned, hashes);
+    B200R_LAUNCH_CHECK("k_part_gather");
+    const int nblk = (int)((L.n_max + PREP_BLOCK - 1) / PREP_BLOCK);
+    k_prep_sums<<<nblk, PREP_BLOCK, 0, st>>>(c_owned, nullptr, (int)L.n_max, 1, block_sums, n_dev);
+    B200R_LAUNCH_CHECK("k_prep_sums(owned)");
+    k_prep_scan<<<nblk, PREP_BLOCK, 0, st>>>(c_owned, nullptr, (int)L.n_max, 1, block_sums, chunk_base,
+                                             tile_first, L.c_max, t->dev, nullptr, nullptr, nullptr, n_dev);
+    B200R_LAUNCH_CHECK("k_prep_scan(owned)");
+    }
+    // grids are estimates (about two shards' worth); the kernels stride over the rest
+    const int64_t est = 2 * rcap < L.n_max ? 2 * rcap : L.n_max;
+    const int wblocks = (int)((est + WARPS_PER_CTA - 1) / WARPS_PER_CTA);
+    const int tblocks = (int)((est + 255) / 256);
+    { ProfScope ps__(PK_CLAIM, st); g_launches += 1;
+    k_claim<<<wblocks, WARPS_PER_CTA * 32, 0, st>>>(t->tab, t->hs, t->cap_log2, t->dev, hashes,
+                                                    chunk_base, 0, L.c_max, avail_mask, tag, slots, n_dev);
+    B200R_LAUNCH_CHECK("k_claim(owned)");
+    }
+    { ProfScope ps__(PK_SELECT, st); g_launches += 1;
+    k_select<<<tblocks, 256, 0, st>>>(t->tab, chunk_base, 0, L.c_max, slots, avail_mask, tag, seed, 0,
+                                     leader, choice, depth, matched, 0u, &dyn->base, pos_owned, n_dev);
+    B200R_LAUNCH_CHECK("k_select(owned)");
+    }
+    { ProfScope ps__(PK_COMMIT, st); g_launches += 1;
+    k_commit<<<tblocks, 256, 0, st>>>(t->tab, t->dev, chunk_base, 0, L.c_max, slots, leader, choice,
+                                     depth, ep, matched, n_dev);
+    B200R_LAUNCH_CHECK("k_commit(owned)");
+    }
+    { ProfScope ps__(PK_PUSH, st); g_launches += 2;
+    k_part_push_results<<<148 * 2, 256, 0, st>>>(dyn, world, rank, ep, depth, matched,
+                                                 (const unsigned long long *)d_peer_bases,
+                                                 L.res_off + (size_t)set * L.res_set, rcap);
+    B200R_LAUNCH_CHECK("k_part_push_results");
+    k_part_publish_res<<<1, P2P_MAX_WORLD, 0, st>>>((const unsigned long long *)d_peer_bases, world,
+                                                    rank, set, epoch, dyn);
+    B200R_LAUNCH_CHECK("k_part_publish_res");
+    }
+    return B200R_OK;
+}
+
+int b200r_part_finish(b200r_trie *t, int64_t n, void *d_my_base, int32_t world, int32_t rank,
+                      int64_t cap, int64_t rcap, uint32_t epoch, void *d_work, int32_t *d_endpoint,
+                      int32_t *d_match_depth, uint64_t *d_matched, void *stream)
+{
+    int rc = part_check(world, rank, cap, rcap, d_my_base, d_work);
+    if (rc) return rc;
+    if (!t || (n > 0 && (!d_endpoint || !d_match_depth || !d_matched))) { set_error("b200r_part_finish: null pointer"); return B200R_E_INVALID; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const PartLayout L = part_layout(world, cap, rcap);
+    const int set = (int)(epoch & 1);
+    uint8_t *base = (uint8_t *)d_my_base, *wk = (uint8_t *)d_work;
+    { ProfScope ps__(PK_WAIT, st); g_launches += 1;
+    k_part_wait_res<<<1, P2P_MAX_WORLD, 0, st>>>((const PartFlags *)base, set, epoch, world, t->dev,
+                                                 (PartDyn *)(wk + L.w_dyn));
+    B200R_LAUNCH_CHECK("k_part_wait_res");
+    }
+    if (n > 0) {
+        ProfScope ps__(PK_RESOLVE, st); g_launches += 1;
+        k_part_scatter<<<(int)((n + 255) / 256), 256, 0, st>>>(
+            (const uint32_t *)(wk + L.w_dest_slot), base, L.res_off + (size_t)set * L.res_set, rcap,
+            (int)n, d_endpoint, d_match_depth, d_matched);
+        B200R_LAUNCH_CHECK("k_part_scatter");
+    }
     return B200R_OK;
 }
 
