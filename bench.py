@@ -90,55 +90,56 @@ def make_trace(args, n_batches):
 
 # ---------------------------------------------------------------- clocks
 class ClockSampler:
-    """Samples SM clock and throttle reasons with NVML from a background thread
-    while the timed region runs (nvidia-smi's own loop is too slow to start for
-    a region of a few milliseconds)."""
+    """SM clock and throttle reasons during the timed region, read through NVML.
+
+    NVML queries take a driver lock and stall kernel launches of every process on the box
+    (measured: a background poller more than doubled the multi-GPU step time), so nothing
+    polls while the host is still enqueueing.  The timed steps are enqueued first; then,
+    while the GPU is still executing them, the main thread samples until the closing event
+    has completed: the samples fall inside the timed region without perturbing it."""
 
     def __init__(self, gpu_index):
         self.gpu = gpu_index
         self.samples, self.reasons = [], set()
-        self.stop_flag = False
-        self.thread = None
         self.max_mhz = None
+        self.h = None
+        try:
+            import pynvml as nv
+            self.nv = nv
+            nv.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            idx = gpu_index
+            if vis and all(x.strip().isdigit() for x in vis.split(",")):
+                idx = int(vis.split(",")[gpu_index])
+            self.h = nv.nvmlDeviceGetHandleByIndex(idx)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)
+        except Exception:
+            self.h = None
 
-    def _run(self):
-        import pynvml as nv
+    def sample(self):
+        if self.h is None:
+            return
+        nv = self.nv
         names = {nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
                  nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
                  nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
                  nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
-        while not self.stop_flag:
-            try:
-                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
-                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
-                for bit, nm in names.items():
-                    if r & bit:
-                        self.reasons.add(nm)
-            except Exception:
-                break
-            time.sleep(0.0005)
-
-    def start(self):
         try:
-            import threading
-            import pynvml as nv
-            nv.nvmlInit()
-            # NVML enumerates physical GPUs; honour CUDA_VISIBLE_DEVICES when it lists indices
-            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
-            idx = self.gpu
-            if vis and all(x.strip().isdigit() for x in vis.split(",")):
-                idx = int(vis.split(",")[self.gpu])
-            self.h = nv.nvmlDeviceGetHandleByIndex(idx)
-            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)
-            self.thread = threading.Thread(target=self._run, daemon=True)
-            self.thread.start()
+            self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+            r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+            for bit, nm in names.items():
+                if r & bit:
+                    self.reasons.add(nm)
         except Exception:
-            self.thread = None
+            self.h = None
 
-    def stop(self):
-        self.stop_flag = True
-        if self.thread is not None:
-            self.thread.join(timeout=2)
+    def sample_until(self, event, limit=64):
+        """Sample while `event` (recorded after the timed steps) has not completed."""
+        self.sample()
+        while not event.query() and len(self.samples) < limit:
+            self.sample()
+
+    def result(self):
         out = {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
                "samples": len(self.samples)}
         if self.samples:
@@ -305,7 +306,6 @@ def run_b200(args):
         seq += args.batch * world
     barrier()
     sampler = ClockSampler(local)
-    sampler.start()
     launches0 = _lib.launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
@@ -315,8 +315,10 @@ def run_b200(args):
         seq += args.batch * world
     host_submit_ms = (time.perf_counter() - th0) * 1e3 / K
     ev1.record()
+    if rank == 0:
+        sampler.sample_until(ev1)        # GPU is still inside the timed region here
     barrier()
-    clocks = sampler.stop()
+    clocks = sampler.result()
     launches = _lib.launch_count() - launches0
     ms = ev0.elapsed_time(ev1)
     if world > 1:
