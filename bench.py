@@ -98,11 +98,13 @@ class ClockSampler:
     while the GPU is still executing them, the main thread samples until the closing event
     has completed: the samples fall inside the timed region without perturbing it."""
 
-    def __init__(self, gpu_index):
+    def __init__(self, gpu_index, enabled=True):
         self.gpu = gpu_index
         self.samples, self.reasons = [], set()
         self.max_mhz = None
         self.h = None
+        if not enabled:                # only one process per box talks to NVML
+            return
         try:
             import pynvml as nv
             self.nv = nv
@@ -133,11 +135,13 @@ class ClockSampler:
         except Exception:
             self.h = None
 
-    def sample_until(self, event, limit=64):
-        """Sample while `event` (recorded after the timed steps) has not completed."""
+    def sample_until(self, event, limit=4):
+        """A few samples while `event` (recorded after the timed steps) has not completed."""
         self.sample()
         while not event.query() and len(self.samples) < limit:
-            self.sample()
+            time.sleep(0.0003)
+            if not event.query():
+                self.sample()
 
     def result(self):
         out = {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
@@ -300,12 +304,16 @@ def run_b200(args):
     # ---- pass 1: device-resident batches, whole timed region bracketed by events
     resident = [p.to(dev, non_blocking=False) for p in host]
     router = new_router()
+    # NVML is initialised here, well before the barrier that opens the timed region: its
+    # start-up takes milliseconds on the host and every rank waits for the slowest one
+    sampler = ClockSampler(local, enabled=(rank == 0))
+    sampler.sample()
+    sampler.samples.clear()
     seq = 0
     for b in range(W):
         route_resident(router, b, seq)
         seq += args.batch * world
     barrier()
-    sampler = ClockSampler(local)
     launches0 = _lib.launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
