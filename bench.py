@@ -299,6 +299,8 @@ def run_b200(args):
     def route_resident(router, b, seq):
         if world == 1:
             return router.route(resident[b], avail_mask(b), SEED, seq, inputs_ready=True)
+        if hasattr(router, "send_stream"):                       # partitioned: pipelined
+            return router.route(resident[b], avail_mask(b), SEED, seq, out=out, inputs_ready=True)
         return router.route(resident[b], avail_mask(b), SEED, seq, out=out)
 
     # ---- pass 1: device-resident batches, whole timed region bracketed by events
@@ -398,6 +400,8 @@ def run_b200(args):
     def submit(b, seq, j):
         if world == 1:
             ep, _, _ = router.route(host[b], avail_mask(b), SEED, seq)
+        elif hasattr(router, "send_stream"):      # host inputs are copied on the send stream
+            ep, _, _ = router.route(host[b], avail_mask(b), SEED, seq, out=out)
         else:
             ep, _, _ = router.route(host[b].to(dev, non_blocking=True), avail_mask(b), SEED, seq,
                                     out=out)

@@ -358,6 +358,11 @@ class PartitionedPrefixRouter:
         self.work = torch.zeros(work_bytes, dtype=torch.uint8, device=self.device)
         self.epoch = 0
         self._shape = None
+        # two-stream pipeline: the send phase of batch b+1 (hashing, never touches the table)
+        # runs on its own stream while route + finish of batch b run on the caller's stream
+        self.send_stream = torch.cuda.Stream(device=self.device)
+        self._sent = torch.cuda.Event()
+        self._finished = [None, None]              # finish events by batch parity
 
     @staticmethod
     def capacities(max_requests: int, max_chunks: int):
@@ -403,13 +408,34 @@ class PartitionedPrefixRouter:
                 self.epoch, _ptr(self.work), _ptr(ep), _ptr(depth), _ptr(matched), _stream()))
         return ep[:n], depth[:n], matched[:n]
 
-    def route(self, p: PackedPrompts, avail_mask: int, seed: int, seq0: int = 0, out=None):
+    def route(self, p: PackedPrompts, avail_mask: int, seed: int, seq0: int = 0, out=None,
+              inputs_ready: bool = False):
+        """Pipelined: the send phase runs on a second stream.  It may not start before this
+        rank has finished batch b-1 (then every peer has consumed the buffer set it is about
+        to overwrite) and, unless inputs_ready, before the caller's stream has produced the
+        inputs; route and finish stay on the caller's stream, in batch order."""
         if self.epoch == 0 and seq0 != 0:
             raise _lib.B200RouterError("PartitionedPrefixRouter keeps the sequence number on the "
                                        "device; it starts at 0")
-        self.phase_send(p)
+        cur = torch.cuda.current_stream(self.device)
+        ss = self.send_stream
+        prev = self._finished[(self.epoch + 1) & 1]      # batch b-1 (same parity as b+1)
+        if prev is not None:
+            ss.wait_event(prev)
+        if p.bytes.device != self.device:
+            inputs_ready = True                          # copied on the send stream below
+        if not inputs_ready:
+            ss.wait_stream(cur)
+        with torch.cuda.stream(ss):
+            self.phase_send(p)
+            self._sent.record(ss)
+        cur.wait_event(self._sent)
         self.phase_route(avail_mask, seed)
-        return self.phase_finish(out)
+        res = self.phase_finish(out)
+        done = torch.cuda.Event()
+        done.record(cur)
+        self._finished[self.epoch & 1] = done
+        return res
 
     def check_status(self, count_nodes=False):
         s = self.trie.check_status(count_nodes)

@@ -1982,7 +1982,7 @@ static PartLayout part_layout(int world, int64_t cap, int64_t rcap)
     L.w_blk_cnt = o;   o += align_up((size_t)L.nblk_max * 2 * world * 4);
     L.w_blk_off = o;   o += align_up((size_t)L.nblk_max * 2 * world * 4);
     L.w_totals = o;    o += align_up((size_t)2 * world * 4);
-    L.w_dest_slot = o; o += align_up((size_t)rcap * 4);
+    L.w_dest_slot = o; o += 2 * align_up((size_t)rcap * 4);     // one per batch parity
     L.w_c_owned = o;   o += align_up((size_t)L.n_max * 4);
     L.w_pos_owned = o; o += align_up((size_t)L.n_max * 4);
     L.w_ep = o;        o += align_up((size_t)L.n_max * 4);
@@ -2044,7 +2044,7 @@ int b200r_part_send(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_star
         k_part_push<<<nblk, PART_BLOCK, 0, st>>>(
             chunk_base, hashes, (int)n, world, rank, blk_off, (const unsigned long long *)d_peer_bases,
             L.hash_off + (size_t)set * L.hash_set, L.info_off + (size_t)set * L.info_set, cap, rcap,
-            (uint32_t *)(wk + L.w_dest_slot));
+            (uint32_t *)(wk + L.w_dest_slot + (size_t)set * align_up((size_t)rcap * 4)));
         B200R_LAUNCH_CHECK("k_part_push");
     } else {
         B200R_CUDA(cudaMemsetAsync(totals, 0, (size_t)2 * world * 4, st));
@@ -2150,7 +2150,8 @@ int b200r_part_finish(b200r_trie *t, int64_t n, void *d_my_base, int32_t world, 
     if (n > 0) {
         ProfScope ps__(PK_RESOLVE, st); g_launches += 1;
         k_part_scatter<<<(int)((n + 255) / 256), 256, 0, st>>>(
-            (const uint32_t *)(wk + L.w_dest_slot), base, L.res_off + (size_t)set * L.res_set, rcap,
+            (const uint32_t *)(wk + L.w_dest_slot + (size_t)set * align_up((size_t)rcap * 4)), base,
+            L.res_off + (size_t)set * L.res_set, rcap,
             (int)n, d_endpoint, d_match_depth, d_matched);
         B200R_LAUNCH_CHECK("k_part_scatter");
     }
