@@ -59,6 +59,7 @@ extern "C" {
 #define B200R_S_TABLE_FULL 1u
 #define B200R_S_CHUNK_CAP 2u
 #define B200R_S_PEER_TIMEOUT 4u /* multi-GPU: a peer's data did not arrive within ~3 s */
+#define B200R_S_LOOKBACK 8u     /* internal: a tile's path-key carry never arrived          */
 
 typedef struct b200r_trie b200r_trie; /* GPU-resident HashTrie replacement     */
 typedef struct b200r_ring b200r_ring; /* GPU-resident consistent-hash ring     */
@@ -177,6 +178,27 @@ int b200r_prefix_route_stage(b200r_trie *t, int64_t n, int64_t max_chunks, uint3
                              int32_t *d_endpoint, int32_t *d_match_depth,
                              uint64_t *d_matched_mask, void *d_scratch, size_t scratch_bytes,
                              void *stream);
+/* Fused variant of a5: after the prep stage (chunk counts, CSR, ragged tails; does not
+ * touch the table) ONE kernel hashes the chunks, computes the path keys (segmented warp
+ * scan + decoupled look-back between tiles) and finds-or-creates the nodes; select and
+ * commit follow.  The chunk hashes never go to memory.  Same results, same scratch size.
+ * b200r_prefix_route_batch_fused = prep stage + fused stage on one stream. */
+int b200r_prefix_prep_stage(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
+                            const int32_t *d_lens, const int32_t *d_nchars, int64_t n,
+                            int64_t max_chunks, uint32_t flags, void *d_scratch,
+                            size_t scratch_bytes, void *stream);
+int b200r_prefix_fused_stage(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
+                             const int32_t *d_lens, const int32_t *d_nchars, int64_t n,
+                             int64_t max_chunks, uint32_t flags, uint64_t avail_mask,
+                             uint64_t seed, uint64_t seq0, int32_t *d_endpoint,
+                             int32_t *d_match_depth, uint64_t *d_matched_mask, void *d_scratch,
+                             size_t scratch_bytes, void *stream);
+int b200r_prefix_route_batch_fused(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
+                                   const int32_t *d_lens, const int32_t *d_nchars, int64_t n,
+                                   int64_t max_chunks, uint32_t flags, uint64_t avail_mask,
+                                   uint64_t seed, uint64_t seq0, int32_t *d_endpoint,
+                                   int32_t *d_match_depth, uint64_t *d_matched_mask,
+                                   void *d_scratch, size_t scratch_bytes, void *stream);
 /* the canonical draw, on the host (same arithmetic as the kernels) */
 uint32_t b200r_pick(uint64_t seed, uint64_t seq, uint32_t n);
 

@@ -211,6 +211,46 @@ def test_route_pipeline_overlapped_batches_vs_oracle():
         t.close()
 
 
+def test_staged_and_fused_paths_agree_with_the_oracle():
+    """b200r_prefix_route_batch (hash kernel + claim kernel) and ..._fused (one kernel with
+    look-back between tiles) on the same trace: both equal the oracle; long prompts make
+    requests span many warp tiles."""
+    from b200_router.trie import GpuHashTrie, RoutePipeline
+    bufL, stL, lnL = traces.long_context_batch(n=300, chars=128 * 45 + 77, group=10,
+                                               shared_frac=0.5, seed=15)
+    tr = traces.SharedPrefixTrace(n_total=9000, batch=3000, n_sys=16, sys_chars=512,
+                                  suffix_lo=1, suffix_hi=400, seed=22)
+    batches = [(0xFF, bufL, stL, lnL)] + [((0xFB if b == 1 else 0xFF),) + tr.batch_arrays(b)
+                                          for b in range(3)]
+    for fused in (False, True):
+        t = GpuHashTrie(cap_log2=18)
+        orc = coracle.TrieOracle()
+        seq = 0
+        for avail, buf, starts, lens in batches:
+            ep, depth, matched = t.route(pack_arrays(buf, starts, lens, pin=False), avail, 4, seq,
+                                         fused=fused)
+            oep, odepth, omatched = orc.route_batch(buf, starts, lens, avail, 4, seq)
+            seq += len(starts)
+            assert (ep.cpu().numpy() == oep).all(), fused
+            assert (depth.cpu().numpy() == odepth).all(), fused
+            assert (u64(matched) == omatched).all(), fused
+        t.check_status()
+        assert t.dump() == orc.dump()
+        t.close()
+    # the batch pipeline in its staged flavour
+    t = GpuHashTrie(cap_log2=18)
+    pipe = RoutePipeline(t, fused=False)
+    orc = coracle.TrieOracle()
+    seq = 0
+    for avail, buf, starts, lens in batches:
+        ep, _, _ = pipe.route(pack_arrays(buf, starts, lens, pin=True), avail, 4, seq)
+        oep, _, _ = orc.route_batch(buf, starts, lens, avail, 4, seq)
+        seq += len(starts)
+        assert (ep.cpu().numpy() == oep).all()
+    assert t.dump() == orc.dump()
+    t.close()
+
+
 def test_route_long_prompts_many_blocks_vs_oracle():
     """Prompts of more than 32 chunks (several warp iterations, carried path key)."""
     from b200_router.trie import GpuHashTrie

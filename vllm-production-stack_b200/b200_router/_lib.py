@@ -39,6 +39,11 @@ SIGNATURES = {
     "b200r_prefix_hash_stage": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _u32, _vp, _sz, _vp]),
     "b200r_prefix_route_stage": (C.c_int, [_vp, _i64, _i64, _u32, _u64, _u64, _u64, _vp, _vp, _vp, _vp,
                                            _sz, _vp]),
+    "b200r_prefix_prep_stage": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _u32, _vp, _sz, _vp]),
+    "b200r_prefix_fused_stage": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _u32, _u64, _u64, _u64,
+                                           _vp, _vp, _vp, _vp, _sz, _vp]),
+    "b200r_prefix_route_batch_fused": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _u32, _u64, _u64,
+                                                 _u64, _vp, _vp, _vp, _vp, _sz, _vp]),
     "b200r_pick": (_u32, [_u64, _u64, _u32]),
     "b200r_trie_dump": (C.c_int, [_vp, _vp, _i64, C.POINTER(_i64), C.POINTER(_u64), _vp]),
     "b200r_trie_apply_remote": (C.c_int, [_vp, _vp, _i64, _u64, _vp]),

@@ -137,10 +137,13 @@ class GpuHashTrie:
                                                           _ptr(ep), _stream()))
 
     # -------------------------------------------------------------------- a5
-    def route(self, p: PackedPrompts, avail_mask: int, seed: int, seq0: int, out=None):
-        """Fused lookup + tie-break + insert for a batch, equal to routing the
-        requests sequentially in index order.  Returns device tensors
-        (endpoint int32[n], depth int32[n], matched int64[n])."""
+    def route(self, p: PackedPrompts, avail_mask: int, seed: int, seq0: int, out=None,
+              fused: bool = True):
+        """Lookup + tie-break + insert for a batch, equal to routing the requests
+        sequentially in index order.  Returns device tensors (endpoint int32[n],
+        depth int32[n], matched int64[n]).  fused=True (default) hashes, keys and claims in
+        one kernel (b200r_prefix_route_batch_fused); fused=False runs the staged kernels
+        (b200r_prefix_route_batch) -- identical results."""
         p = self._dev(p)
         L = _lib.lib()
         n = p.n
@@ -151,8 +154,9 @@ class GpuHashTrie:
         ep, depth, matched = out
         flags = _lib.F_ALL_ASCII if p.all_ascii else 0
         sc = self._scratch_for(L.b200r_prefix_route_scratch_bytes(n, p.max_chunks, flags))
+        entry = L.b200r_prefix_route_batch_fused if fused else L.b200r_prefix_route_batch
         with torch.cuda.device(self.device):
-            _lib.check(L.b200r_prefix_route_batch(
+            _lib.check(entry(
                 self._h, _ptr(p.bytes), _ptr(p.starts), _ptr(p.lens), _ptr(p.nchars), n,
                 p.max_chunks, flags, avail_mask & M64, seed & M64, seq0 & M64, _ptr(ep), _ptr(depth),
                 _ptr(matched), _ptr(sc), sc.numel(), _stream()))
@@ -263,9 +267,14 @@ class RoutePipeline:
     produced and synchronised earlier); otherwise the hash stage waits for the
     caller's stream, which is safe but serialises the two stages."""
 
-    def __init__(self, trie: GpuHashTrie, depth: int = 2):
+    def __init__(self, trie: GpuHashTrie, depth: int = 2, fused: bool = True):
+        """fused=True: the first stage is only the prep (chunk counts, ragged tails) and the
+        second stage hashes + claims in one kernel; fused=False: first stage hashes every
+        chunk, second stage works from the hashes."""
         self.trie = trie
         self.depth = depth
+        self.fused = fused
+        self._inflight = [None] * depth
         self.device = trie.device
         self.hash_stream = torch.cuda.Stream(device=self.device)
         self._scratch = [None] * depth
@@ -317,20 +326,28 @@ class RoutePipeline:
             hs.wait_event(self._done[k])          # scratch k is free again
         if not on_host and not inputs_ready:
             hs.wait_stream(cur)
+        first = L.b200r_prefix_prep_stage if self.fused else L.b200r_prefix_hash_stage
         with torch.cuda.device(self.device), torch.cuda.stream(hs):
             if on_host:
                 p = p.to(self.device, non_blocking=True)
-            _lib.check(L.b200r_prefix_hash_stage(
+            _lib.check(first(
                 self.trie._h, _ptr(p.bytes), _ptr(p.starts), _ptr(p.lens), _ptr(p.nchars), n,
                 p.max_chunks, flags, _ptr(sc), sc.numel(), C.c_void_p(hs.cuda_stream)))
             self._hashed[k].record(hs)
         cur.wait_event(self._hashed[k])
         ep, depth, matched = o
         with torch.cuda.device(self.device):
-            _lib.check(L.b200r_prefix_route_stage(
-                self.trie._h, n, p.max_chunks, flags, avail_mask & M64, seed & M64, seq0 & M64,
-                _ptr(ep), _ptr(depth), _ptr(matched), _ptr(sc), sc.numel(),
-                C.c_void_p(cur.cuda_stream)))
+            if self.fused:       # the fused stage reads the prompt bytes again: keep them alive
+                self._inflight[k] = p
+                _lib.check(L.b200r_prefix_fused_stage(
+                    self.trie._h, _ptr(p.bytes), _ptr(p.starts), _ptr(p.lens), _ptr(p.nchars), n,
+                    p.max_chunks, flags, avail_mask & M64, seed & M64, seq0 & M64, _ptr(ep),
+                    _ptr(depth), _ptr(matched), _ptr(sc), sc.numel(), C.c_void_p(cur.cuda_stream)))
+            else:
+                _lib.check(L.b200r_prefix_route_stage(
+                    self.trie._h, n, p.max_chunks, flags, avail_mask & M64, seed & M64, seq0 & M64,
+                    _ptr(ep), _ptr(depth), _ptr(matched), _ptr(sc), sc.numel(),
+                    C.c_void_p(cur.cuda_stream)))
         done = torch.cuda.Event()
         done.record(cur)
         self._done[k] = done

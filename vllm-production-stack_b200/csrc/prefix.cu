@@ -94,10 +94,12 @@ __device__ __forceinline__ int block_sum_1024(int v, int *s_red)
 
 __global__ void __launch_bounds__(PREP_BLOCK)
 k_prep_sums(const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars, int n, int cc,
-            int32_t *__restrict__ block_sums, const int32_t *__restrict__ n_dev)
+            int32_t *__restrict__ block_sums, const int32_t *__restrict__ n_dev,
+            unsigned int *__restrict__ ticket)
 {
     __shared__ int s_red[32];
     if (n_dev) n = *n_dev;          // batch size known only on the device (partitioned multi-GPU)
+    if (ticket && blockIdx.x == 0 && threadIdx.x == 0) *ticket = 0;   // for the fused kernel
     int i = blockIdx.x * PREP_BLOCK + threadIdx.x;
     int c = (i < n) ? chunks_of(lens, nchars, i, cc) : 0;
     int tot = block_sum_1024(c, s_red);
@@ -109,7 +111,8 @@ k_prep_scan(const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars
             const int32_t *__restrict__ block_sums, int32_t *__restrict__ chunk_base,
             int32_t *__restrict__ tile_first, int64_t max_chunks, TrieDev *dev,
             const uint8_t *__restrict__ bytes, const int64_t *__restrict__ starts,
-            uint64_t *__restrict__ hashes, const int32_t *__restrict__ n_dev)
+            uint64_t *__restrict__ hashes, const int32_t *__restrict__ n_dev,
+            unsigned int *__restrict__ lb_flag)
 {
     __shared__ int s_red[32];
     __shared__ int s_wsum[32];
@@ -146,7 +149,10 @@ k_prep_scan(const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars
             int t0 = (base + 31) / 32;
             int64_t lim = (int64_t)base + c;
             if (lim > max_chunks) lim = max_chunks;
-            for (int t = t0; (int64_t)t * 32 < lim; t++) tile_first[t] = i;
+            for (int t = t0; (int64_t)t * 32 < lim; t++) {
+                tile_first[t] = i;
+                if (lb_flag) lb_flag[t] = 0;          // look-back state of the fused kernel
+            }
             // The ragged last chunk of an ASCII request is hashed here, one thread per
             // request, so that k_hash_chunks is left with full 128-byte chunks only.
             const int ln = lens[i];
@@ -325,16 +331,68 @@ constexpr int HASH_WARPS = 8;             // warps per CTA
 
 struct ReqRec { int b, b1, ln, nc; long long st; };
 
+// Arguments of the fused variant (hash + path keys + claim in one kernel).
+struct FuseArgs {
+    Entry *tab; uint64_t *hs; int cap_log2; TrieDev *dev;
+    uint64_t avail; unsigned long long tag;
+    uint32_t *slots;
+    unsigned int *ticket;            // CTA ticket counter (zeroed by k_prep_sums)
+    unsigned int *lb_flag;           // per warp tile: 0 nothing, 1 partial key published, 2 final
+    uint64_t *lb_part, *lb_final;    // per warp tile: 2 x u64 each
+};
+constexpr uint32_t PREOK_BIT = 0x80000000u;
+
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned *p)
+{
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_u32(unsigned *p, unsigned v)
+{
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void ld_cg_2u64(const uint64_t *p, uint64_t &a, uint64_t &b)
+{
+    asm volatile("ld.global.cg.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+}
+
+// A^n for n = 1..32, both key lanes (A^(2^k) are compile-time constants)
+__device__ __forceinline__ void key_pow(int n, uint64_t &r1, uint64_t &r2)
+{
+    r1 = 1; r2 = 1;
+#define B200R_POW_STEP(BIT)                                                     \
+    if (n & BIT) { r1 = mulc<cpow(KA1, BIT)>(r1); r2 = mulc<cpow(KA2, BIT)>(r2); }
+    B200R_POW_STEP(1) B200R_POW_STEP(2) B200R_POW_STEP(4) B200R_POW_STEP(8) B200R_POW_STEP(16)
+    B200R_POW_STEP(32)
+#undef B200R_POW_STEP
+}
+
+// CLAIM = false: chunk hashing only (a1, and the hash stage of the staged paths).
+// CLAIM = true : fused single-GPU path -- after hashing, the warp computes the path keys
+//   of its 32 chunks (segmented Kogge-Stone scan; a request that started in an earlier
+//   tile gets its carry by decoupled look-back over per-tile published keys, CTAs take
+//   tickets so that a waited-for tile is always running or done), then finds-or-creates
+//   every node and classifies it exactly like k_claim.  The chunk hashes never go to
+//   memory and the table latency of one warp overlaps the hashing of the others.
+template <bool CLAIM>
 __global__ void __launch_bounds__(HASH_WARPS * 32)
-k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ starts,
-              const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars,
-              const int32_t *__restrict__ chunk_base, const int32_t *__restrict__ tile_first,
-              const int32_t *__restrict__ chunk_off, int n, int cc, int64_t max_chunks,
-              uint64_t *__restrict__ hashes)
+k_hash_tiles(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ starts,
+             const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars,
+             const int32_t *__restrict__ chunk_base, const int32_t *__restrict__ tile_first,
+             const int32_t *__restrict__ chunk_off, int n, int cc, int64_t max_chunks,
+             uint64_t *__restrict__ hashes, FuseArgs fa)
 {
     __shared__ __align__(1024) uint8_t s_tile[HASH_WARPS * WTILE * 128];
+    __shared__ unsigned s_bid;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const int64_t tile = (int64_t)blockIdx.x * HASH_WARPS + w;
+    unsigned bid = blockIdx.x;
+    if (CLAIM) {
+        if (threadIdx.x == 0) s_bid = atomicAdd(fa.ticket, 1u);
+        __syncthreads();
+        bid = s_bid;
+    }
+    const int64_t tile = (int64_t)bid * HASH_WARPS + w;
     const int64_t G0 = tile * WTILE;
     int64_t total = chunk_base[n];
     if (total > max_chunks) total = max_chunks;
@@ -343,6 +401,7 @@ k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ sta
     // ---- map: which request owns each of the 32 chunks?
     const int r0 = tile_first[tile];
     ReqRec mine = { 0, 0, 0, 0, 0 };      // record of the request that owns this lane's chunk
+    int mine_r = r0;
     for (int jb = 0;; jb += 32) {
         const int r = r0 + jb + lane;
         ReqRec q = { 0, 0, 0, 0, 0 };
@@ -368,7 +427,10 @@ k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ sta
         const int tb = __shfl_sync(0xffffffffu, q.b, src), tb1 = __shfl_sync(0xffffffffu, q.b1, src);
         const int tln = __shfl_sync(0xffffffffu, q.ln, src), tnc = __shfl_sync(0xffffffffu, q.nc, src);
         const long long tst = __shfl_sync(0xffffffffu, q.st, src);
-        if (below) { mine.b = tb; mine.b1 = tb1; mine.ln = tln; mine.nc = tnc; mine.st = tst; }
+        if (below) {
+            mine.b = tb; mine.b1 = tb1; mine.ln = tln; mine.nc = tnc; mine.st = tst;
+            mine_r = r0 + jb + src;
+        }
         // more requests can start inside the tile only if the last lane's request ends inside it
         const int last_b1 = __shfl_sync(0xffffffffu, q.b1, 31);
         const bool last_live = __shfl_sync(0xffffffffu, (int)live, 31);
@@ -377,10 +439,12 @@ k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ sta
 
     // ---- chunk descriptor
     const int64_t g = G0 + lane;
+    const bool valid = g < total;
     const uint8_t *p = nullptr;
     int clen = 0, kind = 0;               // 0 none / done elsewhere, 1 full staged, 3 generic
-    if (g < total) {
-        const int d = (int)(g - mine.b);
+    int d = 0;                            // depth of the chunk inside its request (0-based)
+    if (valid) {
+        d = (int)(g - mine.b);
         int off;
         if (mine.nc == mine.ln) {                        // ASCII: chunk = cc bytes
             off = d * cc;
@@ -415,12 +479,92 @@ k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ sta
                            (const uint8_t *)(uintptr_t)src + (u << 4), 16);
         }
     }
+    // the ragged last chunk of a request was hashed by k_prep_scan: fetch it meanwhile
+    uint64_t h = 0;
+    if (CLAIM && valid && kind == 0) h = hashes[g];
     cp_async_wait_all();
     __syncwarp();
 
     // ---- hash
-    if (kind == 1) hashes[g] = xxh64_row128(wrow + lane * 128, lane & 7);
-    else if (kind == 3) hashes[g] = xxh64_global(p, clen);
+    if (kind == 1) h = xxh64_row128(wrow + lane * 128, lane & 7);
+    else if (kind == 3) h = xxh64_global(p, clen);
+    if (!CLAIM) {
+        if (kind) hashes[g] = h;
+        return;
+    }
+
+    // ---- path keys: segmented scan over the tile
+    const bool inhead = valid && d > lane;          // request started in an earlier tile
+    const int dseg = !valid ? 0 : (inhead ? lane : d);
+    uint64_t p1 = h, p2 = rotl<32>(h);
+    if (valid && d == 0) { p1 += KA1 * KROOT1; p2 += KA2 * KROOT2; }
+#define B200R_SEG_STEP(S)                                          \
+    {                                                              \
+        const uint64_t t1 = __shfl_up_sync(0xffffffffu, p1, S);    \
+        const uint64_t t2 = __shfl_up_sync(0xffffffffu, p2, S);    \
+        constexpr uint64_t m1 = cpow(KA1, S), m2 = cpow(KA2, S);   \
+        if (dseg >= S) { p1 += m1 * t1; p2 += m2 * t2; }           \
+    }
+    B200R_SEG_STEP(1) B200R_SEG_STEP(2) B200R_SEG_STEP(4) B200R_SEG_STEP(8) B200R_SEG_STEP(16)
+#undef B200R_SEG_STEP
+
+    // publish the key at the end of this tile for the next tile's carry
+    const bool head_tile = __shfl_sync(0xffffffffu, (int)inhead, 0);    // lane 0 continues a request
+    const bool last_valid = __shfl_sync(0xffffffffu, (int)valid, 31);
+    const bool last_inhead = __shfl_sync(0xffffffffu, (int)inhead, 31); // whole tile inside one request
+    if (lane == 31 && last_valid) {
+        uint64_t *dst = (last_inhead ? fa.lb_part : fa.lb_final) + 2 * tile;
+        dst[0] = p1; dst[1] = p2;
+        st_release_u32(fa.lb_flag + tile, last_inhead ? 1u : 2u);
+    }
+    if (head_tile) {
+        // decoupled look-back: K_in = P(T-1) + A^32 P(T-2) + ... + A^(32m) F(j)
+        uint64_t a1 = 0, a2 = 0, m1 = 1, m2 = 1;
+        for (int64_t j = tile - 1; j >= 0; j--) {
+            unsigned f = 0;
+            for (long spins = 0; spins < 40000000L; spins++) {
+                f = ld_acquire_u32(fa.lb_flag + j);
+                if (f) break;
+                __nanosleep(32);
+            }
+            if (!f) { if (lane == 0) atomicOr(&fa.dev->status, B200R_S_LOOKBACK); break; }
+            uint64_t x1, x2;
+            ld_cg_2u64((f == 2 ? fa.lb_final : fa.lb_part) + 2 * j, x1, x2);
+            a1 += m1 * x1; a2 += m2 * x2;
+            if (f == 2) break;
+            m1 = mulc<cpow(KA1, 32)>(m1); m2 = mulc<cpow(KA2, 32)>(m2);
+        }
+        if (inhead) {
+            uint64_t w1, w2;
+            key_pow(lane + 1, w1, w2);
+            p1 += w1 * a1; p2 += w2 * a2;
+        }
+        if (lane == 31 && last_valid && last_inhead) {
+            fa.lb_final[2 * tile] = p1; fa.lb_final[2 * tile + 1] = p2;
+            st_release_u32(fa.lb_flag + tile, 2u);
+        }
+    }
+
+    // ---- find-or-create + classify (same as k_claim)
+    if (valid) {
+        bool created = false;
+        const uint32_t s = table_claim(fa.tab, fa.hs, fa.cap_log2, p1, p2, h, &created);
+        if (s == SLOT_NONE) {
+            atomicOr(&fa.dev->status, B200R_S_TABLE_FULL);
+            fa.slots[g] = SLOT_NONE;
+        } else {
+            const uint64_t m = created ? 0 : fa.tab[s].mask;
+            if (m & fa.avail) {
+                fa.slots[g] = s | PREOK_BIT;
+            } else {
+                fa.slots[g] = s;
+                const unsigned long long minev = fa.tag | (unsigned long long)(~(unsigned)mine_r);
+                unsigned long long cur = 0;
+                if (!created) cur = *(volatile unsigned long long *)&fa.tab[s].first;
+                if (cur < minev) atomicMax(&fa.tab[s].first, minev);
+            }
+        }
+    }
 }
 
 // =========================================================================
@@ -515,7 +659,7 @@ k_insert(Entry *__restrict__ tab, uint64_t *__restrict__ hs, int cap_log2, TrieD
 // masks; record who touches a not-yet-usable node first.
 //   slots[g] = slot | PREOK_BIT   node usable before the batch (mask & avail != 0)
 //   slots[g] = slot               otherwise; entry.first = (epoch, ~min request index)
-constexpr uint32_t PREOK_BIT = 0x80000000u;
+
 
 // Per-rank device-resident bookkeeping of the peer-exchange (P2P) multi-GPU path.
 constexpr int P2P_MAX_WORLD = 64;
@@ -1253,7 +1397,7 @@ static inline size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct Plan {           // carve-up of the caller's scratch buffer
     size_t off_tile_first, off_block_sums, off_nchars, off_chunk_off, off_chunk_base, off_hashes,
-        off_slots, off_leader, off_choice, total;
+        off_slots, off_leader, off_choice, off_ticket, off_lb_flag, off_lb_part, off_lb_final, total;
 };
 
 static Plan make_plan(int64_t n, int64_t max_chunks, uint32_t flags, bool routing)
@@ -1264,6 +1408,10 @@ static Plan make_plan(int64_t n, int64_t max_chunks, uint32_t flags, bool routin
     const int64_t nblk = (n + PREP_BLOCK - 1) / PREP_BLOCK + 1;
     const bool ascii = flags & B200R_F_ALL_ASCII;
     p.off_tile_first = o; o += align_up(ntiles * 4);
+    p.off_ticket = o;     o += 256;
+    p.off_lb_flag = o;    o += align_up(ntiles * 4);
+    p.off_lb_part = o;    o += routing ? align_up(ntiles * 16) : 0;
+    p.off_lb_final = o;   o += routing ? align_up(ntiles * 16) : 0;
     p.off_block_sums = o; o += align_up(nblk * 4);
     p.off_nchars = o;     o += ascii ? 0 : align_up((n + 1) * 4);
     p.off_chunk_off = o;  o += ascii ? 0 : align_up((max_chunks + 1) * 4);
@@ -1295,7 +1443,8 @@ static int check_prompt_args(const void *bytes, const void *starts, const void *
 static int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const int32_t *d_lens,
                        const int32_t *d_nchars, int64_t n, int32_t cc, uint32_t flags,
                        int32_t *d_chunk_base, uint64_t *d_hashes, int64_t max_chunks,
-                       uint8_t *scratch, const Plan &p, TrieDev *dev, cudaStream_t st)
+                       uint8_t *scratch, const Plan &p, TrieDev *dev, cudaStream_t st,
+                       bool prep_only = false)
 {
     int32_t *tile_first = (int32_t *)(scratch + p.off_tile_first);
     int32_t *block_sums = (int32_t *)(scratch + p.off_block_sums);
@@ -1318,12 +1467,14 @@ static int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const in
     }
     const int nblk = (int)((n + PREP_BLOCK - 1) / PREP_BLOCK);
     { ProfScope ps__(PK_PREP, st); g_launches += 1;
-    k_prep_sums<<<nblk, PREP_BLOCK, 0, st>>>(d_lens, d_nchars, (int)n, cc, block_sums, nullptr);
+    k_prep_sums<<<nblk, PREP_BLOCK, 0, st>>>(d_lens, d_nchars, (int)n, cc, block_sums, nullptr,
+                                             (unsigned int *)(scratch + p.off_ticket));
     B200R_LAUNCH_CHECK("k_prep_sums");
     }
     { ProfScope ps__(PK_PREP, st); g_launches += 1;
     k_prep_scan<<<nblk, PREP_BLOCK, 0, st>>>(d_lens, d_nchars, (int)n, cc, block_sums, d_chunk_base,
-                                             tile_first, max_chunks, dev, d_bytes, d_starts, d_hashes, nullptr);
+                                             tile_first, max_chunks, dev, d_bytes, d_starts, d_hashes, nullptr,
+                                             (unsigned int *)(scratch + p.off_lb_flag));
     B200R_LAUNCH_CHECK("k_prep_scan");
     }
     if (!ascii) {
@@ -1334,11 +1485,11 @@ static int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const in
         }
     }
     const int ntiles = (int)((max_chunks + HASH_WARPS * WTILE - 1) / (HASH_WARPS * WTILE));
-    if (ntiles > 0) {
+    if (ntiles > 0 && !prep_only) {
         { ProfScope ps__(PK_HASH, st); g_launches += 1;
-        k_hash_chunks<<<ntiles, HASH_WARPS * 32, 0, st>>>(
+        k_hash_tiles<false><<<ntiles, HASH_WARPS * 32, 0, st>>>(
             d_bytes, d_starts, d_lens, d_nchars, d_chunk_base, tile_first, chunk_off, (int)n, cc,
-            max_chunks, d_hashes);
+            max_chunks, d_hashes, FuseArgs());
         B200R_LAUNCH_CHECK("k_hash_chunks");
         }
     }
@@ -1668,6 +1819,103 @@ int b200r_prefix_route_stage(b200r_trie *t, int64_t n, int64_t max_chunks, uint3
     B200R_LAUNCH_CHECK("k_commit");
     }
     return B200R_OK;
+}
+
+// Fused variant: prep stage (chunk counts, CSR, ragged tails; never touches the table)
+// and fused stage (hash + path keys + claim in ONE kernel, then select and commit).
+int b200r_prefix_prep_stage(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
+                            const int32_t *d_lens, const int32_t *d_nchars, int64_t n,
+                            int64_t max_chunks, uint32_t flags, void *d_scratch,
+                            size_t scratch_bytes, void *stream)
+{
+    if (!t) { set_error("null trie"); return B200R_E_INVALID; }
+    int rc = check_prompt_args(d_bytes, d_starts, d_lens, n, max_chunks, t->chunk_chars);
+    if (rc) return rc;
+    if (n == 0) return B200R_OK;
+    const Plan p = make_plan(n, max_chunks, flags, true);
+    if (!d_scratch || scratch_bytes < p.total) {
+        set_error("scratch too small: need %zu bytes, got %zu", p.total, scratch_bytes);
+        return B200R_E_SCRATCH;
+    }
+    uint8_t *sc = (uint8_t *)d_scratch;
+    return launch_hash(d_bytes, d_starts, d_lens, d_nchars, n, t->chunk_chars, flags,
+                       (int32_t *)(sc + p.off_chunk_base), (uint64_t *)(sc + p.off_hashes),
+                       max_chunks, sc, p, t->dev, (cudaStream_t)stream, true);
+}
+
+int b200r_prefix_fused_stage(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
+                             const int32_t *d_lens, const int32_t *d_nchars, int64_t n,
+                             int64_t max_chunks, uint32_t flags, uint64_t avail_mask,
+                             uint64_t seed, uint64_t seq0, int32_t *d_endpoint,
+                             int32_t *d_match_depth, uint64_t *d_matched_mask, void *d_scratch,
+                             size_t scratch_bytes, void *stream)
+{
+    if (!t) { set_error("null trie"); return B200R_E_INVALID; }
+    int rc = check_prompt_args(d_bytes, d_starts, d_lens, n, max_chunks, t->chunk_chars);
+    if (rc) return rc;
+    if (n == 0) return B200R_OK;
+    if (!d_endpoint || !d_match_depth || !d_matched_mask) { set_error("null output pointer"); return B200R_E_INVALID; }
+    const Plan p = make_plan(n, max_chunks, flags, true);
+    if (!d_scratch || scratch_bytes < p.total) {
+        set_error("scratch too small: need %zu bytes, got %zu", p.total, scratch_bytes);
+        return B200R_E_SCRATCH;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    uint8_t *sc = (uint8_t *)d_scratch;
+    int32_t *chunk_base = (int32_t *)(sc + p.off_chunk_base);
+    uint64_t *hashes = (uint64_t *)(sc + p.off_hashes);
+    uint32_t *slots = (uint32_t *)(sc + p.off_slots);
+    int32_t *leader = (int32_t *)(sc + p.off_leader);
+    int32_t *choice = (int32_t *)(sc + p.off_choice);
+    const bool ascii = flags & B200R_F_ALL_ASCII;
+    const int32_t *nchars = ascii ? nullptr : (d_nchars ? d_nchars : (const int32_t *)(sc + p.off_nchars));
+    const int32_t *chunk_off = ascii ? nullptr : (const int32_t *)(sc + p.off_chunk_off);
+    if (t->epoch >= 0xFFFFFFF0u) { set_error("batch epoch exhausted; b200r_trie_clear or re-create the table"); return B200R_E_INVALID; }
+    t->epoch++;
+    const unsigned long long tag = (unsigned long long)t->epoch << 32;
+    FuseArgs fa;
+    fa.tab = t->tab; fa.hs = t->hs; fa.cap_log2 = t->cap_log2; fa.dev = t->dev;
+    fa.avail = avail_mask; fa.tag = tag; fa.slots = slots;
+    fa.ticket = (unsigned int *)(sc + p.off_ticket);
+    fa.lb_flag = (unsigned int *)(sc + p.off_lb_flag);
+    fa.lb_part = (uint64_t *)(sc + p.off_lb_part);
+    fa.lb_final = (uint64_t *)(sc + p.off_lb_final);
+    const int ntiles = (int)((max_chunks + HASH_WARPS * WTILE - 1) / (HASH_WARPS * WTILE));
+    if (ntiles > 0) {
+        ProfScope ps__(PK_HASH, st); g_launches += 1;
+        k_hash_tiles<true><<<ntiles, HASH_WARPS * 32, 0, st>>>(
+            d_bytes, d_starts, d_lens, nchars, chunk_base, (const int32_t *)(sc + p.off_tile_first),
+            chunk_off, (int)n, t->chunk_chars, max_chunks, hashes, fa);
+        B200R_LAUNCH_CHECK("k_hash_tiles<fused>");
+    }
+    const int tblocks = (int)((n + 255) / 256);
+    { ProfScope ps__(PK_SELECT, st); g_launches += 1;
+    k_select<<<tblocks, 256, 0, st>>>(t->tab, chunk_base, (int)n, max_chunks, slots, avail_mask, tag,
+                                     seed, seq0, leader, choice, d_match_depth, d_matched_mask, 0u,
+                                     nullptr, nullptr, nullptr);
+    B200R_LAUNCH_CHECK("k_select");
+    }
+    { ProfScope ps__(PK_COMMIT, st); g_launches += 1;
+    k_commit<<<tblocks, 256, 0, st>>>(t->tab, t->dev, chunk_base, (int)n, max_chunks, slots, leader,
+                                     choice, d_match_depth, d_endpoint, d_matched_mask, nullptr);
+    B200R_LAUNCH_CHECK("k_commit");
+    }
+    return B200R_OK;
+}
+
+int b200r_prefix_route_batch_fused(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
+                                   const int32_t *d_lens, const int32_t *d_nchars, int64_t n,
+                                   int64_t max_chunks, uint32_t flags, uint64_t avail_mask,
+                                   uint64_t seed, uint64_t seq0, int32_t *d_endpoint,
+                                   int32_t *d_match_depth, uint64_t *d_matched_mask,
+                                   void *d_scratch, size_t scratch_bytes, void *stream)
+{
+    int rc = b200r_prefix_prep_stage(t, d_bytes, d_starts, d_lens, d_nchars, n, max_chunks, flags,
+                                     d_scratch, scratch_bytes, stream);
+    if (rc) return rc;
+    return b200r_prefix_fused_stage(t, d_bytes, d_starts, d_lens, d_nchars, n, max_chunks, flags,
+                                    avail_mask, seed, seq0, d_endpoint, d_match_depth,
+                                    d_matched_mask, d_scratch, scratch_bytes, stream);
 }
 
 int b200r_prefix_route_batch(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
@@ -2094,10 +2342,10 @@ int b200r_part_route(b200r_trie *t, uint64_t avail_mask, uint64_t seed,
                                            c_owned, pos_owned, hashes);
     B200R_LAUNCH_CHECK("k_part_gather");
     const int nblk = (int)((L.n_max + PREP_BLOCK - 1) / PREP_BLOCK);
-    k_prep_sums<<<nblk, PREP_BLOCK, 0, st>>>(c_owned, nullptr, (int)L.n_max, 1, block_sums, n_dev);
+    k_prep_sums<<<nblk, PREP_BLOCK, 0, st>>>(c_owned, nullptr, (int)L.n_max, 1, block_sums, n_dev, nullptr);
     B200R_LAUNCH_CHECK("k_prep_sums(owned)");
     k_prep_scan<<<nblk, PREP_BLOCK, 0, st>>>(c_owned, nullptr, (int)L.n_max, 1, block_sums, chunk_base,
-                                             tile_first, L.c_max, t->dev, nullptr, nullptr, nullptr, n_dev);
+                                             tile_first, L.c_max, t->dev, nullptr, nullptr, nullptr, n_dev, nullptr);
     B200R_LAUNCH_CHECK("k_prep_scan(owned)");
     }
     // grids are estimates (about two shards' worth); the kernels stride over the rest
