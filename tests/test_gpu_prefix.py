@@ -237,9 +237,9 @@ def test_staged_and_fused_paths_agree_with_the_oracle():
         t.check_status()
         assert t.dump() == orc.dump()
         t.close()
-    # the batch pipeline in its staged flavour
+    # the batch pipeline in its fused flavour (the staged one is the default, tested above)
     t = GpuHashTrie(cap_log2=18)
-    pipe = RoutePipeline(t, fused=False)
+    pipe = RoutePipeline(t, fused=True)
     orc = coracle.TrieOracle()
     seq = 0
     for avail, buf, starts, lens in batches:

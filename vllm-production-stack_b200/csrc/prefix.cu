@@ -338,7 +338,7 @@ struct FuseArgs {
     uint32_t *slots;
     unsigned int *ticket;            // CTA ticket counter (zeroed by k_prep_sums)
     unsigned int *lb_flag;           // per warp tile: 0 nothing, 1 partial key published, 2 final
-    uint64_t *lb_part, *lb_final;    // per warp tile: 2 x u64 each
+    uint64_t *lb_part, *lb_final;    // per warp tile: {k1, stamp, k2, stamp}
 };
 constexpr uint32_t PREOK_BIT = 0x80000000u;
 
@@ -351,6 +351,10 @@ __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned *p)
 __device__ __forceinline__ void st_release_u32(unsigned *p, unsigned v)
 {
     asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void st_cg_2u64(uint64_t *p, uint64_t a, uint64_t b)
+{
+    asm volatile("st.global.cg.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(a), "l"(b) : "memory");
 }
 __device__ __forceinline__ void ld_cg_2u64(const uint64_t *p, uint64_t &a, uint64_t &b)
 {
@@ -508,30 +512,37 @@ k_hash_tiles(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ star
     B200R_SEG_STEP(1) B200R_SEG_STEP(2) B200R_SEG_STEP(4) B200R_SEG_STEP(8) B200R_SEG_STEP(16)
 #undef B200R_SEG_STEP
 
-    // publish the key at the end of this tile for the next tile's carry
+    // Publish the key at the end of this tile for the next tile's carry.  Each key half
+    // travels in its own 16-byte word {half, stamp} written with one vector store, and a
+    // reader accepts a word only if its stamp is the one of this batch: no fence, no
+    // acquire (those would invalidate L1, which serves the hot table entries), and no
+    // clearing between batches.
     const bool head_tile = __shfl_sync(0xffffffffu, (int)inhead, 0);    // lane 0 continues a request
     const bool last_valid = __shfl_sync(0xffffffffu, (int)valid, 31);
     const bool last_inhead = __shfl_sync(0xffffffffu, (int)inhead, 31); // whole tile inside one request
+    const uint64_t stamp_part = fa.tag | 1u, stamp_final = fa.tag | 2u;
     if (lane == 31 && last_valid) {
-        uint64_t *dst = (last_inhead ? fa.lb_part : fa.lb_final) + 2 * tile;
-        dst[0] = p1; dst[1] = p2;
-        st_release_u32(fa.lb_flag + tile, last_inhead ? 1u : 2u);
+        if (last_inhead) { st_cg_2u64(fa.lb_part + 4 * tile, p1, stamp_part); st_cg_2u64(fa.lb_part + 4 * tile + 2, p2, stamp_part); }
+        else { st_cg_2u64(fa.lb_final + 4 * tile, p1, stamp_final); st_cg_2u64(fa.lb_final + 4 * tile + 2, p2, stamp_final); }
     }
     if (head_tile) {
         // decoupled look-back: K_in = P(T-1) + A^32 P(T-2) + ... + A^(32m) F(j)
         uint64_t a1 = 0, a2 = 0, m1 = 1, m2 = 1;
         for (int64_t j = tile - 1; j >= 0; j--) {
-            unsigned f = 0;
-            for (long spins = 0; spins < 40000000L; spins++) {
-                f = ld_acquire_u32(fa.lb_flag + j);
-                if (f) break;
+            uint64_t x1 = 0, x2 = 0, s1, s2;
+            int got = 0;
+            for (long spins = 0; spins < 40000000L && !got; spins++) {
+                ld_cg_2u64(fa.lb_final + 4 * j, x1, s1);
+                ld_cg_2u64(fa.lb_final + 4 * j + 2, x2, s2);
+                if (s1 == stamp_final && s2 == stamp_final) { got = 2; break; }
+                ld_cg_2u64(fa.lb_part + 4 * j, x1, s1);
+                ld_cg_2u64(fa.lb_part + 4 * j + 2, x2, s2);
+                if (s1 == stamp_part && s2 == stamp_part) { got = 1; break; }
                 __nanosleep(32);
             }
-            if (!f) { if (lane == 0) atomicOr(&fa.dev->status, B200R_S_LOOKBACK); break; }
-            uint64_t x1, x2;
-            ld_cg_2u64((f == 2 ? fa.lb_final : fa.lb_part) + 2 * j, x1, x2);
+            if (!got) { if (lane == 0) atomicOr(&fa.dev->status, B200R_S_LOOKBACK); break; }
             a1 += m1 * x1; a2 += m2 * x2;
-            if (f == 2) break;
+            if (got == 2) break;
             m1 = mulc<cpow(KA1, 32)>(m1); m2 = mulc<cpow(KA2, 32)>(m2);
         }
         if (inhead) {
@@ -540,8 +551,8 @@ k_hash_tiles(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ star
             p1 += w1 * a1; p2 += w2 * a2;
         }
         if (lane == 31 && last_valid && last_inhead) {
-            fa.lb_final[2 * tile] = p1; fa.lb_final[2 * tile + 1] = p2;
-            st_release_u32(fa.lb_flag + tile, 2u);
+            st_cg_2u64(fa.lb_final + 4 * tile, p1, stamp_final);
+            st_cg_2u64(fa.lb_final + 4 * tile + 2, p2, stamp_final);
         }
     }
 
@@ -1410,8 +1421,8 @@ static Plan make_plan(int64_t n, int64_t max_chunks, uint32_t flags, bool routin
     p.off_tile_first = o; o += align_up(ntiles * 4);
     p.off_ticket = o;     o += 256;
     p.off_lb_flag = o;    o += align_up(ntiles * 4);
-    p.off_lb_part = o;    o += routing ? align_up(ntiles * 16) : 0;
-    p.off_lb_final = o;   o += routing ? align_up(ntiles * 16) : 0;
+    p.off_lb_part = o;    o += routing ? align_up(ntiles * 32) : 0;
+    p.off_lb_final = o;   o += routing ? align_up(ntiles * 32) : 0;
     p.off_block_sums = o; o += align_up(nblk * 4);
     p.off_nchars = o;     o += ascii ? 0 : align_up((n + 1) * 4);
     p.off_chunk_off = o;  o += ascii ? 0 : align_up((max_chunks + 1) * 4);
