@@ -114,9 +114,9 @@ int b200r_xxh64_chunks_noalloc(const uint8_t *d_bytes, const int64_t *d_starts,
 
 /* ------------------------------------------------------------------------
  * a4/a6  TrieNode / HashTrie.__init__               hashtrie.py:24-43
- * The pointer trie becomes an open-addressing table of 32-byte entries
- * {path key (128 bit), chunk hash, endpoint bitmask}; capacity = 2^cap_log2
- * entries (plus 8 bytes per entry of batch bookkeeping).  Endpoints are bit
+ * The pointer trie becomes an open-addressing table of 64-byte entries
+ * {path key (128 bit), endpoint bitmask, batch bookkeeping | chunk hash};
+ * capacity = 2^cap_log2 entries.  Endpoints are bit
  * indices 0..63.  The reference never evicts, neither does the table: size it
  * for the expected node count at load factor <= 0.5 (b200r_trie_status reports
  * the node count; a full table latches B200R_S_TABLE_FULL).
@@ -352,6 +352,9 @@ int b200r_ring_lookup_batch(b200r_ring *r, const uint8_t *d_bytes, const int64_t
  * b200r_launch_count: kernels enqueued by this library
  * since load (process-wide).
  * ---------------------------------------------------------------------- */
+/* tuning switch of the route stage: claim with one warp per 32-chunk tile (default, 1) or
+ * one warp per request (0); identical results */
+int b200r_set_claim_by_tiles(int on);
 #define B200R_PROF_SLOTS 13
 int b200r_prof_enable(int on);
 int b200r_prof_read(float *ms_out, long long *count_out, int nslots);

@@ -383,3 +383,26 @@ def test_router_micro_batched_concurrent_requests_equal_reference(golden_prefix)
     assert [tr["urls"].index(u) for u in urls] == tr["decisions"]
     assert 1 < r.batcher.batches_routed <= (len(prompts) + 63) // 64 + 1
     routers._reset_singletons_for_tests()
+
+
+def test_claim_per_request_and_per_tile_agree_with_the_oracle():
+    """The route stage can claim with one warp per request or one warp per 32-chunk tile
+    (b200r_set_claim_by_tiles); both must equal the oracle, including requests that span
+    several tiles and tiles that hold several requests."""
+    from b200_router import _lib
+    from b200_router.trie import GpuHashTrie
+    bufL, stL, lnL = traces.long_context_batch(n=200, chars=128 * 70 + 3, group=8, shared_frac=0.4, seed=33)
+    try:
+        for by_tiles in (0, 1):
+            _lib.check(_lib.lib().b200r_set_claim_by_tiles(by_tiles))
+            for s in range(3):
+                t = GpuHashTrie(cap_log2=16)
+                batches = [((1 << 64) - 1, bufL, stL, lnL)] if s == 0 else []
+                for avail_idx, prompts in traces.sharing_stress(n_batches=4, batch=200, n_endpoints=7,
+                                                                max_depth=6, alphabet=2, seed=300 + s):
+                    buf, starts, lens, _ = traces.pack_strings(prompts)
+                    batches.append((sum(1 << i for i in avail_idx), buf, starts, lens))
+                _route_vs_oracle(t, batches, seed=s)
+                t.close()
+    finally:
+        _lib.check(_lib.lib().b200r_set_claim_by_tiles(1))

@@ -27,7 +27,7 @@ def _stream():
 class GpuHashTrie:
     """Open-addressing table of trie nodes on one GPU.
 
-    capacity = 2**cap_log2 entries of 32 bytes (+8 bytes bookkeeping each).  The
+    capacity = 2**cap_log2 entries of 64 bytes.  The
     reference never evicts (routing_logic.py:352) and neither does the table;
     `status()` reports the node count, a full table raises."""
 

@@ -50,6 +50,7 @@ struct ProfSpan { int kid; cudaEvent_t a, b; };
 static bool g_prof_on = false;
 static std::vector<ProfSpan> g_spans;
 static long long g_launches = 0;
+static bool g_claim_by_tiles = true;    // route stage: claim per 32-chunk tile (else per request)
 
 struct ProfScope {
     bool on; cudaStream_t st; ProfSpan sp;
@@ -379,19 +380,26 @@ __device__ __forceinline__ void key_pow(int n, uint64_t &r1, uint64_t &r2)
 //   tickets so that a waited-for tile is always running or done), then finds-or-creates
 //   every node and classifies it exactly like k_claim.  The chunk hashes never go to
 //   memory and the table latency of one warp overlaps the hashing of the others.
-template <bool CLAIM>
-__global__ void __launch_bounds__(HASH_WARPS * 32)
+//   MODE 0  chunk hashing only (a1, and the hash stage of the staged paths)
+//   MODE 1  fused: hash + path keys + claim (carry between tiles by decoupled look-back)
+//   MODE 2  claim from hashes already in memory, one warp per 32-chunk tile: every lane
+//           works (a warp per request leaves a third of them idle on ~21-chunk prompts), no
+//           staging buffer, and the carry of a request that started in an earlier tile is
+//           recomputed from that request's earlier hashes (no communication between tiles)
+template <int MODE>
+__global__ void __launch_bounds__(HASH_WARPS * 32, MODE == 2 ? 8 : 6)
 k_hash_tiles(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ starts,
              const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars,
              const int32_t *__restrict__ chunk_base, const int32_t *__restrict__ tile_first,
              const int32_t *__restrict__ chunk_off, int n, int cc, int64_t max_chunks,
              uint64_t *__restrict__ hashes, FuseArgs fa)
 {
-    __shared__ __align__(1024) uint8_t s_tile[HASH_WARPS * WTILE * 128];
+    constexpr bool CLAIM = MODE != 0;
+    __shared__ __align__(1024) uint8_t s_tile[MODE == 2 ? 16 : HASH_WARPS * WTILE * 128];
     __shared__ unsigned s_bid;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     unsigned bid = blockIdx.x;
-    if (CLAIM) {
+    if (MODE == 1) {
         if (threadIdx.x == 0) s_bid = atomicAdd(fa.ticket, 1u);
         __syncthreads();
         bid = s_bid;
@@ -412,8 +420,10 @@ k_hash_tiles(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ star
         bool live = false;
         if (r < n) {
             q.b = chunk_base[r]; q.b1 = chunk_base[r + 1];
-            q.st = starts[r]; q.ln = lens[r];
-            q.nc = nchars ? nchars[r] : q.ln;
+            if (MODE != 2) {                 // MODE 2 works from hashes: no prompt bytes needed
+                q.st = starts[r]; q.ln = lens[r];
+                q.nc = nchars ? nchars[r] : q.ln;
+            }
             live = (int64_t)q.b < G0 + WTILE;
         }
         const bool nonempty = live && q.b1 > q.b;
@@ -447,8 +457,8 @@ k_hash_tiles(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ star
     const uint8_t *p = nullptr;
     int clen = 0, kind = 0;               // 0 none / done elsewhere, 1 full staged, 3 generic
     int d = 0;                            // depth of the chunk inside its request (0-based)
-    if (valid) {
-        d = (int)(g - mine.b);
+    if (valid) d = (int)(g - mine.b);
+    if (valid && MODE != 2) {
         int off;
         if (mine.nc == mine.ln) {                        // ASCII: chunk = cc bytes
             off = d * cc;
@@ -465,9 +475,12 @@ k_hash_tiles(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ star
         kind = tail_done_by_prep ? 0 : ((aligned && clen == 128) ? 1 : 3);
     }
 
-    // ---- stage this warp's full chunks
-    const uint32_t wrow = (uint32_t)__cvta_generic_to_shared(s_tile) + (uint32_t)(w * WTILE) * 128;
-    {
+    // ---- stage this warp's full chunks, then hash (MODE 2: the hashes are in memory already)
+    uint64_t h = 0;
+    if (MODE == 2) {
+        if (valid) h = hashes[g];
+    } else {
+        const uint32_t wrow = (uint32_t)__cvta_generic_to_shared(s_tile) + (uint32_t)(w * WTILE) * 128;
         const unsigned long long my_src = kind == 1 ? (unsigned long long)(uintptr_t)p : 0ULL;
         // lane copies unit u of chunk c = 4k + sub; (c & 7) = sub ^ 4(k&1), so the swizzled
         // destination is one of two per-lane bases plus k * 512
@@ -482,16 +495,13 @@ k_hash_tiles(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ star
                 cp_async16(((k & 1) ? d_odd : d_even) + k * 512,
                            (const uint8_t *)(uintptr_t)src + (u << 4), 16);
         }
+        // the ragged last chunk of a request was hashed by k_prep_scan: fetch it meanwhile
+        if (MODE == 1 && valid && kind == 0) h = hashes[g];
+        cp_async_wait_all();
+        __syncwarp();
+        if (kind == 1) h = xxh64_row128(wrow + lane * 128, lane & 7);
+        else if (kind == 3) h = xxh64_global(p, clen);
     }
-    // the ragged last chunk of a request was hashed by k_prep_scan: fetch it meanwhile
-    uint64_t h = 0;
-    if (CLAIM && valid && kind == 0) h = hashes[g];
-    cp_async_wait_all();
-    __syncwarp();
-
-    // ---- hash
-    if (kind == 1) h = xxh64_row128(wrow + lane * 128, lane & 7);
-    else if (kind == 3) h = xxh64_global(p, clen);
     if (!CLAIM) {
         if (kind) hashes[g] = h;
         return;
@@ -521,11 +531,31 @@ k_hash_tiles(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ star
     const bool last_valid = __shfl_sync(0xffffffffu, (int)valid, 31);
     const bool last_inhead = __shfl_sync(0xffffffffu, (int)inhead, 31); // whole tile inside one request
     const uint64_t stamp_part = fa.tag | 1u, stamp_final = fa.tag | 2u;
-    if (lane == 31 && last_valid) {
+    if (MODE == 1 && lane == 31 && last_valid) {
         if (last_inhead) { st_cg_2u64(fa.lb_part + 4 * tile, p1, stamp_part); st_cg_2u64(fa.lb_part + 4 * tile + 2, p2, stamp_part); }
         else { st_cg_2u64(fa.lb_final + 4 * tile, p1, stamp_final); st_cg_2u64(fa.lb_final + 4 * tile + 2, p2, stamp_final); }
     }
-    if (head_tile) {
+    if (MODE == 2 && head_tile) {
+        // the request of lane 0 started d0 chunks before this tile: recompute the key at its
+        // depth d0 from its earlier hashes (they are in memory; typically one warp load)
+        const int d0 = __shfl_sync(0xffffffffu, d, 0);
+        const int b_req = __shfl_sync(0xffffffffu, mine.b, 0);
+        Key carry = { KROOT1, KROOT2 };
+        for (int pb = 0; pb < d0; pb += 32) {
+            const int x = pb + lane;
+            const uint64_t hh = x < d0 ? hashes[b_req + x] : 0;
+            const Key k = key_scan_warp(hh, carry, lane);
+            const int last = min(31, d0 - 1 - pb);
+            carry.k1 = __shfl_sync(0xffffffffu, k.k1, last);
+            carry.k2 = __shfl_sync(0xffffffffu, k.k2, last);
+        }
+        if (inhead) {
+            uint64_t w1, w2;
+            key_pow(lane + 1, w1, w2);
+            p1 += w1 * carry.k1; p2 += w2 * carry.k2;
+        }
+    }
+    if (MODE == 1 && head_tile) {
         // decoupled look-back: K_in = P(T-1) + A^32 P(T-2) + ... + A^(32m) F(j)
         uint64_t a1 = 0, a2 = 0, m1 = 1, m2 = 1;
         for (int64_t j = tile - 1; j >= 0; j--) {
@@ -1365,7 +1395,7 @@ __global__ void k_dump(const Entry *__restrict__ tab, const uint64_t *__restrict
             if ((int64_t)idx < max_nodes) {
                 out[4 * idx + 0] = e.k1;
                 out[4 * idx + 1] = e.k2;
-                out[4 * idx + 2] = hs[s];
+                out[4 * idx + 2] = e.h;
                 out[4 * idx + 3] = e.mask;
             }
         }
@@ -1498,7 +1528,7 @@ static int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const in
     const int ntiles = (int)((max_chunks + HASH_WARPS * WTILE - 1) / (HASH_WARPS * WTILE));
     if (ntiles > 0 && !prep_only) {
         { ProfScope ps__(PK_HASH, st); g_launches += 1;
-        k_hash_tiles<false><<<ntiles, HASH_WARPS * 32, 0, st>>>(
+        k_hash_tiles<0><<<ntiles, HASH_WARPS * 32, 0, st>>>(
             d_bytes, d_starts, d_lens, d_nchars, d_chunk_base, tile_first, chunk_off, (int)n, cc,
             max_chunks, d_hashes, FuseArgs());
         B200R_LAUNCH_CHECK("k_hash_chunks");
@@ -1512,6 +1542,12 @@ extern "C" {
 int b200r_abi_version(void) { return B200R_ABI_VERSION; }
 const char *b200r_last_error(void) { return g_err; }
 uint32_t b200r_pick(uint64_t seed, uint64_t seq, uint32_t n) { return pick(seed, seq, n); }
+
+int b200r_set_claim_by_tiles(int on)
+{
+    g_claim_by_tiles = on != 0;
+    return B200R_OK;
+}
 
 int b200r_prof_enable(int on)
 {
@@ -1660,12 +1696,12 @@ int b200r_trie_create(int32_t cap_log2, int32_t chunk_chars, b200r_trie **out)
     const size_t cap = (size_t)1 << cap_log2;
     cudaError_t e;
     if ((e = cudaMalloc(&t->tab, cap * sizeof(Entry))) != cudaSuccess ||
-        (e = cudaMalloc(&t->hs, cap * 8)) != cudaSuccess ||
         (e = cudaMalloc(&t->dev, sizeof(TrieDev))) != cudaSuccess) {
-        cudaFree(t->tab); cudaFree(t->hs); cudaFree(t->dev);
+        cudaFree(t->tab); cudaFree(t->dev);
         delete t;
         return cuda_fail(e, "cudaMalloc(trie)");
     }
+    t->hs = (uint64_t *)t->tab;      // non-null: "store the chunk hash in the entry"
     int rc = b200r_trie_clear(t, nullptr);
     if (rc) { b200r_trie_destroy(t); return rc; }
     B200R_CUDA(cudaStreamSynchronize(nullptr));
@@ -1676,7 +1712,7 @@ int b200r_trie_create(int32_t cap_log2, int32_t chunk_chars, b200r_trie **out)
 int b200r_trie_destroy(b200r_trie *t)
 {
     if (!t) return B200R_OK;
-    cudaFree(t->tab); cudaFree(t->hs); cudaFree(t->dev);
+    cudaFree(t->tab); cudaFree(t->dev);
     delete t;
     return B200R_OK;
 }
@@ -1814,8 +1850,20 @@ int b200r_prefix_route_stage(b200r_trie *t, int64_t n, int64_t max_chunks, uint3
     const int thr = WARPS_PER_CTA * 32;
     const int tblocks = (int)((n + 255) / 256);
     { ProfScope ps__(PK_CLAIM, st); g_launches += 1;
-    k_claim<<<blocks, thr, 0, st>>>(t->tab, t->hs, t->cap_log2, t->dev, hashes, chunk_base,
-                                    (int)n, max_chunks, avail_mask, tag, slots, nullptr);
+    if (g_claim_by_tiles) {
+        // one warp per 32-chunk tile (dense lanes), carry recomputed from the hashes
+        FuseArgs fa = FuseArgs();
+        fa.tab = t->tab; fa.hs = t->hs; fa.cap_log2 = t->cap_log2; fa.dev = t->dev;
+        fa.avail = avail_mask; fa.tag = tag; fa.slots = slots;
+        const int ntiles = (int)((max_chunks + HASH_WARPS * WTILE - 1) / (HASH_WARPS * WTILE));
+        if (ntiles > 0)
+            k_hash_tiles<2><<<ntiles, HASH_WARPS * 32, 0, st>>>(
+                nullptr, nullptr, nullptr, nullptr, chunk_base, (const int32_t *)(sc + p.off_tile_first),
+                nullptr, (int)n, t->chunk_chars, max_chunks, hashes, fa);
+    } else {
+        k_claim<<<blocks, thr, 0, st>>>(t->tab, t->hs, t->cap_log2, t->dev, hashes, chunk_base,
+                                        (int)n, max_chunks, avail_mask, tag, slots, nullptr);
+    }
     B200R_LAUNCH_CHECK("k_claim");
     }
     { ProfScope ps__(PK_SELECT, st); g_launches += 1;
@@ -1894,7 +1942,7 @@ int b200r_prefix_fused_stage(b200r_trie *t, const uint8_t *d_bytes, const int64_
     const int ntiles = (int)((max_chunks + HASH_WARPS * WTILE - 1) / (HASH_WARPS * WTILE));
     if (ntiles > 0) {
         ProfScope ps__(PK_HASH, st); g_launches += 1;
-        k_hash_tiles<true><<<ntiles, HASH_WARPS * 32, 0, st>>>(
+        k_hash_tiles<1><<<ntiles, HASH_WARPS * 32, 0, st>>>(
             d_bytes, d_starts, d_lens, nchars, chunk_base, (const int32_t *)(sc + p.off_tile_first),
             chunk_off, (int)n, t->chunk_chars, max_chunks, hashes, fa);
         B200R_LAUNCH_CHECK("k_hash_tiles<fused>");
