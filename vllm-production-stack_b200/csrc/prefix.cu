@@ -1185,18 +1185,27 @@ k_part_count(const int32_t *__restrict__ chunk_base, const uint64_t *__restrict_
         blk_cnt[(size_t)blockIdx.x * 2 * world + k] = s_cnt[k];
 }
 
-// exclusive scan over the blocks, per owner (one thread per owner and kind)
+// exclusive scan over the blocks, per owner and kind (one warp each, 32 blocks per step)
 __global__ void k_part_scan(const int32_t *__restrict__ blk_cnt, int nblk, int world,
                             int32_t *__restrict__ blk_off, int32_t *__restrict__ totals)
 {
-    const int k = threadIdx.x;
-    if (k >= 2 * world) return;
-    int run = 0;
-    for (int b = 0; b < nblk; b++) {
-        blk_off[(size_t)b * 2 * world + k] = run;
-        run += blk_cnt[(size_t)b * 2 * world + k];
+    const int lane = threadIdx.x & 31;
+    const int nwarps = blockDim.x >> 5;
+    for (int k = threadIdx.x >> 5; k < 2 * world; k += nwarps) {
+        int run = 0;
+        for (int b0 = 0; b0 < nblk; b0 += 32) {
+            const int b = b0 + lane;
+            const int v = b < nblk ? blk_cnt[(size_t)b * 2 * world + k] : 0;
+            int inc = v;
+            for (int sft = 1; sft < 32; sft <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, inc, sft);
+                if (lane >= sft) inc += t;
+            }
+            if (b < nblk) blk_off[(size_t)b * 2 * world + k] = run + inc - v;
+            run += __shfl_sync(0xffffffffu, inc, 31);
+        }
+        if (lane == 0) totals[k] = run;
     }
-    totals[k] = run;
 }
 
 // order-preserving compaction per owner + push into the owners' buffers
@@ -2346,7 +2355,7 @@ int b200r_part_send(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_star
         g_launches += 3;
         k_part_count<<<nblk, PART_BLOCK, 0, st>>>(chunk_base, hashes, (int)n, world, blk_cnt);
         B200R_LAUNCH_CHECK("k_part_count");
-        k_part_scan<<<1, 2 * P2P_MAX_WORLD, 0, st>>>(blk_cnt, nblk, world, blk_off, totals);
+        k_part_scan<<<1, 1024, 0, st>>>(blk_cnt, nblk, world, blk_off, totals);
         B200R_LAUNCH_CHECK("k_part_scan");
         k_part_push<<<nblk, PART_BLOCK, 0, st>>>(
             chunk_base, hashes, (int)n, world, rank, blk_off, (const unsigned long long *)d_peer_bases,
