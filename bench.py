@@ -52,8 +52,9 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=16)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="prefix", choices=["prefix", "session"],
-                    help="prefix = BASELINE metric (default); session = configs[1], 1M session ids")
+    ap.add_argument("--workload", default="prefix", choices=["prefix", "session", "mrqa"],
+                    help="prefix = BASELINE metric (default); session = configs[1], 1M session ids; "
+                         "mrqa = configs[4], multi-round-QA trace replay")
     ap.add_argument("--batch", type=int, default=BATCH, help=argparse.SUPPRESS)
     ap.add_argument("--cpu-sample", type=int, default=BATCH, help=argparse.SUPPRESS)
     ap.add_argument("--no-cpu", action="store_true", help=argparse.SUPPRESS)
@@ -545,6 +546,97 @@ def run_session(args):
         "md5_blocks_per_sec": n * K / (ms * 1e-3), "cpu_baseline": cpu, "gpu_launches": K}))
 
 
+def run_mrqa(args):
+    """configs[4]: replay of a benchmarks/multi-round-qa style trace (users x rounds, every
+    round carries the whole chat history) through the GPU router, one batch per round, vs
+    the Python restatement of the reference on a sample of the same trace (1 GPU)."""
+    import torch
+    from b200_router import traces
+    from b200_router.packing import pack_prompts
+    from b200_router.trie import GpuHashTrie, RoutePipeline
+    users, rounds = 5000, 10
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(0)
+    prompts, _ = traces.multi_round_qa(users=users, rounds=rounds, sys_len=1000, hist_len=200,
+                                       answer_len=100)
+    host = [pack_prompts(prompts[r * users:(r + 1) * users]) for r in range(rounds)]
+    resident = [p.to(dev, non_blocking=False) for p in host]
+    payload = sum(p.payload_bytes for p in host)
+    avail = (1 << 4) - 1
+
+    def run(pipe, batches, ready):
+        seq = 0
+        for p in batches:
+            out = pipe.route(p, avail, SEED, seq, inputs_ready=ready)
+            seq += p.n
+        return out
+    for _ in range(max(args.warmup, 1)):                # warm-up on throw-away tables
+        t = GpuHashTrie(cap_log2=22, device=dev)
+        run(RoutePipeline(t), resident, True)
+        torch.cuda.synchronize()
+        t.close()
+    t = GpuHashTrie(cap_log2=22, device=dev)
+    pipe = RoutePipeline(t)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    run(pipe, resident, True)
+    ev1.record()
+    torch.cuda.synchronize()
+    ms = ev0.elapsed_time(ev1)
+    nodes = t.check_status(count_nodes=True)["num_nodes"]
+    t.close()
+    t = GpuHashTrie(cap_log2=22, device=dev)
+    pipe = RoutePipeline(t)
+    t0 = time.perf_counter()
+    last = run(pipe, host, False)
+    got = last[0].cpu()
+    e2e_s = time.perf_counter() - t0
+    t.close()
+    cpu = None
+    if not args.no_cpu:
+        sample = prompts[:users * 2]                    # the first two rounds
+        rate, want = cpu_port_rate_generic(sample, 4)
+        t = GpuHashTrie(cap_log2=20, device=dev)
+        ep0, _, _ = t.route(host[0].to(dev), avail, SEED, 0)
+        ep1, _, _ = t.route(host[1].to(dev), avail, SEED, users)
+        parity = (ep0.cpu().tolist() + ep1.cpu().tolist()) == want
+        t.close()
+        cpu = {"value": rate, "unit": UNIT, "cores": 1, "kind": "port", "parity_sample_ok": parity,
+               "sample": "first 2 rounds (%d requests) through oracle/prefix_ref.py" % len(sample)}
+    peaks, _ = load_peaks()
+    n = users * rounds
+    print(json.dumps({
+        "metric": METRIC, "value": n / (ms * 1e-3), "unit": UNIT, "n_gpus": 1, "steps": rounds,
+        "warmup": max(args.warmup, 1), "ms_per_step": ms / rounds, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": {"workload": "C5: multi-round-QA replay, %d users x %d rounds, 4 endpoints, one "
+                               "batch per round, prompts %.1f KB on average" % (users, rounds,
+                                                                                payload / n / 1e3)},
+        "prompt_gbs": payload / (ms * 1e-3) / 1e9,
+        "prompt_frac_of_hbm": payload / (ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
+        "e2e": {"value": n / e2e_s, "unit": UNIT, "h2d_bytes_per_step": sum(p.h2d_bytes() for p in host) // rounds,
+                "d2h_bytes_per_step": users * 4},
+        "cpu_baseline": cpu, "table": {"nodes": nodes}, "gpu_launches": int(_lib_launches())}))
+
+
+def _lib_launches():
+    from b200_router import _lib
+    return _lib.launch_count()
+
+
+def cpu_port_rate_generic(prompts, n_endpoints, seed=SEED):
+    from oracle import prefix_ref
+    from oracle.chooser import ChoiceShim
+    from b200_router import traces
+    urls = traces.endpoint_urls(n_endpoints)
+    index_of = {u: i for i, u in enumerate(urls)}
+    router = prefix_ref.PrefixRouterRef(ChoiceShim(index_of, seed))
+    t0 = time.perf_counter()
+    got = router.route_many(urls, prompts)
+    dt = time.perf_counter() - t0
+    return len(prompts) / dt, [index_of[u] for u in got]
+
+
 def load_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     try:
@@ -560,5 +652,7 @@ if __name__ == "__main__":
         run_reference(a)
     elif a.workload == "session":
         run_session(a)
+    elif a.workload == "mrqa":
+        run_mrqa(a)
     else:
         run_b200(a)
