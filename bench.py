@@ -258,6 +258,8 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=dev)
     W, K = args.warmup, args.steps
     nb = W + K
+    if os.environ.get("BENCH_CLAIM_MODE"):      # tuning experiments only (see include/b200_router.h)
+        _lib.check(_lib.lib().b200r_set_claim_by_tiles(int(os.environ["BENCH_CLAIM_MODE"])))
 
     # ---- synthetic batches (host, pinned), this rank's shard of every global batch
     tr = make_trace(args, nb * world)
