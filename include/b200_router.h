@@ -307,7 +307,8 @@ int b200r_p2p_commit(b200r_trie *t, int64_t n, void *d_my_base, int32_t world, i
  * Buffers: one peer-addressable buffer of b200r_part_layout(...)[0] bytes per
  * rank (zeroed once, before the first batch) and a private work buffer of
  * [1] bytes (zeroed once); d_peer_bases = u64[world] base addresses.  cap /
- * rcap = per-rank chunk / request capacity of a batch; epoch = 1, 2, 3, ...
+ * rcap = per-rank chunk / request capacity of a batch (both even: the exchange
+ * ships 16-byte vectors); epoch = 1, 2, 3, ...
  * Per batch and rank: b200r_part_send, b200r_part_route, b200r_part_finish.
  * ---------------------------------------------------------------------- */
 int b200r_part_layout(int32_t world, int64_t cap, int64_t rcap, size_t out[2]);

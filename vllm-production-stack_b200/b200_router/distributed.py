@@ -366,7 +366,8 @@ class PartitionedPrefixRouter:
 
     @staticmethod
     def capacities(max_requests: int, max_chunks: int):
-        return max(int(max_chunks), 64), max(int(max_requests), 4)
+        # even capacities: the exchange ships 16-byte vectors into per-source regions
+        return (max(int(max_chunks), 64) + 1) // 2 * 2, (max(int(max_requests), 4) + 1) // 2 * 2
 
     @staticmethod
     def symm_bytes_for(world: int, max_requests: int, max_chunks: int) -> int:
