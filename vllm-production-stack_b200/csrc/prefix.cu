@@ -2399,28 +2399,24 @@ int b200r_part_send(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_star
     int32_t *totals = (int32_t *)(wk + L.w_totals);
     const int set = (int)(epoch & 1);
     const int nblk = (int)((n + PART_BLOCK - 1) / PART_BLOCK);
+    ProfScope ps__(PK_PUSH, st);
     if (nblk > 0) {
         g_launches += 3;
-        { ProfScope q__(PK_CLASSIFY, st);
         k_part_count<<<nblk, PART_BLOCK, 0, st>>>(chunk_base, hashes, (int)n, world, blk_cnt);
-        B200R_LAUNCH_CHECK("k_part_count"); }
-        { ProfScope q__(PK_APPLY, st);
+        B200R_LAUNCH_CHECK("k_part_count");
         k_part_scan<<<1, 1024, 0, st>>>(blk_cnt, nblk, world, blk_off, totals);
-        B200R_LAUNCH_CHECK("k_part_scan"); }
+        B200R_LAUNCH_CHECK("k_part_scan");
         uint32_t *dest_slot = (uint32_t *)(wk + L.w_dest_slot + (size_t)set * align_up((size_t)rcap * 4));
         uint32_t *req_dst = (uint32_t *)(wk + L.w_req_dst);
         uint64_t *hash_stage = (uint64_t *)(wk + L.w_hash_stage);
         unsigned long long *info_stage = (unsigned long long *)(wk + L.w_info_stage);
-        { ProfScope q__(PK_PUSH, st);
         k_part_push<<<nblk, PART_BLOCK, 0, st>>>(chunk_base, hashes, (int)n, world, blk_off, totals,
                                                  info_stage, dest_slot, req_dst);
-        B200R_LAUNCH_CHECK("k_part_push"); }
+        B200R_LAUNCH_CHECK("k_part_push");
         g_launches += 2;
-        { ProfScope q__(PK_LOOKUP, st);
         k_part_copy<<<(unsigned)std::min<int64_t>((n + WARPS_PER_CTA - 1) / WARPS_PER_CTA, 148 * 8),
                       WARPS_PER_CTA * 32, 0, st>>>(chunk_base, hashes, (int)n, req_dst, hash_stage);
-        B200R_LAUNCH_CHECK("k_part_copy"); }
-        ProfScope q__(PK_INSERT, st);
+        B200R_LAUNCH_CHECK("k_part_copy");
         k_part_bulk<<<148 * 2, 256, 0, st>>>(hash_stage, info_stage, totals, world, rank,
                                              (const unsigned long long *)d_peer_bases,
                                              L.hash_off + (size_t)set * L.hash_set,
