@@ -27,8 +27,7 @@ def build(force: bool = False) -> str:
 def lib():
     global _lib
     if _lib is None:
-        if not os.path.exists(_SO):
-            build()
+        build()                      # no-op unless oracle.c is newer than the library
         L = C.CDLL(_SO)
         L.orc_xxh64.restype = C.c_uint64
         L.orc_xxh64.argtypes = [C.c_void_p, C.c_int64, C.c_uint64]
@@ -73,10 +72,11 @@ def xxh64(data: bytes, seed: int = 0) -> int:
     return lib().orc_xxh64(buf, len(data), seed)
 
 
-def xxh64_chunks(data: bytes, chunk_chars: int = 128):
+def xxh64_chunks(data: bytes, chunk_chars: int = 128, by_bytes: bool = False):
     cap = len(data) // chunk_chars + 2
     out = np.zeros(cap, dtype=np.uint64)
     buf = np.frombuffer(data or b"\0", dtype=np.uint8)
+    lib().orc_set_chunk_by_bytes(int(by_bytes))
     n = lib().orc_xxh64_chunks(_ptr(buf), len(data), chunk_chars, _ptr(out), cap)
     assert n <= cap
     return out[:n]
@@ -108,9 +108,11 @@ class Packed:
 class TrieOracle:
     """Sequential pointer trie with endpoint bitmasks (oracle.c)."""
 
-    def __init__(self, chunk_chars: int = 128):
+    def __init__(self, chunk_chars: int = 128, by_bytes: bool = False):
+        """by_bytes: chunk the UTF-8 bytes (gateway picker) instead of the code points (router)."""
         self.h = lib().orc_trie_new()
         self.chunk_chars = chunk_chars
+        self.by_bytes = by_bytes
 
     def __del__(self):
         try:
@@ -128,6 +130,7 @@ class TrieOracle:
         byts = np.ascontiguousarray(byts, dtype=np.uint8)
         starts = np.ascontiguousarray(starts, dtype=np.int64)
         lens = np.ascontiguousarray(lens, dtype=np.int32)
+        lib().orc_set_chunk_by_bytes(int(self.by_bytes))
         lib().orc_route_batch(self.h, _ptr(byts), _ptr(starts), _ptr(lens), n, self.chunk_chars,
                               avail, seed, seq0, _ptr(ep), _ptr(depth), _ptr(matched))
         return ep, depth, matched
@@ -139,6 +142,7 @@ class TrieOracle:
         byts = np.ascontiguousarray(byts, dtype=np.uint8)
         starts = np.ascontiguousarray(starts, dtype=np.int64)
         lens = np.ascontiguousarray(lens, dtype=np.int32)
+        lib().orc_set_chunk_by_bytes(int(self.by_bytes))
         lib().orc_lookup_batch(self.h, _ptr(byts), _ptr(starts), _ptr(lens), n, self.chunk_chars,
                                avail, _ptr(depth), _ptr(matched))
         return depth, matched
@@ -148,6 +152,7 @@ class TrieOracle:
         starts = np.ascontiguousarray(starts, dtype=np.int64)
         lens = np.ascontiguousarray(lens, dtype=np.int32)
         endpoint = np.ascontiguousarray(endpoint, dtype=np.int32)
+        lib().orc_set_chunk_by_bytes(int(self.by_bytes))
         lib().orc_insert_batch(self.h, _ptr(byts), _ptr(starts), _ptr(lens), len(starts),
                                self.chunk_chars, _ptr(endpoint))
 

@@ -21,6 +21,7 @@ Outputs (small, committed):
 import asyncio
 import json
 import os
+import random
 import sys
 import types
 
@@ -214,11 +215,74 @@ def gen_md5_ring():
             "ring_answers": {k: ring.get_node(k) for k in probe}}
 
 
+def gen_go_picker():
+    """Byte-chunk mode: the gateway picker (src/gateway_inference_extension/prefix_aware_picker.go)
+    cannot be compiled here (no Go toolchain), so its three trie functions are restated below,
+    statement by statement, over python-xxhash (xxhash.Sum64 == XXH64 seed 0):
+      chunkAndHash :154-165  slices the Go string by BYTE index, 128 bytes per chunk
+      insert       :167-189  endpoint added to the root and to every node of the path
+      longestPrefixMatch :191-213  starts from root.endpoints & available (unlike the router,
+                             which starts from `available`), stops at a missing child or an
+                             empty intersection."""
+    import xxhash
+
+    def chunk_and_hash(s: str):
+        b = s.encode("utf-8")
+        return [xxhash.xxh64(b[i:i + 128]).intdigest() for i in range(0, len(b), 128)]
+
+    class Node:
+        def __init__(self):
+            self.children, self.endpoints = {}, set()
+
+    root = Node()
+
+    def insert(key, ep):
+        node = root
+        node.endpoints.add(ep)
+        for h in chunk_and_hash(key):
+            node = node.children.setdefault(h, Node())
+            node.endpoints.add(ep)
+
+    def match(key, avail):
+        node = root
+        matched = node.endpoints & avail
+        for h in chunk_and_hash(key):
+            child = node.children.get(h)
+            if child is None:
+                break
+            node = child
+            cand = node.endpoints & avail
+            if not cand:
+                break
+            matched = cand
+        return matched
+
+    texts = ["", "a", "x" * 128, "y" * 129, "\u00e9" * 64, "\u00e9" * 65, "\u65e5\u672c\u8a9e" * 50,
+             "ab\u00e9" * 100, "hi " * 42 + "hi", "\U0001f600" * 33 + "tail"]
+    chunks = [{"utf8_hex": t.encode().hex(), "hashes": ["%016x" % h for h in chunk_and_hash(t)]}
+              for t in texts]
+    rng = random.Random(11)
+    eps = ["pod-%d" % i for i in range(5)]
+    stems = ["\u00e9" * 70, "sys " * 80, "\u65e5\u672c" * 60]
+    ops = []
+    for step in range(60):
+        key = rng.choice(stems) + "".join(rng.choice("ab\u00e9") for _ in range(rng.randint(0, 200)))
+        avail = sorted(rng.sample(eps, rng.randint(1, 5)))
+        if step % 3 == 2:
+            ops.append({"op": "match", "key": key, "avail": avail, "matched": sorted(match(key, set(avail)))})
+        else:
+            ep = rng.choice(avail)
+            ops.append({"op": "insert", "key": key, "endpoint": ep})
+            insert(key, ep)
+    return {"source": "restatement of prefix_aware_picker.go:154-213 over python-xxhash %s"
+                      % xxhash.VERSION, "endpoints": eps, "chunks": chunks, "ops": ops}
+
+
 def main():
     gold = os.path.join(ROOT, "tests", "golden")
     os.makedirs(gold, exist_ok=True)
     for name, fn in (("xxh64_kat.json", gen_xxh64), ("prefix_traces.json", gen_prefix),
-                     ("md5_ring_kat.json", gen_md5_ring)):
+                     ("md5_ring_kat.json", gen_md5_ring), ("go_picker_kat.json", gen_go_picker)):
         with open(os.path.join(gold, name), "w") as f:
             json.dump(fn(), f, ensure_ascii=True, separators=(",", ":"))
         print(name, os.path.getsize(os.path.join(gold, name)), "bytes")

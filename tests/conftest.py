@@ -51,3 +51,8 @@ def golden_xxh():
 @pytest.fixture(scope="session")
 def golden_md5():
     return load_golden("md5_ring_kat.json")
+
+
+@pytest.fixture(scope="session")
+def golden_go():
+    return load_golden("go_picker_kat.json")

@@ -406,3 +406,78 @@ def test_claim_per_request_and_per_tile_agree_with_the_oracle():
                 t.close()
     finally:
         _lib.check(_lib.lib().b200r_set_claim_by_tiles(1))
+
+
+def test_byte_chunk_mode_reproduces_the_gateway_picker(trie, golden_go):
+    """chunk_by="bytes" (+ from_root_endpoints for lookups) against the restated gateway picker
+    (tests/golden/go_picker_kat.json; prefix_aware_picker.go:154-213): chunk hashes of UTF-8
+    text cut at byte 128 -- inside multi-byte sequences -- and the insert / match trace."""
+    texts = [bytes.fromhex(c["utf8_hex"]).decode() for c in golden_go["chunks"]]
+    base, hs = trie.hash_chunks(pack_prompts(texts, chunk_by="bytes"))
+    base, hs = base.cpu().numpy(), u64(hs)
+    for i, c in enumerate(golden_go["chunks"]):
+        assert ["%016x" % int(h) for h in hs[base[i]:base[i + 1]]] == c["hashes"], i
+    eps = golden_go["endpoints"]
+    for op in golden_go["ops"]:
+        p = pack_prompts([op["key"]], chunk_by="bytes")
+        if op["op"] == "insert":
+            trie.insert(p, torch.tensor([eps.index(op["endpoint"])], dtype=torch.int32))
+        else:
+            avail = sum(1 << eps.index(e) for e in op["avail"])
+            _, matched = trie.longest_prefix_match(p, avail, from_root_endpoints=True)
+            m = int(matched.cpu()[0]) & 0xFFFFFFFFFFFFFFFF
+            assert sorted(e for i, e in enumerate(eps) if m >> i & 1) == op["matched"]
+    trie.check_status()
+
+
+def test_route_in_byte_chunk_mode_vs_oracle():
+    """Sequential-equivalent batch routing with 128-BYTE chunks over non-ASCII prompts."""
+    import random
+    from b200_router.trie import GpuHashTrie
+    rng = random.Random(9)
+    stems = ["é" * 150, "日本語" * 90, "sys " * 100, "\U0001f600" * 70]
+    t = GpuHashTrie(cap_log2=16)
+    orc = coracle.TrieOracle(128, by_bytes=True)
+    seq = 0
+    for b in range(5):
+        prompts = [rng.choice(stems) + "".join(rng.choice("abé日") for _ in range(rng.randint(0, 300)))
+                   for _ in range(300)]
+        avail = 0x3F & ~(1 << 2) if b == 2 else 0x3F
+        p = pack_prompts(prompts, chunk_by="bytes")
+        ep, depth, matched = t.route(p, avail, 5, seq)
+        pk = coracle.Packed([s.encode() for s in prompts])
+        oep, odepth, omatched = orc.route_batch(pk.bytes, pk.starts, pk.lens, avail, 5, seq)
+        seq += len(prompts)
+        assert (ep.cpu().numpy() == oep).all() and (depth.cpu().numpy() == odepth).all()
+        assert (u64(matched) == omatched).all()
+    t.check_status()
+    assert t.dump() == orc.dump()
+    t.close()
+
+
+def test_router_packs_message_parts_without_joining():
+    """route_request hands the chat contents to the native packer as parts; the decisions are
+    those of routing the "\\n".join(...) strings (routing_logic.py:389-407)."""
+    from b200_router import routers
+
+    class Ep:
+        def __init__(self, url): self.url = url
+    eps = [Ep("http://e%d" % i) for i in range(4)]
+    convs = []
+    for u in range(40):
+        msgs = [{"role": "system", "content": "You are helpful. " * 20},
+                {"role": "user", "content": "user %d asks é " % (u % 7) * 30}]
+        for turn in range(u % 4):
+            msgs.append({"role": "assistant", "content": "Hello " * (50 + turn)})
+            msgs.append({"role": "user", "content": [{"type": "text", "text": "more %d" % turn},
+                                                     {"type": "image_url", "image_url": "x"},
+                                                     {"type": "text", "text": "please"}]})
+        convs.append({"messages": msgs})
+    routers._reset_singletons_for_tests()
+    r = routers.PrefixAwareRouter(seed=3)
+    got = [asyncio.run(r.route_request(eps, None, None, None, js)) for js in convs]
+    routers._reset_singletons_for_tests()
+    r2 = routers.PrefixAwareRouter(seed=3)
+    want = [r2.route_batch(eps, [routers.extract_prompt(js)])[0] for js in convs]
+    routers._reset_singletons_for_tests()
+    assert got == want and len(set(got)) > 1

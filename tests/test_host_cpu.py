@@ -79,6 +79,79 @@ def test_pack_prompts_layout():
     assert q.all_ascii and q.nchars is None and q.max_chunks == 4 and q.payload_bytes == 301
 
 
+def test_native_packer_exports_its_header_and_equals_the_python_packer():
+    """libb200pack.so (csrc/packer.cpp): symbols == include/b200_pack.h, and byte-identical
+    output to the pure-Python packer for str prompts, multi-part prompts, both chunking units."""
+    import random
+    L = packing.pack_lib()
+    assert L is not None, "libb200pack.so is not built (python vllm-production-stack_b200/build.py)"
+    text = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "b200_pack.h")).read(), flags=re.S)
+    declared = sorted(set(re.findall(r"\b(b200p_[a-z0-9_]+)\s*\(", text)))
+    out = subprocess.check_output(["nm", "-D", "--defined-only", packing.PACK_LIB_PATH], text=True)
+    assert sorted(set(re.findall(r"\b(b200p_[a-z0-9_]+)\b", out))) == declared and len(declared) == 3
+    rng = random.Random(5)
+    alphabet = ["a", "b", " ", "\u00e9", "\u65e5", "\U0001f600", "\n"]
+
+    def rand_str(lo, hi):
+        return "".join(rng.choice(alphabet) for _ in range(rng.randint(lo, hi)))
+
+    cases = [[], [""], ["", "", ""], ["x" * 16, "y" * 17, "z" * 15], [("a", "b"), (), ("",), ["p", "", "q"]]]
+    for _ in range(30):
+        batch = []
+        for _ in range(rng.randint(1, 40)):
+            if rng.random() < 0.4:
+                batch.append(tuple(rand_str(0, 300) for _ in range(rng.randint(0, 5))))
+            else:
+                batch.append(rand_str(0, 700))
+        cases.append(batch)
+    for batch in cases:
+        for by in ("chars", "bytes"):
+            for sep in ("\n", " \u00e9 "):
+                a = packing._pack_prompts_py(batch, 128, False, by == "bytes", sep)
+                b = packing.pack_prompts(batch, pin=False, chunk_by=by, sep=sep)
+                assert bytes(a.bytes.numpy()) == bytes(b.bytes.numpy())
+                assert a.starts.tolist() == b.starts.tolist() and a.lens.tolist() == b.lens.tolist()
+                assert (a.nchars is None) == (b.nchars is None)
+                assert a.nchars is None or a.nchars.tolist() == b.nchars.tolist()
+                assert (a.n, a.max_chunks, a.all_ascii, a.payload_bytes) == \
+                       (b.n, b.max_chunks, b.all_ascii, b.payload_bytes)
+    arena = packing.PackArena(slots=2, pin=False)
+    first = packing.pack_prompts(["abc", "de"], pin=False, arena=arena)
+    kept = bytes(first.bytes.numpy())
+    packing.pack_prompts(["zzzzzzzz"], pin=False, arena=arena)          # other slot
+    assert bytes(first.bytes.numpy()) == kept
+    with pytest.raises(TypeError):
+        packing.pack_prompts(["ok", 3], pin=False)
+    with pytest.raises(TypeError):
+        packing.pack_prompts([("ok", b"bytes")], pin=False)
+    with pytest.raises(ValueError):
+        packing.pack_prompts(["x"], chunk_by="words")
+
+
+def test_byte_chunk_mode_is_the_gateway_pickers_chunking(golden_go):
+    """chunk_by="bytes": lens == nchars, i.e. the device chunks 128 BYTES
+    (prefix_aware_picker.go:154-165); chunk counts match the golden chunk lists."""
+    texts = [bytes.fromhex(c["utf8_hex"]).decode() for c in golden_go["chunks"]]
+    p = packing.pack_prompts(texts, pin=False, chunk_by="bytes")
+    assert p.all_ascii and p.nchars is None
+    assert p.max_chunks == sum(len(c["hashes"]) for c in golden_go["chunks"])
+    q = packing.pack_prompts(texts, pin=False)
+    assert not q.all_ascii and q.max_chunks < p.max_chunks
+
+
+def test_extract_prompt_parts_stand_for_the_joined_prompt(golden_prefix):
+    tr = [t for t in golden_prefix["traces"] if t["name"] == "request_json_shapes"][0]
+    for js in tr["json_inputs"]:
+        parts = routers.extract_prompt_parts(js)
+        joined = parts if isinstance(parts, str) else "\n".join(parts)
+        assert joined == prefix_ref.flatten_prompt(js)
+        a = packing.pack_prompts([parts], pin=False)
+        b = packing.pack_prompts([joined], pin=False)
+        assert bytes(a.bytes.numpy()) == bytes(b.bytes.numpy()) and a.max_chunks == b.max_chunks
+    with pytest.raises(KeyError):
+        routers.extract_prompt_parts({"neither": 1})
+
+
 def test_extract_prompt_matches_reference_shapes(golden_prefix):
     tr = [t for t in golden_prefix["traces"] if t["name"] == "request_json_shapes"][0]
     for js in tr["json_inputs"]:

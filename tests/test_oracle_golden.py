@@ -161,3 +161,24 @@ def test_session_ref_properties():
     a = r.route_request(eps, None, stats, Rq({"session_id": "abc123"}))
     assert a == r.route_request(eps, None, stats, Rq({"session_id": "abc123"}))
     assert r.route_request(eps, None, stats, Rq({})) == "http://engine2.com"
+
+
+def test_go_picker_byte_chunks_and_trie(golden_go):
+    """Byte-chunk mode of the C oracle against the restated gateway picker
+    (scripts/gen_golden.py:gen_go_picker; prefix_aware_picker.go:154-213): chunk hashes, then
+    the insert / longestPrefixMatch trace (match starts from root.endpoints & available)."""
+    for c in golden_go["chunks"]:
+        data = bytes.fromhex(c["utf8_hex"])
+        got = coracle.xxh64_chunks(data, 128, by_bytes=True)
+        assert ["%016x" % int(h) for h in got] == c["hashes"]
+    eps = golden_go["endpoints"]
+    t = coracle.TrieOracle(128, by_bytes=True)
+    for op in golden_go["ops"]:
+        pk = coracle.Packed([op["key"].encode()])
+        if op["op"] == "insert":
+            t.insert_batch(pk.bytes, pk.starts, pk.lens, np.array([eps.index(op["endpoint"])], dtype=np.int32))
+        else:
+            avail = sum(1 << eps.index(e) for e in op["avail"])
+            depth, matched = t.lookup_batch(pk.bytes, pk.starts, pk.lens, avail)
+            m = int(matched[0]) if depth[0] > 0 else (t.dump()[()] & avail)
+            assert sorted(e for i, e in enumerate(eps) if m >> i & 1) == op["matched"]

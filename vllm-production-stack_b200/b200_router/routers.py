@@ -21,7 +21,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from .packing import PackedPrompts, pack_prompts
+from .packing import PackArena, PackedPrompts, pack_prompts
 from .ring import GpuHashRing
 from .trie import GpuHashTrie
 
@@ -138,15 +138,42 @@ def extract_prompt(request_json: Dict) -> str:
     return request_json["prompt"]
 
 
+def extract_prompt_parts(request_json: Dict):
+    """extract_prompt without the final join: a tuple of parts standing for "\n".join(parts)
+    (or the completions prompt itself).  pack_prompts lays the parts end to end with the
+    separator between them, so long chat histories are copied once, into the packed buffer,
+    instead of twice (routing_logic.py:407 builds the joined string first)."""
+    if "messages" in request_json:
+        messages = request_json["messages"]
+        if not messages:
+            return ""
+        parts = []
+        for message in messages:
+            content = message.get("content", "")
+            if isinstance(content, list):
+                parts.append(" ".join(part.get("text", "") for part in content
+                                      if part.get("type") == "text"))
+            elif content is not None:
+                parts.append(content)
+        return tuple(parts)
+    return request_json["prompt"]
+
+
 class PrefixAwareRouter(_RefPrefix):
     """GPU-backed `prefixaware` routing logic (drop-in for routing_logic.py:347-423)."""
 
     def __init__(self, cap_log2: int = 22, seed: int = 0, device=None,
-                 micro_batch_ms: float = 0.0, micro_batch_max: int = 4096):
+                 micro_batch_ms: float = 0.0, micro_batch_max: int = 4096, chunk_by: str = "chars"):
         """micro_batch_ms > 0: concurrent route_request calls arriving within that window
-        are routed as one GPU batch, in arrival order (b200_router.batching.MicroBatcher)."""
+        are routed as one GPU batch, in arrival order (b200_router.batching.MicroBatcher).
+        chunk_by: "chars" = 128 code points per chunk (this router, hashtrie.py:55); "bytes" =
+        128 UTF-8 bytes per chunk (the gateway picker, prefix_aware_picker.go:154-165)."""
         if hasattr(self, "_initialized"):
             return
+        if chunk_by not in ("chars", "bytes"):
+            raise ValueError("chunk_by must be 'chars' or 'bytes'")
+        self.chunk_by = chunk_by
+        self._arena = PackArena(slots=3)
         self.hashtrie = GpuHashTrie(cap_log2=cap_log2, chunk_chars=128, device=device)
         self.registry = EndpointRegistry()
         self.seed = seed
@@ -164,12 +191,14 @@ class PrefixAwareRouter(_RefPrefix):
         self.seq += packed.n
         return out
 
-    def route_batch(self, endpoints, prompts: Sequence[str]) -> List[str]:
-        """Route prompts in list order against one endpoint set; returns urls."""
+    def route_batch(self, endpoints, prompts: Sequence) -> List[str]:
+        """Route prompts in list order against one endpoint set; returns urls.  A prompt is a
+        str or a tuple of parts (extract_prompt_parts)."""
         if len(prompts) == 0:
             return []
         avail = self.registry.mask(endpoints)
-        ep, _, _ = self.route_packed(avail, pack_prompts(prompts))
+        ep, _, _ = self.route_packed(avail, pack_prompts(prompts, chunk_by=self.chunk_by,
+                                                         arena=self._arena))
         idx = ep.cpu().tolist()
         self.hashtrie.check_status()
         if any(i < 0 for i in idx):
@@ -179,7 +208,7 @@ class PrefixAwareRouter(_RefPrefix):
     # ---- reference API
     async def route_request(self, endpoints, engine_stats, request_stats, request,
                             request_json) -> str:
-        prompt = extract_prompt(request_json)
+        prompt = extract_prompt_parts(request_json)
         if self.batcher is not None:
             return await self.batcher.route(endpoints, prompt)
         return self.route_batch(endpoints, [prompt])[0]

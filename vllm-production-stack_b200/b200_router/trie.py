@@ -110,10 +110,20 @@ class GpuHashTrie:
         return chunk_base, hashes
 
     # -------------------------------------------------------------------- a2
-    def longest_prefix_match(self, p: PackedPrompts, avail_mask: int):
-        """Batch of HashTrie.longest_prefix_match: (depth int32[n], matched int64[n])."""
+    def longest_prefix_match(self, p: PackedPrompts, avail_mask: int, from_root_endpoints: bool = False):
+        """Batch of HashTrie.longest_prefix_match: (depth int32[n], matched int64[n]).
+
+        from_root_endpoints=True gives the gateway picker's variant
+        (prefix_aware_picker.go:191-213): a request that matches no chunk gets
+        root.endpoints & available instead of `available`; together with prompts packed with
+        chunk_by="bytes" this reproduces that picker's trie."""
         chunk_base, hashes = self.hash_chunks(p)
-        return self.lookup_hashes(hashes, chunk_base, p.n, avail_mask)
+        depth, matched = self.lookup_hashes(hashes, chunk_base, p.n, avail_mask)
+        if from_root_endpoints:
+            root = self.status()["root_mask"] & avail_mask & M64
+            root = root - (1 << 64) if root >= (1 << 63) else root
+            matched = torch.where(depth == 0, torch.full_like(matched, root), matched)
+        return depth, matched
 
     def lookup_hashes(self, hashes, chunk_base, n: int, avail_mask: int):
         depth = torch.empty(max(n, 1), dtype=torch.int32, device=self.device)
