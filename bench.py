@@ -438,6 +438,40 @@ def run_b200(args):
     e2e = {"value": n_dec / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
            "d2h_bytes_per_step": args.batch * 4, "ms_per_step": e2e_s / K * 1e3}
 
+    # ---- the same from Python str objects (what a caller of route_batch holds): native packer
+    #      (libb200pack.so) into a pinned arena + H2D + route + D2H, pipelined.  Host-bound:
+    #      reported next to e2e, not instead of it.
+    e2e_strings = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        from b200_router.packing import PackArena, pack_prompts
+        ns = min(4, nb)
+        strs = [prompts_of(*tr.batch_arrays(b), args.batch) for b in range(ns)]
+        arena = PackArena(slots=3)
+        pack_s = 0.0
+        for rep in range(2):                      # rep 0 warms the arena
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            pack_s = 0.0
+            prev = None
+            for k in range(ns):
+                tp = time.perf_counter()
+                pk = pack_prompts(strs[k], arena=arena)
+                pack_s += time.perf_counter() - tp
+                ep, _, _ = router.route(pk, avail_mask(W), SEED, seq)
+                seq += args.batch
+                res_host[k % 3][:ep.numel()].copy_(ep, non_blocking=True)
+                res_ev[k % 3].record()
+                if prev is not None:
+                    res_ev[prev].synchronize()
+                prev = k % 3
+            res_ev[prev].synchronize()
+            str_s = time.perf_counter() - t0
+        e2e_strings = {"value": ns * args.batch / str_s, "unit": UNIT, "ms_per_step": str_s / ns * 1e3,
+                       "pack_ms_per_step": pack_s / ns * 1e3,
+                       "note": "input = list of Python str per step; pack (native, %d cpus) + H2D + "
+                               "route + D2H" % os.cpu_count()}
+        del strs
+
     # ---- CPU baseline (rank 0, N=1 only) + parity of the same sample on a fresh table
     cpu = None
     parity = None
@@ -466,7 +500,8 @@ def run_b200(args):
                 "config": workload_config(args, world),
                 "prompt_gbs": payload / (ms * 1e-3) / 1e9,
                 "prompt_frac_of_hbm": payload / (ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
-                "clocks": clocks, "host_submit_ms_per_step": host_submit_ms, "e2e": e2e, "gpu_launches": int(launches),
+                "clocks": clocks, "host_submit_ms_per_step": host_submit_ms, "e2e": e2e, "e2e_strings": e2e_strings,
+                "gpu_launches": int(launches),
                 "roofline": {"bound": "hbm", "kernel": "k_hash_chunks", "achieved": achieved,
                              "peak": peaks["hbm_gbs"], "unit": "GB/s",
                              "frac": achieved / peaks["hbm_gbs"],

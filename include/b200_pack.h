@@ -30,9 +30,11 @@ int b200p_measure(struct _object *prompts, struct _object *sep, int64_t chunk_ch
 
 /* buf: out[0] bytes; starts/lens/nchars: one entry per prompt.  Padding is zeroed.
  * by_bytes != 0: nchars[i] = lens[i], i.e. chunks are 128 BYTES -- the chunking of the
- * gateway picker (src/gateway_inference_extension/prefix_aware_picker.go:154-165). */
+ * gateway picker (src/gateway_inference_extension/prefix_aware_picker.go:154-165).
+ * threads: worker threads for the copies (0 = automatic, at most 8; 1 = copy on the calling
+ * thread); the Python objects themselves are only touched by the calling thread. */
 int b200p_fill(struct _object *prompts, struct _object *sep, uint8_t *buf, int64_t buf_bytes,
-               int64_t *starts, int32_t *lens, int32_t *nchars, int by_bytes);
+               int64_t *starts, int32_t *lens, int32_t *nchars, int by_bytes, int threads);
 
 #pragma GCC visibility pop
 #ifdef __cplusplus

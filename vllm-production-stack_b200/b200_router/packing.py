@@ -99,7 +99,7 @@ def pack_lib():
             L.b200p_measure.argtypes = [C.py_object, C.py_object, C.c_int64, C.c_int, C.POINTER(C.c_int64)]
             L.b200p_fill.restype = C.c_int
             L.b200p_fill.argtypes = [C.py_object, C.py_object, C.c_void_p, C.c_int64, C.c_void_p,
-                                     C.c_void_p, C.c_void_p, C.c_int]
+                                     C.c_void_p, C.c_void_p, C.c_int, C.c_int]
             _PACK_LIB = L
     return _PACK_LIB or None
 
@@ -128,14 +128,15 @@ class PackArena:
 
 
 def pack_prompts(prompts: Sequence, chunk_chars: int = 128, pin: bool = True, chunk_by: str = "chars",
-                 sep: str = "\n", arena: Optional[PackArena] = None) -> PackedPrompts:
+                 sep: str = "\n", arena: Optional[PackArena] = None, threads: int = 0) -> PackedPrompts:
     """Pack prompts on the host (pinned when a GPU is present).
 
     A prompt is a str, or a list/tuple of str parts standing for sep.join(parts) -- the chat
     messages' contents of routing_logic.py:389-407 -- which is packed without building the joined
     string.  chunk_by="chars" chunks by code points like the reference router (hashtrie.py:55);
     "bytes" chunks the UTF-8 bytes like the gateway picker (prefix_aware_picker.go:154-165).
-    The work is done by the native packer (csrc/packer.cpp) when it is built."""
+    The work is done by the native packer (csrc/packer.cpp) when it is built; `threads` = copy
+    threads for large batches (0 = automatic, up to 8)."""
     if chunk_by not in ("chars", "bytes"):
         raise ValueError("chunk_by must be 'chars' or 'bytes'")
     by_bytes = chunk_by == "bytes"
@@ -158,7 +159,7 @@ def pack_prompts(prompts: Sequence, chunk_chars: int = 128, pin: bool = True, ch
         lens = torch.empty(n, dtype=torch.int32, pin_memory=pinned)
         nchars = torch.empty(n, dtype=torch.int32, pin_memory=pinned)
     if L.b200p_fill(prompts, sep, buf.data_ptr(), total, starts.data_ptr(), lens.data_ptr(),
-                    nchars.data_ptr(), int(by_bytes)):
+                    nchars.data_ptr(), int(by_bytes), threads):
         raise TypeError(L.b200p_last_error().decode())
     same = ascii_ or by_bytes
     return PackedPrompts(buf, starts, lens, None if same else nchars, n, max_chunks, same, payload)

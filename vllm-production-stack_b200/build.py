@@ -45,7 +45,7 @@ def build(force=False, verbose=False):
 def build_packer():
     """The CPython-facing packer: plain C++, needs only Python.h."""
     import sysconfig
-    cmd = [os.environ.get("CXX", "g++"), "-O3", "-std=c++17", "-fPIC", "-shared", "-fvisibility=hidden",
+    cmd = [os.environ.get("CXX", "g++"), "-O3", "-std=c++17", "-fPIC", "-shared", "-fvisibility=hidden", "-pthread",
            "-I", sysconfig.get_paths()["include"], "-I", os.path.join(ROOT, "include"),
            os.path.join(CSRC, "packer.cpp"), "-o", PACK_OUT]
     subprocess.check_call(cmd)

@@ -17,6 +17,8 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
+#include <thread>
+#include <vector>
 
 namespace {
 
@@ -111,9 +113,13 @@ int b200p_measure(PyObject *prompts, PyObject *sep_obj, int64_t chunk_chars, int
 // Pass 2: copy.  buf has out[0] bytes from b200p_measure; starts/lens/nchars have n entries.
 // Padding bytes are zeroed.  by_bytes != 0: nchars[i] = lens[i] (chunk by bytes, the
 // gateway picker's semantics, prefix_aware_picker.go:154-165).
+// threads: worker threads for the copies (0 = pick: one per ~8 MB, at most 8; 1 = none).  The
+// Python objects are only read by the calling thread, which holds the GIL throughout; the
+// workers see raw (pointer, length, destination) triples, which stay valid because the
+// caller's list keeps the strings alive.
 __attribute__((visibility("default")))
 int b200p_fill(PyObject *prompts, PyObject *sep_obj, uint8_t *buf, int64_t buf_bytes, int64_t *starts,
-               int32_t *lens, int32_t *nchars, int by_bytes)
+               int32_t *lens, int32_t *nchars, int by_bytes, int threads)
 {
     if (!prompts || !(PyList_Check(prompts) || PyTuple_Check(prompts))) return fail("prompts must be a list or tuple");
     Piece sep = { "", 0, 0 };
@@ -121,25 +127,55 @@ int b200p_fill(PyObject *prompts, PyObject *sep_obj, uint8_t *buf, int64_t buf_b
     PyObject **items = PySequence_Fast_ITEMS(prompts);
     const Py_ssize_t n = PySequence_Fast_GET_SIZE(prompts);
     if (!buf || (n > 0 && (!starts || !lens || !nchars))) return fail("null output buffer");
+    struct Job { const char *src; int64_t bytes, dst; };      // src == nullptr: zero fill
+    std::vector<Job> jobs;
+    jobs.reserve((size_t)n + (size_t)n / 2 + 4);
     int64_t off = 0;
     for (Py_ssize_t i = 0; i < n; i++) {
         int64_t nb = 0, nc = 0;
-        bool overflow = false;
         const bool ok = for_pieces(items[i], sep, [&](const Piece &pc) {
-            if (off + nb + pc.bytes > buf_bytes) { overflow = true; return; }
-            memcpy(buf + off + nb, pc.p, (size_t)pc.bytes);
+            if (pc.bytes) jobs.push_back({ pc.p, (int64_t)pc.bytes, off + nb });
             nb += pc.bytes; nc += pc.chars;
         });
         if (!ok) return fail("every prompt must be a str or a list/tuple of str");
         const int64_t pitch = (nb + ALIGN - 1) / ALIGN * ALIGN;
-        if (overflow || off + pitch > buf_bytes) return fail("packed buffer too small (prompts changed since b200p_measure?)");
-        memset(buf + off + nb, 0, (size_t)(pitch - nb));
+        if (off + pitch > buf_bytes) return fail("packed buffer too small (prompts changed since b200p_measure?)");
+        if (pitch > nb) jobs.push_back({ nullptr, pitch - nb, off + nb });
         starts[i] = off;
         lens[i] = (int32_t)nb;
         nchars[i] = (int32_t)(by_bytes ? nb : nc);
         off += pitch;
     }
     if (off == 0 && buf_bytes >= ALIGN) memset(buf, 0, ALIGN);
+    auto run = [&](size_t a, size_t b) {
+        for (size_t j = a; j < b; j++) {
+            if (jobs[j].src) memcpy(buf + jobs[j].dst, jobs[j].src, (size_t)jobs[j].bytes);
+            else memset(buf + jobs[j].dst, 0, (size_t)jobs[j].bytes);
+        }
+    };
+    int T = threads;
+    if (T <= 0) {
+        T = (int)(off >> 23) + 1;
+        const int hw = (int)std::thread::hardware_concurrency();
+        if (T > 8) T = 8;
+        if (hw > 0 && T > hw) T = hw;
+    }
+    if (T <= 1 || jobs.size() < 64) {
+        run(0, jobs.size());
+        return 0;
+    }
+    // equal byte shares: jobs are in destination order, so job j ends at dst + bytes
+    std::vector<std::thread> pool;
+    size_t a = 0;
+    for (int t = 0; t < T; t++) {
+        size_t b = a;
+        const int64_t until = off / T * (t + 1);
+        if (t == T - 1) b = jobs.size();
+        else while (b < jobs.size() && jobs[b].dst + jobs[b].bytes <= until) b++;
+        if (b > a) pool.emplace_back(run, a, b);
+        a = b;
+    }
+    for (auto &th : pool) th.join();
     return 0;
 }
 
