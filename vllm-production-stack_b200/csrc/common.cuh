@@ -293,6 +293,65 @@ __device__ __forceinline__ uint32_t table_claim(Entry *tab, uint64_t *hs, int ca
     return SLOT_NONE;
 }
 
+// One 32-byte load of the probe sector {k1, k2, mask, first} (LDG.256, sm_100): a probe
+// that finds its node needs no second access for the mask and the first-toucher word.
+__device__ __forceinline__ void ld_entry_l1(const Entry *e, uint64_t &a, uint64_t &b, uint64_t &mask,
+                                            uint64_t &first)
+{
+    asm volatile("ld.global.ca.v4.u64 {%0, %1, %2, %3}, [%4];"
+                 : "=l"(a), "=l"(b), "=l"(mask), "=l"(first) : "l"(e) : "memory");
+}
+
+// table_claim that also returns the node's mask and first-toucher word as seen by the
+// probe.  For a node that did not exist when it was probed both are 0, which is also the
+// truth for the rest of the claim kernel (masks only change in the commit kernel; a stale
+// `first` is only a hint that saves an atomicMax).
+__device__ __forceinline__ uint32_t table_claim_mf(Entry *tab, int cap_log2, uint64_t k1, uint64_t k2,
+                                                   uint64_t h, bool *created, uint64_t *mask,
+                                                   uint64_t *first)
+{
+    if (k1 == 0) k1 = 1;
+    if (k2 == 0) k2 = 1;
+    const uint32_t m = (1u << cap_log2) - 1;
+    uint32_t s = slot_of(k1, k2, cap_log2);
+    *created = false;
+    for (uint32_t probe = 0; probe <= m; probe++) {
+        Entry *e = tab + s;
+        uint64_t a, b;
+        ld_entry_l1(e, a, b, *mask, *first);
+        for (;;) {
+            if (a == k1 && b == k2) return s;
+            if (a == 0 && b == 0) {
+                cas128(e, k1, k2, a, b);
+                *mask = 0; *first = 0;
+                if (a == 0 && b == 0) {
+                    e->h = h;
+                    *created = true;
+                    return s;
+                }
+                continue;           // somebody else took it: re-examine (a,b)
+            }
+            if ((a == k1 && b == 0) || (a == 0 && b == k2)) {   // torn read: retry
+                ld_key(e, a, b);
+                *mask = 0; *first = 0;
+                continue;
+            }
+            break;                  // other key
+        }
+        s = (s + 1) & m;
+    }
+    return SLOT_NONE;
+}
+
+// A^(n+1) for n = 0..31, both key lanes: carry multipliers of a 32-chunk tile
+#define B200R_KP(N) { cpow(KA1, N), cpow(KA2, N) }
+__device__ const ulonglong2 g_key_pow[32] = {
+    B200R_KP(1), B200R_KP(2), B200R_KP(3), B200R_KP(4), B200R_KP(5), B200R_KP(6), B200R_KP(7), B200R_KP(8),
+    B200R_KP(9), B200R_KP(10), B200R_KP(11), B200R_KP(12), B200R_KP(13), B200R_KP(14), B200R_KP(15), B200R_KP(16),
+    B200R_KP(17), B200R_KP(18), B200R_KP(19), B200R_KP(20), B200R_KP(21), B200R_KP(22), B200R_KP(23), B200R_KP(24),
+    B200R_KP(25), B200R_KP(26), B200R_KP(27), B200R_KP(28), B200R_KP(29), B200R_KP(30), B200R_KP(31), B200R_KP(32) };
+#undef B200R_KP
+
 // --------------------------------------------------------------- tie-break
 __device__ __host__ __forceinline__ uint32_t pick(uint64_t seed, uint64_t seq, uint32_t n)
 {

@@ -338,6 +338,7 @@ struct FuseArgs {
     Entry *tab; uint64_t *hs; int cap_log2; TrieDev *dev;
     uint64_t avail; unsigned long long tag;
     uint32_t *slots;
+    int32_t *chunk_req;              // request owning each chunk: written by MODE 0, read by MODE 2
     unsigned int *ticket;            // CTA ticket counter (zeroed by k_prep_sums)
     unsigned int *lb_flag;           // per warp tile: 0 nothing, 1 partial key published, 2 final
     uint64_t *lb_part, *lb_final;    // per warp tile: {k1, stamp, k2, stamp}
@@ -411,11 +412,18 @@ k_hash_tiles(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ star
     if (total > max_chunks) total = max_chunks;
     if (G0 >= total) return;                                   // whole warp
 
-    // ---- map: which request owns each of the 32 chunks?
-    const int r0 = tile_first[tile];
+    // ---- map: which request owns each of the 32 chunks?  (MODE 2 reads what MODE 0 found)
     ReqRec mine = { 0, 0, 0, 0, 0 };      // record of the request that owns this lane's chunk
-    int mine_r = r0;
-    for (int jb = 0;; jb += 32) {
+    int mine_r = 0;
+    if (MODE == 2) {
+        if (G0 + lane < total) {
+            mine_r = fa.chunk_req[G0 + lane];
+            mine.b = chunk_base[mine_r];
+        }
+    }
+    const int r0 = MODE == 2 ? 0 : tile_first[tile];
+    if (MODE != 2) mine_r = r0;
+    for (int jb = 0; MODE != 2; jb += 32) {
         const int r = r0 + jb + lane;
         ReqRec q = { 0, 0, 0, 0, 0 };
         bool live = false;
@@ -455,6 +463,8 @@ k_hash_tiles(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ star
     // ---- chunk descriptor
     const int64_t g = G0 + lane;
     const bool valid = g < total;
+    // chunk -> request map for the tile claim kernel (stored now: mine_r is not needed again)
+    if (MODE == 0 && valid && fa.chunk_req) fa.chunk_req[g] = mine_r;
     const uint8_t *p = nullptr;
     int clen = 0, kind = 0;               // 0 none / done elsewhere, 1 full staged, 3 generic
     int d = 0;                            // depth of the chunk inside its request (0-based)
@@ -551,9 +561,8 @@ k_hash_tiles(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ star
             carry.k2 = __shfl_sync(0xffffffffu, k.k2, last);
         }
         if (inhead) {
-            uint64_t w1, w2;
-            key_pow(lane + 1, w1, w2);
-            p1 += w1 * carry.k1; p2 += w2 * carry.k2;
+            const ulonglong2 w = g_key_pow[lane];
+            p1 += w.x * carry.k1; p2 += w.y * carry.k2;
         }
     }
     if (MODE == 1 && head_tile) {
@@ -590,21 +599,24 @@ k_hash_tiles(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ star
     // ---- find-or-create + classify (same as k_claim)
     if (valid) {
         bool created = false;
-        const uint32_t s = table_claim(fa.tab, fa.hs, fa.cap_log2, p1, p2, h, &created);
+        uint64_t m = 0, cur = 0;
+        uint32_t s;
+        if (MODE == 2) {
+            s = table_claim_mf(fa.tab, fa.cap_log2, p1, p2, h, &created, &m, &cur);
+        } else {
+            s = table_claim(fa.tab, fa.hs, fa.cap_log2, p1, p2, h, &created);
+            if (s != SLOT_NONE && !created) m = fa.tab[s].mask;
+        }
         if (s == SLOT_NONE) {
             atomicOr(&fa.dev->status, B200R_S_TABLE_FULL);
             fa.slots[g] = SLOT_NONE;
+        } else if (m & fa.avail) {
+            fa.slots[g] = s | PREOK_BIT;
         } else {
-            const uint64_t m = created ? 0 : fa.tab[s].mask;
-            if (m & fa.avail) {
-                fa.slots[g] = s | PREOK_BIT;
-            } else {
-                fa.slots[g] = s;
-                const unsigned long long minev = fa.tag | (unsigned long long)(~(unsigned)mine_r);
-                unsigned long long cur = 0;
-                if (!created) cur = *(volatile unsigned long long *)&fa.tab[s].first;
-                if (cur < minev) atomicMax(&fa.tab[s].first, minev);
-            }
+            fa.slots[g] = s;
+            const unsigned long long minev = fa.tag | (unsigned long long)(~(unsigned)mine_r);
+            if (MODE != 2 && !created) cur = *(volatile unsigned long long *)&fa.tab[s].first;
+            if (cur < minev) atomicMax(&fa.tab[s].first, minev);
         }
     }
 }
@@ -1492,7 +1504,7 @@ static inline size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct Plan {           // carve-up of the caller's scratch buffer
     size_t off_tile_first, off_block_sums, off_nchars, off_chunk_off, off_chunk_base, off_hashes,
-        off_slots, off_leader, off_choice, off_ticket, off_lb_flag, off_lb_part, off_lb_final, total;
+        off_slots, off_leader, off_choice, off_ticket, off_lb_flag, off_lb_part, off_lb_final, off_chunk_req, total;
 };
 
 static Plan make_plan(int64_t n, int64_t max_chunks, uint32_t flags, bool routing)
@@ -1515,6 +1527,7 @@ static Plan make_plan(int64_t n, int64_t max_chunks, uint32_t flags, bool routin
     p.off_slots = o;      o += routing ? align_up((max_chunks + 1) * 4) : 0;
     p.off_leader = o;     o += routing ? align_up((n + 1) * 4) : 0;
     p.off_choice = o;     o += routing ? align_up((n + 1) * 4) : 0;
+    p.off_chunk_req = o;  o += routing ? align_up((max_chunks + 1) * 4) : 0;
     p.total = o + 256;
     return p;
 }
@@ -1539,7 +1552,7 @@ static int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const in
                        const int32_t *d_nchars, int64_t n, int32_t cc, uint32_t flags,
                        int32_t *d_chunk_base, uint64_t *d_hashes, int64_t max_chunks,
                        uint8_t *scratch, const Plan &p, TrieDev *dev, cudaStream_t st,
-                       bool prep_only = false)
+                       bool prep_only = false, int32_t *chunk_req = nullptr)
 {
     int32_t *tile_first = (int32_t *)(scratch + p.off_tile_first);
     int32_t *block_sums = (int32_t *)(scratch + p.off_block_sums);
@@ -1582,9 +1595,11 @@ static int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const in
     const int ntiles = (int)((max_chunks + HASH_WARPS * WTILE - 1) / (HASH_WARPS * WTILE));
     if (ntiles > 0 && !prep_only) {
         { ProfScope ps__(PK_HASH, st); g_launches += 1;
+        FuseArgs fa0 = FuseArgs();
+        fa0.chunk_req = chunk_req;          // chunk -> request map for the tile claim kernel
         k_hash_tiles<0><<<ntiles, HASH_WARPS * 32, 0, st>>>(
             d_bytes, d_starts, d_lens, d_nchars, d_chunk_base, tile_first, chunk_off, (int)n, cc,
-            max_chunks, d_hashes, FuseArgs());
+            max_chunks, d_hashes, fa0);
         B200R_LAUNCH_CHECK("k_hash_chunks");
         }
     }
@@ -1865,7 +1880,8 @@ int b200r_prefix_hash_stage(b200r_trie *t, const uint8_t *d_bytes, const int64_t
     uint8_t *sc = (uint8_t *)d_scratch;
     return launch_hash(d_bytes, d_starts, d_lens, d_nchars, n, t->chunk_chars, flags,
                        (int32_t *)(sc + p.off_chunk_base), (uint64_t *)(sc + p.off_hashes),
-                       max_chunks, sc, p, t->dev, (cudaStream_t)stream);
+                       max_chunks, sc, p, t->dev, (cudaStream_t)stream, false,
+                       (int32_t *)(sc + p.off_chunk_req));
 }
 
 int b200r_prefix_route_stage(b200r_trie *t, int64_t n, int64_t max_chunks, uint32_t flags,
@@ -1909,6 +1925,7 @@ int b200r_prefix_route_stage(b200r_trie *t, int64_t n, int64_t max_chunks, uint3
         FuseArgs fa = FuseArgs();
         fa.tab = t->tab; fa.hs = t->hs; fa.cap_log2 = t->cap_log2; fa.dev = t->dev;
         fa.avail = avail_mask; fa.tag = tag; fa.slots = slots;
+        fa.chunk_req = (int32_t *)(sc + p.off_chunk_req);
         const int ntiles = (int)((max_chunks + HASH_WARPS * WTILE - 1) / (HASH_WARPS * WTILE));
         if (ntiles > 0)
             k_hash_tiles<2><<<ntiles, HASH_WARPS * 32, 0, st>>>(
