@@ -152,6 +152,21 @@ def test_extract_prompt_parts_stand_for_the_joined_prompt(golden_prefix):
         routers.extract_prompt_parts({"neither": 1})
 
 
+def test_register_tail_hash_equals_xxh64_on_the_host(tmp_path):
+    """csrc/tailhash.cuh (the ragged-last-chunk hash of k_prep_scan, written with static
+    register indexing) compiled for the host and held against the oracle's XXH64 for every
+    length 1..127 on random bytes."""
+    from oracle import coracle
+    coracle.lib()
+    exe = str(tmp_path / "tailhash_host_test")
+    odir = os.path.join(ROOT, "oracle")
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-I", os.path.join(ROOT, "vllm-production-stack_b200", "csrc"),
+                           os.path.join(ROOT, "tests", "tailhash_host_test.cpp"),
+                           os.path.join(odir, "liboracle.so"), "-Wl,-rpath," + odir, "-o", exe])
+    out = subprocess.check_output([exe], text=True)
+    assert "bad = 0" in out
+
+
 def test_extract_prompt_matches_reference_shapes(golden_prefix):
     tr = [t for t in golden_prefix["traces"] if t["name"] == "request_json_shapes"][0]
     for js in tr["json_inputs"]:

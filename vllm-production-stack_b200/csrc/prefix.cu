@@ -21,6 +21,10 @@
 #include <vector>
 
 #include "common.cuh"
+#define B200R_TH_FN __device__ __forceinline__
+#define B200R_TH_MUL(C, x) ::b200r::mulc<C>(x)
+#define B200R_TH_ROTL(R, x) ::b200r::rotl<R>(x)
+#include "tailhash.cuh"
 
 namespace b200r {
 
@@ -165,14 +169,18 @@ k_prep_scan(const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars
                 const uint8_t *q = bytes + starts[i];
                 if ((((uintptr_t)q) & 15) == 0) {
                     const uint8_t *tp = q + (ln - tail);
-                    if (tail <= 128 && (((uintptr_t)tp) & 15) == 0) {
+                    if (tail < 128 && (((uintptr_t)tp) & 15) == 0) {
                         // fetch the whole tail with independent 16-byte loads first (one DRAM
-                        // round trip instead of one per stripe), then hash it out of local memory
-                        uint4 loc[8];
+                        // round trip instead of one per stripe), then hash it out of registers
+                        // (tailhash.cuh: static register indexing, no local memory)
+                        uint64_t wv[16];
 #pragma unroll
-                        for (int u = 0; u < 8; u++)
-                            loc[u] = (u * 16 < tail) ? __ldg((const uint4 *)tp + u) : make_uint4(0, 0, 0, 0);
-                        hashes[gl] = xxh64_global((const uint8_t *)loc, tail);
+                        for (int u = 0; u < 8; u++) {
+                            const uint4 q = (u * 16 < tail) ? __ldg((const uint4 *)tp + u) : make_uint4(0, 0, 0, 0);
+                            wv[2 * u] = u64_of(q.x, q.y);
+                            wv[2 * u + 1] = u64_of(q.z, q.w);
+                        }
+                        hashes[gl] = b200r_th::xxh64_tail_words(wv, tail);
                     } else {
                         hashes[gl] = xxh64_global(tp, tail);
                     }
@@ -795,12 +803,15 @@ select_request(int i, const Entry *__restrict__ tab, const int32_t *__restrict__
     int dstar = 0;
     uint32_t star_slot = SLOT_NONE, star_first = 0;
     bool go = true;
-    for (int d0 = 0; d0 < sp.C && go; d0 += 4) {
-        uint32_t v[4];
+    // slots are fetched eight at a time (independent loads: one L2 round trip per group); the
+    // first-toucher words stay lazy -- the walk usually ends at the first of them, and each
+    // is a random table sector
+    for (int d0 = 0; d0 < sp.C && go; d0 += 8) {
+        uint32_t v[8];
 #pragma unroll
-        for (int k = 0; k < 4; k++) v[k] = (d0 + k < sp.C) ? sl[d0 + k] : SLOT_NONE;
+        for (int k = 0; k < 8; k++) v[k] = (d0 + k < sp.C) ? sl[d0 + k] : SLOT_NONE;
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
+        for (int k = 0; k < 8; k++) {
             if (!go) break;
             const uint32_t x = v[k];
             bool ok = false;
@@ -869,9 +880,15 @@ commit_request(int i, Entry *__restrict__ tab, TrieDev *dev, const int32_t *__re
     const uint64_t bit = 1ULL << e;
     if (!(dev->root_mask & bit)) atomicOr((unsigned long long *)&dev->root_mask, bit);
     const ReqSpan sp = req_span(chunk_base, i, max_chunks);
-    for (int d = depth[i]; d < sp.C; d++) {
-        const uint32_t x = slots[sp.b0 + d];
-        if (x != SLOT_NONE) atomicOr((unsigned long long *)&tab[x & ~PREOK_BIT].mask, bit);
+    // slot loads first, eight at a time, then the atomics: the compiler will not move a load
+    // across an atomic, and one L2 round trip per node would serialise the new tail of a path
+    for (int d = depth[i]; d < sp.C; d += 8) {
+        uint32_t x[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) x[k] = (d + k < sp.C) ? slots[sp.b0 + d + k] : SLOT_NONE;
+#pragma unroll
+        for (int k = 0; k < 8; k++)
+            if (x[k] != SLOT_NONE) atomicOr((unsigned long long *)&tab[x[k] & ~PREOK_BIT].mask, bit);
     }
 }
 
