@@ -880,15 +880,11 @@ commit_request(int i, Entry *__restrict__ tab, TrieDev *dev, const int32_t *__re
     const uint64_t bit = 1ULL << e;
     if (!(dev->root_mask & bit)) atomicOr((unsigned long long *)&dev->root_mask, bit);
     const ReqSpan sp = req_span(chunk_base, i, max_chunks);
-    // slot loads first, eight at a time, then the atomics: the compiler will not move a load
-    // across an atomic, and one L2 round trip per node would serialise the new tail of a path
-    for (int d = depth[i]; d < sp.C; d += 8) {
-        uint32_t x[8];
-#pragma unroll
-        for (int k = 0; k < 8; k++) x[k] = (d + k < sp.C) ? slots[sp.b0 + d + k] : SLOT_NONE;
-#pragma unroll
-        for (int k = 0; k < 8; k++)
-            if (x[k] != SLOT_NONE) atomicOr((unsigned long long *)&tab[x[k] & ~PREOK_BIT].mask, bit);
+    // (fetching the slots eight at a time before the atomics was tried: same time live, slower
+    // cold -- the atomics then start later; the plain loop lets them trail the loads)
+    for (int d = depth[i]; d < sp.C; d++) {
+        const uint32_t x = slots[sp.b0 + d];
+        if (x != SLOT_NONE) atomicOr((unsigned long long *)&tab[x & ~PREOK_BIT].mask, bit);
     }
 }
 
