@@ -1,4 +1,7 @@
-"""World-size-2 run of the sharded routing orchestration on CPUs (gloo).
+"""World-size-2 runs of the multi-GPU routing designs on CPUs (gloo).
+
+Second test: the partitioned design as an algorithm (tests/fake_part_router.py).
+First test:
 
 The device steps are emulated (tests/fake_shard_ops.py); what is under test is
 b200_router.distributed.ShardedPrefixRouter: shard bookkeeping, the three
@@ -71,3 +74,46 @@ def test_two_rank_sharded_routing_equals_sequential_oracle():
         assert got_depth == odepth.tolist(), b
         assert got_matched == omatched.tolist(), b
     assert res[0][1] == res[1][1] == orc.dump()
+
+
+def _part_worker(rank, initfile, resfile):
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    sys.path.insert(0, here)
+    from fake_part_router import FakePartitionedRouter
+    dist.init_process_group("gloo", init_method="file://" + initfile, rank=rank, world_size=WORLD)
+    router = FakePartitionedRouter()
+    results = []
+    for avail, p0, p1 in _shards():
+        results.append(router.route((p0, p1)[rank], avail, 77))
+    with open(resfile + str(rank), "wb") as f:
+        pickle.dump((results, router.dump()), f)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_partitioned_routing_equals_sequential_oracle():
+    """The partitioned design (bench.py --gpus N default; kernels in csrc/prefix.cu k_part_*)
+    as an algorithm, in two real processes over gloo: ownership by first-chunk hash, each
+    partition routed in global order, tie-break counter from the global position.  Decisions
+    equal sequential routing of the rank-major batch and the union of the partitions is the
+    sequential trie (root masks OR-ed, no node in two partitions)."""
+    tmp = tempfile.mkdtemp()
+    initfile, resfile = os.path.join(tmp, "init"), os.path.join(tmp, "res")
+    mp.spawn(_part_worker, args=(initfile, resfile), nprocs=WORLD, join=True)
+    res = [pickle.load(open(resfile + str(r), "rb")) for r in range(WORLD)]
+    orc = coracle.TrieOracle()
+    seq = 0
+    for b, (avail, p0, p1) in enumerate(_shards()):
+        buf, starts, lens, _ = traces.pack_strings(p0 + p1)
+        oep, odepth, omatched = orc.route_batch(buf, starts, lens, avail, 77, seq)
+        seq += len(p0) + len(p1)
+        for k, want in enumerate((oep, odepth, omatched)):
+            assert res[0][0][b][k] + res[1][0][b][k] == want.tolist(), (b, k)
+    d0, d1 = res[0][1], res[1][1]
+    assert not (set(d0) & set(d1)) - {()}
+    merged = dict(d0)
+    merged.update(d1)
+    merged[()] = d0[()] | d1[()]
+    assert merged == orc.dump()
+    assert len(d0) > 1 and len(d1) > 1          # both partitions hold something
