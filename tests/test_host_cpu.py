@@ -120,6 +120,18 @@ def test_native_packer_exports_its_header_and_equals_the_python_packer():
     kept = bytes(first.bytes.numpy())
     packing.pack_prompts(["zzzzzzzz"], pin=False, arena=arena)          # other slot
     assert bytes(first.bytes.numpy()) == kept
+    pipe = packing.PackPipeline(arena=packing.PackArena(slots=4, pin=False), workers=2, pin=False)
+    sets = [["p%d-%d" % (b, i) * (i % 7 + 1) for i in range(50)] for b in range(6)]
+    for b in sets[:3]:
+        pipe.submit(b)
+    with pytest.raises(RuntimeError):       # a 4-slot arena holds 3 queued batches + 1 in use
+        pipe.submit(sets[3])
+    for k, b in enumerate(sets):            # results come back in submission order
+        got = pipe.next()
+        assert bytes(got.bytes.numpy()) == bytes(packing._pack_prompts_py(b, 128, False, False, "\n").bytes.numpy())
+        if k + 3 < len(sets):
+            pipe.submit(sets[k + 3])
+    pipe.close()
     with pytest.raises(TypeError):
         packing.pack_prompts(["ok", 3], pin=False)
     with pytest.raises(TypeError):

@@ -8,6 +8,7 @@ carries Python's len(str) (code points) because the reference chunks the *str*
 """
 import ctypes as C
 import os
+import threading
 from dataclasses import dataclass
 from typing import List, Optional, Sequence
 
@@ -113,6 +114,7 @@ class PackArena:
         self.pin = pin and torch.cuda.is_available()
         self._slots = [dict() for _ in range(max(slots, 1))]
         self._i = 0
+        self._lock = threading.Lock()
 
     def _get(self, slot, name, numel, dtype):
         t = slot.get(name)
@@ -121,10 +123,37 @@ class PackArena:
         return t[:numel]
 
     def take(self, nbytes: int, n: int):
-        slot = self._slots[self._i % len(self._slots)]
-        self._i += 1
+        with self._lock:
+            slot = self._slots[self._i % len(self._slots)]
+            self._i += 1
         return (self._get(slot, "bytes", nbytes, torch.uint8), self._get(slot, "starts", n, torch.int64),
                 self._get(slot, "lens", n, torch.int32), self._get(slot, "nchars", n, torch.int32))
+
+
+class PackPipeline:
+    """Packs batches ahead of their use on worker threads.  The copy phase of the native packer
+    runs without the GIL, so two batches in flight roughly double the packing rate; results
+    come back in submission order."""
+
+    def __init__(self, arena: Optional["PackArena"] = None, workers: int = 2, **pack_kwargs):
+        from concurrent.futures import ThreadPoolExecutor
+        self.arena = arena if arena is not None else PackArena(slots=workers + 2)
+        self.kwargs = pack_kwargs
+        self._pool = ThreadPoolExecutor(max_workers=max(workers, 1))
+        self._queue = []
+
+    def submit(self, prompts):
+        # every batch in the queue, and every result the caller still uses, holds one arena slot
+        if len(self._queue) >= len(self.arena._slots) - 1:
+            raise RuntimeError("PackPipeline: %d batches already queued for an arena of %d slots"
+                               % (len(self._queue), len(self.arena._slots)))
+        self._queue.append(self._pool.submit(pack_prompts, prompts, arena=self.arena, **self.kwargs))
+
+    def next(self) -> "PackedPrompts":
+        return self._queue.pop(0).result()
+
+    def close(self):
+        self._pool.shutdown(wait=True)
 
 
 def pack_prompts(prompts: Sequence, chunk_chars: int = 128, pin: bool = True, chunk_by: str = "chars",

@@ -114,9 +114,10 @@ int b200p_measure(PyObject *prompts, PyObject *sep_obj, int64_t chunk_chars, int
 // Padding bytes are zeroed.  by_bytes != 0: nchars[i] = lens[i] (chunk by bytes, the
 // gateway picker's semantics, prefix_aware_picker.go:154-165).
 // threads: worker threads for the copies (0 = pick: one per ~8 MB, at most 8; 1 = none).  The
-// Python objects are only read by the calling thread, which holds the GIL throughout; the
-// workers see raw (pointer, length, destination) triples, which stay valid because the
-// caller's list keeps the strings alive.
+// Python objects are only read by the calling thread, with the GIL held; the copies work on raw
+// (pointer, length, destination) triples and run with the GIL RELEASED -- the triples stay
+// valid as long as the caller keeps the list (and so the strings) alive and unmodified
+// until the call returns.
 __attribute__((visibility("default")))
 int b200p_fill(PyObject *prompts, PyObject *sep_obj, uint8_t *buf, int64_t buf_bytes, int64_t *starts,
                int32_t *lens, int32_t *nchars, int by_bytes, int threads)
@@ -160,8 +161,12 @@ int b200p_fill(PyObject *prompts, PyObject *sep_obj, uint8_t *buf, int64_t buf_b
         if (T > 8) T = 8;
         if (hw > 0 && T > hw) T = hw;
     }
+    // From here on no Python object is touched: let other Python threads run (a second
+    // batch can be measured / gathered while this one is being copied).
+    PyThreadState *ts = PyEval_SaveThread();
     if (T <= 1 || jobs.size() < 64) {
         run(0, jobs.size());
+        PyEval_RestoreThread(ts);
         return 0;
     }
     // equal byte shares: jobs are in destination order, so job j ends at dst + bytes
@@ -176,6 +181,7 @@ int b200p_fill(PyObject *prompts, PyObject *sep_obj, uint8_t *buf, int64_t buf_b
         a = b;
     }
     for (auto &th : pool) th.join();
+    PyEval_RestoreThread(ts);
     return 0;
 }
 
