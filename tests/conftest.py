@@ -17,6 +17,17 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
 
 
+def pytest_sessionstart(session):
+    """Build the libraries when they are missing or older than their sources (nvcc / g++
+    cross-compile without a GPU); a failure here is reported by the tests that need them."""
+    try:
+        import build as b200_build
+        if b200_build.needs_build():
+            b200_build.build()
+    except Exception as e:                      # pragma: no cover
+        print("conftest: could not build the libraries: %r" % (e,))
+
+
 def pytest_collection_modifyitems(config, items):
     # Without a device the gpu-marked tests cannot run; the driver selects them
     # with -m gpu on the B200 box and with -m "not gpu" here.
