@@ -277,7 +277,8 @@ def run_b200(args):
             # public single-GPU API: table + two-stream batch pipeline (hash stage of batch
             # b+1 overlaps the route stage of batch b; results stay sequential)
             from b200_router.trie import RoutePipeline
-            pipe = RoutePipeline(GpuHashTrie(cap_log2=cap_log2, device=dev))
+            pipe = RoutePipeline(GpuHashTrie(cap_log2=cap_log2, device=dev),
+                                 depth=int(os.environ.get("BENCH_PIPE_DEPTH", "2")))
             pipe.reserve(args.batch, max_chunks)
             return pipe
         # multi-GPU: table partitioned by first-chunk hash, chunk hashes and results shipped
