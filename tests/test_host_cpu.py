@@ -115,6 +115,14 @@ def test_native_packer_exports_its_header_and_equals_the_python_packer():
                 assert a.nchars is None or a.nchars.tolist() == b.nchars.tolist()
                 assert (a.n, a.max_chunks, a.all_ascii, a.payload_bytes) == \
                        (b.n, b.max_chunks, b.all_ascii, b.payload_bytes)
+    # the multi-threaded copy path (taken for >= 64 pieces): every thread count, ragged sizes
+    big = [rand_str(0, 900) if rng.random() < 0.7 else tuple(rand_str(0, 200) for _ in range(rng.randint(0, 6)))
+           for _ in range(3000)]
+    want = packing._pack_prompts_py(big, 128, False, False, "\n")
+    for th in (1, 2, 3, 8, 0):
+        got = packing.pack_prompts(big, pin=False, threads=th)
+        assert bytes(got.bytes.numpy()) == bytes(want.bytes.numpy()), th
+        assert got.starts.tolist() == want.starts.tolist() and got.nchars.tolist() == want.nchars.tolist()
     arena = packing.PackArena(slots=2, pin=False)
     first = packing.pack_prompts(["abc", "de"], pin=False, arena=arena)
     kept = bytes(first.bytes.numpy())
