@@ -239,6 +239,21 @@ __device__ __forceinline__ void cp_async16(uint32_t smem_dst, const void *src, i
                  "r"(src_bytes)
                  : "memory");
 }
+// the same with an L2 evict-first hint: prompt bytes are read exactly once, so they should not
+// push the table entries and scratch arrays of the route stage (running on the other stream)
+// out of L2
+__device__ __forceinline__ uint64_t l2_evict_first_policy()
+{
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void cp_async16_stream(uint32_t smem_dst, const void *src, uint64_t pol)
+{
+    asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;\n" ::"r"(smem_dst), "l"(src),
+                 "l"(pol)
+                 : "memory");
+}
 __device__ __forceinline__ void cp_async_wait_all()
 {
     asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
@@ -504,6 +519,7 @@ k_hash_tiles(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ star
         // lane copies unit u of chunk c = 4k + sub; (c & 7) = sub ^ 4(k&1), so the swizzled
         // destination is one of two per-lane bases plus k * 512
         const int u = lane & 7, sub = lane >> 3;
+        const uint64_t pol = l2_evict_first_policy();
         uint32_t d_even = wrow + sub * 128 + ((u ^ sub) << 4);
         asm volatile("" : "+r"(d_even));
         const uint32_t d_odd = d_even ^ 64u;
@@ -511,8 +527,8 @@ k_hash_tiles(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ star
         for (int k = 0; k < 8; k++) {
             const unsigned long long src = __shfl_sync(0xffffffffu, my_src, 4 * k + sub);
             if (src)
-                cp_async16(((k & 1) ? d_odd : d_even) + k * 512,
-                           (const uint8_t *)(uintptr_t)src + (u << 4), 16);
+                cp_async16_stream(((k & 1) ? d_odd : d_even) + k * 512,
+                                  (const uint8_t *)(uintptr_t)src + (u << 4), pol);
         }
         // the ragged last chunk of a request was hashed by k_prep_scan: fetch it meanwhile
         if (MODE == 1 && valid && kind == 0) h = hashes[g];
