@@ -258,8 +258,6 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=dev)
     W, K = args.warmup, args.steps
     nb = W + K
-    if os.environ.get("BENCH_CLAIM_MODE"):      # tuning experiments only (see include/b200_router.h)
-        _lib.check(_lib.lib().b200r_set_claim_by_tiles(int(os.environ["BENCH_CLAIM_MODE"])))
 
     # ---- synthetic batches (host, pinned), this rank's shard of every global batch
     tr = make_trace(args, nb * world)
@@ -285,9 +283,8 @@ def run_b200(args):
         # over NVLink peer memory by the library's own kernels (the variant that scales).
         # BENCH_EXCHANGE=replicated / nccl select the replicated-table variants (peer-memory
         # or NCCL all-gather exchange of inserted nodes) for comparison.
-        from b200_router.distributed import (P2PShardedRouter, PartitionedPrefixRouter,
-                                             ShardedPrefixRouter)
-        cls = {"nccl": ShardedPrefixRouter, "replicated": P2PShardedRouter}.get(
+        from b200_router.distributed import PartitionedPrefixRouter, ShardedPrefixRouter
+        cls = {"nccl": ShardedPrefixRouter, "replicated": ShardedPrefixRouter}.get(
             os.environ.get("BENCH_EXCHANGE", ""), PartitionedPrefixRouter)
         return cls(cap_log2=cap_log2, device=dev, max_requests=args.batch, max_chunks=max_chunks)
 

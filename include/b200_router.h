@@ -43,7 +43,7 @@ extern "C" {
 #pragma GCC visibility push(default) /* the library is built with -fvisibility=hidden */
 #endif
 
-#define B200R_ABI_VERSION 1
+#define B200R_ABI_VERSION 2
 
 #define B200R_OK 0
 #define B200R_E_INVALID (-1)  /* bad argument                                  */
@@ -59,7 +59,7 @@ extern "C" {
 #define B200R_S_TABLE_FULL 1u
 #define B200R_S_CHUNK_CAP 2u
 #define B200R_S_PEER_TIMEOUT 4u /* multi-GPU: a peer's data did not arrive within ~3 s */
-#define B200R_S_LOOKBACK 8u     /* internal: a tile's path-key carry never arrived          */
+#define B200R_S_INTERNAL 8u     /* internal: a run head was published without its record     */
 
 typedef struct b200r_trie b200r_trie; /* GPU-resident HashTrie replacement     */
 typedef struct b200r_ring b200r_ring; /* GPU-resident consistent-hash ring     */
@@ -114,12 +114,19 @@ int b200r_xxh64_chunks_noalloc(const uint8_t *d_bytes, const int64_t *d_starts,
 
 /* ------------------------------------------------------------------------
  * a4/a6  TrieNode / HashTrie.__init__               hashtrie.py:24-43
- * The pointer trie becomes an open-addressing table of 64-byte entries
- * {path key (128 bit), endpoint bitmask, batch bookkeeping | chunk hash};
- * capacity = 2^cap_log2 entries.  Endpoints are bit
- * indices 0..63.  The reference never evicts, neither does the table: size it
- * for the expected node count at load factor <= 0.5 (b200r_trie_status reports
- * the node count; a full table latches B200R_S_TABLE_FULL).
+ * The pointer trie becomes a node log plus a hash table of run heads.  Every
+ * node is one 32-byte record {chunk hash, endpoint bitmask, batch bookkeeping}
+ * and is identified by its index in the log.  The nodes one request creates in
+ * one go are consecutive records (a run); only the first node of a run is
+ * entered in an open-addressing table keyed by (parent node index, chunk hash)
+ * -- exactly parent.children[chunk_hash] -- with value (log index, run length).
+ * Walking a stored path compares consecutive records with the request's chunk
+ * hashes.  Capacity = 2^cap_log2 nodes (log records) and 2^(cap_log2+1) table
+ * entries of 32 bytes (load factor <= 0.5 even if every node heads its own
+ * run): 96 bytes of device memory per node of capacity.  Endpoints are bit
+ * indices 0..63.  The reference never evicts, neither does the log:
+ * b200r_trie_status reports the node count; a full log latches
+ * B200R_S_TABLE_FULL.
  * ---------------------------------------------------------------------- */
 int b200r_trie_create(int32_t cap_log2, int32_t chunk_chars, b200r_trie **out);
 int b200r_trie_destroy(b200r_trie *t);
@@ -127,6 +134,20 @@ int b200r_trie_clear(b200r_trie *t, void *stream);
 /* synchronises `stream`; any of the outputs may be NULL */
 int b200r_trie_status(b200r_trie *t, void *stream, uint32_t *status_bits, int64_t *num_nodes,
                       uint64_t *root_mask, int64_t *capacity);
+/* The latched status word copied to a DEVICE word in stream order (no host sync), so that a
+ * caller can bring it back in the same device-to-host copy as the batch's decisions. */
+int b200r_trie_status_async(b200r_trie *t, uint32_t *d_status_out, void *stream);
+/* a11 endpoint indexing (service_discovery.py:651 mints a new url per pod restart; the
+ * reference keeps stale urls in its sets forever and filters them by intersection with the
+ * available set, hashtrie.py:96).  Masks are one 64-bit word, so the bit of an endpoint that
+ * is gone for good has to be recycled: this sweep clears `bits` from every endpoint set and
+ * from the root set.  Decisions are unchanged as long as those endpoints never become
+ * available again under the same bit. */
+int b200r_trie_retire_endpoints(b200r_trie *t, uint64_t bits, void *stream);
+/* Test hook: set the batch epoch (the counter behind the per-node "first toucher" words).
+ * The epoch advances once per routed batch; when its 32 bits run out the library zeroes
+ * those words with one sweep and restarts at 1 -- nothing else changes. */
+int b200r_trie_set_epoch(b200r_trie *t, uint32_t epoch);
 
 /* ------------------------------------------------------------------------
  * a2  HashTrie.longest_prefix_match                 hashtrie.py:76-103
@@ -178,122 +199,36 @@ int b200r_prefix_route_stage(b200r_trie *t, int64_t n, int64_t max_chunks, uint3
                              int32_t *d_endpoint, int32_t *d_match_depth,
                              uint64_t *d_matched_mask, void *d_scratch, size_t scratch_bytes,
                              void *stream);
-/* Fused variant of a5: after the prep stage (chunk counts, CSR, ragged tails; does not
- * touch the table) ONE kernel hashes the chunks, computes the path keys (segmented warp
- * scan + decoupled look-back between tiles) and finds-or-creates the nodes; select and
- * commit follow.  The chunk hashes never go to memory.  Same results, same scratch size.
- * b200r_prefix_route_batch_fused = prep stage + fused stage on one stream. */
-int b200r_prefix_prep_stage(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
-                            const int32_t *d_lens, const int32_t *d_nchars, int64_t n,
-                            int64_t max_chunks, uint32_t flags, void *d_scratch,
-                            size_t scratch_bytes, void *stream);
-int b200r_prefix_fused_stage(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
-                             const int32_t *d_lens, const int32_t *d_nchars, int64_t n,
-                             int64_t max_chunks, uint32_t flags, uint64_t avail_mask,
-                             uint64_t seed, uint64_t seq0, int32_t *d_endpoint,
-                             int32_t *d_match_depth, uint64_t *d_matched_mask, void *d_scratch,
-                             size_t scratch_bytes, void *stream);
-int b200r_prefix_route_batch_fused(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
-                                   const int32_t *d_lens, const int32_t *d_nchars, int64_t n,
-                                   int64_t max_chunks, uint32_t flags, uint64_t avail_mask,
-                                   uint64_t seed, uint64_t seq0, int32_t *d_endpoint,
-                                   int32_t *d_match_depth, uint64_t *d_matched_mask,
-                                   void *d_scratch, size_t scratch_bytes, void *stream);
+/* The route stage from chunk hashes the caller already holds (CSR exactly as b200r_xxh64_chunks
+ * writes it): claim / select / commit, same results as b200r_prefix_route_batch on the prompts
+ * those hashes came from.  Used where hashes of several sources are merged before routing
+ * (replicated multi-GPU tables: every rank all-gathers the ranks' hashes and routes the global
+ * batch).  Scratch: b200r_prefix_route_scratch_bytes(n, max_chunks, B200R_F_ALL_ASCII). */
+int b200r_prefix_route_hashes(b200r_trie *t, const uint64_t *d_hashes, const int32_t *d_chunk_base,
+                              int64_t n, int64_t max_chunks, uint64_t avail_mask, uint64_t seed,
+                              uint64_t seq0, int32_t *d_endpoint, int32_t *d_match_depth,
+                              uint64_t *d_matched_mask, void *d_scratch, size_t scratch_bytes,
+                              void *stream);
 /* the canonical draw, on the host (same arithmetic as the kernels) */
 uint32_t b200r_pick(uint64_t seed, uint64_t seq, uint32_t n);
 
 /* ------------------------------------------------------------------------
  * Trie state export (parity / checkpoint; the reference has no counterpart
  * beyond walking TrieNode.children, hashtrie.py:24-32).  Writes up to
- * max_nodes entries {key_lo, key_hi, chunk_hash, mask} (4 x u64 each) to
- * d_out and the number of occupied entries to *count (may exceed max_nodes).
- * Synchronises.  Path keys are invertible: see DESIGN.md "Path keys".
+ * max_nodes entries of 4 x u64
+ *   {log index | run length << 32 (length on the first node of a run, else 0),
+ *    parent's log index (0xFFFFFFFF = the root), chunk hash, mask}
+ * to d_out and the number of nodes to *count (may exceed max_nodes).
+ * Synchronises.  Paths follow from the parent links.
  * ---------------------------------------------------------------------- */
 int b200r_trie_dump(b200r_trie *t, uint64_t *d_out, int64_t max_nodes, int64_t *count,
                     uint64_t *root_mask, void *stream);
-/* Re-insert dumped entries (checkpoint restore / multi-GPU merge of nodes
- * created on other ranks): ORs mask into the entry with that key, creating it. */
-int b200r_trie_apply_remote(b200r_trie *t, const uint64_t *d_entries, int64_t count,
-                            uint64_t root_mask_or, void *stream);
-/* constants of the path-key recurrence, for host-side decoding of dumps:
- * out[0..5] = {A1, A2, ROOT1, ROOT2, A1^-1, A2^-1} */
-void b200r_trie_key_constants(uint64_t out[6]);
-
-/* ------------------------------------------------------------------------
- * Multi-GPU routing of one global batch (no counterpart in the reference, whose
- * router replicas share nothing).  The global batch is the
- * rank-major concatenation of the shards and is routed as if sequentially;
- * every rank keeps a full replica of the table.  Call order per batch, on
- * every rank (the all-gathers between the calls are the host's job, e.g.
- * torch.distributed over NCCL):
- *   b200r_shard_classify  hash + frozen lookup of the own shard; emits one
- *        32-byte record {key_lo, key_hi, chunk_hash, u32 request index inside
- *        the shard, u32 depth} per chunk whose node is not usable yet
- *        -> all-gather record counts and records (rank q at q*stride)
- *   b200r_shard_apply     applies all ranks' records to the local replica
- *   b200r_shard_select    leaders / choices / match depths of the own shard
- *        -> all-gather them (rank q at q*rstride)
- *   b200r_shard_commit    resolves every request's endpoint, inserts it into
- *        every replica, writes the own shard's results
- * d_rec_count = u32[2], written by classify as {record count, shard size n}; the
- * all-gather of it is d_meta = int32 [world][2].  req_off (select) = global
- * position of the own shard's request 0 = sum of the earlier shards' sizes.
- * d_lcd_all = int32 [world][3][rstride]: every rank's leaders, choices, depths.  The scratch buffer
- * (b200r_prefix_route_scratch_bytes) must be the same for all four calls.
- * ---------------------------------------------------------------------- */
-#define B200R_SHARD_RECORD_BYTES 32
-int b200r_shard_classify(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
-                         const int32_t *d_lens, const int32_t *d_nchars, int64_t n,
-                         int64_t max_chunks, uint32_t flags, uint64_t avail_mask,
-                         void *d_records, uint32_t *d_rec_count, void *d_scratch,
-                         size_t scratch_bytes, void *stream);
-int b200r_shard_apply(b200r_trie *t, const void *d_records_all, const int32_t *d_meta,
-                      int32_t world, int64_t stride, int32_t my_rank, int64_t n,
-                      int64_t max_chunks, uint32_t flags, uint32_t *d_rec_slot, void *d_scratch,
-                      void *stream);
-int b200r_shard_select(b200r_trie *t, int64_t n, int64_t max_chunks, uint32_t flags,
-                       uint64_t avail_mask, uint64_t seed, uint64_t seq0, uint32_t req_off,
-                       int32_t *d_leader, int32_t *d_choice, int32_t *d_depth,
-                       uint64_t *d_matched, void *d_scratch, void *stream);
-int b200r_shard_commit(b200r_trie *t, const void *d_records_all, const int32_t *d_meta,
-                       int32_t world, int64_t stride, const uint32_t *d_rec_slot,
-                       const int32_t *d_lcd_all, int64_t rstride, int32_t my_rank, int64_t n,
-                       int32_t *d_endpoint_all, int32_t *d_endpoint, int32_t *d_match_depth,
-                       uint64_t *d_matched, void *stream);
-
-/* ------------------------------------------------------------------------
- * The same multi-GPU batch with the exchange done by this library's own kernels
- * over NVLink peer memory instead of NCCL all-gathers (no host round trip at
- * all).  Every rank allocates one buffer of b200r_p2p_layout(...)[0] bytes that
- * all peers can address (e.g. torch.distributed._symmetric_memory) and passes
- * the table of all ranks' base addresses (d_peer_bases, u64[world], device).
- * cap = record capacity per rank and batch (>= max_chunks of any shard), rcap =
- * request capacity per rank (multiple of 4); epoch = batch number, 1, 2, 3, ...,
- * the same on all ranks.  The global tie-break sequence number is kept on the
- * device (d_dyn, 1 KB, zero-initialised by the caller).  Per batch, per rank:
- *   b200r_p2p_classify  hash + lookup; pushes the records into every peer
- *   b200r_p2p_route     waits for all peers' records, applies them, selects,
- *                       pushes leaders / choices / depths into every peer
- *   b200r_p2p_commit    waits for those, resolves and inserts; own results
- * A peer that does not deliver within ~3 s latches B200R_S_PEER_TIMEOUT.
- * ---------------------------------------------------------------------- */
-#define B200R_P2P_DYN_BYTES 1024
-int b200r_p2p_layout(int32_t world, int64_t cap, int64_t rcap, size_t out[3]);
-int b200r_p2p_classify(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
-                       const int32_t *d_lens, const int32_t *d_nchars, int64_t n,
-                       int64_t max_chunks, uint32_t flags, uint64_t avail_mask,
-                       const uint64_t *d_peer_bases, int32_t world, int32_t rank, int64_t cap,
-                       int64_t rcap, uint32_t epoch, void *d_recs_local, uint32_t *d_rec_count,
-                       void *d_scratch, size_t scratch_bytes, void *stream);
-int b200r_p2p_route(b200r_trie *t, int64_t n, int64_t max_chunks, uint32_t flags,
-                    uint64_t avail_mask, uint64_t seed, const uint64_t *d_peer_bases,
-                    void *d_my_base, int32_t world, int32_t rank, int64_t cap, int64_t rcap,
-                    uint32_t epoch, void *d_dyn, uint32_t *d_rec_slot, int32_t *d_lcd_local,
-                    uint64_t *d_matched, void *d_scratch, void *stream);
-int b200r_p2p_commit(b200r_trie *t, int64_t n, void *d_my_base, int32_t world, int32_t rank,
-                     int64_t cap, int64_t rcap, uint32_t epoch, void *d_dyn,
-                     const uint32_t *d_rec_slot, int32_t *d_endpoint_all, int32_t *d_endpoint,
-                     int32_t *d_match_depth, uint64_t *d_matched, void *stream);
+/* Checkpoint restore: writes dumped entries back at their log indices and their run
+ * heads back into the table, so the restored table has the layout of the saved one.
+ * Node identity is the log position, hence only into an EMPTY table (fresh or cleared)
+ * of at least the dump's capacity; otherwise B200R_E_INVALID.  Synchronises once. */
+int b200r_trie_restore(b200r_trie *t, const uint64_t *d_entries, int64_t count,
+                       uint64_t root_mask, void *stream);
 
 /* ------------------------------------------------------------------------
  * Multi-GPU with a PARTITIONED table (scalable variant; no counterpart in the
@@ -353,9 +288,6 @@ int b200r_ring_lookup_batch(b200r_ring *r, const uint8_t *d_bytes, const int64_t
  * b200r_launch_count: kernels enqueued by this library
  * since load (process-wide).
  * ---------------------------------------------------------------------- */
-/* tuning switch of the route stage: claim with one warp per 32-chunk tile (default, 1) or
- * one warp per request (0); identical results */
-int b200r_set_claim_by_tiles(int on);
 #define B200R_PROF_SLOTS 13
 int b200r_prof_enable(int on);
 int b200r_prof_read(float *ms_out, long long *count_out, int nslots);

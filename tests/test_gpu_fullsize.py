@@ -68,21 +68,17 @@ def test_c3_one_million_prompts_batch_64k():
     got = np.sort(arr[:, 2] * np.uint64(0x9E3779B97F4A7C15) ^ arr[:, 3])
     want = np.sort(oh[1:] * np.uint64(0x9E3779B97F4A7C15) ^ omask[1:])
     assert (got == want).all()
-    # trie invariant child.mask subset-of parent.mask, checked through the inverted key recurrence
-    from b200_router.trie import key_constants
-    a1, a2, r1, r2, i1, i2 = (np.uint64(x) for x in key_constants())
-    order = np.lexsort((arr[:, 1], arr[:, 0]))
-    keys = arr[order]
-    pk1 = (keys[:, 0] - keys[:, 2]) * i1
-    hrot = (keys[:, 2] << np.uint64(32)) | (keys[:, 2] >> np.uint64(32))
-    pk2 = (keys[:, 1] - hrot) * i2
-    is_top = (pk1 == r1) & (pk2 == r2)
-    pos = np.searchsorted(keys[:, 0], pk1)
-    pos = np.minimum(pos, len(keys) - 1)
-    found = (keys[pos, 0] == pk1) & (keys[pos, 1] == pk2)
-    assert (found | is_top).all()                     # prefix-closed: every parent exists
-    sub = (keys[:, 3] & ~keys[pos, 3]) == 0
-    assert (sub | is_top).all()                       # nested endpoint sets
+    # trie invariant child.mask subset-of parent.mask, checked through the parent links
+    idx = arr[:, 0] & np.uint64(0xFFFFFFFF)
+    order = np.argsort(idx)
+    sidx, smask, spar = idx[order], arr[order, 3], arr[order, 1]
+    assert (np.diff(sidx.astype(np.int64)) > 0).all()         # every node has its own log record
+    is_top = spar == np.uint64(0xFFFFFFFF)
+    pos = np.minimum(np.searchsorted(sidx, spar), len(sidx) - 1)
+    assert ((sidx[pos] == spar) | is_top).all()               # prefix-closed: every parent exists
+    assert (((smask & ~smask[pos]) == 0) | is_top).all()      # nested endpoint sets
+    # runs: the lengths on the run heads add up to the node count
+    assert int((arr[:, 0] >> np.uint64(32)).sum()) == len(arr)
     t.close()
 
 

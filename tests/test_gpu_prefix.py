@@ -211,43 +211,107 @@ def test_route_pipeline_overlapped_batches_vs_oracle():
         t.close()
 
 
-def test_staged_and_fused_paths_agree_with_the_oracle():
-    """b200r_prefix_route_batch (hash kernel + claim kernel) and ..._fused (one kernel with
-    look-back between tiles) on the same trace: both equal the oracle; long prompts make
-    requests span many warp tiles."""
-    from b200_router.trie import GpuHashTrie, RoutePipeline
+def test_long_and_short_prompts_mixed_vs_oracle():
+    """Prompts of 45 chunks (several 32-depth windows of the walk, runs longer than a warp) next
+    to C3-shaped ones with suffixes down to one character, with availability churn."""
+    from b200_router.trie import GpuHashTrie
     bufL, stL, lnL = traces.long_context_batch(n=300, chars=128 * 45 + 77, group=10,
                                                shared_frac=0.5, seed=15)
     tr = traces.SharedPrefixTrace(n_total=9000, batch=3000, n_sys=16, sys_chars=512,
                                   suffix_lo=1, suffix_hi=400, seed=22)
     batches = [(0xFF, bufL, stL, lnL)] + [((0xFB if b == 1 else 0xFF),) + tr.batch_arrays(b)
                                           for b in range(3)]
-    for fused in (False, True):
-        t = GpuHashTrie(cap_log2=18)
-        orc = coracle.TrieOracle()
-        seq = 0
-        for avail, buf, starts, lens in batches:
-            ep, depth, matched = t.route(pack_arrays(buf, starts, lens, pin=False), avail, 4, seq,
-                                         fused=fused)
-            oep, odepth, omatched = orc.route_batch(buf, starts, lens, avail, 4, seq)
-            seq += len(starts)
-            assert (ep.cpu().numpy() == oep).all(), fused
-            assert (depth.cpu().numpy() == odepth).all(), fused
-            assert (u64(matched) == omatched).all(), fused
-        t.check_status()
-        assert t.dump() == orc.dump()
-        t.close()
-    # the batch pipeline in its fused flavour (the staged one is the default, tested above)
     t = GpuHashTrie(cap_log2=18)
-    pipe = RoutePipeline(t, fused=True)
+    _route_vs_oracle(t, batches, seed=4)
+    t.close()
+
+
+def test_route_from_hashes_and_on_a_restored_table_vs_oracle():
+    """b200r_prefix_route_hashes (route stage from caller-held chunk hashes) equals routing the
+    prompts; a table restored from a dump keeps routing like the original (same layout), and a
+    dump can only be restored into an empty table."""
+    from b200_router import B200RouterError
+    from b200_router.trie import GpuHashTrie
+    tr = traces.SharedPrefixTrace(n_total=8000, batch=2000, n_sys=8, sys_chars=1024,
+                                  suffix_lo=1, suffix_hi=600, seed=31)
+    bufL, stL, lnL = traces.long_context_batch(n=64, chars=128 * 40 + 9, group=8, shared_frac=0.7, seed=2)
     orc = coracle.TrieOracle()
+    t = GpuHashTrie(cap_log2=17)
     seq = 0
-    for avail, buf, starts, lens in batches:
-        ep, _, _ = pipe.route(pack_arrays(buf, starts, lens, pin=True), avail, 4, seq)
-        oep, _, _ = orc.route_batch(buf, starts, lens, avail, 4, seq)
+    first = [(0xFF, bufL, stL, lnL)] + [(0xFF,) + tr.batch_arrays(b) for b in range(2)]
+    for k, (avail, buf, starts, lens) in enumerate(first):
+        p = pack_arrays(buf, starts, lens, pin=False)
+        if k == 1:                                    # this batch through the hashes entry point
+            base, hs = t.hash_chunks(p)
+            ep, depth, matched = t.route_hashes(hs, base, p.n, p.max_chunks, avail, 6, seq)
+        else:
+            ep, depth, matched = t.route(p, avail, 6, seq)
+        oep, odepth, omatched = orc.route_batch(buf, starts, lens, avail, 6, seq)
+        seq += len(starts)
+        assert (ep.cpu().numpy() == oep).all(), k
+        assert (depth.cpu().numpy() == odepth).all(), k
+        assert (u64(matched) == omatched).all(), k
+    arr, root = t.dump_raw()
+    t2 = GpuHashTrie(cap_log2=17)
+    t2.restore_entries(torch.from_numpy(arr.view(np.int64).copy()), root)
+    assert t2.dump() == orc.dump()
+    assert t2.status()["num_nodes"] == t.status()["num_nodes"]
+    for avail, buf, starts, lens in [(0xF7,) + tr.batch_arrays(2), (0xFF, bufL, stL, lnL),
+                                     (0xFF,) + tr.batch_arrays(3)]:
+        ep, depth, matched = t2.route(pack_arrays(buf, starts, lens, pin=False), avail, 6, seq)
+        oep, odepth, omatched = orc.route_batch(buf, starts, lens, avail, 6, seq)
         seq += len(starts)
         assert (ep.cpu().numpy() == oep).all()
+        assert (depth.cpu().numpy() == odepth).all()
+        assert (u64(matched) == omatched).all()
+    t2.check_status()
+    assert t2.dump() == orc.dump()
+    with pytest.raises(B200RouterError):
+        t2.restore_entries(torch.from_numpy(arr.view(np.int64).copy()), root)
+    t.close()
+    t2.close()
+
+
+def test_batch_epoch_wraps_without_losing_the_table():
+    """The per-node first-toucher words are tagged with a 32-bit batch epoch.  When it runs out
+    the library sweeps those words and restarts the count; learned prefixes stay
+    (routing_logic.py:352: the reference trie has no lifetime limit)."""
+    from b200_router import _lib
+    from b200_router.trie import GpuHashTrie
+    t = GpuHashTrie(cap_log2=12)
+    batches = []
+    for avail_idx, prompts in traces.sharing_stress(n_batches=6, batch=150, n_endpoints=7,
+                                                    max_depth=6, alphabet=2, seed=4242):
+        buf, starts, lens, _ = traces.pack_strings(prompts)
+        batches.append((sum(1 << i for i in avail_idx), buf, starts, lens))
+    orc = coracle.TrieOracle()
+    seq = 0
+    for b, (avail, buf, starts, lens) in enumerate(batches):
+        if b == 2:
+            _lib.check(_lib.lib().b200r_trie_set_epoch(t._h, 0xFFFFFFEF))    # one batch before the limit
+        ep, depth, matched = t.route(pack_arrays(buf, starts, lens, pin=False), avail, 11, seq)
+        oep, odepth, omatched = orc.route_batch(buf, starts, lens, avail, 11, seq)
+        seq += len(starts)
+        assert (ep.cpu().numpy() == oep).all(), b
+        assert (depth.cpu().numpy() == odepth).all(), b
+        assert (u64(matched) == omatched).all(), b
+    t.check_status()
     assert t.dump() == orc.dump()
+    t.close()
+
+
+def test_retire_endpoints_clears_their_bits_everywhere():
+    from b200_router.trie import GpuHashTrie
+    t = GpuHashTrie(cap_log2=14)
+    _, prompts = traces.sharing_stress(n_batches=1, batch=400, n_endpoints=6, seed=5)[0]
+    p = pack_prompts(prompts)
+    t.route(p, 0x3F, 2, 0)
+    before = t.dump()
+    assert any(m & 0b1010 for m in before.values())
+    t.retire_endpoints(0b1010)
+    after = t.dump()
+    assert set(after) == set(before)
+    assert all(after[k] == before[k] & ~0b1010 for k in before)
     t.close()
 
 
@@ -291,7 +355,7 @@ def test_dump_restore_roundtrip(trie):
     trie.route(p, 0x3F, 1, 0)
     arr, root = trie.dump_raw()
     t2 = GpuHashTrie(cap_log2=13)
-    t2.apply_entries(torch.from_numpy(arr.view(np.int64).copy()), root)
+    t2.restore_entries(torch.from_numpy(arr.view(np.int64).copy()), root)
     assert t2.dump() == trie.dump()
     assert t2.status()["num_nodes"] == trie.status()["num_nodes"]
     d1, m1 = trie.longest_prefix_match(p, 0x3F)
@@ -383,29 +447,6 @@ def test_router_micro_batched_concurrent_requests_equal_reference(golden_prefix)
     assert [tr["urls"].index(u) for u in urls] == tr["decisions"]
     assert 1 < r.batcher.batches_routed <= (len(prompts) + 63) // 64 + 1
     routers._reset_singletons_for_tests()
-
-
-def test_claim_per_request_and_per_tile_agree_with_the_oracle():
-    """The route stage can claim with one warp per request or one warp per 32-chunk tile
-    (b200r_set_claim_by_tiles); both must equal the oracle, including requests that span
-    several tiles and tiles that hold several requests."""
-    from b200_router import _lib
-    from b200_router.trie import GpuHashTrie
-    bufL, stL, lnL = traces.long_context_batch(n=200, chars=128 * 70 + 3, group=8, shared_frac=0.4, seed=33)
-    try:
-        for by_tiles in (0, 1):
-            _lib.check(_lib.lib().b200r_set_claim_by_tiles(by_tiles))
-            for s in range(3):
-                t = GpuHashTrie(cap_log2=16)
-                batches = [((1 << 64) - 1, bufL, stL, lnL)] if s == 0 else []
-                for avail_idx, prompts in traces.sharing_stress(n_batches=4, batch=200, n_endpoints=7,
-                                                                max_depth=6, alphabet=2, seed=300 + s):
-                    buf, starts, lens, _ = traces.pack_strings(prompts)
-                    batches.append((sum(1 << i for i in avail_idx), buf, starts, lens))
-                _route_vs_oracle(t, batches, seed=s)
-                t.close()
-    finally:
-        _lib.check(_lib.lib().b200r_set_claim_by_tiles(1))
 
 
 def test_byte_chunk_mode_reproduces_the_gateway_picker(trie, golden_go):

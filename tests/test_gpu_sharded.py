@@ -1,7 +1,8 @@
-"""The multi-GPU path (b200r_shard_* entry points + ShardedPrefixRouter) on ONE
-device: the ranks are threads of this process, each with its own table replica,
-and the all-gathers are done through shared memory (the orchestration code is the
-product's; only the collective is swapped).  Results must equal routing the
+"""The multi-GPU paths on ONE device.  Replicated design (ShardedPrefixRouter over
+b200r_xxh64_chunks + b200r_prefix_route_hashes): the ranks are threads of this process, each
+with its own table replica, and the all-gathers are done through shared memory (the
+orchestration code is the product's; only the collective is swapped).  Partitioned design
+(b200r_part_*): the ranks run their phases in lock-step.  Results must equal routing the
 rank-major concatenation sequentially (C oracle); all replicas must be identical.
 The real NCCL path is exercised by `torchrun ... bench.py --gpus N`."""
 import threading
@@ -116,69 +117,6 @@ def test_sharded_uneven_and_empty_shards():
     shards0 = [traces.pack_strings(prompts[:50])[:3], traces.pack_strings([])[:3]]
     shards1 = [traces.pack_strings(prompts[:7])[:3], traces.pack_strings(prompts[7:])[:3]]
     _check(world, [(0x3F, shards0), (0x15, shards1)], seed=2)
-
-
-def _check_p2p_lockstep(world, batches_np, seed):
-    """The peer-memory exchange path on ONE device: all 'ranks' live in this process and
-    their phases run in lock-step (every flag is already set when a consumer looks), so
-    nothing ever spins; peer buffers are plain device allocations."""
-    from b200_router.distributed import P2PShardedRouter
-    max_req = max(len(s[1]) for _, shards in batches_np for s in shards)
-    batches = [(a, [pack_arrays(*s, pin=False) for s in shards]) for a, shards in batches_np]
-    max_chunks = max(p.max_chunks for _, shards in batches for p in shards)
-    nbytes = P2PShardedRouter.symm_bytes_for(world, max_req, max_chunks)
-    bufs = [torch.zeros(nbytes, dtype=torch.uint8, device="cuda:0") for _ in range(world)]
-    ranks = [P2PShardedRouter(cap_log2=17, device="cuda:0", max_requests=max_req,
-                              max_chunks=max_chunks,
-                              _sim={"world": world, "rank": r, "buffers": bufs}) for r in range(world)]
-    orc = coracle.TrieOracle()
-    seq = 0
-    for avail, shards in batches:
-        for r in range(world):
-            ranks[r].phase_classify(shards[r], avail)
-        for r in range(world):
-            ranks[r].phase_route(seed)
-        outs = [ranks[r].phase_commit() for r in range(world)]
-        torch.cuda.synchronize()
-        off = 0
-        for r, p in enumerate(shards):
-            buf, st, ln = p.bytes.cpu().numpy(), p.starts.cpu().numpy(), p.lens.cpu().numpy()
-            oep, odepth, omatched = orc.route_batch(buf, st, ln, avail, seed, seq + off)
-            off += p.n
-            ep, depth, matched = outs[r]
-            assert (ep.cpu().numpy() == oep).all(), r
-            assert (depth.cpu().numpy() == odepth).all(), r
-            assert (u64(matched) == omatched).all(), r
-        seq += off
-    want = orc.dump()
-    for rk in ranks:
-        rk.check_status()
-        assert rk.dump() == want
-
-
-def test_p2p_exchange_lockstep_heavy_sharing():
-    for world in (2, 3):
-        batches = []
-        for avail_idx, prompts in traces.sharing_stress(n_batches=5, batch=90, n_endpoints=7,
-                                                        max_depth=6, alphabet=2, seed=70 + world):
-            cuts = np.linspace(0, len(prompts), world + 1).astype(int)
-            shards = [traces.pack_strings(prompts[cuts[r]:cuts[r + 1]])[:3] for r in range(world)]
-            batches.append((sum(1 << i for i in avail_idx), shards))
-        _check_p2p_lockstep(world, batches, seed=6)
-
-
-def test_p2p_exchange_lockstep_shared_prefix_and_empty_shard():
-    world = 4
-    tr = traces.SharedPrefixTrace(n_total=16000, batch=1000, n_sys=8, sys_chars=512,
-                                  suffix_lo=100, suffix_hi=300, seed=19)
-    batches = []
-    for g in range(4):
-        avail = 0xFF & ~(1 << 1) if g in (1, 2) else 0xFF
-        shards = [tr.batch_arrays(g * world + r) for r in range(world)]
-        if g == 2:
-            shards[1] = traces.pack_strings([])[:3]
-        batches.append((avail, shards))
-    _check_p2p_lockstep(world, batches, seed=13)
 
 
 def _merge_partitions(dumps):

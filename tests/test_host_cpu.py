@@ -40,7 +40,7 @@ def test_library_exports_every_declared_symbol():
 def test_abi_version_and_host_side_pick():
     from oracle.chooser import pick
     lib = _lib.lib()
-    assert lib.b200r_abi_version() == 1
+    assert lib.b200r_abi_version() == 2
     for seed, seq, n in [(0, 0, 1), (7, 123456789, 8), (2**63, 2**40 + 3, 64), (5, 9, 3)]:
         assert lib.b200r_pick(seed, seq, n) == pick(seed, seq, n)
 

@@ -18,7 +18,7 @@ from .packing import PackedPrompts, pack_arrays, pack_prompts  # noqa: F401
 
 def __getattr__(name):
     # torch-heavy modules are imported on first use
-    if name in ("GpuHashTrie", "decode_dump", "key_constants"):
+    if name in ("GpuHashTrie", "decode_dump"):
         from . import trie
         return getattr(trie, name)
     if name == "GpuHashRing":

@@ -15,6 +15,7 @@ F_ALL_ASCII = 1
 S_TABLE_FULL = 1
 S_CHUNK_CAP = 2
 S_PEER_TIMEOUT = 4
+S_INTERNAL = 8
 NOALLOC_SCRATCH_BYTES = 4 * 1024 * 1024
 
 _vp, _i64, _i32, _u32, _u64, _sz = C.c_void_p, C.c_int64, C.c_int32, C.c_uint32, C.c_uint64, C.c_size_t
@@ -31,6 +32,9 @@ SIGNATURES = {
     "b200r_trie_clear": (C.c_int, [_vp, _vp]),
     "b200r_trie_status": (C.c_int, [_vp, _vp, C.POINTER(_u32), C.POINTER(_i64), C.POINTER(_u64),
                                     C.POINTER(_i64)]),
+    "b200r_trie_status_async": (C.c_int, [_vp, _vp, _vp]),
+    "b200r_trie_retire_endpoints": (C.c_int, [_vp, _u64, _vp]),
+    "b200r_trie_set_epoch": (C.c_int, [_vp, _u32]),
     "b200r_trie_lookup_batch": (C.c_int, [_vp, _vp, _vp, _i64, _u64, _vp, _vp, _vp]),
     "b200r_trie_insert_batch": (C.c_int, [_vp, _vp, _vp, _i64, _vp, _vp]),
     "b200r_prefix_route_scratch_bytes": (_sz, [_i64, _i64, _u32]),
@@ -39,35 +43,16 @@ SIGNATURES = {
     "b200r_prefix_hash_stage": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _u32, _vp, _sz, _vp]),
     "b200r_prefix_route_stage": (C.c_int, [_vp, _i64, _i64, _u32, _u64, _u64, _u64, _vp, _vp, _vp, _vp,
                                            _sz, _vp]),
-    "b200r_prefix_prep_stage": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _u32, _vp, _sz, _vp]),
-    "b200r_prefix_fused_stage": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _u32, _u64, _u64, _u64,
-                                           _vp, _vp, _vp, _vp, _sz, _vp]),
-    "b200r_prefix_route_batch_fused": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _u32, _u64, _u64,
-                                                 _u64, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "b200r_prefix_route_hashes": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _u64, _u64, _u64, _vp, _vp, _vp, _vp,
+                                            _sz, _vp]),
     "b200r_pick": (_u32, [_u64, _u64, _u32]),
     "b200r_trie_dump": (C.c_int, [_vp, _vp, _i64, C.POINTER(_i64), C.POINTER(_u64), _vp]),
-    "b200r_trie_apply_remote": (C.c_int, [_vp, _vp, _i64, _u64, _vp]),
-    "b200r_trie_key_constants": (None, [C.POINTER(_u64)]),
-    "b200r_shard_classify": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _u32, _u64, _vp, _vp,
-                                       _vp, _sz, _vp]),
-    "b200r_shard_apply": (C.c_int, [_vp, _vp, _vp, _i32, _i64, _i32, _i64, _i64, _u32, _vp, _vp, _vp]),
-    "b200r_shard_select": (C.c_int, [_vp, _i64, _i64, _u32, _u64, _u64, _u64, _u32, _vp, _vp, _vp, _vp,
-                                     _vp, _vp]),
-    "b200r_shard_commit": (C.c_int, [_vp, _vp, _vp, _i32, _i64, _vp, _vp, _i64, _i32, _i64, _vp, _vp,
-                                     _vp, _vp, _vp]),
-    "b200r_p2p_layout": (C.c_int, [_i32, _i64, _i64, C.POINTER(_sz)]),
-    "b200r_p2p_classify": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _u32, _u64, _vp, _i32, _i32, _i64,
-                                     _i64, _u32, _vp, _vp, _vp, _sz, _vp]),
-    "b200r_p2p_route": (C.c_int, [_vp, _i64, _i64, _u32, _u64, _u64, _vp, _vp, _i32, _i32, _i64, _i64, _u32,
-                                  _vp, _vp, _vp, _vp, _vp, _vp]),
-    "b200r_p2p_commit": (C.c_int, [_vp, _i64, _vp, _i32, _i32, _i64, _i64, _u32, _vp, _vp, _vp, _vp, _vp,
-                                   _vp, _vp]),
+    "b200r_trie_restore": (C.c_int, [_vp, _vp, _i64, _u64, _vp]),
     "b200r_part_layout": (C.c_int, [_i32, _i64, _i64, C.POINTER(_sz)]),
     "b200r_part_send": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _u32, _vp, _i32, _i32, _i64, _i64,
                                   _u32, _vp, _vp, _sz, _vp]),
     "b200r_part_route": (C.c_int, [_vp, _u64, _u64, _vp, _vp, _i32, _i32, _i64, _i64, _u32, _vp, _vp]),
     "b200r_part_finish": (C.c_int, [_vp, _i64, _vp, _i32, _i32, _i64, _i64, _u32, _vp, _vp, _vp, _vp, _vp]),
-    "b200r_set_claim_by_tiles": (C.c_int, [C.c_int]),
     "b200r_prof_enable": (C.c_int, [C.c_int]),
     "b200r_prof_read": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_longlong), C.c_int]),
     "b200r_launch_count": (C.c_longlong, []),
@@ -98,7 +83,7 @@ def lib():
             fn = getattr(L, name)
             fn.restype = res
             fn.argtypes = args
-        if L.b200r_abi_version() != 1:
+        if L.b200r_abi_version() != 2:
             raise B200RouterError("libb200router.so ABI mismatch")
         _lib = L
     return _lib

@@ -27,9 +27,10 @@ def _stream():
 class GpuHashTrie:
     """Open-addressing table of trie nodes on one GPU.
 
-    capacity = 2**cap_log2 entries of 64 bytes.  The
-    reference never evicts (routing_logic.py:352) and neither does the table;
-    `status()` reports the node count, a full table raises."""
+    Node log + hash table of run heads (csrc/trie.cuh); capacity = 2**cap_log2 nodes, 96 bytes
+    of device memory per node of capacity.  The reference never evicts
+    (routing_logic.py:352) and neither does the log; `status()` reports the node count, a
+    full log raises."""
 
     def __init__(self, cap_log2: int = 22, chunk_chars: int = 128, device=None):
         torch_ = _lib.require_cuda()
@@ -147,15 +148,10 @@ class GpuHashTrie:
                                                           _ptr(ep), _stream()))
 
     # -------------------------------------------------------------------- a5
-    def route(self, p: PackedPrompts, avail_mask: int, seed: int, seq0: int, out=None,
-              fused: bool = False):
+    def route(self, p: PackedPrompts, avail_mask: int, seed: int, seq0: int, out=None):
         """Lookup + tie-break + insert for a batch, equal to routing the requests
-        sequentially in index order.  Returns device tensors (endpoint int32[n],
-        depth int32[n], matched int64[n]).  fused=False (default) runs the staged kernels
-        (b200r_prefix_route_batch: hash kernel, then claim kernel); fused=True hashes, keys and
-        claims in one kernel (b200r_prefix_route_batch_fused).  Identical results; on B200 the
-        staged path measured faster (hash 47 us + claim 49 us vs 115 us fused per 64K batch:
-        a fused warp keeps its staging buffer while it waits on table latency)."""
+        sequentially in index order (b200r_prefix_route_batch).  Returns device tensors
+        (endpoint int32[n], depth int32[n], matched int64[n])."""
         p = self._dev(p)
         L = _lib.lib()
         n = p.n
@@ -166,17 +162,36 @@ class GpuHashTrie:
         ep, depth, matched = out
         flags = _lib.F_ALL_ASCII if p.all_ascii else 0
         sc = self._scratch_for(L.b200r_prefix_route_scratch_bytes(n, p.max_chunks, flags))
-        entry = L.b200r_prefix_route_batch_fused if fused else L.b200r_prefix_route_batch
         with torch.cuda.device(self.device):
-            _lib.check(entry(
+            _lib.check(L.b200r_prefix_route_batch(
                 self._h, _ptr(p.bytes), _ptr(p.starts), _ptr(p.lens), _ptr(p.nchars), n,
                 p.max_chunks, flags, avail_mask & M64, seed & M64, seq0 & M64, _ptr(ep), _ptr(depth),
                 _ptr(matched), _ptr(sc), sc.numel(), _stream()))
         return ep[:n], depth[:n], matched[:n]
 
+    # ------------------------------------------------- a5 from chunk hashes
+    def route_hashes(self, hashes: torch.Tensor, chunk_base: torch.Tensor, n: int, max_chunks: int,
+                     avail_mask: int, seed: int, seq0: int, out=None):
+        """The route stage from chunk hashes in CSR form (as hash_chunks returns them):
+        b200r_prefix_route_hashes.  Same results as route() on the prompts behind them."""
+        L = _lib.lib()
+        if out is None:
+            out = (torch.empty(max(n, 1), dtype=torch.int32, device=self.device),
+                   torch.empty(max(n, 1), dtype=torch.int32, device=self.device),
+                   torch.empty(max(n, 1), dtype=torch.int64, device=self.device))
+        ep, depth, matched = out
+        sc = self._scratch_for(L.b200r_prefix_route_scratch_bytes(n, max_chunks, _lib.F_ALL_ASCII))
+        with torch.cuda.device(self.device):
+            _lib.check(L.b200r_prefix_route_hashes(
+                self._h, _ptr(hashes), _ptr(chunk_base), n, max_chunks, avail_mask & M64,
+                seed & M64, seq0 & M64, _ptr(ep), _ptr(depth), _ptr(matched), _ptr(sc), sc.numel(),
+                _stream()))
+        return ep[:n], depth[:n], matched[:n]
+
     # --------------------------------------------------------------- dump etc
     def dump_raw(self):
-        """(entries uint64[count,4] = key_lo,key_hi,chunk_hash,mask ; root_mask)."""
+        """(entries uint64[count,4], root_mask); an entry is {log index | run length << 32 (on
+        the first node of a run), parent's log index (0xFFFFFFFF = root), chunk hash, mask}."""
         s = self.status()
         cap = max(int(s["num_nodes"]), 1)
         out = torch.empty(cap * 4, dtype=torch.int64, device=self.device)
@@ -189,34 +204,51 @@ class GpuHashTrie:
         arr = out.cpu().numpy().view(np.uint64).reshape(-1, 4)[:cnt.value]
         return arr, rm.value
 
-    def apply_entries(self, entries: torch.Tensor, root_mask_or: int = 0):
-        """Merge dumped entries (restore / nodes created on another GPU)."""
+    def restore_entries(self, entries: torch.Tensor, root_mask: int = 0):
+        """Put dumped entries back (b200r_trie_restore); the table must be empty."""
         ent = entries.to(self.device).contiguous()
         with torch.cuda.device(self.device):
-            _lib.check(_lib.lib().b200r_trie_apply_remote(self._h, _ptr(ent), ent.numel() // 4,
-                                                          root_mask_or & M64, _stream()))
+            _lib.check(_lib.lib().b200r_trie_restore(self._h, _ptr(ent), ent.numel() // 4,
+                                                     root_mask & M64, _stream()))
+
+    def retire_endpoints(self, bits: int):
+        """Clear the given endpoint bits from every node and from the root (the bit of an
+        endpoint that is gone for good can then be handed to a new url)."""
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().b200r_trie_retire_endpoints(self._h, bits & M64, _stream()))
 
     # ------------------------------------------------------- checkpoint (f4)
-    def save(self, path: str):
-        """Write the table to disk (the reference has no checkpoint; its trie dies
-        with the process).  Format: npz with entries uint64[count,4] =
-        {key_lo, key_hi, chunk_hash, mask}, root mask, chunk size, format version."""
+    def save(self, path, extra: Optional[Dict] = None):
+        """Write the table to disk (the reference has no checkpoint; its trie dies with the
+        process).  Format: npz with entries uint64[count,4] (see dump_raw), root mask, chunk
+        size, format version, plus whatever the caller adds in `extra` (the router stores its
+        url <-> bit registry there, without which the masks mean nothing to a new process).
+        `path` is used as given (no suffix is appended)."""
         arr, root = self.dump_raw()
-        np.savez(path, entries=arr, root_mask=np.uint64(root),
-                 chunk_chars=np.int32(self.chunk_chars), version=np.int32(1))
+        fields = dict(entries=arr, root_mask=np.uint64(root), chunk_chars=np.int32(self.chunk_chars),
+                      version=np.int32(2))
+        for k, v in (extra or {}).items():
+            fields["x_" + k] = np.asarray(v)
+        with open(path, "wb") as f:
+            np.savez(f, **fields)
 
     @classmethod
-    def load(cls, path: str, cap_log2: Optional[int] = None, device=None) -> "GpuHashTrie":
-        z = np.load(path)
-        if int(z["version"]) != 1:
+    def load(cls, path, cap_log2: Optional[int] = None, device=None, with_extra: bool = False):
+        with open(path, "rb") as f:
+            z = dict(np.load(f, allow_pickle=False))
+        if int(z["version"]) != 2:
             raise _lib.B200RouterError("unknown trie checkpoint version %d" % int(z["version"]))
         arr = z["entries"]
+        need = int((arr[:, 0] & np.uint64(0xFFFFFFFF)).max()) + 1 if len(arr) else 1
         if cap_log2 is None:
-            cap_log2 = max(12, int(np.ceil(np.log2(max(len(arr), 1) * 2.5))))
+            cap_log2 = max(12, int(np.ceil(np.log2(need * 1.5))))
+        if (1 << cap_log2) < need:
+            raise _lib.B200RouterError("checkpoint needs a capacity of at least %d nodes" % need)
         t = cls(cap_log2=cap_log2, chunk_chars=int(z["chunk_chars"]), device=device)
-        if len(arr):
-            t.apply_entries(torch.from_numpy(arr.view(np.int64).copy()), int(z["root_mask"]))
+        t.restore_entries(torch.from_numpy(arr.view(np.int64).copy()), int(z["root_mask"]))
         t.check_status()
+        if with_extra:
+            return t, {k[2:]: v for k, v in z.items() if k.startswith("x_")}
         return t
 
     def dump(self) -> Dict[tuple, int]:
@@ -226,40 +258,34 @@ class GpuHashTrie:
         return decode_dump(arr, root)
 
 
-def key_constants():
-    out = (C.c_uint64 * 6)()
-    _lib.lib().b200r_trie_key_constants(out)
-    return [int(x) for x in out]
-
-
-def _rotl32of64(h: int) -> int:
-    return ((h << 32) | (h >> 32)) & M64
+ROOT_IDX = 0xFFFFFFFF
 
 
 def decode_dump(arr: np.ndarray, root_mask: int) -> Dict[tuple, int]:
-    """Invert the path-key recurrence (csrc/common.cuh): parent key =
-    ((k1 - h) * A1^-1, (k2 - rotl(h,32)) * A2^-1); walk up to the root key."""
-    a1, a2, r1, r2, i1, i2 = key_constants()
-    nodes = {(int(k1), int(k2)): (int(h), int(m)) for k1, k2, h, m in arr}
-    paths: Dict[Tuple[int, int], tuple] = {(r1, r2): ()}
+    """Follow the parent links of a dump up to the root: {hash path: mask}."""
+    nodes = {int(e0) & 0xFFFFFFFF: (int(par), int(h), int(m)) for e0, par, h, m in arr}
+    paths: Dict[int, tuple] = {ROOT_IDX: ()}
 
-    def path_of(key):
+    def path_of(idx):
         chain = []
-        while key not in paths:
-            if key not in nodes:
+        while idx not in paths:
+            if idx not in nodes:
                 raise ValueError("dump is not prefix-closed: missing parent of a node")
-            h, _ = nodes[key]
-            chain.append((key, h))
-            key = (((key[0] - h) * i1) & M64, ((key[1] - _rotl32of64(h)) * i2) & M64)
-        base = paths[key]
+            par, h, _ = nodes[idx]
+            chain.append((idx, h))
+            idx = par
+        base = paths[idx]
         for k, h in reversed(chain):
             base = base + (h,)
             paths[k] = base
         return base
 
     out = {(): int(root_mask)}
-    for key, (h, m) in nodes.items():
-        out[path_of(key)] = m
+    for idx, (_, _, m) in nodes.items():
+        p = path_of(idx)
+        if p in out:
+            raise ValueError("two nodes with the same path in a dump")
+        out[p] = m
     return out
 
 
@@ -279,14 +305,9 @@ class RoutePipeline:
     produced and synchronised earlier); otherwise the hash stage waits for the
     caller's stream, which is safe but serialises the two stages."""
 
-    def __init__(self, trie: GpuHashTrie, depth: int = 2, fused: bool = False):
-        """fused=True: the first stage is only the prep (chunk counts, ragged tails) and the
-        second stage hashes + claims in one kernel; fused=False: first stage hashes every
-        chunk, second stage works from the hashes."""
+    def __init__(self, trie: GpuHashTrie, depth: int = 2):
         self.trie = trie
         self.depth = depth
-        self.fused = fused
-        self._inflight = [None] * depth
         self.device = trie.device
         self.hash_stream = torch.cuda.Stream(device=self.device)
         self._scratch = [None] * depth
@@ -338,28 +359,20 @@ class RoutePipeline:
             hs.wait_event(self._done[k])          # scratch k is free again
         if not on_host and not inputs_ready:
             hs.wait_stream(cur)
-        first = L.b200r_prefix_prep_stage if self.fused else L.b200r_prefix_hash_stage
         with torch.cuda.device(self.device), torch.cuda.stream(hs):
             if on_host:
                 p = p.to(self.device, non_blocking=True)
-            _lib.check(first(
+            _lib.check(L.b200r_prefix_hash_stage(
                 self.trie._h, _ptr(p.bytes), _ptr(p.starts), _ptr(p.lens), _ptr(p.nchars), n,
                 p.max_chunks, flags, _ptr(sc), sc.numel(), C.c_void_p(hs.cuda_stream)))
             self._hashed[k].record(hs)
         cur.wait_event(self._hashed[k])
         ep, depth, matched = o
         with torch.cuda.device(self.device):
-            if self.fused:       # the fused stage reads the prompt bytes again: keep them alive
-                self._inflight[k] = p
-                _lib.check(L.b200r_prefix_fused_stage(
-                    self.trie._h, _ptr(p.bytes), _ptr(p.starts), _ptr(p.lens), _ptr(p.nchars), n,
-                    p.max_chunks, flags, avail_mask & M64, seed & M64, seq0 & M64, _ptr(ep),
-                    _ptr(depth), _ptr(matched), _ptr(sc), sc.numel(), C.c_void_p(cur.cuda_stream)))
-            else:
-                _lib.check(L.b200r_prefix_route_stage(
-                    self.trie._h, n, p.max_chunks, flags, avail_mask & M64, seed & M64, seq0 & M64,
-                    _ptr(ep), _ptr(depth), _ptr(matched), _ptr(sc), sc.numel(),
-                    C.c_void_p(cur.cuda_stream)))
+            _lib.check(L.b200r_prefix_route_stage(
+                self.trie._h, n, p.max_chunks, flags, avail_mask & M64, seed & M64, seq0 & M64,
+                _ptr(ep), _ptr(depth), _ptr(matched), _ptr(sc), sc.numel(),
+                C.c_void_p(cur.cuda_stream)))
         done = torch.cuda.Event()
         done.record(cur)
         self._done[k] = done

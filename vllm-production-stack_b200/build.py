@@ -9,7 +9,7 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "b200_router", "libb200router.so")
 PACK_OUT = os.path.join(HERE, "b200_router", "libb200pack.so")
-SOURCES = ["prefix.cu", "session.cu"]
+SOURCES = ["prefix.cu", "multigpu.cu", "session.cu"]
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC,-fvisibility=hidden", "-shared", "-cudart", "shared",
          "-I", os.path.join(ROOT, "include"), "-I", CSRC]

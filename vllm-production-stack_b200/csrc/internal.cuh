@@ -1,0 +1,94 @@
+// internal.cuh -- host-side pieces shared by prefix.cu (hashing, single-GPU routing, C ABI)
+// and multigpu.cu (the partitioned multi-GPU exchange).
+#pragma once
+#include <vector>
+
+#include "trie.cuh"
+
+namespace b200r {
+
+// ------------------------------------------------------------- profiling
+// Optional per-kernel timing with CUDA events on the launching stream
+// (b200r_prof_enable / b200r_prof_read).  Off by default: the hot path then
+// records nothing.  g_launches counts every kernel this library enqueues.
+enum { PK_PREP = 0, PK_UTF8, PK_HASH, PK_CLAIM, PK_SELECT, PK_COMMIT, PK_LOOKUP, PK_INSERT,
+       PK_CLASSIFY, PK_PUSH, PK_WAIT, PK_APPLY, PK_RESOLVE, PK_COUNT };
+struct ProfSpan { int kid; cudaEvent_t a, b; };
+extern bool g_prof_on;
+extern std::vector<ProfSpan> g_spans;
+extern long long g_launches;
+
+struct ProfScope {
+    bool on; cudaStream_t st; ProfSpan sp;
+    ProfScope(int kid, cudaStream_t s) : on(g_prof_on), st(s)
+    {
+        if (!on) return;
+        sp.kid = kid;
+        cudaEventCreate(&sp.a); cudaEventCreate(&sp.b);
+        cudaEventRecord(sp.a, st);
+    }
+    ~ProfScope()
+    {
+        if (!on) return;
+        cudaEventRecord(sp.b, st);
+        g_spans.push_back(sp);
+    }
+};
+
+constexpr int WARPS_PER_CTA = 8;       // per-request kernels: one warp per request
+constexpr int WALK_MAX_CTAS = 148 * 8; // persistent grid of the walk kernels (<= NWSLOT warps)
+
+// Device-resident bookkeeping of the partitioned multi-GPU path (read by k_select).
+constexpr int P2P_MAX_WORLD = 64;
+struct P2PDyn {
+    unsigned long long seq_base;     // global sequence number of the next batch's request 0
+    uint32_t my_off, total_n;        // position of this shard / size of the current global batch
+};
+
+static inline size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
+
+struct Plan {           // carve-up of the caller's scratch buffer
+    size_t off_tile_first, off_block_sums, off_nchars, off_chunk_off, off_chunk_base, off_hashes,
+        off_slots, off_leader, off_choice, off_dpre, off_cand, total;
+};
+Plan make_plan(int64_t n, int64_t max_chunks, uint32_t flags, bool routing);
+
+int check_prompt_args(const void *bytes, const void *starts, const void *lens, int64_t n,
+                      int64_t max_chunks, int32_t cc);
+
+// prep + (utf8) + chunk hashing
+int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const int32_t *d_lens,
+                const int32_t *d_nchars, int64_t n, int32_t cc, uint32_t flags,
+                int32_t *d_chunk_base, uint64_t *d_hashes, int64_t max_chunks, uint8_t *scratch,
+                const Plan &p, TrieDev *dev, cudaStream_t st);
+
+// CSR of given per-request chunk counts; the count of requests is known only on the device
+int launch_prep_counts(const int32_t *d_counts, int64_t n_max, const int32_t *n_dev,
+                       int32_t *block_sums, int32_t *chunk_base, int64_t c_max, TrieDev *dev,
+                       cudaStream_t st);
+
+// claim -> select -> commit over chunk hashes already in memory.  `n` sizes the grids; when the
+// real count lives on the device (n_dev) it is an estimate and the kernels stride.
+struct RouteCore {
+    const uint64_t *hashes; const int32_t *chunk_base; int64_t n; int64_t max_chunks;
+    uint64_t avail, seed, seq0;
+    uint32_t *slots; int32_t *leader, *choice, *dpre; uint64_t *cand;
+    int32_t *endpoint, *depth; uint64_t *matched;
+    const P2PDyn *dyn; const uint32_t *pos; const int32_t *n_dev;
+};
+int launch_route_core(b200r_trie *t, const RouteCore &rc, cudaStream_t st);
+
+TrieRef trie_ref(const b200r_trie *t);
+
+}  // namespace b200r
+
+struct b200r_trie {
+    int device;
+    int cap_log2;
+    int chunk_chars;
+    b200r::Head *tab;
+    b200r::Rec *log;
+    uint2 *wblk;
+    b200r::TrieDev *dev;
+    uint32_t epoch;
+};

@@ -1,0 +1,534 @@
+// multigpu.cu -- prefix-aware routing of one global batch over several GPUs with a
+// PARTITIONED table (one process per GPU; no counterpart in the reference, whose router
+// replicas share nothing).  C ABI: b200r_part_* (include/b200_router.h).  The replicated-table
+// variant needs no kernels of its own: it all-gathers chunk hashes on the host side (NCCL) and
+// routes the global batch with b200r_prefix_route_hashes (prefix.cu).
+#include <algorithm>
+
+#include "internal.cuh"
+
+namespace b200r {
+
+__device__ __forceinline__ bool p2p_spin(const volatile unsigned long long *flag,
+                                         unsigned long long epoch, unsigned long long *val)
+{
+    const long long t0 = clock64();
+    for (;;) {
+        const unsigned long long v = *flag;
+        if ((v >> 32) == epoch) { *val = v; return true; }
+        if (clock64() - t0 > 6000000000LL) return false;     // ~3 s: a peer is gone
+        __nanosleep(200);
+    }
+}
+
+
+// =========================================================================
+// =========================================================================
+// Multi-GPU, PARTITIONED table (the scalable variant; SURVEY.md 8e fallback).
+// A request's whole path hangs under its first chunk, so requests with
+// different first-chunk hashes never meet in the trie.  The table is therefore
+// partitioned by owner(first chunk hash) = mix(h0) % world and nothing is
+// replicated: per batch every rank
+//   send    hashes its own shard (as before) and pushes, per owner, the chunk
+//           hashes + {local index, chunk count} of the requests that owner
+//           holds, order preserved, straight into the owner's buffer (NVLink
+//           peer stores, ~6 % of the prompt bytes), then publishes flags;
+//   route   waits for all sources, concatenates what it received in rank
+//           order (= global order of the requests it owns), runs the ordinary
+//           claim / select / commit on that batch against ITS partition, and
+//           pushes {endpoint, depth, candidates} back to the sources;
+//   finish  waits for all owners and scatters the results to request order.
+// Sequential equivalence holds per partition and partitions are independent;
+// the tie-break counter uses the request's position in the global order.
+// Per-GPU work no longer grows with the number of GPUs.
+// =========================================================================
+struct PartFlags {
+    unsigned long long in_req[2][P2P_MAX_WORLD], in_chunk[2][P2P_MAX_WORLD], in_n[2][P2P_MAX_WORLD],
+        res[2][P2P_MAX_WORLD];
+};
+static_assert(sizeof(PartFlags) <= 4096, "flag block");
+struct PartRes { int32_t ep, depth; uint64_t matched; };
+struct PartDyn {
+    P2PDyn base;                              // seq_base, total_n (my_off stays 0)
+    int32_t n_owned, c_owned;
+    uint32_t reqbase[P2P_MAX_WORLD + 1], chunkbase[P2P_MAX_WORLD + 1], off[P2P_MAX_WORLD + 1];
+};
+
+__device__ __forceinline__ int part_owner(const uint64_t *hashes, int b, int C, int world)
+{
+    if (C == 0) return 0;                     // empty prompt: touches only a root
+    uint64_t x = hashes[b] * 0x9E3779B97F4A7C15ULL;
+    return (int)((x >> 33) % (uint64_t)world);
+}
+
+constexpr int PART_BLOCK = 256;
+
+// per block of 256 requests: how many requests / chunks go to each owner
+__global__ void __launch_bounds__(PART_BLOCK)
+k_part_count(const int32_t *__restrict__ chunk_base, const uint64_t *__restrict__ hashes, int n,
+             int world, int32_t *__restrict__ blk_cnt)
+{
+    __shared__ int s_cnt[2 * P2P_MAX_WORLD];
+    for (int k = threadIdx.x; k < 2 * world; k += PART_BLOCK) s_cnt[k] = 0;
+    __syncthreads();
+    const int i = blockIdx.x * PART_BLOCK + threadIdx.x;
+    if (i < n) {
+        const int b = chunk_base[i], C = chunk_base[i + 1] - b;
+        const int o = part_owner(hashes, b, C, world);
+        atomicAdd(&s_cnt[2 * o], 1);
+        atomicAdd(&s_cnt[2 * o + 1], C);
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < 2 * world; k += PART_BLOCK)
+        blk_cnt[(size_t)blockIdx.x * 2 * world + k] = s_cnt[k];
+}
+
+// exclusive scan over the blocks, per owner and kind (one warp each, 32 blocks per step)
+__global__ void k_part_scan(const int32_t *__restrict__ blk_cnt, int nblk, int world,
+                            int32_t *__restrict__ blk_off, int32_t *__restrict__ totals)
+{
+    const int lane = threadIdx.x & 31;
+    const int nwarps = blockDim.x >> 5;
+    for (int k = threadIdx.x >> 5; k < 2 * world; k += nwarps) {
+        int run = 0;
+        for (int b0 = 0; b0 < nblk; b0 += 32) {
+            const int b = b0 + lane;
+            const int v = b < nblk ? blk_cnt[(size_t)b * 2 * world + k] : 0;
+            int inc = v;
+            for (int sft = 1; sft < 32; sft <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, inc, sft);
+                if (lane >= sft) inc += t;
+            }
+            if (b < nblk) blk_off[(size_t)b * 2 * world + k] = run + inc - v;
+            run += __shfl_sync(0xffffffffu, inc, 31);
+        }
+        if (lane == 0) totals[k] = run;
+    }
+    // starts of the per-owner segments in the local staging buffers (even, so that every
+    // segment can be copied with 16-byte vectors): totals[2*world + 2*o] requests, [+1] chunks
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int r = 0, c = 0;
+        for (int o = 0; o < world; o++) {
+            totals[2 * world + 2 * o] = r; totals[2 * world + 2 * o + 1] = c;
+            r += (totals[2 * o] + 1) & ~1; c += (totals[2 * o + 1] + 1) & ~1;
+        }
+    }
+}
+
+// order-preserving compaction per owner: where does every request (and its run of chunk
+// hashes) go in its owner's buffer?  The {local index, chunk count} words and the hashes
+// are first compacted into LOCAL staging buffers, one contiguous segment per owner, and then
+// shipped by k_part_bulk with full-line 16-byte vector stores: NVLink moves the same bytes
+// several times faster in 128-byte lines than as 8-byte words or ragged ~170-byte runs
+// (measured at 2 GPUs: 47 us per shard for direct scattered peer stores).
+__global__ void __launch_bounds__(PART_BLOCK)
+k_part_push(const int32_t *__restrict__ chunk_base, const uint64_t *__restrict__ hashes, int n,
+            int world, const int32_t *__restrict__ blk_off, const int32_t *__restrict__ totals,
+            unsigned long long *__restrict__ info_stage, uint32_t *__restrict__ dest_slot,
+            uint32_t *__restrict__ req_dst)
+{
+    __shared__ int s_w[PART_BLOCK / 32][2 * P2P_MAX_WORLD];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int i = blockIdx.x * PART_BLOCK + threadIdx.x;
+    int b = 0, C = 0, o = -1;
+    if (i < n) {
+        b = chunk_base[i];
+        C = chunk_base[i + 1] - b;
+        o = part_owner(hashes, b, C, world);
+    }
+    // rank of this request / its chunks among the warp's earlier requests of the same owner
+    int rreq = 0, rchunk = 0;
+    for (int d = 0; d < world; d++) {
+        const unsigned m = __ballot_sync(0xffffffffu, o == d);
+        int v = (o == d) ? C : 0, inc = v;
+        for (int sft = 1; sft < 32; sft <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, sft);
+            if (lane >= sft) inc += t;
+        }
+        if (o == d) { rreq = __popc(m & ((1u << lane) - 1)); rchunk = inc - v; }
+        if (lane == 31) { s_w[w][2 * d] = __popc(m); s_w[w][2 * d + 1] = inc; }
+    }
+    __syncthreads();
+    if (o >= 0) {
+        int breq = blk_off[(size_t)blockIdx.x * 2 * world + 2 * o];
+        int bchunk = blk_off[(size_t)blockIdx.x * 2 * world + 2 * o + 1];
+        for (int k = 0; k < w; k++) { breq += s_w[k][2 * o]; bchunk += s_w[k][2 * o + 1]; }
+        rreq += breq;
+        rchunk += bchunk;
+        dest_slot[i] = ((uint32_t)o << 24) | (uint32_t)rreq;
+        req_dst[i] = (uint32_t)(totals[2 * world + 2 * o + 1] + rchunk);
+        info_stage[totals[2 * world + 2 * o] + rreq] =
+            (unsigned long long)(uint32_t)i | ((unsigned long long)(uint32_t)C << 32);
+    }
+}
+
+// chunk hashes -> local staging, one warp per request (coalesced both ways)
+__global__ void __launch_bounds__(WARPS_PER_CTA * 32)
+k_part_copy(const int32_t *__restrict__ chunk_base, const uint64_t *__restrict__ hashes, int n,
+            const uint32_t *__restrict__ req_dst, uint64_t *__restrict__ hash_stage)
+{
+    const int lane = threadIdx.x & 31;
+    const int nw = (gridDim.x * blockDim.x) >> 5;
+    for (int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < n; i += nw) {
+        const int b = chunk_base[i], C = chunk_base[i + 1] - b;
+        uint64_t *dst = hash_stage + req_dst[i];
+        for (int c = lane; c < C; c += 32) dst[c] = hashes[b + c];
+    }
+}
+
+// staging segments -> the owners' buffers: 16-byte vectors, whole lines.  Persistent grid, one
+// system-scope fence per CTA at the end (MEMBAR.SYS costs microseconds: not once per wave).
+__global__ void __launch_bounds__(256)
+k_part_bulk(const uint64_t *__restrict__ hash_stage, const unsigned long long *__restrict__ info_stage,
+            const int32_t *__restrict__ totals, int world, int my_rank,
+            const unsigned long long *__restrict__ peer_bases, size_t hash_off, size_t info_off,
+            int64_t cap, int64_t rcap)
+{
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
+    for (int k = 0; k < world; k++) {
+        const int o = (my_rank + 1 + k) % world;       // start with the next rank: spread the links
+        const int nreq = totals[2 * o], nchunk = totals[2 * o + 1];
+        const uint4 *hs = (const uint4 *)(hash_stage + totals[2 * world + 2 * o + 1]);
+        uint4 *hd = (uint4 *)((uint64_t *)(uintptr_t)(peer_bases[o] + hash_off) + (size_t)my_rank * cap);
+        for (int64_t x = tid; x < (nchunk + 1) / 2; x += nthr) hd[x] = hs[x];
+        const uint4 *is = (const uint4 *)(info_stage + totals[2 * world + 2 * o]);
+        uint4 *id = (uint4 *)((unsigned long long *)(uintptr_t)(peer_bases[o] + info_off) + (size_t)my_rank * rcap);
+        for (int64_t x = tid; x < (nreq + 1) / 2; x += nthr) id[x] = is[x];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) __threadfence_system();
+}
+
+__global__ void k_part_publish_in(const unsigned long long *__restrict__ peer_bases, int world,
+                                  int my_rank, int set, unsigned long long epoch,
+                                  const int32_t *__restrict__ totals, unsigned int n)
+{
+    const int d = threadIdx.x;
+    if (d >= world) return;
+    PartFlags *f = (PartFlags *)(uintptr_t)peer_bases[d];
+    __threadfence_system();
+    *(volatile unsigned long long *)&f->in_n[set][my_rank] = (epoch << 32) | n;
+    *(volatile unsigned long long *)&f->in_chunk[set][my_rank] = (epoch << 32) | (uint32_t)totals[2 * d + 1];
+    *(volatile unsigned long long *)&f->in_req[set][my_rank] = (epoch << 32) | (uint32_t)totals[2 * d];
+    __threadfence_system();
+}
+
+__global__ void k_part_wait_meta(const PartFlags *__restrict__ mine, int set, unsigned long long epoch,
+                                 int world, PartDyn *dyn, TrieDev *dev)
+{
+    __shared__ uint32_t s_req[P2P_MAX_WORLD], s_chunk[P2P_MAX_WORLD], s_n[P2P_MAX_WORLD];
+    const int q = threadIdx.x;
+    if (q < world) {
+        unsigned long long a = 0, b = 0, c = 0;
+        const bool ok = p2p_spin(&mine->in_req[set][q], epoch, &a) &&
+                        p2p_spin(&mine->in_chunk[set][q], epoch, &b) &&
+                        p2p_spin(&mine->in_n[set][q], epoch, &c);
+        if (!ok) atomicOr(&dev->status, B200R_S_PEER_TIMEOUT);
+        s_req[q] = ok ? (uint32_t)a : 0; s_chunk[q] = ok ? (uint32_t)b : 0; s_n[q] = ok ? (uint32_t)c : 0;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t r = 0, c = 0, o = 0;
+        for (int k = 0; k < world; k++) {
+            dyn->reqbase[k] = r; dyn->chunkbase[k] = c; dyn->off[k] = o;
+            r += s_req[k]; c += s_chunk[k]; o += s_n[k];
+        }
+        dyn->reqbase[world] = r; dyn->chunkbase[world] = c; dyn->off[world] = o;
+        dyn->n_owned = (int32_t)r; dyn->c_owned = (int32_t)c;
+        dyn->base.my_off = 0; dyn->base.total_n = o;
+    }
+    __threadfence_system();
+}
+
+// concatenate what the sources sent, in rank order
+__global__ void k_part_gather(const uint8_t *__restrict__ my_base, size_t hash_off, size_t info_off,
+                              int64_t cap, int64_t rcap, int world, const PartDyn *__restrict__ dyn,
+                              int32_t *__restrict__ c_owned, uint32_t *__restrict__ pos_owned,
+                              uint64_t *__restrict__ hashes_owned)
+{
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t step = (int64_t)gridDim.x * blockDim.x;
+    const unsigned long long *info = (const unsigned long long *)(my_base + info_off);
+    const uint64_t *hin = (const uint64_t *)(my_base + hash_off);
+    for (int64_t j = tid; j < dyn->n_owned; j += step) {
+        int q = 0;
+        while (q + 1 < world && j >= dyn->reqbase[q + 1]) q++;
+        const unsigned long long v = info[(size_t)q * rcap + (j - dyn->reqbase[q])];
+        c_owned[j] = (int32_t)(v >> 32);
+        pos_owned[j] = dyn->off[q] + (uint32_t)v;
+    }
+    for (int64_t x = tid; x < dyn->c_owned; x += step) {
+        int q = 0;
+        while (q + 1 < world && x >= dyn->chunkbase[q + 1]) q++;
+        hashes_owned[x] = hin[(size_t)q * cap + (x - dyn->chunkbase[q])];
+    }
+}
+
+__global__ void k_part_push_results(const PartDyn *__restrict__ dyn, int world, int my_rank,
+                                    const int32_t *__restrict__ ep, const int32_t *__restrict__ depth,
+                                    const uint64_t *__restrict__ matched,
+                                    const unsigned long long *__restrict__ peer_bases,
+                                    size_t res_off, int64_t rcap)
+{
+    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < dyn->n_owned;
+         j += (int64_t)gridDim.x * blockDim.x) {
+        int q = 0;
+        while (q + 1 < world && j >= dyn->reqbase[q + 1]) q++;
+        PartRes r;
+        r.ep = ep[j]; r.depth = depth[j]; r.matched = matched[j];
+        ((PartRes *)(uintptr_t)(peer_bases[q] + res_off))[(size_t)my_rank * rcap + (j - dyn->reqbase[q])] = r;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) __threadfence_system();
+}
+
+__global__ void k_part_publish_res(const unsigned long long *__restrict__ peer_bases, int world,
+                                   int my_rank, int set, unsigned long long epoch,
+                                   const PartDyn *__restrict__ dyn)
+{
+    const int q = threadIdx.x;
+    if (q >= world) return;
+    PartFlags *f = (PartFlags *)(uintptr_t)peer_bases[q];
+    __threadfence_system();
+    *(volatile unsigned long long *)&f->res[set][my_rank] =
+        (epoch << 32) | (dyn->reqbase[q + 1] - dyn->reqbase[q]);
+    __threadfence_system();
+}
+
+__global__ void k_part_wait_res(const PartFlags *__restrict__ mine, int set, unsigned long long epoch,
+                                int world, TrieDev *dev, PartDyn *dyn)
+{
+    const int q = threadIdx.x;
+    if (q < world) {
+        unsigned long long v;
+        if (!p2p_spin(&mine->res[set][q], epoch, &v)) atomicOr(&dev->status, B200R_S_PEER_TIMEOUT);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) dyn->base.seq_base += dyn->base.total_n;   // next batch's request 0
+    __threadfence_system();
+}
+
+__global__ void k_part_scatter(const uint32_t *__restrict__ dest_slot, const uint8_t *__restrict__ my_base,
+                               size_t res_off, int64_t rcap, int n, int32_t *__restrict__ endpoint,
+                               int32_t *__restrict__ depth, uint64_t *__restrict__ matched)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t ds = dest_slot[i];
+    const PartRes r = ((const PartRes *)(my_base + res_off))[(size_t)(ds >> 24) * rcap + (ds & 0xFFFFFFu)];
+    endpoint[i] = r.ep; depth[i] = r.depth; matched[i] = r.matched;
+}
+
+}  // namespace b200r
+
+using namespace b200r;
+
+extern "C" {
+
+// ------------------------------------------------------ multi-GPU, partitioned
+struct PartLayout {
+    size_t symm_total, hash_off, info_off, res_off, hash_set, info_set, res_set;
+    // local work buffer
+    size_t work_total, w_dyn, w_blk_cnt, w_blk_off, w_totals, w_dest_slot, w_req_dst, w_hash_stage, w_info_stage, w_c_owned, w_pos_owned,
+        w_ep, w_depth, w_matched, w_plan;
+    int64_t n_max, c_max;
+    int nblk_max;
+};
+
+static PartLayout part_layout(int world, int64_t cap, int64_t rcap)
+{
+    PartLayout L;
+    L.hash_off = 4096;
+    L.hash_set = (size_t)world * cap * 8;
+    L.info_off = L.hash_off + 2 * L.hash_set;
+    L.info_set = (size_t)world * rcap * 8;
+    L.res_off = L.info_off + 2 * L.info_set;
+    L.res_set = (size_t)world * rcap * sizeof(PartRes);
+    L.symm_total = align_up(L.res_off + 2 * L.res_set);
+    L.n_max = (int64_t)world * rcap;
+    L.c_max = (int64_t)world * cap;
+    L.nblk_max = (int)((rcap + PART_BLOCK - 1) / PART_BLOCK);
+    size_t o = 0;
+    L.w_dyn = o;       o += align_up(sizeof(PartDyn));
+    L.w_blk_cnt = o;   o += align_up((size_t)L.nblk_max * 2 * world * 4);
+    L.w_blk_off = o;   o += align_up((size_t)L.nblk_max * 2 * world * 4);
+    L.w_totals = o;    o += align_up((size_t)4 * world * 4);
+    L.w_dest_slot = o; o += 2 * align_up((size_t)rcap * 4);     // one per batch parity
+    L.w_req_dst = o;   o += align_up((size_t)rcap * 4);
+    L.w_hash_stage = o; o += align_up((size_t)(cap + 2 * world + 2) * 8);
+    L.w_info_stage = o; o += align_up((size_t)(rcap + 2 * world + 2) * 8);
+    L.w_c_owned = o;   o += align_up((size_t)L.n_max * 4);
+    L.w_pos_owned = o; o += align_up((size_t)L.n_max * 4);
+    L.w_ep = o;        o += align_up((size_t)L.n_max * 4);
+    L.w_depth = o;     o += align_up((size_t)L.n_max * 4);
+    L.w_matched = o;   o += align_up((size_t)L.n_max * 8);
+    L.w_plan = o;      o += make_plan(L.n_max, L.c_max, B200R_F_ALL_ASCII, true).total;
+    L.work_total = o + 256;
+    return L;
+}
+
+static int part_check(int world, int rank, int64_t cap, int64_t rcap, const void *a, const void *b)
+{
+    if (world <= 0 || world > P2P_MAX_WORLD || rank < 0 || rank >= world || cap <= 0 || rcap <= 0 ||
+        (cap & 1) || (rcap & 1) ||
+        rcap >= (1 << 24) || (int64_t)world * cap > 0x7fffffff - 4096 || !a || !b) {
+        set_error("partitioned routing: need 1 <= world <= %d, 0 <= rank < world, 0 < rcap < 2^24, "
+                  "cap and rcap even, world * cap < 2^31, non-null buffers", P2P_MAX_WORLD);
+        return B200R_E_INVALID;
+    }
+    return B200R_OK;
+}
+
+int b200r_part_layout(int32_t world, int64_t cap, int64_t rcap, size_t out[2])
+{
+    if (world <= 0 || world > P2P_MAX_WORLD || cap <= 0 || rcap <= 0 || !out) { set_error("b200r_part_layout: bad argument"); return B200R_E_INVALID; }
+    const PartLayout L = part_layout(world, cap, rcap);
+    out[0] = L.symm_total; out[1] = L.work_total;
+    return B200R_OK;
+}
+
+int b200r_part_send(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
+                    const int32_t *d_lens, const int32_t *d_nchars, int64_t n, int64_t max_chunks,
+                    uint32_t flags, const uint64_t *d_peer_bases, int32_t world, int32_t rank,
+                    int64_t cap, int64_t rcap, uint32_t epoch, void *d_work, void *d_scratch,
+                    size_t scratch_bytes, void *stream)
+{
+    int rc = part_check(world, rank, cap, rcap, d_peer_bases, d_work);
+    if (rc) return rc;
+    if (max_chunks > cap || n > rcap) { set_error("partitioned routing: batch (n=%lld, max_chunks=%lld) exceeds the exchange capacity (rcap=%lld, cap=%lld)", (long long)n, (long long)max_chunks, (long long)rcap, (long long)cap); return B200R_E_INVALID; }
+    rc = b200r_prefix_hash_stage(t, d_bytes, d_starts, d_lens, d_nchars, n, max_chunks, flags,
+                                 d_scratch, scratch_bytes, stream);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const PartLayout L = part_layout(world, cap, rcap);
+    const Plan p = make_plan(n, max_chunks, flags, true);
+    uint8_t *sc = (uint8_t *)d_scratch, *wk = (uint8_t *)d_work;
+    const int32_t *chunk_base = (const int32_t *)(sc + p.off_chunk_base);
+    const uint64_t *hashes = (const uint64_t *)(sc + p.off_hashes);
+    int32_t *blk_cnt = (int32_t *)(wk + L.w_blk_cnt), *blk_off = (int32_t *)(wk + L.w_blk_off);
+    int32_t *totals = (int32_t *)(wk + L.w_totals);
+    const int set = (int)(epoch & 1);
+    const int nblk = (int)((n + PART_BLOCK - 1) / PART_BLOCK);
+    ProfScope ps__(PK_PUSH, st);
+    if (nblk > 0) {
+        g_launches += 3;
+        k_part_count<<<nblk, PART_BLOCK, 0, st>>>(chunk_base, hashes, (int)n, world, blk_cnt);
+        B200R_LAUNCH_CHECK("k_part_count");
+        k_part_scan<<<1, 1024, 0, st>>>(blk_cnt, nblk, world, blk_off, totals);
+        B200R_LAUNCH_CHECK("k_part_scan");
+        uint32_t *dest_slot = (uint32_t *)(wk + L.w_dest_slot + (size_t)set * align_up((size_t)rcap * 4));
+        uint32_t *req_dst = (uint32_t *)(wk + L.w_req_dst);
+        uint64_t *hash_stage = (uint64_t *)(wk + L.w_hash_stage);
+        unsigned long long *info_stage = (unsigned long long *)(wk + L.w_info_stage);
+        k_part_push<<<nblk, PART_BLOCK, 0, st>>>(chunk_base, hashes, (int)n, world, blk_off, totals,
+                                                 info_stage, dest_slot, req_dst);
+        B200R_LAUNCH_CHECK("k_part_push");
+        g_launches += 2;
+        k_part_copy<<<(unsigned)std::min<int64_t>((n + WARPS_PER_CTA - 1) / WARPS_PER_CTA, 148 * 8),
+                      WARPS_PER_CTA * 32, 0, st>>>(chunk_base, hashes, (int)n, req_dst, hash_stage);
+        B200R_LAUNCH_CHECK("k_part_copy");
+        k_part_bulk<<<148 * 2, 256, 0, st>>>(hash_stage, info_stage, totals, world, rank,
+                                             (const unsigned long long *)d_peer_bases,
+                                             L.hash_off + (size_t)set * L.hash_set,
+                                             L.info_off + (size_t)set * L.info_set, cap, rcap);
+        B200R_LAUNCH_CHECK("k_part_bulk");
+    } else {
+        B200R_CUDA(cudaMemsetAsync(totals, 0, (size_t)4 * world * 4, st));
+    }
+    g_launches += 1;
+    k_part_publish_in<<<1, P2P_MAX_WORLD, 0, st>>>((const unsigned long long *)d_peer_bases, world, rank,
+                                                   set, epoch, totals, (unsigned)n);
+    B200R_LAUNCH_CHECK("k_part_publish_in");
+    return B200R_OK;
+}
+
+int b200r_part_route(b200r_trie *t, uint64_t avail_mask, uint64_t seed,
+                     const uint64_t *d_peer_bases, void *d_my_base, int32_t world, int32_t rank,
+                     int64_t cap, int64_t rcap, uint32_t epoch, void *d_work, void *stream)
+{
+    int rc = part_check(world, rank, cap, rcap, d_peer_bases, d_work);
+    if (rc) return rc;
+    if (!t || !d_my_base) { set_error("b200r_part_route: null pointer"); return B200R_E_INVALID; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const PartLayout L = part_layout(world, cap, rcap);
+    const Plan p = make_plan(L.n_max, L.c_max, B200R_F_ALL_ASCII, true);
+    const int set = (int)(epoch & 1);
+    uint8_t *base = (uint8_t *)d_my_base, *wk = (uint8_t *)d_work, *sc = wk + L.w_plan;
+    PartDyn *dyn = (PartDyn *)(wk + L.w_dyn);
+    int32_t *c_owned = (int32_t *)(wk + L.w_c_owned);
+    uint32_t *pos_owned = (uint32_t *)(wk + L.w_pos_owned);
+    int32_t *ep = (int32_t *)(wk + L.w_ep), *depth = (int32_t *)(wk + L.w_depth);
+    uint64_t *matched = (uint64_t *)(wk + L.w_matched);
+    int32_t *chunk_base = (int32_t *)(sc + p.off_chunk_base);
+    uint64_t *hashes = (uint64_t *)(sc + p.off_hashes);
+    uint32_t *slots = (uint32_t *)(sc + p.off_slots);
+    int32_t *leader = (int32_t *)(sc + p.off_leader), *choice = (int32_t *)(sc + p.off_choice);
+    int32_t *block_sums = (int32_t *)(sc + p.off_block_sums);
+    const int32_t *n_dev = &dyn->n_owned;
+
+    { ProfScope ps__(PK_WAIT, st); g_launches += 1;
+    k_part_wait_meta<<<1, P2P_MAX_WORLD, 0, st>>>((const PartFlags *)base, set, epoch, world, dyn, t->dev);
+    B200R_LAUNCH_CHECK("k_part_wait_meta");
+    }
+    { ProfScope ps__(PK_PREP, st); g_launches += 1;
+    k_part_gather<<<148 * 4, 256, 0, st>>>(base, L.hash_off + (size_t)set * L.hash_set,
+                                           L.info_off + (size_t)set * L.info_set, cap, rcap, world, dyn,
+                                           c_owned, pos_owned, hashes);
+    B200R_LAUNCH_CHECK("k_part_gather");
+    rc = launch_prep_counts(c_owned, L.n_max, n_dev, block_sums, chunk_base, L.c_max, t->dev, st);
+    if (rc) return rc;
+    }
+    // grids are estimates (about two shards' worth); the kernels stride over the rest
+    RouteCore core = RouteCore();
+    core.hashes = hashes; core.chunk_base = chunk_base;
+    core.n = 2 * rcap < L.n_max ? 2 * rcap : L.n_max;
+    core.max_chunks = L.c_max;
+    core.avail = avail_mask; core.seed = seed; core.seq0 = 0;
+    core.slots = slots; core.leader = leader; core.choice = choice;
+    core.dpre = (int32_t *)(sc + p.off_dpre); core.cand = (uint64_t *)(sc + p.off_cand);
+    core.endpoint = ep; core.depth = depth; core.matched = matched;
+    core.dyn = &dyn->base; core.pos = pos_owned; core.n_dev = n_dev;
+    rc = launch_route_core(t, core, st);
+    if (rc) return rc;
+    { ProfScope ps__(PK_PUSH, st); g_launches += 2;
+    k_part_push_results<<<148 * 2, 256, 0, st>>>(dyn, world, rank, ep, depth, matched,
+                                                 (const unsigned long long *)d_peer_bases,
+                                                 L.res_off + (size_t)set * L.res_set, rcap);
+    B200R_LAUNCH_CHECK("k_part_push_results");
+    k_part_publish_res<<<1, P2P_MAX_WORLD, 0, st>>>((const unsigned long long *)d_peer_bases, world,
+                                                    rank, set, epoch, dyn);
+    B200R_LAUNCH_CHECK("k_part_publish_res");
+    }
+    return B200R_OK;
+}
+
+int b200r_part_finish(b200r_trie *t, int64_t n, void *d_my_base, int32_t world, int32_t rank,
+                      int64_t cap, int64_t rcap, uint32_t epoch, void *d_work, int32_t *d_endpoint,
+                      int32_t *d_match_depth, uint64_t *d_matched, void *stream)
+{
+    int rc = part_check(world, rank, cap, rcap, d_my_base, d_work);
+    if (rc) return rc;
+    if (!t || (n > 0 && (!d_endpoint || !d_match_depth || !d_matched))) { set_error("b200r_part_finish: null pointer"); return B200R_E_INVALID; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const PartLayout L = part_layout(world, cap, rcap);
+    const int set = (int)(epoch & 1);
+    uint8_t *base = (uint8_t *)d_my_base, *wk = (uint8_t *)d_work;
+    { ProfScope ps__(PK_WAIT, st); g_launches += 1;
+    k_part_wait_res<<<1, P2P_MAX_WORLD, 0, st>>>((const PartFlags *)base, set, epoch, world, t->dev,
+                                                 (PartDyn *)(wk + L.w_dyn));
+    B200R_LAUNCH_CHECK("k_part_wait_res");
+    }
+    if (n > 0) {
+        ProfScope ps__(PK_RESOLVE, st); g_launches += 1;
+        k_part_scatter<<<(int)((n + 255) / 256), 256, 0, st>>>(
+            (const uint32_t *)(wk + L.w_dest_slot + (size_t)set * align_up((size_t)rcap * 4)), base,
+            L.res_off + (size_t)set * L.res_set, rcap,
+            (int)n, d_endpoint, d_match_depth, d_matched);
+        B200R_LAUNCH_CHECK("k_part_scatter");
+    }
+    return B200R_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,434 @@
+// trie.cuh -- the GPU-resident HashTrie: a node log plus a hash table of run heads.
+//
+// Reference structure: TrieNode {children: dict[chunk hash -> TrieNode], endpoints: set}
+// (src/vllm_router/prefix/hashtrie.py:24-32).  Here every trie node is one 32-byte record
+// in an append-only LOG, and a node's identity is its log index.  The nodes a request
+// creates in one go (the part of its path that did not exist yet) are laid out as one
+// contiguous RUN of records, in depth order, so that
+//   - creating a path is one coalesced write of its records,
+//   - walking along a stored path is a coalesced read of consecutive records whose chunk
+//     hashes are compared with the request's (no hashing, no random access), and
+//   - only the FIRST node of a run has to be findable: the open-addressing hash table maps
+//     (parent node index, chunk hash) -> (log index, run length) for run heads only.  That
+//     key is exactly `parent.children[chunk_hash]`, so node identity is exact -- no path
+//     fingerprints and no collision probability beyond XXH64's own.
+// A node is therefore either a run head (in the table) or the in-run successor of its
+// parent (the record right behind the parent's record).  Every node still has its own
+// endpoint mask and batch bookkeeping word, so the routing semantics are node-per-chunk
+// exactly like the reference; only the addressing differs.  A request that shares a stored
+// path up to some depth and then diverges starts a new run whose head hangs under a node
+// in the middle of the older run.
+#pragma once
+#include "common.cuh"
+
+namespace b200r {
+
+struct __align__(32) Rec {       // one trie node
+    uint64_t h;                  // chunk hash of the edge parent -> node
+    uint64_t mask;               // endpoint set
+    unsigned long long first;    // (epoch << 32) | ~request: first request of batch `epoch`
+                                 // that touched the node (merged with atomicMax)
+    uint64_t pad;
+};
+
+struct __align__(32) Head {      // hash-table entry: the run that starts at child `h` of `parent`
+    uint64_t h;                  // chunk hash of the run's first node
+    uint64_t pkey;               // parent log index + 1 (root: ROOT_IDX + 1); 0 = empty slot
+    unsigned long long run;      // (length << 32) | log index; 0 = key claimed, not yet published
+    uint64_t pad;
+};
+
+struct TrieDev {                 // device-resident control block
+    uint64_t root_mask;
+    unsigned long long num_nodes;    // filled on demand (status / dump), not on the hot path
+    unsigned int status;
+    unsigned int pad0;
+    unsigned long long dump_count;
+    unsigned long long log_count;    // bump allocator of the node log (may overshoot log_cap)
+};
+
+struct TrieRef {                 // by-value handle for kernels
+    Head *tab;                   // 2^tab_log2 entries = 2 per node of capacity: load <= 0.5
+    Rec *log;                    // log_cap = 2^cap_log2 records
+    TrieDev *dev;
+    uint2 *wblk;                 // per warp slot: private allocation block [x, y) kept across launches
+    int tab_log2;
+    uint32_t log_cap;
+};
+
+constexpr uint32_t ROOT_IDX = 0xFFFFFFFFu;      // "log index" of the root (it has no record)
+constexpr uint32_t SLOT_NONE = 0xFFFFFFFFu;
+constexpr uint32_t PREOK_BIT = 0x80000000u;     // slots[]: node usable before the batch
+constexpr uint32_t IDX_MASK = 0x7FFFFFFFu;
+constexpr int NWSLOT = 16384;                   // warp slots with a persistent allocation block
+constexpr unsigned FULLW = 0xffffffffu;
+#define B200R_S_INTERNAL 8u                     /* latched: a published run head had no record */
+
+// ------------------------------------------------------------------ memory ops
+__device__ __forceinline__ void ld_rec(const Rec *r, uint64_t &h, uint64_t &mask, unsigned long long &first)
+{   // one 32-byte load (LDG.256).  L1 may serve it: h never changes once the run is
+    // published, masks only change in kernels that do not read them through this path, and a
+    // stale `first` only costs a redundant atomicMax.
+    uint64_t pad;
+    asm volatile("ld.global.ca.v4.u64 {%0, %1, %2, %3}, [%4];"
+                 : "=l"(h), "=l"(mask), "=l"(first), "=l"(pad) : "l"(r) : "memory");
+    (void)pad;
+}
+__device__ __forceinline__ void st_rec(Rec *r, uint64_t h, uint64_t mask, unsigned long long first)
+{
+    asm volatile("st.global.v4.u64 [%0], {%1, %2, %3, %4};"
+                 :: "l"(r), "l"(h), "l"(mask), "l"(first), "l"(0ULL) : "memory");
+}
+__device__ __forceinline__ void ld_head(const Head *e, uint64_t &a, uint64_t &b, unsigned long long &run)
+{
+    uint64_t pad;
+    asm volatile("ld.global.ca.v4.u64 {%0, %1, %2, %3}, [%4];"
+                 : "=l"(a), "=l"(b), "=l"(run), "=l"(pad) : "l"(e) : "memory");
+    (void)pad;
+}
+__device__ __forceinline__ void ld_head_cg(const Head *e, uint64_t &a, uint64_t &b, unsigned long long &run)
+{   // L2-coherent re-read (torn key halves, or a run word that is about to be published)
+    uint64_t pad;
+    asm volatile("ld.global.cg.v4.u64 {%0, %1, %2, %3}, [%4];"
+                 : "=l"(a), "=l"(b), "=l"(run), "=l"(pad) : "l"(e) : "memory");
+    (void)pad;
+}
+__device__ __forceinline__ void cas128(Head *e, uint64_t n1, uint64_t n2, uint64_t &o1, uint64_t &o2)
+{   // compare the key with (0,0), swap in (n1,n2); returns the previous key
+    asm volatile(
+        "{\n\t"
+        ".reg .b128 cmp, nw, old;\n\t"
+        "mov.b128 cmp, {%2, %3};\n\t"
+        "mov.b128 nw, {%4, %5};\n\t"
+        "atom.global.relaxed.gpu.cas.b128 old, [%6], cmp, nw;\n\t"
+        "mov.b128 {%0, %1}, old;\n\t"
+        "}\n"
+        : "=l"(o1), "=l"(o2)
+        : "l"(0ULL), "l"(0ULL), "l"(n1), "l"(n2), "l"(e)
+        : "memory");
+}
+
+__device__ __forceinline__ uint32_t slot_of(uint64_t h, uint64_t pkey, int tab_log2)
+{
+    const uint64_t x = (h ^ (pkey * 0xD6E8FEB86659FD93ULL)) * 0x9E3779B97F4A7C15ULL;
+    return (uint32_t)(x >> (64 - tab_log2));
+}
+
+// ------------------------------------------------------------------ head table
+// Run word of child `h` of the node with key pkey, or 0 when no run starts there.  An
+// "absent" answer may come from a stale L1 line; callers that act on it (creation) confirm
+// with the CAS in head_publish.  coherent = read past L1 from the start.
+__device__ __forceinline__ unsigned long long head_find(const Head *tab, int tab_log2, uint64_t h,
+                                                        uint64_t pkey, bool coherent = false)
+{
+    const uint32_t m = (1u << tab_log2) - 1;
+    uint32_t s = slot_of(h, pkey, tab_log2);
+    for (uint32_t probe = 0; probe <= m; probe++) {
+        const Head *e = tab + s;
+        uint64_t a, b;
+        unsigned long long run;
+        if (coherent) ld_head_cg(e, a, b, run);
+        else ld_head(e, a, b, run);
+        for (;;) {
+            if (b == 0) return 0;                               // empty slot: not there
+            if (a == h && b == pkey) {
+                if (run) return run;
+                ld_head_cg(e, a, b, run);                       // publisher sits between CAS and store
+                continue;
+            }
+            break;                                              // another key: next slot
+        }
+        s = (s + 1) & m;
+    }
+    return 0;
+}
+
+// Publish a run under (h, pkey).  True when this call published it; false when that child
+// exists already (someone else created it first) or the table is full.
+__device__ __forceinline__ bool head_publish(Head *tab, int tab_log2, uint64_t h, uint64_t pkey,
+                                             unsigned long long run)
+{
+    const uint32_t m = (1u << tab_log2) - 1;
+    uint32_t s = slot_of(h, pkey, tab_log2);
+    for (uint32_t probe = 0; probe <= m; probe++) {
+        Head *e = tab + s;
+        uint64_t a, b;
+        unsigned long long r;
+        ld_head(e, a, b, r);
+        for (;;) {
+            if (b == 0) {
+                cas128(e, h, pkey, a, b);
+                if (a == 0 && b == 0) {
+                    *(volatile unsigned long long *)&e->run = run;
+                    return true;
+                }
+                continue;                       // the slot was taken meanwhile: look at who took it
+            }
+            if (a == h && b == pkey) return false;
+            break;
+        }
+        s = (s + 1) & m;
+    }
+    return false;
+}
+
+// ------------------------------------------------------------------ log allocation
+// A warp keeps a private block of log records [cur, end) in registers and, between launches,
+// in t.wblk[warp slot], so a run costs no global atomic in the common case.  Runs at least as
+// long as the block size are allocated directly.  The block size scales with the log so that
+// the space parked in blocks stays a small part of a small table.
+struct WarpAlloc { uint32_t cur, end; };
+
+__device__ __forceinline__ uint32_t alloc_block_size(uint32_t log_cap)
+{
+    const uint32_t b = log_cap >> 17;
+    return b > 128u ? 128u : b;
+}
+
+// warp-uniform: every lane passes the same arguments and receives the same result
+__device__ __forceinline__ uint32_t warp_alloc(const TrieRef &t, WarpAlloc &wa, uint32_t L, int lane,
+                                               bool &from_block)
+{
+    if (L <= wa.end - wa.cur) {
+        const uint32_t base = wa.cur;
+        wa.cur += L;
+        from_block = true;
+        return base;
+    }
+    const uint32_t blk = alloc_block_size(t.log_cap);
+    const uint32_t take = L >= blk ? L : blk;
+    unsigned long long b = 0;
+    if (lane == 0) b = atomicAdd(&t.dev->log_count, (unsigned long long)take);
+    b = __shfl_sync(FULLW, b, 0);
+    from_block = false;
+    if (b + L > (unsigned long long)t.log_cap) {
+        if (lane == 0) atomicOr(&t.dev->status, B200R_S_TABLE_FULL);
+        return SLOT_NONE;
+    }
+    if (take > L) {                             // a fresh block; what is left of the old one is dropped
+        unsigned long long e = b + take;
+        if (e > (unsigned long long)t.log_cap) e = t.log_cap;
+        wa.cur = (uint32_t)b + L;
+        wa.end = (uint32_t)e;
+        from_block = true;
+    }
+    return (uint32_t)b;
+}
+
+// ------------------------------------------------------------------ request walk
+struct ReqSpan { int b0, C; };
+
+__device__ __forceinline__ ReqSpan req_span(const int32_t *chunk_base, int i, int64_t max_chunks)
+{
+    ReqSpan s;
+    s.b0 = chunk_base[i];
+    int64_t e = chunk_base[i + 1];
+    if (e > max_chunks) e = max_chunks;
+    s.C = (e > s.b0) ? (int)(e - s.b0) : 0;
+    return s;
+}
+
+enum { W_LOOKUP = 0, W_CLAIM = 1, W_INSERT = 2 };
+
+struct WalkArgs {
+    TrieRef t;
+    const uint64_t *hashes;
+    const int32_t *chunk_base;
+    int64_t max_chunks;
+    uint64_t avail;               // lookup / claim
+    unsigned long long tag;       // claim: epoch << 32
+    uint32_t *slots;              // claim: log index (| PREOK_BIT) per chunk
+    int32_t *dpre;                // claim: per request, number of leading nodes usable before the batch
+    uint64_t *cand;               // claim: per request, mask & avail of the deepest such node (avail if none)
+    int32_t *depth_out;           // lookup
+    uint64_t *matched_out;        // lookup
+    const int32_t *endpoint;      // insert
+};
+
+__device__ __forceinline__ int leading_ones(unsigned bal)
+{
+    return (bal == FULLW) ? 32 : (__ffs(~bal) - 1);
+}
+
+// One warp walks request i down the trie, 32 depths (one window) per step.
+//   A  while the last resolved node sits at log index pidx inside a run that extends to pend,
+//      the next nodes can only be the records behind it: lanes compare the chunk hashes of
+//      records pidx+1+k with their own chunks (coalesced 32-byte loads); the leading matches
+//      are resolved.
+//   B  at the first mismatch (or at the end of a run) the child, if it exists, heads another
+//      run: one lane probes the hash table with (pidx, chunk hash).  A hit re-bases A on that
+//      run (the head's own record is validated by the next A step).
+//   absent  no record and no head: by prefix closure nothing deeper exists either.
+//      W_CLAIM / W_INSERT create the rest of the path as ONE run (records written first,
+//      device-scope fence, then the head is published with a 128-bit CAS).  Losing that race
+//      to another request of the batch gives the records back and walks the request again,
+//      now through the winner's run.
+template <int MODE>
+__device__ __forceinline__ void walk_request(const WalkArgs &a, int i, int lane, WarpAlloc &wa)
+{
+    const ReqSpan sp = req_span(a.chunk_base, i, a.max_chunks);
+    const int C = sp.C;
+    const uint64_t *hs = a.hashes + sp.b0;
+    const TrieRef &t = a.t;
+    uint64_t bit = 0;
+    if (MODE == W_INSERT) {
+        const int e = a.endpoint[i];
+        if (e < 0 || e > 63) return;
+        bit = 1ULL << e;
+        if (lane == 0 && !(t.dev->root_mask & bit)) atomicOr((unsigned long long *)&t.dev->root_mask, bit);
+    }
+    const unsigned long long mine = a.tag | (unsigned long long)(~(unsigned)i);
+    bool lost = false;                    // lost a creation race: probe the table past L1 from now on
+
+restart:
+    uint32_t pidx = ROOT_IDX, pend = 0;   // last resolved node is log[pidx]; its run ends at pend
+    bool tryA = false, afterB = false;
+    int npre = 0;                         // leading nodes with mask & avail != 0 (lookup depth / claim dpre)
+    bool allpre = true;
+    uint64_t sel = a.avail;
+    bool finished = false;
+
+    for (int w0 = 0; w0 < C && !finished; w0 += 32) {
+        const int d = w0 + lane;
+        const bool valid = d < C;
+        const int nvalid = (C - w0) < 32 ? (C - w0) : 32;
+        const uint64_t h = valid ? hs[d] : 0;
+        int r = 0;                        // lanes [0, r) of the window are resolved
+        while (r < nvalid) {
+            const int off = lane - r;
+            if (!tryA) {
+                // ---- B: does child h_r of node pidx head a run?
+                unsigned long long run = 0;
+                if (off == 0) run = head_find(t.tab, t.tab_log2, h, (uint64_t)pidx + 1, lost);
+                run = __shfl_sync(FULLW, run, r);
+                if (run == 0) break;                            // absent at depth w0 + r
+                pidx = (uint32_t)run - 1;                       // so that the head itself is pidx + 1
+                pend = (uint32_t)run + (uint32_t)(run >> 32);
+                tryA = true;
+                afterB = true;
+            }
+            // ---- A: records behind pidx
+            const uint32_t room = pend - pidx - 1;
+            uint32_t idx = 0;
+            uint64_t m = 0;
+            unsigned long long f = 0;
+            bool ok = false;
+            if (valid && off >= 0 && (uint32_t)off < room) {
+                uint64_t rh;
+                idx = pidx + 1 + (uint32_t)off;
+                ld_rec(t.log + idx, rh, m, f);
+                ok = (rh == h);
+            }
+            const int nres = leading_ones(__ballot_sync(FULLW, ok) >> r);
+            if (nres == 0) {
+                tryA = false;
+                if (afterB) {                                   // a head without its record: never
+                    if (lane == 0) atomicOr(&t.dev->status, B200R_S_INTERNAL);
+                    finished = true;
+                    break;
+                }
+                continue;                                       // end of run / mismatch: probe the table
+            }
+            afterB = false;
+            pidx += (uint32_t)nres;
+            if (r + nres < 32) tryA = false;                    // the run ended or diverged inside the window
+            // ---- lanes [r, r + nres) hold resolved nodes
+            const bool res = off >= 0 && off < nres;
+            const bool use = res && (m & a.avail);
+            if (MODE == W_CLAIM) {
+                if (res) {
+                    if (use) {
+                        a.slots[sp.b0 + d] = idx | PREOK_BIT;
+                    } else {
+                        a.slots[sp.b0 + d] = idx;
+                        if (f < mine) atomicMax(&t.log[idx].first, mine);
+                    }
+                }
+            } else if (MODE == W_INSERT) {
+                if (res && !(m & bit)) atomicOr((unsigned long long *)&t.log[idx].mask, bit);
+            }
+            if (MODE != W_INSERT && allpre) {
+                const int nok0 = leading_ones(__ballot_sync(FULLW, use) >> r);
+                const int nok = nok0 < nres ? nok0 : nres;
+                if (nok > 0) {
+                    sel = __shfl_sync(FULLW, m & a.avail, r + nok - 1);
+                    npre += nok;
+                }
+                if (nok < nres) {
+                    allpre = false;
+                    if (MODE == W_LOOKUP) { finished = true; break; }
+                }
+            }
+            r += nres;
+        }
+        if (finished || r >= nvalid) continue;          // window done (or lookup ended)
+
+        // ---- depth w0 + r is absent, and so is everything below it
+        finished = true;
+        if (MODE == W_LOOKUP) break;
+        const int pos = w0 + r;
+        const uint32_t L = (uint32_t)(C - pos);
+        bool from_block = false;
+        const uint32_t base = warp_alloc(t, wa, L, lane, from_block);
+        if (base == SLOT_NONE) {
+            if (MODE == W_CLAIM)
+                for (int d2 = pos + lane; d2 < C; d2 += 32) a.slots[sp.b0 + d2] = SLOT_NONE;
+            break;
+        }
+        const uint64_t mask0 = MODE == W_INSERT ? bit : 0ULL;
+        const unsigned long long first0 = MODE == W_CLAIM ? mine : 0ULL;
+        if (valid && lane >= r) {
+            const uint32_t x = base + (uint32_t)(lane - r);
+            st_rec(t.log + x, h, mask0, first0);
+            if (MODE == W_CLAIM) a.slots[sp.b0 + d] = x;
+        }
+        for (int d2 = w0 + 32 + lane; d2 < C; d2 += 32) {
+            const uint32_t x = base + (uint32_t)(d2 - pos);
+            st_rec(t.log + x, hs[d2], mask0, first0);
+            if (MODE == W_CLAIM) a.slots[sp.b0 + d2] = x;
+        }
+        const uint64_t hh = __shfl_sync(FULLW, h, r);
+        __syncwarp();
+        int won = 0;
+        if (lane == 0) {
+            __threadfence();                            // records before the head
+            won = head_publish(t.tab, t.tab_log2, hh, (uint64_t)pidx + 1, ((unsigned long long)L << 32) | base) ? 1 : 0;
+        }
+        won = __shfl_sync(FULLW, won, 0);
+        if (!won) {
+            // another request of the batch created this child first: give the records back and
+            // walk again (rare; everything done so far is idempotent)
+            if (from_block) wa.cur -= L;
+            lost = true;
+            goto restart;
+        }
+    }
+    if (lane == 0) {
+        if (MODE == W_LOOKUP) {
+            a.depth_out[i] = npre;
+            a.matched_out[i] = sel;
+        } else if (MODE == W_CLAIM) {
+            a.dpre[i] = npre;
+            a.cand[i] = sel;
+        }
+    }
+}
+
+// One warp per request, persistent grid-stride; the allocation block of each warp slot
+// survives the launch in t.wblk.
+template <int MODE>
+__global__ void __launch_bounds__(256, 5)
+k_walk(WalkArgs a, int n, const int32_t *__restrict__ n_dev)
+{
+    const int lane = threadIdx.x & 31;
+    const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int nw = (gridDim.x * blockDim.x) >> 5;
+    if (n_dev) n = *n_dev;
+    WarpAlloc wa = { 0, 0 };
+    constexpr bool ALLOC = (MODE == W_CLAIM || MODE == W_INSERT);
+    if (ALLOC) { const uint2 v = a.t.wblk[gw]; wa.cur = v.x; wa.end = v.y; }
+    for (int i = gw; i < n; i += nw) walk_request<MODE>(a, i, lane, wa);
+    if (ALLOC && lane == 0) a.t.wblk[gw] = make_uint2(wa.cur, wa.end);
+}
+
+}  // namespace b200r
