@@ -10,7 +10,10 @@ The test drives the entry point through the C ABI exactly as such a caller
 would (inputs and outputs only) and requires bit-identical results -- these are
 integer hashes, so the tolerance is zero -- to the regular b200r_xxh64_chunks on
 two calls in a row: the second call reuses the area with whatever the first one
-left behind.  The file sorts last on purpose (pytest collects it after every
+left behind.  The hashes are also held to the CPU oracle (an independent
+implementation), and the device-wide free-memory figure must not drop across a
+call -- that also catches a cudaMalloc made inside the library, which torch's own
+allocator statistics would not see.  The file sorts last on purpose (pytest collects it after every
 other test file), and it must pass on its own in a fresh process as well.
 """
 import ctypes as C
@@ -19,6 +22,7 @@ import numpy as np
 import pytest
 import torch
 
+from oracle import coracle
 from b200_router import _lib, traces
 from b200_router.packing import pack_arrays, pack_prompts
 
@@ -48,8 +52,12 @@ def _hash_regular(p, chunk=128):
     return base.cpu().numpy(), hashes.cpu().numpy()
 
 
-def _hash_noalloc(p, chunk=128):
-    """Inputs and outputs only -- no scratch argument, nothing allocated by the call."""
+def _hash_noalloc(p, chunk=128, check_free=False):
+    """Inputs and outputs only -- no scratch argument, nothing allocated by the call.
+
+    check_free: compare the DEVICE-WIDE free memory (cudaMemGetInfo) before and after the
+    call.  Only meaningful once an earlier call has loaded the library's kernels and looked
+    up the built-in area (the CUDA runtime loads a module lazily on first use)."""
     L = _lib.lib()
     dev = p.bytes.device
     base = torch.empty(p.n + 1, dtype=torch.int32, device=dev)
@@ -57,12 +65,25 @@ def _hash_noalloc(p, chunk=128):
     flags = _lib.F_ALL_ASCII if p.all_ascii else 0
     torch.cuda.synchronize()
     before = torch.cuda.memory_allocated()
+    free_before = torch.cuda.mem_get_info(dev)[0]
     _lib.check(L.b200r_xxh64_chunks_noalloc(_vp(p.bytes), _vp(p.starts), _vp(p.lens),
                                             _vp(p.nchars), p.n, chunk, flags, _vp(base),
                                             _vp(hashes), p.max_chunks, _stream()))
     torch.cuda.synchronize()
+    free_after = torch.cuda.mem_get_info(dev)[0]
     assert torch.cuda.memory_allocated() == before
+    if check_free:
+        assert free_after >= free_before, "device memory was allocated inside the call"
     return base.cpu().numpy(), hashes.cpu().numpy()
+
+
+def _same_as_oracle(base, hs, prompts, chunk=128):
+    """Every chunk hash equals the CPU oracle's (oracle/oracle.c, pinned to python-xxhash)."""
+    hs = hs.view(np.uint64)
+    for i, s in prompts:
+        want = coracle.xxh64_chunks(s.encode("utf-8"), chunk)
+        assert base[i + 1] - base[i] == len(want), i
+        assert (hs[base[i]:base[i + 1]] == want).all(), i
 
 
 def _same(a, b):
@@ -80,6 +101,10 @@ def test_noalloc_matches_regular_entry_point_twice_in_a_row():
     big = pack_arrays(*tr.batch_arrays(0), pin=False).to(dev)
     first = _hash_noalloc(big)
     _same(first, _hash_regular(big))
+    buf, starts, lens = tr.batch_arrays(0)
+    _same_as_oracle(first[0], first[1],
+                    [(i, buf[int(starts[i]):int(starts[i]) + int(lens[i])].tobytes().decode("ascii"))
+                     for i in range(0, 20000, 997)])
     # call 2, straight after: smaller, mixed ASCII / multi-byte UTF-8, ragged and empty
     # prompts -- uses the code-point counts and chunk offsets parts of the area as well
     rng = np.random.default_rng(5)
@@ -87,10 +112,11 @@ def test_noalloc_matches_regular_entry_point_twice_in_a_row():
     prompts = ["".join(rng.choice(alphabet, size=n)) for n in (0, 1, 127, 128, 129, 300, 1000, 5000)]
     prompts += ["", "x" * 4096, "é" * 128]
     small = pack_prompts(prompts, pin=False).to(dev)
-    second = _hash_noalloc(small)
+    second = _hash_noalloc(small, check_free=True)
     _same(second, _hash_regular(small))
-    # and the first batch again: same answer as before
-    _same(_hash_noalloc(big), first)
+    _same_as_oracle(second[0], second[1], list(enumerate(prompts)))
+    # and the first batch again: same answer as before, and no device memory taken
+    _same(_hash_noalloc(big, check_free=True), first)
 
 
 def test_noalloc_rejects_batches_beyond_the_built_in_area():
