@@ -195,7 +195,7 @@ def test_extract_prompt_matches_reference_shapes(golden_prefix):
         routers.extract_prompt({"neither": 1})
 
 
-def test_endpoint_registry_is_append_only():
+def test_endpoint_registry_keeps_bits_and_recycles_idle_ones():
     reg = routers.EndpointRegistry()
 
     class Ep:
@@ -203,10 +203,32 @@ def test_endpoint_registry_is_append_only():
     a = reg.mask([Ep("u1"), Ep("u2")])
     b = reg.mask([Ep("u3"), Ep("u1")])
     assert a == 0b011 and b == 0b101 and reg.urls == ["u1", "u2", "u3"]
+    # more endpoints at once than mask bits: an error, like before
     small = routers.EndpointRegistry(limit=2)
     small.mask(["a", "b"])
     with pytest.raises(b200_router.B200RouterError):
-        small.bit("c")
+        small.mask(["a", "b", "c"])
+    # pod churn (service_discovery.py:651: a new url per restart): more than `limit` urls over
+    # the lifetime.  Bits of urls that are no longer listed are retired (cleared from the
+    # table through on_retire) and handed out again; live endpoints keep theirs.
+    retired = []
+    reg = routers.EndpointRegistry(limit=4, on_retire=retired.append)
+    live = ["p0", "p1", "p2"]
+    seen_bits = {}
+    for gen in range(3, 40):
+        m = reg.mask(live)
+        assert bin(m).count("1") == 3
+        for u in live:
+            seen_bits.setdefault(u, reg.index[u])
+            assert reg.index[u] == seen_bits[u]          # stable while the endpoint is listed
+        live = live[1:] + ["p%d" % gen]                  # oldest pod restarts under a new url
+    assert len([u for u in reg.urls if u]) <= 4 and reg.retired >= 30
+    assert len(retired) == reg.retired and all(bin(b).count('1') == 1 for b in retired)
+    # state for checkpoints: urls in bit order
+    st = reg.state()
+    reg2 = routers.EndpointRegistry(limit=4)
+    reg2.load_state(st)
+    assert reg2.mask(live) == reg.mask(live)
 
 
 def test_qps_routing_rule():

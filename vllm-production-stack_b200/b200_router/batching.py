@@ -9,8 +9,14 @@ batch, in arrival order, so the outcome equals the reference's one-by-one
 routing of the same arrival sequence.  A batch needs one constant endpoint set,
 so a request whose endpoint list differs from the pending ones first flushes
 them (arrival order is kept across the split).
+
+A flush does not run on the event loop: packing, the H2D copy, the kernels and the
+wait for the decisions happen on ONE worker thread (batches stay in submission
+order), and the waiters are resolved back on the loop when it is done -- the loop
+keeps accepting requests (they form the next batch) while a batch is on the GPU.
 """
 import asyncio
+from concurrent.futures import ThreadPoolExecutor
 from typing import Any, Callable, List, Optional, Sequence, Tuple
 
 
@@ -25,6 +31,7 @@ class MicroBatcher:
         self._endpoints: Optional[Sequence[Any]] = None
         self._key: Optional[tuple] = None
         self._timer: Optional[asyncio.TimerHandle] = None
+        self._worker = ThreadPoolExecutor(max_workers=1, thread_name_prefix="b200r-batch")
         self.batches_routed = 0
         self.requests_routed = 0
 
@@ -40,18 +47,22 @@ class MicroBatcher:
             return
         pending, endpoints = self._pending, self._endpoints
         self._pending, self._endpoints, self._key = [], None, None
-        try:
-            urls = self._route_batch(endpoints, [p for p, _ in pending])
-        except Exception as exc:                      # every waiter sees the failure
-            for _, fut in pending:
-                if not fut.done():
-                    fut.set_exception(exc)
-            return
-        self.batches_routed += 1
-        self.requests_routed += len(pending)
-        for (_, fut), url in zip(pending, urls):
-            if not fut.done():
-                fut.set_result(url)
+        loop = asyncio.get_running_loop()
+        job = loop.run_in_executor(self._worker, self._route_batch, endpoints, [p for p, _ in pending])
+
+        def done(fut):
+            exc = fut.exception()
+            if exc is not None:                           # every waiter sees the failure
+                for _, w in pending:
+                    if not w.done():
+                        w.set_exception(exc)
+                return
+            self.batches_routed += 1
+            self.requests_routed += len(pending)
+            for (_, w), url in zip(pending, fut.result()):
+                if not w.done():
+                    w.set_result(url)
+        job.add_done_callback(done)
 
     async def route(self, endpoints: Sequence[Any], prompt: str) -> str:
         loop = asyncio.get_running_loop()

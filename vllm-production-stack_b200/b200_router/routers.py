@@ -26,12 +26,12 @@ from .ring import GpuHashRing
 from .trie import GpuHashTrie
 
 try:  # drop-in mode: inherit from the real classes when they are importable
-    from vllm_router.routers import routing_logic as _ref_rl          # pragma: no cover
-    from vllm_router.utils import SingletonABCMeta                    # pragma: no cover
-    _RefPrefix, _RefSession = _ref_rl.PrefixAwareRouter, _ref_rl.SessionRouter  # pragma: no cover
-    RoutingInterface = _ref_rl.RoutingInterface                       # pragma: no cover
-    RoutingLogic = _ref_rl.RoutingLogic                               # pragma: no cover
-    HAVE_REFERENCE = True                                             # pragma: no cover
+    from vllm_router.routers import routing_logic as _ref_rl
+    from vllm_router.utils import SingletonABCMeta          
+    _RefPrefix, _RefSession = _ref_rl.PrefixAwareRouter, _ref_rl.SessionRouter
+    RoutingInterface = _ref_rl.RoutingInterface             
+    RoutingLogic = _ref_rl.RoutingLogic                     
+    HAVE_REFERENCE = True                                   
 except Exception:
     HAVE_REFERENCE = False
 
@@ -89,53 +89,107 @@ MAX_ENDPOINTS = 64
 
 
 class EndpointRegistry:
-    """Stable url -> bit index map feeding the endpoint masks.  Append-only: the
-    reference trie keeps stale endpoints forever and filters them by
-    intersection with the available set (hashtrie.py:96), so a bit is never
-    reused.  EndpointInfo.url is the only identity the hot
-    path uses (service_discovery.py:80-110, routing_logic.py:414)."""
+    """Stable url -> bit index map feeding the endpoint masks (EndpointInfo.url is the only
+    identity the hot path uses: service_discovery.py:80-110, routing_logic.py:414).
 
-    def __init__(self, limit: int = MAX_ENDPOINTS):
+    The reference trie keeps stale endpoints forever and filters them by intersection with
+    the available set (hashtrie.py:96), so a bit stays assigned after its endpoint disappears
+    (SURVEY.md 7.3 H3).  Masks are one 64-bit word, though, and K8s discovery mints a new url
+    per pod restart (service_discovery.py:651): when a 65th url shows up, the bits of urls
+    that are not in the current endpoint list are RETIRED -- least recently seen first -- by
+    clearing them from every node (`on_retire(bits)`, one sweep kernel) and handed out again.
+    Decisions are unaffected unless a retired url comes back (it then starts without history).
+    Only more than 64 endpoints available AT ONCE is an error."""
+
+    def __init__(self, limit: int = MAX_ENDPOINTS, on_retire=None):
         self.limit = limit
-        self.urls: List[str] = []
+        self.urls: List[Optional[str]] = []       # bit -> url (None = free)
         self.index: Dict[str, int] = {}
+        self.last_seen: Dict[str, int] = {}
+        self.on_retire = on_retire
+        self.retired = 0
+        self._tick = 0
+        self._mask_cache = (None, 0)
 
-    def bit(self, url: str) -> int:
+    def _free_bits(self, keep) -> None:
+        """Retire the least recently seen urls that are not in `keep` (half of them, at least
+        one, so that the sweep is rare)."""
+        idle = sorted((u for u in self.index if u not in keep), key=lambda u: self.last_seen.get(u, 0))
+        if not idle:
+            raise _lib.B200RouterError(
+                "more than %d endpoints are available at once: endpoint masks are one 64-bit "
+                "word" % self.limit)
+        victims = idle[:max(1, len(idle) // 2)]
+        bits = 0
+        for u in victims:
+            b = self.index.pop(u)
+            self.last_seen.pop(u, None)
+            self.urls[b] = None
+            bits |= 1 << b
+        self.retired += len(victims)
+        if self.on_retire is not None:
+            self.on_retire(bits)
+
+    def bit(self, url: str, keep=()) -> int:
         i = self.index.get(url)
         if i is None:
-            if len(self.urls) >= self.limit:
-                raise _lib.B200RouterError(
-                    "more than %d distinct endpoint urls seen: endpoint masks are one 64-bit "
-                    "word" % self.limit)
-            i = self.index[url] = len(self.urls)
-            self.urls.append(url)
+            if len(self.index) >= self.limit:
+                self._free_bits(set(keep) | {url})
+            if None in self.urls:
+                i = self.urls.index(None)
+                self.urls[i] = url
+            else:
+                i = len(self.urls)
+                self.urls.append(url)
+            self.index[url] = i
+            self._mask_cache = (None, 0)
         return i
 
     def mask(self, endpoints) -> int:
+        urls = tuple(e.url if hasattr(e, "url") else e for e in endpoints)
+        if self._mask_cache[0] == urls:
+            return self._mask_cache[1]
+        self._tick += 1
         m = 0
-        for e in endpoints:
-            m |= 1 << self.bit(e.url if hasattr(e, "url") else e)
+        for u in urls:
+            m |= 1 << self.bit(u, keep=urls)
+            self.last_seen[u] = self._tick
+        self._mask_cache = (urls, m)
         return m
+
+    def state(self) -> List[str]:
+        """urls in bit order ('' = free bit), for checkpoints."""
+        return [u or "" for u in self.urls]
+
+    def load_state(self, urls) -> None:
+        self.urls = [str(u) or None for u in urls]
+        self.index = {u: i for i, u in enumerate(self.urls) if u}
+        self.last_seen = {}
+        self._mask_cache = (None, 0)
+
+
+def _message_parts(request_json: Dict):
+    """The pieces the reference joins with a newline (routing_logic.py:388-412): one per chat
+    message (text parts of multimodal content joined by a blank); None for a completions
+    request."""
+    if "messages" not in request_json:
+        return None
+    parts = []
+    for message in request_json["messages"] or ():
+        content = message.get("content", "")
+        if isinstance(content, list):
+            parts.append(" ".join(part.get("text", "") for part in content
+                                  if part.get("type") == "text"))
+        elif content is not None:
+            parts.append(content)
+    return parts
 
 
 def extract_prompt(request_json: Dict) -> str:
-    """Prompt text the reference hashes (routing_logic.py:388-412): chat
-    messages' contents joined by newline (text parts of multimodal content
-    joined by a blank), else the completions `prompt` (KeyError if absent)."""
-    if "messages" in request_json:
-        messages = request_json["messages"]
-        if not messages:
-            return ""
-        parts = []
-        for message in messages:
-            content = message.get("content", "")
-            if isinstance(content, list):
-                parts.append(" ".join(part.get("text", "") for part in content
-                                      if part.get("type") == "text"))
-            elif content is not None:
-                parts.append(content)
-        return "\n".join(parts)
-    return request_json["prompt"]
+    """Prompt text the reference hashes (routing_logic.py:388-412): chat messages' contents
+    joined by newline, else the completions `prompt` (KeyError if absent)."""
+    parts = _message_parts(request_json)
+    return request_json["prompt"] if parts is None else "\n".join(parts)
 
 
 def extract_prompt_parts(request_json: Dict):
@@ -143,20 +197,10 @@ def extract_prompt_parts(request_json: Dict):
     (or the completions prompt itself).  pack_prompts lays the parts end to end with the
     separator between them, so long chat histories are copied once, into the packed buffer,
     instead of twice (routing_logic.py:407 builds the joined string first)."""
-    if "messages" in request_json:
-        messages = request_json["messages"]
-        if not messages:
-            return ""
-        parts = []
-        for message in messages:
-            content = message.get("content", "")
-            if isinstance(content, list):
-                parts.append(" ".join(part.get("text", "") for part in content
-                                      if part.get("type") == "text"))
-            elif content is not None:
-                parts.append(content)
-        return tuple(parts)
-    return request_json["prompt"]
+    parts = _message_parts(request_json)
+    if parts is None:
+        return request_json["prompt"]
+    return tuple(parts) if parts else ""
 
 
 class PrefixAwareRouter(_RefPrefix):
@@ -175,9 +219,12 @@ class PrefixAwareRouter(_RefPrefix):
         self.chunk_by = chunk_by
         self._arena = PackArena(slots=3)
         self.hashtrie = GpuHashTrie(cap_log2=cap_log2, chunk_chars=128, device=device)
-        self.registry = EndpointRegistry()
+        self.registry = EndpointRegistry(on_retire=self.hashtrie.retire_endpoints)
         self.seed = seed
         self.seq = 0                      # global request sequence number (tie-break counter)
+        self._res_dev = None              # decisions + latched status word, one D2H per batch
+        self._res_host = None
+        self._aux = None
         self.batcher = None
         if micro_batch_ms > 0:
             from .batching import MicroBatcher
@@ -185,25 +232,44 @@ class PrefixAwareRouter(_RefPrefix):
         self._initialized = True
 
     # ---- batch API
-    def route_packed(self, avail_mask: int, packed: PackedPrompts):
+    def route_packed(self, avail_mask: int, packed: PackedPrompts, out=None):
         """Route a packed batch; returns device tensors (endpoint idx, depth, matched)."""
-        out = self.hashtrie.route(packed, avail_mask, self.seed, self.seq)
+        res = self.hashtrie.route(packed, avail_mask, self.seed, self.seq, out=out)
         self.seq += packed.n
-        return out
+        return res
+
+    def _result_buffers(self, n: int):
+        if self._res_dev is None or self._res_dev.numel() < n + 1:
+            cap = max(256, int((n + 1) * 1.5))
+            dev = self.hashtrie.device
+            self._res_dev = torch.empty(cap, dtype=torch.int32, device=dev)
+            self._res_host = torch.empty(cap, dtype=torch.int32).pin_memory()
+            self._aux = (torch.empty(cap, dtype=torch.int32, device=dev),
+                         torch.empty(cap, dtype=torch.int64, device=dev))
+        return self._res_dev, self._res_host, self._aux
 
     def route_batch(self, endpoints, prompts: Sequence) -> List[str]:
         """Route prompts in list order against one endpoint set; returns urls.  A prompt is a
-        str or a tuple of parts (extract_prompt_parts)."""
-        if len(prompts) == 0:
+        str or a tuple of parts (extract_prompt_parts).  One host synchronisation per batch:
+        the decisions and the table's latched status word come back in the same copy."""
+        n = len(prompts)
+        if n == 0:
             return []
         avail = self.registry.mask(endpoints)
-        ep, _, _ = self.route_packed(avail, pack_prompts(prompts, chunk_by=self.chunk_by,
-                                                         arena=self._arena))
-        idx = ep.cpu().tolist()
-        self.hashtrie.check_status()
+        rd, rh, (depth, matched) = self._result_buffers(n)
+        trie = self.hashtrie
+        with torch.cuda.device(trie.device):
+            self.route_packed(avail, pack_prompts(prompts, chunk_by=self.chunk_by, arena=self._arena),
+                              out=(rd[:n], depth, matched))
+            trie.status_async(rd[n:n + 1])
+            rh[:n + 1].copy_(rd[:n + 1], non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+        idx = rh[:n].tolist()
+        trie.raise_for_status(int(rh[n]) & 0xFFFFFFFF)
         if any(i < 0 for i in idx):
             raise IndexError("Cannot choose from an empty sequence")   # random.choice([])
-        return [self.registry.urls[i] for i in idx]
+        urls = self.registry.urls
+        return [urls[i] for i in idx]
 
     # ---- reference API
     async def route_request(self, endpoints, engine_stats, request_stats, request,
@@ -212,6 +278,28 @@ class PrefixAwareRouter(_RefPrefix):
         if self.batcher is not None:
             return await self.batcher.route(endpoints, prompt)
         return self.route_batch(endpoints, [prompt])[0]
+
+    # ---- checkpoint (the reference has none: its trie dies with the process)
+    def save(self, path):
+        """Table + what gives its masks a meaning: the url of every mask bit, the chunking
+        mode, the tie-break counter."""
+        self.hashtrie.save(path, extra={"urls": np.array(self.registry.state(), dtype=np.str_),
+                                        "chunk_by": np.array(self.chunk_by),
+                                        "seq": np.int64(self.seq), "seed": np.int64(self.seed)})
+
+    def load(self, path, cap_log2: Optional[int] = None):
+        """Replace this router's table by a saved one (same process-wide singleton)."""
+        trie, extra = GpuHashTrie.load(path, cap_log2=cap_log2 or self.hashtrie.cap_log2,
+                                       device=self.hashtrie.device, with_extra=True)
+        if str(extra["chunk_by"]) != self.chunk_by:
+            trie.close()
+            raise _lib.B200RouterError("checkpoint was written with chunk_by=%s" % extra["chunk_by"])
+        self.hashtrie.close()
+        self.hashtrie = trie
+        self.registry = EndpointRegistry(on_retire=trie.retire_endpoints)
+        self.registry.load_state([str(u) for u in extra["urls"]])
+        self.seq = int(extra["seq"])
+        self.seed = int(extra["seed"])
 
 
 class SessionRouter(_RefSession):
@@ -259,7 +347,7 @@ def initialize_routing_logic(routing_logic, *args, **kwargs):
     if rl == RoutingLogic.PREFIXAWARE:
         return PrefixAwareRouter()
     if rl.value in _OUT_OF_SCOPE:
-        if HAVE_REFERENCE:                                            # pragma: no cover
+        if HAVE_REFERENCE:                                  
             return _ref_rl.initialize_routing_logic(rl, *args, **kwargs)
         raise ValueError("routing logic %r is not on the GPU path; use the reference router" % rl.value)
     raise ValueError(f"Invalid routing logic {routing_logic}")

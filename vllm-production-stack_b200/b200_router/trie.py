@@ -84,14 +84,24 @@ class GpuHashTrie:
         return {"status": st.value, "num_nodes": nn.value, "root_mask": rm.value,
                 "capacity": cap.value}
 
+    def raise_for_status(self, bits: int):
+        if bits & _lib.S_TABLE_FULL:
+            raise _lib.B200RouterError("GPU trie is full (capacity %d nodes): create it "
+                                       "with a larger cap_log2" % (1 << self.cap_log2))
+        if bits & _lib.S_CHUNK_CAP:
+            raise _lib.B200RouterError("chunk capacity exceeded: max_chunks was too small")
+        if bits & _lib.S_INTERNAL:
+            raise _lib.B200RouterError("internal error: inconsistent trie table")
+
     def check_status(self, count_nodes: bool = False):
         s = self.status(count_nodes)
-        if s["status"] & _lib.S_TABLE_FULL:
-            raise _lib.B200RouterError("GPU trie table is full (capacity %d entries): create it "
-                                       "with a larger cap_log2" % s["capacity"])
-        if s["status"] & _lib.S_CHUNK_CAP:
-            raise _lib.B200RouterError("chunk capacity exceeded: max_chunks was too small")
+        self.raise_for_status(s["status"])
         return s
+
+    def status_async(self, out_word: torch.Tensor):
+        """Copy the latched status word into a device int32 in stream order (no host sync)."""
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().b200r_trie_status_async(self._h, _ptr(out_word), _stream()))
 
     # -------------------------------------------------------------------- a1
     def hash_chunks(self, p: PackedPrompts) -> Tuple[torch.Tensor, torch.Tensor]:
