@@ -52,7 +52,25 @@ struct PartDyn {
     P2PDyn base;                              // seq_base, total_n (my_off stays 0)
     int32_t n_owned, c_owned;
     uint32_t reqbase[P2P_MAX_WORLD + 1], chunkbase[P2P_MAX_WORLD + 1], off[P2P_MAX_WORLD + 1];
+    unsigned int ticket_bulk, ticket_res;     // "last CTA publishes" counters (self-resetting)
 };
+
+// Every CTA calls this after its last peer store: one system-scope fence per CTA, then a
+// ticket; the CTA that draws the last ticket knows that all peer stores of the grid are
+// visible system-wide and may publish the arrival flags (returns true for it, block-wide).
+__device__ __forceinline__ bool last_cta_after_peer_stores(unsigned int *ticket)
+{
+    __shared__ int s_last;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        const unsigned int t = atomicAdd(ticket, 1u);
+        s_last = (t == gridDim.x - 1);
+        if (s_last) *ticket = 0;              // ready for the next launch
+    }
+    __syncthreads();
+    return s_last != 0;
+}
 
 __device__ __forceinline__ int part_owner(const uint64_t *hashes, int b, int C, int world)
 {
@@ -123,12 +141,14 @@ __global__ void k_part_scan(const int32_t *__restrict__ blk_cnt, int nblk, int w
 // several times faster in 128-byte lines than as 8-byte words or ragged ~170-byte runs
 // (measured at 2 GPUs: 47 us per shard for direct scattered peer stores).
 __global__ void __launch_bounds__(PART_BLOCK)
-k_part_push(const int32_t *__restrict__ chunk_base, const uint64_t *__restrict__ hashes, int n,
-            int world, const int32_t *__restrict__ blk_off, const int32_t *__restrict__ totals,
-            unsigned long long *__restrict__ info_stage, uint32_t *__restrict__ dest_slot,
-            uint32_t *__restrict__ req_dst)
+k_part_place(const int32_t *__restrict__ chunk_base, const uint64_t *__restrict__ hashes, int n,
+             int world, const int32_t *__restrict__ blk_off, const int32_t *__restrict__ totals,
+             unsigned long long *__restrict__ info_stage, uint32_t *__restrict__ dest_slot,
+             uint64_t *__restrict__ hash_stage)
 {
     __shared__ int s_w[PART_BLOCK / 32][2 * P2P_MAX_WORLD];
+    __shared__ int s_b[PART_BLOCK], s_c[PART_BLOCK];
+    __shared__ uint32_t s_dst[PART_BLOCK];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int i = blockIdx.x * PART_BLOCK + threadIdx.x;
     int b = 0, C = 0, o = -1;
@@ -150,6 +170,7 @@ k_part_push(const int32_t *__restrict__ chunk_base, const uint64_t *__restrict__
         if (lane == 31) { s_w[w][2 * d] = __popc(m); s_w[w][2 * d + 1] = inc; }
     }
     __syncthreads();
+    s_b[threadIdx.x] = b; s_c[threadIdx.x] = 0; s_dst[threadIdx.x] = 0;
     if (o >= 0) {
         int breq = blk_off[(size_t)blockIdx.x * 2 * world + 2 * o];
         int bchunk = blk_off[(size_t)blockIdx.x * 2 * world + 2 * o + 1];
@@ -157,33 +178,30 @@ k_part_push(const int32_t *__restrict__ chunk_base, const uint64_t *__restrict__
         rreq += breq;
         rchunk += bchunk;
         dest_slot[i] = ((uint32_t)o << 24) | (uint32_t)rreq;
-        req_dst[i] = (uint32_t)(totals[2 * world + 2 * o + 1] + rchunk);
+        s_c[threadIdx.x] = C;
+        s_dst[threadIdx.x] = (uint32_t)(totals[2 * world + 2 * o + 1] + rchunk);
         info_stage[totals[2 * world + 2 * o] + rreq] =
             (unsigned long long)(uint32_t)i | ((unsigned long long)(uint32_t)C << 32);
     }
-}
-
-// chunk hashes -> local staging, one warp per request (coalesced both ways)
-__global__ void __launch_bounds__(WARPS_PER_CTA * 32)
-k_part_copy(const int32_t *__restrict__ chunk_base, const uint64_t *__restrict__ hashes, int n,
-            const uint32_t *__restrict__ req_dst, uint64_t *__restrict__ hash_stage)
-{
-    const int lane = threadIdx.x & 31;
-    const int nw = (gridDim.x * blockDim.x) >> 5;
-    for (int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < n; i += nw) {
-        const int b = chunk_base[i], C = chunk_base[i + 1] - b;
-        uint64_t *dst = hash_stage + req_dst[i];
-        for (int c = lane; c < C; c += 32) dst[c] = hashes[b + c];
+    __syncthreads();
+    // chunk hashes -> local staging: each warp copies the runs of its 32 requests (coalesced)
+    for (int k = 0; k < 32; k++) {
+        const int t = w * 32 + k;
+        const int cb = s_b[t], cc = s_c[t];
+        uint64_t *dst = hash_stage + s_dst[t];
+        for (int c = lane; c < cc; c += 32) dst[c] = hashes[cb + c];
     }
 }
 
 // staging segments -> the owners' buffers: 16-byte vectors, whole lines.  Persistent grid, one
-// system-scope fence per CTA at the end (MEMBAR.SYS costs microseconds: not once per wave).
+// system-scope fence per CTA at the end (MEMBAR.SYS costs microseconds: not once per wave);
+// the last CTA to finish publishes the arrival flags (no separate launch).
 __global__ void __launch_bounds__(256)
 k_part_bulk(const uint64_t *__restrict__ hash_stage, const unsigned long long *__restrict__ info_stage,
             const int32_t *__restrict__ totals, int world, int my_rank,
             const unsigned long long *__restrict__ peer_bases, size_t hash_off, size_t info_off,
-            int64_t cap, int64_t rcap)
+            int64_t cap, int64_t rcap, unsigned int *ticket, int set, unsigned long long epoch,
+            unsigned int n)
 {
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
@@ -197,10 +215,17 @@ k_part_bulk(const uint64_t *__restrict__ hash_stage, const unsigned long long *_
         uint4 *id = (uint4 *)((unsigned long long *)(uintptr_t)(peer_bases[o] + info_off) + (size_t)my_rank * rcap);
         for (int64_t x = tid; x < (nreq + 1) / 2; x += nthr) id[x] = is[x];
     }
-    __syncthreads();
-    if (threadIdx.x == 0) __threadfence_system();
+    if (last_cta_after_peer_stores(ticket) && (int)threadIdx.x < world) {
+        const int d = threadIdx.x;
+        PartFlags *f = (PartFlags *)(uintptr_t)peer_bases[d];
+        *(volatile unsigned long long *)&f->in_n[set][my_rank] = (epoch << 32) | n;
+        *(volatile unsigned long long *)&f->in_chunk[set][my_rank] = (epoch << 32) | (uint32_t)totals[2 * d + 1];
+        *(volatile unsigned long long *)&f->in_req[set][my_rank] = (epoch << 32) | (uint32_t)totals[2 * d];
+        __threadfence_system();
+    }
 }
 
+// batch with no request at all on this rank: only the flags
 __global__ void k_part_publish_in(const unsigned long long *__restrict__ peer_bases, int world,
                                   int my_rank, int set, unsigned long long epoch,
                                   const int32_t *__restrict__ totals, unsigned int n)
@@ -215,10 +240,17 @@ __global__ void k_part_publish_in(const unsigned long long *__restrict__ peer_ba
     __threadfence_system();
 }
 
-__global__ void k_part_wait_meta(const PartFlags *__restrict__ mine, int set, unsigned long long epoch,
-                                 int world, PartDyn *dyn, TrieDev *dev)
+// Wait for all sources (every CTA spins on the flags itself: they are local memory), then
+// concatenate what they sent, in rank order.  Block 0 also leaves the batch's bookkeeping in
+// `dyn` for the kernels that follow.
+__global__ void __launch_bounds__(256)
+k_part_gather(const uint8_t *__restrict__ my_base, int set, unsigned long long epoch,
+              size_t hash_off, size_t info_off, int64_t cap, int64_t rcap, int world,
+              PartDyn *dyn, TrieDev *dev, int32_t *__restrict__ c_owned,
+              uint32_t *__restrict__ pos_owned, uint64_t *__restrict__ hashes_owned)
 {
-    __shared__ uint32_t s_req[P2P_MAX_WORLD], s_chunk[P2P_MAX_WORLD], s_n[P2P_MAX_WORLD];
+    __shared__ uint32_t s_req[P2P_MAX_WORLD + 1], s_chunk[P2P_MAX_WORLD + 1], s_n[P2P_MAX_WORLD + 1];
+    const PartFlags *mine = (const PartFlags *)my_base;
     const int q = threadIdx.x;
     if (q < world) {
         unsigned long long a = 0, b = 0, c = 0;
@@ -227,50 +259,49 @@ __global__ void k_part_wait_meta(const PartFlags *__restrict__ mine, int set, un
                         p2p_spin(&mine->in_n[set][q], epoch, &c);
         if (!ok) atomicOr(&dev->status, B200R_S_PEER_TIMEOUT);
         s_req[q] = ok ? (uint32_t)a : 0; s_chunk[q] = ok ? (uint32_t)b : 0; s_n[q] = ok ? (uint32_t)c : 0;
+        __threadfence();                      // flags before data
     }
     __syncthreads();
-    if (threadIdx.x == 0) {
+    if (threadIdx.x == 0) {                   // counts -> exclusive bases, in place
         uint32_t r = 0, c = 0, o = 0;
         for (int k = 0; k < world; k++) {
-            dyn->reqbase[k] = r; dyn->chunkbase[k] = c; dyn->off[k] = o;
-            r += s_req[k]; c += s_chunk[k]; o += s_n[k];
+            const uint32_t a = s_req[k], b = s_chunk[k], d = s_n[k];
+            s_req[k] = r; s_chunk[k] = c; s_n[k] = o;
+            r += a; c += b; o += d;
         }
-        dyn->reqbase[world] = r; dyn->chunkbase[world] = c; dyn->off[world] = o;
-        dyn->n_owned = (int32_t)r; dyn->c_owned = (int32_t)c;
-        dyn->base.my_off = 0; dyn->base.total_n = o;
+        s_req[world] = r; s_chunk[world] = c; s_n[world] = o;
+        if (blockIdx.x == 0) {
+            for (int k = 0; k <= world; k++) { dyn->reqbase[k] = s_req[k]; dyn->chunkbase[k] = s_chunk[k]; dyn->off[k] = s_n[k]; }
+            dyn->n_owned = (int32_t)r; dyn->c_owned = (int32_t)c;
+            dyn->base.my_off = 0; dyn->base.total_n = o;
+        }
     }
-    __threadfence_system();
-}
-
-// concatenate what the sources sent, in rank order
-__global__ void k_part_gather(const uint8_t *__restrict__ my_base, size_t hash_off, size_t info_off,
-                              int64_t cap, int64_t rcap, int world, const PartDyn *__restrict__ dyn,
-                              int32_t *__restrict__ c_owned, uint32_t *__restrict__ pos_owned,
-                              uint64_t *__restrict__ hashes_owned)
-{
+    __syncthreads();
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t step = (int64_t)gridDim.x * blockDim.x;
     const unsigned long long *info = (const unsigned long long *)(my_base + info_off);
     const uint64_t *hin = (const uint64_t *)(my_base + hash_off);
-    for (int64_t j = tid; j < dyn->n_owned; j += step) {
-        int q = 0;
-        while (q + 1 < world && j >= dyn->reqbase[q + 1]) q++;
-        const unsigned long long v = info[(size_t)q * rcap + (j - dyn->reqbase[q])];
+    const int64_t n_owned = s_req[world], ch_owned = s_chunk[world];
+    for (int64_t j = tid; j < n_owned; j += step) {
+        int k = 0;
+        while (k + 1 < world && j >= s_req[k + 1]) k++;
+        const unsigned long long v = info[(size_t)k * rcap + (j - s_req[k])];
         c_owned[j] = (int32_t)(v >> 32);
-        pos_owned[j] = dyn->off[q] + (uint32_t)v;
+        pos_owned[j] = s_n[k] + (uint32_t)v;
     }
-    for (int64_t x = tid; x < dyn->c_owned; x += step) {
-        int q = 0;
-        while (q + 1 < world && x >= dyn->chunkbase[q + 1]) q++;
-        hashes_owned[x] = hin[(size_t)q * cap + (x - dyn->chunkbase[q])];
+    for (int64_t x = tid; x < ch_owned; x += step) {
+        int k = 0;
+        while (k + 1 < world && x >= s_chunk[k + 1]) k++;
+        hashes_owned[x] = hin[(size_t)k * cap + (x - s_chunk[k])];
     }
 }
 
-__global__ void k_part_push_results(const PartDyn *__restrict__ dyn, int world, int my_rank,
-                                    const int32_t *__restrict__ ep, const int32_t *__restrict__ depth,
-                                    const uint64_t *__restrict__ matched,
-                                    const unsigned long long *__restrict__ peer_bases,
-                                    size_t res_off, int64_t rcap)
+__global__ void __launch_bounds__(256)
+k_part_push_results(PartDyn *dyn, int world, int my_rank,
+                    const int32_t *__restrict__ ep, const int32_t *__restrict__ depth,
+                    const uint64_t *__restrict__ matched,
+                    const unsigned long long *__restrict__ peer_bases,
+                    size_t res_off, int64_t rcap, int set, unsigned long long epoch)
 {
     for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < dyn->n_owned;
          j += (int64_t)gridDim.x * blockDim.x) {
@@ -280,40 +311,31 @@ __global__ void k_part_push_results(const PartDyn *__restrict__ dyn, int world, 
         r.ep = ep[j]; r.depth = depth[j]; r.matched = matched[j];
         ((PartRes *)(uintptr_t)(peer_bases[q] + res_off))[(size_t)my_rank * rcap + (j - dyn->reqbase[q])] = r;
     }
-    __syncthreads();
-    if (threadIdx.x == 0) __threadfence_system();
+    if (last_cta_after_peer_stores(&dyn->ticket_res) && (int)threadIdx.x < world) {
+        const int q = threadIdx.x;
+        PartFlags *f = (PartFlags *)(uintptr_t)peer_bases[q];
+        *(volatile unsigned long long *)&f->res[set][my_rank] =
+            (epoch << 32) | (dyn->reqbase[q + 1] - dyn->reqbase[q]);
+        __threadfence_system();
+    }
 }
 
-__global__ void k_part_publish_res(const unsigned long long *__restrict__ peer_bases, int world,
-                                   int my_rank, int set, unsigned long long epoch,
-                                   const PartDyn *__restrict__ dyn)
+// wait for all owners' results (every CTA spins on the local flags), then scatter them to
+// request order; block 0 advances the global sequence number to the next batch's request 0
+__global__ void __launch_bounds__(256)
+k_part_scatter(const uint32_t *__restrict__ dest_slot, const uint8_t *__restrict__ my_base,
+               int set, unsigned long long epoch, int world, TrieDev *dev, PartDyn *dyn,
+               size_t res_off, int64_t rcap, int n, int32_t *__restrict__ endpoint,
+               int32_t *__restrict__ depth, uint64_t *__restrict__ matched)
 {
-    const int q = threadIdx.x;
-    if (q >= world) return;
-    PartFlags *f = (PartFlags *)(uintptr_t)peer_bases[q];
-    __threadfence_system();
-    *(volatile unsigned long long *)&f->res[set][my_rank] =
-        (epoch << 32) | (dyn->reqbase[q + 1] - dyn->reqbase[q]);
-    __threadfence_system();
-}
-
-__global__ void k_part_wait_res(const PartFlags *__restrict__ mine, int set, unsigned long long epoch,
-                                int world, TrieDev *dev, PartDyn *dyn)
-{
-    const int q = threadIdx.x;
-    if (q < world) {
+    const PartFlags *mine = (const PartFlags *)my_base;
+    if ((int)threadIdx.x < world) {
         unsigned long long v;
-        if (!p2p_spin(&mine->res[set][q], epoch, &v)) atomicOr(&dev->status, B200R_S_PEER_TIMEOUT);
+        if (!p2p_spin(&mine->res[set][threadIdx.x], epoch, &v)) atomicOr(&dev->status, B200R_S_PEER_TIMEOUT);
+        __threadfence();
     }
     __syncthreads();
-    if (threadIdx.x == 0) dyn->base.seq_base += dyn->base.total_n;   // next batch's request 0
-    __threadfence_system();
-}
-
-__global__ void k_part_scatter(const uint32_t *__restrict__ dest_slot, const uint8_t *__restrict__ my_base,
-                               size_t res_off, int64_t rcap, int n, int32_t *__restrict__ endpoint,
-                               int32_t *__restrict__ depth, uint64_t *__restrict__ matched)
-{
+    if (blockIdx.x == 0 && threadIdx.x == 0) dyn->base.seq_base += dyn->base.total_n;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const uint32_t ds = dest_slot[i];
@@ -411,36 +433,33 @@ int b200r_part_send(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_star
     int32_t *totals = (int32_t *)(wk + L.w_totals);
     const int set = (int)(epoch & 1);
     const int nblk = (int)((n + PART_BLOCK - 1) / PART_BLOCK);
+    PartDyn *dyn = (PartDyn *)(wk + L.w_dyn);
     ProfScope ps__(PK_PUSH, st);
     if (nblk > 0) {
-        g_launches += 3;
+        g_launches += 4;
         k_part_count<<<nblk, PART_BLOCK, 0, st>>>(chunk_base, hashes, (int)n, world, blk_cnt);
         B200R_LAUNCH_CHECK("k_part_count");
         k_part_scan<<<1, 1024, 0, st>>>(blk_cnt, nblk, world, blk_off, totals);
         B200R_LAUNCH_CHECK("k_part_scan");
         uint32_t *dest_slot = (uint32_t *)(wk + L.w_dest_slot + (size_t)set * align_up((size_t)rcap * 4));
-        uint32_t *req_dst = (uint32_t *)(wk + L.w_req_dst);
         uint64_t *hash_stage = (uint64_t *)(wk + L.w_hash_stage);
         unsigned long long *info_stage = (unsigned long long *)(wk + L.w_info_stage);
-        k_part_push<<<nblk, PART_BLOCK, 0, st>>>(chunk_base, hashes, (int)n, world, blk_off, totals,
-                                                 info_stage, dest_slot, req_dst);
-        B200R_LAUNCH_CHECK("k_part_push");
-        g_launches += 2;
-        k_part_copy<<<(unsigned)std::min<int64_t>((n + WARPS_PER_CTA - 1) / WARPS_PER_CTA, 148 * 8),
-                      WARPS_PER_CTA * 32, 0, st>>>(chunk_base, hashes, (int)n, req_dst, hash_stage);
-        B200R_LAUNCH_CHECK("k_part_copy");
+        k_part_place<<<nblk, PART_BLOCK, 0, st>>>(chunk_base, hashes, (int)n, world, blk_off, totals,
+                                                  info_stage, dest_slot, hash_stage);
+        B200R_LAUNCH_CHECK("k_part_place");
         k_part_bulk<<<148 * 2, 256, 0, st>>>(hash_stage, info_stage, totals, world, rank,
                                              (const unsigned long long *)d_peer_bases,
                                              L.hash_off + (size_t)set * L.hash_set,
-                                             L.info_off + (size_t)set * L.info_set, cap, rcap);
+                                             L.info_off + (size_t)set * L.info_set, cap, rcap,
+                                             &dyn->ticket_bulk, set, (unsigned long long)epoch, (unsigned)n);
         B200R_LAUNCH_CHECK("k_part_bulk");
     } else {
         B200R_CUDA(cudaMemsetAsync(totals, 0, (size_t)4 * world * 4, st));
+        g_launches += 1;
+        k_part_publish_in<<<1, P2P_MAX_WORLD, 0, st>>>((const unsigned long long *)d_peer_bases, world, rank,
+                                                       set, epoch, totals, (unsigned)n);
+        B200R_LAUNCH_CHECK("k_part_publish_in");
     }
-    g_launches += 1;
-    k_part_publish_in<<<1, P2P_MAX_WORLD, 0, st>>>((const unsigned long long *)d_peer_bases, world, rank,
-                                                   set, epoch, totals, (unsigned)n);
-    B200R_LAUNCH_CHECK("k_part_publish_in");
     return B200R_OK;
 }
 
@@ -469,14 +488,13 @@ int b200r_part_route(b200r_trie *t, uint64_t avail_mask, uint64_t seed,
     const int32_t *n_dev = &dyn->n_owned;
 
     { ProfScope ps__(PK_WAIT, st); g_launches += 1;
-    k_part_wait_meta<<<1, P2P_MAX_WORLD, 0, st>>>((const PartFlags *)base, set, epoch, world, dyn, t->dev);
-    B200R_LAUNCH_CHECK("k_part_wait_meta");
-    }
-    { ProfScope ps__(PK_PREP, st); g_launches += 1;
-    k_part_gather<<<148 * 4, 256, 0, st>>>(base, L.hash_off + (size_t)set * L.hash_set,
+    k_part_gather<<<148 * 4, 256, 0, st>>>(base, set, (unsigned long long)epoch,
+                                           L.hash_off + (size_t)set * L.hash_set,
                                            L.info_off + (size_t)set * L.info_set, cap, rcap, world, dyn,
-                                           c_owned, pos_owned, hashes);
+                                           t->dev, c_owned, pos_owned, hashes);
     B200R_LAUNCH_CHECK("k_part_gather");
+    }
+    { ProfScope ps__(PK_PREP, st);
     rc = launch_prep_counts(c_owned, L.n_max, n_dev, block_sums, chunk_base, L.c_max, t->dev, st);
     if (rc) return rc;
     }
@@ -492,14 +510,12 @@ int b200r_part_route(b200r_trie *t, uint64_t avail_mask, uint64_t seed,
     core.dyn = &dyn->base; core.pos = pos_owned; core.n_dev = n_dev;
     rc = launch_route_core(t, core, st);
     if (rc) return rc;
-    { ProfScope ps__(PK_PUSH, st); g_launches += 2;
+    { ProfScope ps__(PK_PUSH, st); g_launches += 1;
     k_part_push_results<<<148 * 2, 256, 0, st>>>(dyn, world, rank, ep, depth, matched,
                                                  (const unsigned long long *)d_peer_bases,
-                                                 L.res_off + (size_t)set * L.res_set, rcap);
+                                                 L.res_off + (size_t)set * L.res_set, rcap, set,
+                                                 (unsigned long long)epoch);
     B200R_LAUNCH_CHECK("k_part_push_results");
-    k_part_publish_res<<<1, P2P_MAX_WORLD, 0, st>>>((const unsigned long long *)d_peer_bases, world,
-                                                    rank, set, epoch, dyn);
-    B200R_LAUNCH_CHECK("k_part_publish_res");
     }
     return B200R_OK;
 }
@@ -515,18 +531,12 @@ int b200r_part_finish(b200r_trie *t, int64_t n, void *d_my_base, int32_t world, 
     const PartLayout L = part_layout(world, cap, rcap);
     const int set = (int)(epoch & 1);
     uint8_t *base = (uint8_t *)d_my_base, *wk = (uint8_t *)d_work;
-    { ProfScope ps__(PK_WAIT, st); g_launches += 1;
-    k_part_wait_res<<<1, P2P_MAX_WORLD, 0, st>>>((const PartFlags *)base, set, epoch, world, t->dev,
-                                                 (PartDyn *)(wk + L.w_dyn));
-    B200R_LAUNCH_CHECK("k_part_wait_res");
-    }
-    if (n > 0) {
-        ProfScope ps__(PK_RESOLVE, st); g_launches += 1;
-        k_part_scatter<<<(int)((n + 255) / 256), 256, 0, st>>>(
-            (const uint32_t *)(wk + L.w_dest_slot + (size_t)set * align_up((size_t)rcap * 4)), base,
-            L.res_off + (size_t)set * L.res_set, rcap,
-            (int)n, d_endpoint, d_match_depth, d_matched);
-        B200R_LAUNCH_CHECK("k_part_scatter");
+    { ProfScope ps__(PK_RESOLVE, st); g_launches += 1;
+    k_part_scatter<<<(int)((n + 255) / 256) > 0 ? (int)((n + 255) / 256) : 1, 256, 0, st>>>(
+        (const uint32_t *)(wk + L.w_dest_slot + (size_t)set * align_up((size_t)rcap * 4)), base, set,
+        (unsigned long long)epoch, world, t->dev, (PartDyn *)(wk + L.w_dyn),
+        L.res_off + (size_t)set * L.res_set, rcap, (int)n, d_endpoint, d_match_depth, d_matched);
+    B200R_LAUNCH_CHECK("k_part_scatter");
     }
     return B200R_OK;
 }

@@ -79,7 +79,10 @@ k_prep_sums(const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars
             int32_t *__restrict__ block_sums, const int32_t *__restrict__ n_dev)
 {
     __shared__ int s_red[32];
-    if (n_dev) n = *n_dev;          // batch size known only on the device (partitioned multi-GPU)
+    if (n_dev) {                    // batch size known only on the device (partitioned multi-GPU):
+        n = *n_dev;                 // the grid covers the capacity, blocks past the batch leave
+        if ((int)blockIdx.x * PREP_BLOCK >= n) return;
+    }
     int i = blockIdx.x * PREP_BLOCK + threadIdx.x;
     int c = (i < n) ? chunks_of(lens, nchars, i, cc) : 0;
     int tot = block_sum_1024(c, s_red);
@@ -98,6 +101,7 @@ k_prep_scan(const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars
     if (n_dev) {
         n = *n_dev;
         if (n == 0 && blockIdx.x == 0 && threadIdx.x == 0) chunk_base[0] = 0;
+        if ((int)blockIdx.x * PREP_BLOCK >= n) return;
     }
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     // offset of this block = sum of the sums of all earlier blocks
