@@ -326,7 +326,7 @@ def new_router(cx, cap_log2, max_requests, max_chunks):
         # b+1 overlaps the route stage of batch b; results stay sequential)
         from b200_router.trie import GpuHashTrie, RoutePipeline
         pipe = RoutePipeline(GpuHashTrie(cap_log2=cap_log2, device=cx.dev),
-                             depth=int(os.environ.get("BENCH_PIPE_DEPTH", "2")))
+                             depth=int(os.environ.get("BENCH_PIPE_DEPTH", "3")))
         pipe.reserve(max_requests, max_chunks)
         return pipe
     # multi-GPU: table partitioned by first-chunk hash, chunk hashes and results shipped

@@ -54,6 +54,12 @@ extern "C" {
 
 /* flags for the prompt entry points */
 #define B200R_F_ALL_ASCII 1u /* caller guarantees nchars[i] == lens[i] for all i */
+/* b200r_prefix_hash_stage only: split it once more, so that three batches can be in flight.
+ * PREP_ONLY runs everything but the chunk-hashing kernel (chunk counts, CSR, tile map, UTF-8
+ * chunk offsets, ragged last chunks: latency-bound, a few MB); PREP_DONE runs only the
+ * chunk-hashing kernel on a scratch buffer that a PREP_ONLY call has prepared. */
+#define B200R_F_PREP_ONLY 2u
+#define B200R_F_PREP_DONE 4u
 
 /* latched device status bits (b200r_trie_status) */
 #define B200R_S_TABLE_FULL 1u

@@ -12,6 +12,8 @@ LIB_PATH = os.path.join(_HERE, "libb200router.so")
 
 OK = 0
 F_ALL_ASCII = 1
+F_PREP_ONLY = 2
+F_PREP_DONE = 4
 S_TABLE_FULL = 1
 S_CHUNK_CAP = 2
 S_PEER_TIMEOUT = 4

@@ -302,26 +302,30 @@ def decode_dump(arr: np.ndarray, root_mask: int) -> Dict[tuple, int]:
 class RoutePipeline:
     """Overlaps consecutive batches on one GPU.
 
-    A routed batch is a hash stage (prep + chunk hashing: streams the prompt bytes,
-    never touches the table) and a route stage (claim / select / commit: table
-    probes, latency bound).  The pipeline runs the hash stage of batch b+1 on its
-    own stream while the route stage of batch b runs on the caller's stream; the
-    stages meet in one scratch buffer per batch in flight.  Route stages stay in
-    submission order, so results are still those of sequential routing.
+    A routed batch is three steps that meet only in its scratch buffer:
+      prep    chunk counts, CSR, tile map, ragged last chunks (latency-bound, a few MB)
+      hash    XXH64 of every full chunk: streams the prompt bytes (HBM-bound)
+      route   claim / select / commit: walks and extends the table (latency-bound)
+    Only `route` touches the table.  The pipeline runs prep of batch b+2 and hash of batch b+1
+    on their own streams while route of batch b runs on the caller's stream; route stages stay
+    in submission order, so results are still those of sequential routing.  One scratch buffer
+    per batch in flight (depth 3).
 
-    Host (pinned) inputs are copied to the device on the hash stream, so the H2D
-    copy of batch b+1 also overlaps the routing of batch b.  For inputs that are
-    already on the device pass inputs_ready=True when they are complete (e.g.
-    produced and synchronised earlier); otherwise the hash stage waits for the
-    caller's stream, which is safe but serialises the two stages."""
+    Host (pinned) inputs are copied to the device on the prep stream, so the H2D copy of a
+    later batch also overlaps the routing of the current one.  For inputs that are already on
+    the device pass inputs_ready=True when they are complete (e.g. produced and synchronised
+    earlier); otherwise the prep stage waits for the caller's stream, which is safe but
+    serialises the stages."""
 
-    def __init__(self, trie: GpuHashTrie, depth: int = 2):
+    def __init__(self, trie: GpuHashTrie, depth: int = 3):
         self.trie = trie
         self.depth = depth
         self.device = trie.device
+        self.prep_stream = torch.cuda.Stream(device=self.device)
         self.hash_stream = torch.cuda.Stream(device=self.device)
         self._scratch = [None] * depth
         self._done = [None] * depth
+        self._prepped = [torch.cuda.Event() for _ in range(depth)]
         self._hashed = [torch.cuda.Event() for _ in range(depth)]
         self._outs = [None] * (depth + 1)
         self._i = 0
@@ -360,25 +364,39 @@ class RoutePipeline:
         self._i += 1
         n = p.n
         cur = torch.cuda.current_stream(self.device)
-        hs = self.hash_stream
+        ps, hs = self.prep_stream, self.hash_stream
         flags = _lib.F_ALL_ASCII if p.all_ascii else 0
         need = L.b200r_prefix_route_scratch_bytes(n, p.max_chunks, flags)
         sc = self._scratch_for(k, need)
         on_host = p.bytes.device.type == "cpu"
         if self._done[k] is not None:
-            hs.wait_event(self._done[k])          # scratch k is free again
+            ps.wait_event(self._done[k])          # scratch k is free again
         if not on_host and not inputs_ready:
-            hs.wait_stream(cur)
-        with torch.cuda.device(self.device), torch.cuda.stream(hs):
-            if on_host:
-                p = p.to(self.device, non_blocking=True)
-            _lib.check(L.b200r_prefix_hash_stage(
-                self.trie._h, _ptr(p.bytes), _ptr(p.starts), _ptr(p.lens), _ptr(p.nchars), n,
-                p.max_chunks, flags, _ptr(sc), sc.numel(), C.c_void_p(hs.cuda_stream)))
-            self._hashed[k].record(hs)
-        cur.wait_event(self._hashed[k])
-        ep, depth, matched = o
+            ps.wait_stream(cur)
         with torch.cuda.device(self.device):
+            with torch.cuda.stream(ps):
+                if on_host:
+                    p = p.to(self.device, non_blocking=True)
+                _lib.check(L.b200r_prefix_hash_stage(
+                    self.trie._h, _ptr(p.bytes), _ptr(p.starts), _ptr(p.lens), _ptr(p.nchars), n,
+                    p.max_chunks, flags | _lib.F_PREP_ONLY, _ptr(sc), sc.numel(),
+                    C.c_void_p(ps.cuda_stream)))
+                self._prepped[k].record(ps)
+            hs.wait_event(self._prepped[k])
+            with torch.cuda.stream(hs):
+                _lib.check(L.b200r_prefix_hash_stage(
+                    self.trie._h, _ptr(p.bytes), _ptr(p.starts), _ptr(p.lens), _ptr(p.nchars), n,
+                    p.max_chunks, flags | _lib.F_PREP_DONE, _ptr(sc), sc.numel(),
+                    C.c_void_p(hs.cuda_stream)))
+                self._hashed[k].record(hs)
+                if on_host:
+                    p.bytes.record_stream(hs)     # allocated on the prep stream, read on this one
+                    p.starts.record_stream(hs)
+                    p.lens.record_stream(hs)
+                    if p.nchars is not None:
+                        p.nchars.record_stream(hs)
+            cur.wait_event(self._hashed[k])
+            ep, depth, matched = o
             _lib.check(L.b200r_prefix_route_stage(
                 self.trie._h, n, p.max_chunks, flags, avail_mask & M64, seed & M64, seq0 & M64,
                 _ptr(ep), _ptr(depth), _ptr(matched), _ptr(sc), sc.numel(),

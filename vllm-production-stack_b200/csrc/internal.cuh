@@ -60,7 +60,7 @@ int check_prompt_args(const void *bytes, const void *starts, const void *lens, i
 int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const int32_t *d_lens,
                 const int32_t *d_nchars, int64_t n, int32_t cc, uint32_t flags,
                 int32_t *d_chunk_base, uint64_t *d_hashes, int64_t max_chunks, uint8_t *scratch,
-                const Plan &p, TrieDev *dev, cudaStream_t st);
+                const Plan &p, TrieDev *dev, cudaStream_t st, int phase = 0);
 
 // CSR of given per-request chunk counts; the count of requests is known only on the device
 int launch_prep_counts(const int32_t *d_counts, int64_t n_max, const int32_t *n_dev,

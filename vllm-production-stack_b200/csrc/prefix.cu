@@ -619,8 +619,10 @@ int check_prompt_args(const void *bytes, const void *starts, const void *lens, i
 int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const int32_t *d_lens,
                 const int32_t *d_nchars, int64_t n, int32_t cc, uint32_t flags,
                 int32_t *d_chunk_base, uint64_t *d_hashes, int64_t max_chunks,
-                uint8_t *scratch, const Plan &p, TrieDev *dev, cudaStream_t st)
+                uint8_t *scratch, const Plan &p, TrieDev *dev, cudaStream_t st, int phase)
 {
+    // phase 0: everything; 1: all but the chunk-hashing kernel (the "prep" part: code-point
+    // counts, CSR, tile map, UTF-8 chunk offsets, ragged tails); 2: the chunk-hashing kernel only
     int32_t *tile_first = (int32_t *)(scratch + p.off_tile_first);
     int32_t *block_sums = (int32_t *)(scratch + p.off_block_sums);
     int32_t *chunk_off = nullptr;
@@ -630,6 +632,7 @@ int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const int32_t *
         d_nchars = nullptr;                     // nchars == lens by contract
     } else {
         chunk_off = (int32_t *)(scratch + p.off_chunk_off);
+        if (!d_nchars && phase == 2) d_nchars = (int32_t *)(scratch + p.off_nchars);
         if (!d_nchars) {
             int32_t *tmp = (int32_t *)(scratch + p.off_nchars);
             { ProfScope ps__(PK_UTF8, st); g_launches += 1;
@@ -641,6 +644,7 @@ int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const int32_t *
         }
     }
     const int nblk = (int)((n + PREP_BLOCK - 1) / PREP_BLOCK);
+    if (phase != 2) {
     { ProfScope ps__(PK_PREP, st); g_launches += 1;
     k_prep_sums<<<nblk, PREP_BLOCK, 0, st>>>(d_lens, d_nchars, (int)n, cc, block_sums, nullptr);
     B200R_LAUNCH_CHECK("k_prep_sums");
@@ -657,8 +661,9 @@ int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const int32_t *
         B200R_LAUNCH_CHECK("k_utf8_bounds");
         }
     }
+    }
     const int ntiles = (int)((max_chunks + HASH_WARPS * WTILE - 1) / (HASH_WARPS * WTILE));
-    if (ntiles > 0) {
+    if (ntiles > 0 && phase != 1) {
         ProfScope ps__(PK_HASH, st); g_launches += 1;
         k_hash_chunks<<<ntiles, HASH_WARPS * 32, 0, st>>>(
             d_bytes, d_starts, d_lens, d_nchars, d_chunk_base, tile_first, chunk_off, (int)n, cc,
@@ -810,7 +815,7 @@ int b200r_xxh64_chunks(const uint8_t *d_bytes, const int64_t *d_starts, const in
         return B200R_OK;
     }
     return launch_hash(d_bytes, d_starts, d_lens, d_nchars, n, chunk_chars, flags, d_chunk_base,
-                       d_hashes, max_chunks, (uint8_t *)d_scratch, p, nullptr, st);
+                       d_hashes, max_chunks, (uint8_t *)d_scratch, p, nullptr, st, 0);
 }
 
 // ---------------------------------------------------------------------------
@@ -883,7 +888,7 @@ int b200r_xxh64_chunks_noalloc(const uint8_t *d_bytes, const int64_t *d_starts,
     // sums by the prep kernels, counts/offsets by the UTF-8 kernels), so stale
     // contents of the previous call are never observed.
     return launch_hash(d_bytes, d_starts, d_lens, d_nchars, n, chunk_chars, flags, d_chunk_base,
-                       d_hashes, max_chunks, scratch, p, nullptr, st);
+                       d_hashes, max_chunks, scratch, p, nullptr, st, 0);
 }
 
 
@@ -1046,9 +1051,10 @@ int b200r_prefix_hash_stage(b200r_trie *t, const uint8_t *d_bytes, const int64_t
         return B200R_E_SCRATCH;
     }
     uint8_t *sc = (uint8_t *)d_scratch;
+    const int phase = (flags & B200R_F_PREP_ONLY) ? 1 : ((flags & B200R_F_PREP_DONE) ? 2 : 0);
     return launch_hash(d_bytes, d_starts, d_lens, d_nchars, n, t->chunk_chars, flags,
                        (int32_t *)(sc + p.off_chunk_base), (uint64_t *)(sc + p.off_hashes),
-                       max_chunks, sc, p, t->dev, (cudaStream_t)stream);
+                       max_chunks, sc, p, t->dev, (cudaStream_t)stream, phase);
 }
 
 static int route_from(b200r_trie *t, const uint64_t *hashes, const int32_t *chunk_base, int64_t n,
