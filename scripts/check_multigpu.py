@@ -2,11 +2,12 @@
 """Multi-GPU parity check (test infrastructure; launch with torchrun, one rank per GPU):
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
-        --master-port 29520 scripts/check_multigpu.py [part|p2p|nccl]
+        --master-port 29520 scripts/check_multigpu.py [part|nccl]
 
-Routes a C3-shaped trace with availability churn through the sharded router (real NVLink
-peer-memory exchange or NCCL all-gathers) and compares every rank's decisions, and every
-replica's final table, with the sequential C oracle on the rank-major concatenation.
+Routes a C3-shaped trace with availability churn through the multi-GPU router -- part:
+partitioned table, real NVLink peer-memory exchange; nccl: replicated table, NCCL all-gather of
+the chunk hashes -- and compares every rank's decisions, and the final table (union of the
+partitions / every replica), with the sequential C oracle on the rank-major concatenation.
 """
 import os
 import sys
@@ -20,8 +21,7 @@ import torch
 import torch.distributed as dist
 
 from b200_router import traces
-from b200_router.distributed import (P2PShardedRouter, PartitionedPrefixRouter,
-                                     ShardedPrefixRouter)
+from b200_router.distributed import PartitionedPrefixRouter, ShardedPrefixRouter
 from b200_router.packing import pack_arrays
 from oracle import coracle
 
@@ -38,9 +38,7 @@ def main():
                                   suffix_lo=100, suffix_hi=400, seed=31)
     shards = [[tr.batch_arrays(b * world + r) for r in range(world)] for b in range(nb)]
     max_chunks = max(int(((s[2] + 127) // 128).sum()) for row in shards for s in row)
-    if mode == "p2p":
-        router = P2PShardedRouter(cap_log2=20, device=dev, max_requests=per, max_chunks=max_chunks)
-    elif mode == "part":
+    if mode == "part":
         router = PartitionedPrefixRouter(cap_log2=20, device=dev, max_requests=per,
                                          max_chunks=max_chunks)
     else:
