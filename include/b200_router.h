@@ -125,11 +125,11 @@ int b200r_xxh64_chunks_noalloc(const uint8_t *d_bytes, const int64_t *d_starts,
  * and is identified by its index in the log.  The nodes one request creates in
  * one go are consecutive records (a run); only the first node of a run is
  * entered in an open-addressing table keyed by (parent node index, chunk hash)
- * -- exactly parent.children[chunk_hash] -- with value (log index, run length).
+ * -- exactly parent.children[chunk_hash] -- with the log index as value.
  * Walking a stored path compares consecutive records with the request's chunk
- * hashes.  Capacity = 2^cap_log2 nodes (log records) and 2^(cap_log2+1) table
- * entries of 32 bytes (load factor <= 0.5 even if every node heads its own
- * run): 96 bytes of device memory per node of capacity.  Endpoints are bit
+ * hashes.  Capacity = 2^cap_log2 nodes (log records of 32 bytes) and
+ * 2^(cap_log2+1) table entries of 16 bytes (load factor <= 0.5 even if every
+ * node heads its own run): 64 bytes of device memory per node of capacity.  Endpoints are bit
  * indices 0..63.  The reference never evicts, neither does the log:
  * b200r_trie_status reports the node count; a full log latches
  * B200R_S_TABLE_FULL.
@@ -222,8 +222,9 @@ uint32_t b200r_pick(uint64_t seed, uint64_t seq, uint32_t n);
  * Trie state export (parity / checkpoint; the reference has no counterpart
  * beyond walking TrieNode.children, hashtrie.py:24-32).  Writes up to
  * max_nodes entries of 4 x u64
- *   {log index | run length << 32 (length on the first node of a run, else 0),
- *    parent's log index (0xFFFFFFFF = the root), chunk hash, mask}
+ *   {log index | records left in its run << 32,
+ *    parent's log index (0xFFFFFFFF = the root) | 1 << 63 on the first node of a run,
+ *    chunk hash, mask}
  * to d_out and the number of nodes to *count (may exceed max_nodes).
  * Synchronises.  Paths follow from the parent links.
  * ---------------------------------------------------------------------- */

@@ -71,14 +71,15 @@ def test_c3_one_million_prompts_batch_64k():
     # trie invariant child.mask subset-of parent.mask, checked through the parent links
     idx = arr[:, 0] & np.uint64(0xFFFFFFFF)
     order = np.argsort(idx)
-    sidx, smask, spar = idx[order], arr[order, 3], arr[order, 1]
+    sidx, smask, spar = idx[order], arr[order, 3], arr[order, 1] & np.uint64(0xFFFFFFFF)
     assert (np.diff(sidx.astype(np.int64)) > 0).all()         # every node has its own log record
     is_top = spar == np.uint64(0xFFFFFFFF)
     pos = np.minimum(np.searchsorted(sidx, spar), len(sidx) - 1)
     assert ((sidx[pos] == spar) | is_top).all()               # prefix-closed: every parent exists
     assert (((smask & ~smask[pos]) == 0) | is_top).all()      # nested endpoint sets
     # runs: the lengths on the run heads add up to the node count
-    assert int((arr[:, 0] >> np.uint64(32)).sum()) == len(arr)
+    heads = (arr[:, 1] >> np.uint64(63)) == 1
+    assert int((arr[heads, 0] >> np.uint64(32)).sum()) == len(arr)
     t.close()
 
 

@@ -27,7 +27,7 @@ def _stream():
 class GpuHashTrie:
     """Open-addressing table of trie nodes on one GPU.
 
-    Node log + hash table of run heads (csrc/trie.cuh); capacity = 2**cap_log2 nodes, 96 bytes
+    Node log + hash table of run heads (csrc/trie.cuh); capacity = 2**cap_log2 nodes, 64 bytes
     of device memory per node of capacity.  The reference never evicts
     (routing_logic.py:352) and neither does the log; `status()` reports the node count, a
     full log raises."""
@@ -200,8 +200,9 @@ class GpuHashTrie:
 
     # --------------------------------------------------------------- dump etc
     def dump_raw(self):
-        """(entries uint64[count,4], root_mask); an entry is {log index | run length << 32 (on
-        the first node of a run), parent's log index (0xFFFFFFFF = root), chunk hash, mask}."""
+        """(entries uint64[count,4], root_mask); an entry is {log index | records left in its run
+        << 32, parent's log index (0xFFFFFFFF = root) | 1 << 63 on the first node of a run, chunk
+        hash, mask}."""
         s = self.status()
         cap = max(int(s["num_nodes"]), 1)
         out = torch.empty(cap * 4, dtype=torch.int64, device=self.device)
@@ -273,7 +274,7 @@ ROOT_IDX = 0xFFFFFFFF
 
 def decode_dump(arr: np.ndarray, root_mask: int) -> Dict[tuple, int]:
     """Follow the parent links of a dump up to the root: {hash path: mask}."""
-    nodes = {int(e0) & 0xFFFFFFFF: (int(par), int(h), int(m)) for e0, par, h, m in arr}
+    nodes = {int(e0) & 0xFFFFFFFF: (int(par) & 0xFFFFFFFF, int(h), int(m)) for e0, par, h, m in arr}
     paths: Dict[int, tuple] = {ROOT_IDX: ()}
 
     def path_of(idx):

@@ -492,35 +492,37 @@ k_commit(Rec *__restrict__ log, TrieDev *dev, const int32_t *__restrict__ chunk_
 }
 
 // ------------------------------------------------------------ dump / restore / sweeps
-__global__ void k_count_nodes(const Head *__restrict__ tab, int64_t cap, TrieDev *dev)
+__global__ void k_count_nodes(const Head *__restrict__ tab, const Rec *__restrict__ log, int64_t cap,
+                              TrieDev *dev)
 {
     unsigned long long mine = 0;
     for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < cap;
          s += (int64_t)gridDim.x * blockDim.x) {
         const Head e = tab[s];
-        if (e.pkey) mine += e.run >> 32;
+        if (e.pk) mine += log[(uint32_t)e.pk].rem;
     }
     for (int o = 16; o; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
     if ((threadIdx.x & 31) == 0 && mine) atomicAdd(&dev->num_nodes, mine);
 }
 
 // One thread per run head: the run's records in depth order, as
-//   {log index | run length << 32 (length only on the head, 0 on the others),
-//    parent log index (ROOT_IDX for depth-1 nodes), chunk hash, mask}
+//   {log index | records left in the run << 32, parent log index (ROOT_IDX for depth-1 nodes)
+//    | 1 << 63 on the first node of a run, chunk hash, mask}
 __global__ void k_dump(const Head *__restrict__ tab, const Rec *__restrict__ log, int64_t cap,
                        TrieDev *dev, uint64_t *__restrict__ out, int64_t max_nodes)
 {
     for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < cap;
          s += (int64_t)gridDim.x * blockDim.x) {
         const Head e = tab[s];
-        if (!e.pkey) continue;
-        const uint32_t idx = (uint32_t)e.run, len = (uint32_t)(e.run >> 32);
+        if (!e.pk) continue;
+        const uint32_t idx = (uint32_t)e.pk;
+        const uint32_t len = (uint32_t)log[idx].rem;
         const unsigned long long at = atomicAdd(&dev->dump_count, (unsigned long long)len);
         for (uint32_t j = 0; j < len; j++) {
             if ((int64_t)(at + j) >= max_nodes) break;
             const Rec r = log[idx + j];
-            out[4 * (at + j) + 0] = (uint64_t)(idx + j) | (j ? 0ULL : ((uint64_t)len << 32));
-            out[4 * (at + j) + 1] = j ? (uint64_t)(idx + j - 1) : (e.pkey - 1);
+            out[4 * (at + j) + 0] = (uint64_t)(idx + j) | ((uint64_t)(len - j) << 32);
+            out[4 * (at + j) + 1] = j ? (uint64_t)(idx + j - 1) : ((uint64_t)((uint32_t)(e.pk >> 32) - 2u) | (1ULL << 63));
             out[4 * (at + j) + 2] = r.h;
             out[4 * (at + j) + 3] = r.mask;
         }
@@ -534,17 +536,15 @@ __global__ void k_restore(TrieRef t, const uint64_t *__restrict__ ent, int64_t c
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i == 0 && root_or) atomicOr((unsigned long long *)&t.dev->root_mask, root_or);
     if (i >= count) return;
-    const uint64_t e0 = ent[4 * i], parent = ent[4 * i + 1], h = ent[4 * i + 2], m = ent[4 * i + 3];
-    const uint32_t idx = (uint32_t)e0, len = (uint32_t)(e0 >> 32);
-    if (idx >= t.log_cap || (len && (uint64_t)idx + len > t.log_cap)) {
+    const uint64_t e0 = ent[4 * i], e1 = ent[4 * i + 1], h = ent[4 * i + 2], m = ent[4 * i + 3];
+    const uint32_t idx = (uint32_t)e0, rem = (uint32_t)(e0 >> 32), parent = (uint32_t)e1;
+    if (rem == 0 || (uint64_t)idx + rem > t.log_cap) {
         atomicOr(&t.dev->status, B200R_S_TABLE_FULL);
         return;
     }
-    st_rec(t.log + idx, h, m, 0);
+    st_rec(t.log + idx, h, m, 0, rem);
     atomicMax(&t.dev->log_count, (unsigned long long)idx + 1);
-    // heads are published without waiting for the other records of their run: nothing walks
-    // the table while it is being restored (the call is stream-ordered)
-    if (len && !head_publish(t.tab, t.tab_log2, h, parent + 1, ((unsigned long long)len << 32) | idx))
+    if ((e1 >> 63) && head_publish(t.tab, t.tab_log2, h, parent_key(parent), idx) != idx)
         atomicOr(&t.dev->status, B200R_S_INTERNAL);
 }
 
@@ -934,8 +934,10 @@ int b200r_trie_clear(b200r_trie *t, void *stream)
     if (!t) { set_error("null trie"); return B200R_E_INVALID; }
     cudaStream_t st = (cudaStream_t)stream;
     const size_t cap = (size_t)1 << t->cap_log2;
-    // the head table must start empty; log records are written before they become reachable
+    // the head table starts empty, and so does the log: an all-zero record means "not written
+    // yet" to a reader that got there ahead of the writer's store (trie.cuh)
     B200R_CUDA(cudaMemsetAsync(t->tab, 0, 2 * cap * sizeof(Head), st));
+    B200R_CUDA(cudaMemsetAsync(t->log, 0, cap * sizeof(Rec), st));
     B200R_CUDA(cudaMemsetAsync(t->wblk, 0, (size_t)NWSLOT * sizeof(uint2), st));
     B200R_CUDA(cudaMemsetAsync(t->dev, 0, sizeof(TrieDev), st));
     t->epoch = 0;
@@ -952,7 +954,7 @@ int b200r_trie_status(b200r_trie *t, void *stream, uint32_t *status_bits, int64_
         int blocks = (int)((cap + 255) / 256);
         if (blocks > 148 * 16) blocks = 148 * 16;
         B200R_CUDA(cudaMemsetAsync(&t->dev->num_nodes, 0, 8, st));
-        k_count_nodes<<<blocks, 256, 0, st>>>(t->tab, cap, t->dev);
+        k_count_nodes<<<blocks, 256, 0, st>>>(t->tab, t->log, cap, t->dev);
         B200R_LAUNCH_CHECK("k_count_nodes");
     }
     TrieDev h;

@@ -28,15 +28,15 @@ struct __align__(32) Rec {       // one trie node
     uint64_t mask;               // endpoint set
     unsigned long long first;    // (epoch << 32) | ~request: first request of batch `epoch`
                                  // that touched the node (merged with atomicMax)
-    uint64_t pad;
+    uint64_t rem;                // records from this one to the end of its run (>= 1); 0 = the
+                                 // record has not been written (yet): the log starts zeroed and
+                                 // every record is written exactly once, by one 32-byte store
 };
 
-struct __align__(32) Head {      // hash-table entry: the run that starts at child `h` of `parent`
+struct __align__(16) Head {      // hash-table entry: the run that starts at child `h` of `parent`
     uint64_t h;                  // chunk hash of the run's first node
-    uint64_t pkey;               // parent log index + 1 (root: ROOT_IDX + 1); 0 = empty slot
-    unsigned long long run;      // (length << 32) | log index; 0 = key claimed, not yet published
-    uint64_t pad;
-};
+    uint64_t pk;                 // (parent key << 32) | log index of the first node; 0 = empty
+};                               // parent key = parent's log index + 2, the root's is 1
 
 struct TrieDev {                 // device-resident control block
     uint64_t root_mask;
@@ -62,39 +62,44 @@ constexpr uint32_t PREOK_BIT = 0x80000000u;     // slots[]: node usable before t
 constexpr uint32_t IDX_MASK = 0x7FFFFFFFu;
 constexpr int NWSLOT = 16384;                   // warp slots with a persistent allocation block
 constexpr unsigned FULLW = 0xffffffffu;
-#define B200R_S_INTERNAL 8u                     /* latched: a published run head had no record */
+#define B200R_S_INTERNAL 8u                     /* latched: inconsistent table (never expected) */
+
+__device__ __forceinline__ uint32_t parent_key(uint32_t pidx) { return pidx + 2u; }   // ROOT_IDX -> 1
 
 // ------------------------------------------------------------------ memory ops
-__device__ __forceinline__ void ld_rec(const Rec *r, uint64_t &h, uint64_t &mask, unsigned long long &first)
-{   // one 32-byte load (LDG.256).  L1 may serve it: h never changes once the run is
-    // published, masks only change in kernels that do not read them through this path, and a
-    // stale `first` only costs a redundant atomicMax.
-    uint64_t pad;
+// Publication needs no fence.  A run becomes reachable when its head entry appears in the
+// table (one 128-bit CAS carrying key and log index); its records may become visible a
+// little later, so a reader that finds an in-range record still unwritten (rem == 0) re-reads
+// it past L1 until it is there.  Records are immutable in h / rem once written.
+__device__ __forceinline__ void ld_rec(const Rec *r, uint64_t &h, uint64_t &mask, unsigned long long &first,
+                                       uint64_t &rem)
+{   // one 32-byte load (LDG.256).  L1 may serve it: masks only change in kernels that do not
+    // read them through this path, and a stale `first` only costs a redundant atomicMax.
     asm volatile("ld.global.ca.v4.u64 {%0, %1, %2, %3}, [%4];"
-                 : "=l"(h), "=l"(mask), "=l"(first), "=l"(pad) : "l"(r) : "memory");
-    (void)pad;
+                 : "=l"(h), "=l"(mask), "=l"(first), "=l"(rem) : "l"(r) : "memory");
 }
-__device__ __forceinline__ void st_rec(Rec *r, uint64_t h, uint64_t mask, unsigned long long first)
+__device__ __forceinline__ void ld_rec_cg(const Rec *r, uint64_t &h, uint64_t &mask, unsigned long long &first,
+                                          uint64_t &rem)
+{
+    asm volatile("ld.global.cg.v4.u64 {%0, %1, %2, %3}, [%4];"
+                 : "=l"(h), "=l"(mask), "=l"(first), "=l"(rem) : "l"(r) : "memory");
+}
+__device__ __forceinline__ void st_rec(Rec *r, uint64_t h, uint64_t mask, unsigned long long first,
+                                       uint64_t rem)
 {
     asm volatile("st.global.v4.u64 [%0], {%1, %2, %3, %4};"
-                 :: "l"(r), "l"(h), "l"(mask), "l"(first), "l"(0ULL) : "memory");
+                 :: "l"(r), "l"(h), "l"(mask), "l"(first), "l"(rem) : "memory");
 }
-__device__ __forceinline__ void ld_head(const Head *e, uint64_t &a, uint64_t &b, unsigned long long &run)
+__device__ __forceinline__ void ld_head(const Head *e, uint64_t &a, uint64_t &b)
 {
-    uint64_t pad;
-    asm volatile("ld.global.ca.v4.u64 {%0, %1, %2, %3}, [%4];"
-                 : "=l"(a), "=l"(b), "=l"(run), "=l"(pad) : "l"(e) : "memory");
-    (void)pad;
+    asm volatile("ld.global.ca.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(e) : "memory");
 }
-__device__ __forceinline__ void ld_head_cg(const Head *e, uint64_t &a, uint64_t &b, unsigned long long &run)
-{   // L2-coherent re-read (torn key halves, or a run word that is about to be published)
-    uint64_t pad;
-    asm volatile("ld.global.cg.v4.u64 {%0, %1, %2, %3}, [%4];"
-                 : "=l"(a), "=l"(b), "=l"(run), "=l"(pad) : "l"(e) : "memory");
-    (void)pad;
+__device__ __forceinline__ void ld_head_cg(const Head *e, uint64_t &a, uint64_t &b)
+{
+    asm volatile("ld.global.cg.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(e) : "memory");
 }
 __device__ __forceinline__ void cas128(Head *e, uint64_t n1, uint64_t n2, uint64_t &o1, uint64_t &o2)
-{   // compare the key with (0,0), swap in (n1,n2); returns the previous key
+{   // compare the entry with (0,0), swap in (n1,n2); returns the previous entry
     asm volatile(
         "{\n\t"
         ".reg .b128 cmp, nw, old;\n\t"
@@ -108,68 +113,53 @@ __device__ __forceinline__ void cas128(Head *e, uint64_t n1, uint64_t n2, uint64
         : "memory");
 }
 
-__device__ __forceinline__ uint32_t slot_of(uint64_t h, uint64_t pkey, int tab_log2)
+__device__ __forceinline__ uint32_t slot_of(uint64_t h, uint32_t pkey, int tab_log2)
 {
-    const uint64_t x = (h ^ (pkey * 0xD6E8FEB86659FD93ULL)) * 0x9E3779B97F4A7C15ULL;
+    const uint64_t x = (h ^ ((uint64_t)pkey << 32 | pkey)) * 0x9E3779B97F4A7C15ULL;
     return (uint32_t)(x >> (64 - tab_log2));
 }
 
 // ------------------------------------------------------------------ head table
-// Run word of child `h` of the node with key pkey, or 0 when no run starts there.  An
-// "absent" answer may come from a stale L1 line; callers that act on it (creation) confirm
+// Log index of child `h` of the node with parent key `pkey`, if it heads a run; else SLOT_NONE.
+// An "absent" answer may come from a stale L1 line; callers that act on it (creation) confirm
 // with the CAS in head_publish.  coherent = read past L1 from the start.
-__device__ __forceinline__ unsigned long long head_find(const Head *tab, int tab_log2, uint64_t h,
-                                                        uint64_t pkey, bool coherent = false)
+__device__ __forceinline__ uint32_t head_find(const Head *tab, int tab_log2, uint64_t h, uint32_t pkey,
+                                              bool coherent = false)
 {
     const uint32_t m = (1u << tab_log2) - 1;
     uint32_t s = slot_of(h, pkey, tab_log2);
     for (uint32_t probe = 0; probe <= m; probe++) {
-        const Head *e = tab + s;
         uint64_t a, b;
-        unsigned long long run;
-        if (coherent) ld_head_cg(e, a, b, run);
-        else ld_head(e, a, b, run);
-        for (;;) {
-            if (b == 0) return 0;                               // empty slot: not there
-            if (a == h && b == pkey) {
-                if (run) return run;
-                ld_head_cg(e, a, b, run);                       // publisher sits between CAS and store
-                continue;
-            }
-            break;                                              // another key: next slot
-        }
+        if (coherent) ld_head_cg(tab + s, a, b);
+        else ld_head(tab + s, a, b);
+        if (b == 0) return SLOT_NONE;                           // empty slot: not there
+        if (a == h && (uint32_t)(b >> 32) == pkey) return (uint32_t)b;
         s = (s + 1) & m;
     }
-    return 0;
+    return SLOT_NONE;
 }
 
-// Publish a run under (h, pkey).  True when this call published it; false when that child
-// exists already (someone else created it first) or the table is full.
-__device__ __forceinline__ bool head_publish(Head *tab, int tab_log2, uint64_t h, uint64_t pkey,
-                                             unsigned long long run)
+// Enter the run starting at log index idx under (h, pkey).  Returns idx when this call entered
+// it; the log index of the existing run when that child exists already (someone else created
+// it first); SLOT_NONE if the table is full.
+__device__ __forceinline__ uint32_t head_publish(Head *tab, int tab_log2, uint64_t h, uint32_t pkey,
+                                                 uint32_t idx)
 {
     const uint32_t m = (1u << tab_log2) - 1;
+    const uint64_t pk = ((uint64_t)pkey << 32) | idx;
     uint32_t s = slot_of(h, pkey, tab_log2);
     for (uint32_t probe = 0; probe <= m; probe++) {
         Head *e = tab + s;
         uint64_t a, b;
-        unsigned long long r;
-        ld_head(e, a, b, r);
-        for (;;) {
-            if (b == 0) {
-                cas128(e, h, pkey, a, b);
-                if (a == 0 && b == 0) {
-                    *(volatile unsigned long long *)&e->run = run;
-                    return true;
-                }
-                continue;                       // the slot was taken meanwhile: look at who took it
-            }
-            if (a == h && b == pkey) return false;
-            break;
-        }
+        ld_head(e, a, b);
+        if (b == 0) {
+            cas128(e, h, pk, a, b);
+            if (a == 0 && b == 0) return idx;
+        }                                       // else (a, b) is what sits there now
+        if (a == h && (uint32_t)(b >> 32) == pkey) return (uint32_t)b;
         s = (s + 1) & m;
     }
-    return false;
+    return SLOT_NONE;
 }
 
 // ------------------------------------------------------------------ log allocation
@@ -186,13 +176,11 @@ __device__ __forceinline__ uint32_t alloc_block_size(uint32_t log_cap)
 }
 
 // warp-uniform: every lane passes the same arguments and receives the same result
-__device__ __forceinline__ uint32_t warp_alloc(const TrieRef &t, WarpAlloc &wa, uint32_t L, int lane,
-                                               bool &from_block)
+__device__ __forceinline__ uint32_t warp_alloc(const TrieRef &t, WarpAlloc &wa, uint32_t L, int lane)
 {
     if (L <= wa.end - wa.cur) {
         const uint32_t base = wa.cur;
         wa.cur += L;
-        from_block = true;
         return base;
     }
     const uint32_t blk = alloc_block_size(t.log_cap);
@@ -200,7 +188,6 @@ __device__ __forceinline__ uint32_t warp_alloc(const TrieRef &t, WarpAlloc &wa, 
     unsigned long long b = 0;
     if (lane == 0) b = atomicAdd(&t.dev->log_count, (unsigned long long)take);
     b = __shfl_sync(FULLW, b, 0);
-    from_block = false;
     if (b + L > (unsigned long long)t.log_cap) {
         if (lane == 0) atomicOr(&t.dev->status, B200R_S_TABLE_FULL);
         return SLOT_NONE;
@@ -210,7 +197,6 @@ __device__ __forceinline__ uint32_t warp_alloc(const TrieRef &t, WarpAlloc &wa, 
         if (e > (unsigned long long)t.log_cap) e = t.log_cap;
         wa.cur = (uint32_t)b + L;
         wa.end = (uint32_t)e;
-        from_block = true;
     }
     return (uint32_t)b;
 }
@@ -251,18 +237,16 @@ __device__ __forceinline__ int leading_ones(unsigned bal)
 }
 
 // One warp walks request i down the trie, 32 depths (one window) per step.
-//   A  while the last resolved node sits at log index pidx inside a run that extends to pend,
-//      the next nodes can only be the records behind it: lanes compare the chunk hashes of
-//      records pidx+1+k with their own chunks (coalesced 32-byte loads); the leading matches
-//      are resolved.
-//   B  at the first mismatch (or at the end of a run) the child, if it exists, heads another
-//      run: one lane probes the hash table with (pidx, chunk hash).  A hit re-bases A on that
-//      run (the head's own record is validated by the next A step).
+//   B  the child of the last resolved node, if it exists and is not the record right behind
+//      it, heads a run: one lane probes the hash table with (parent index, chunk hash).
+//   A  from a known log position the next nodes can only be consecutive records: lanes read
+//      records base+k (coalesced 32-byte loads; the first one tells how long the run is)
+//      and compare their chunk hashes with their own chunks; the leading matches are resolved.
+//      A mismatch or the end of the run sends the walk back to B.
 //   absent  no record and no head: by prefix closure nothing deeper exists either.
-//      W_CLAIM / W_INSERT create the rest of the path as ONE run (records written first,
-//      device-scope fence, then the head is published with a 128-bit CAS).  Losing that race
-//      to another request of the batch gives the records back and walks the request again,
-//      now through the winner's run.
+//      W_CLAIM / W_INSERT append the rest of the path as ONE run and enter its head in the
+//      table with a 128-bit CAS.  If another request of the batch entered that child first, the
+//      walk simply goes on through the winner's run (the records just written stay unused).
 template <int MODE>
 __device__ __forceinline__ void walk_request(const WalkArgs &a, int i, int lane, WarpAlloc &wa)
 {
@@ -278,11 +262,10 @@ __device__ __forceinline__ void walk_request(const WalkArgs &a, int i, int lane,
         if (lane == 0 && !(t.dev->root_mask & bit)) atomicOr((unsigned long long *)&t.dev->root_mask, bit);
     }
     const unsigned long long mine = a.tag | (unsigned long long)(~(unsigned)i);
-    bool lost = false;                    // lost a creation race: probe the table past L1 from now on
-
-restart:
-    uint32_t pidx = ROOT_IDX, pend = 0;   // last resolved node is log[pidx]; its run ends at pend
-    bool tryA = false, afterB = false;
+    uint32_t pidx = ROOT_IDX;             // last resolved node
+    uint32_t base = 0, room = 0;          // A: candidates start at log[base]; room = records of the
+    bool have_base = false;               //    run from base on (0 = not known yet)
+    bool lost = false;                    // lost a creation race: probe the table past L1
     int npre = 0;                         // leading nodes with mask & avail != 0 (lookup depth / claim dpre)
     bool allpre = true;
     uint64_t sel = a.avail;
@@ -296,42 +279,67 @@ restart:
         int r = 0;                        // lanes [0, r) of the window are resolved
         while (r < nvalid) {
             const int off = lane - r;
-            if (!tryA) {
-                // ---- B: does child h_r of node pidx head a run?
-                unsigned long long run = 0;
-                if (off == 0) run = head_find(t.tab, t.tab_log2, h, (uint64_t)pidx + 1, lost);
-                run = __shfl_sync(FULLW, run, r);
-                if (run == 0) break;                            // absent at depth w0 + r
-                pidx = (uint32_t)run - 1;                       // so that the head itself is pidx + 1
-                pend = (uint32_t)run + (uint32_t)(run >> 32);
-                tryA = true;
-                afterB = true;
-            }
-            // ---- A: records behind pidx
-            const uint32_t room = pend - pidx - 1;
-            uint32_t idx = 0;
-            uint64_t m = 0;
-            unsigned long long f = 0;
-            bool ok = false;
-            if (valid && off >= 0 && (uint32_t)off < room) {
-                uint64_t rh;
-                idx = pidx + 1 + (uint32_t)off;
-                ld_rec(t.log + idx, rh, m, f);
-                ok = (rh == h);
-            }
-            const int nres = leading_ones(__ballot_sync(FULLW, ok) >> r);
-            if (nres == 0) {
-                tryA = false;
-                if (afterB) {                                   // a head without its record: never
-                    if (lane == 0) atomicOr(&t.dev->status, B200R_S_INTERNAL);
-                    finished = true;
-                    break;
+            if (!have_base) {
+                // ---- B
+                uint32_t idx = SLOT_NONE;
+                if (off == 0) idx = head_find(t.tab, t.tab_log2, h, parent_key(pidx), lost);
+                idx = __shfl_sync(FULLW, idx, r);
+                if (idx == SLOT_NONE) {
+                    // ---- absent at depth w0 + r, and so is everything below it
+                    if (MODE == W_LOOKUP) { finished = true; break; }
+                    const int pos = w0 + r;
+                    const uint32_t L = (uint32_t)(C - pos);
+                    const uint32_t nb = warp_alloc(t, wa, L, lane);
+                    if (nb == SLOT_NONE) {
+                        if (MODE == W_CLAIM)
+                            for (int d2 = pos + lane; d2 < C; d2 += 32) a.slots[sp.b0 + d2] = SLOT_NONE;
+                        finished = true;
+                        break;
+                    }
+                    const uint64_t mask0 = MODE == W_INSERT ? bit : 0ULL;
+                    const unsigned long long first0 = MODE == W_CLAIM ? mine : 0ULL;
+                    for (int d2 = pos + lane; d2 < C; d2 += 32) {
+                        const uint32_t x = nb + (uint32_t)(d2 - pos);
+                        st_rec(t.log + x, hs[d2], mask0, first0, (uint64_t)(C - d2));
+                        if (MODE == W_CLAIM) a.slots[sp.b0 + d2] = x;
+                    }
+                    uint32_t got = 0;
+                    if (off == 0) got = head_publish(t.tab, t.tab_log2, h, parent_key(pidx), nb);
+                    got = __shfl_sync(FULLW, got, r);
+                    if (got == nb) { finished = true; break; }          // the path is complete
+                    if (got == SLOT_NONE) {
+                        if (lane == 0) atomicOr(&t.dev->status, B200R_S_TABLE_FULL);
+                        finished = true;
+                        break;
+                    }
+                    lost = true;                                        // walk on through the winner's run
+                    idx = got;
                 }
-                continue;                                       // end of run / mismatch: probe the table
+                base = idx;
+                room = 0;
+                have_base = true;
             }
-            afterB = false;
-            pidx += (uint32_t)nres;
-            if (r + nres < 32) tryA = false;                    // the run ended or diverged inside the window
+            // ---- A
+            uint32_t idx = base + (uint32_t)off;
+            uint64_t rh = 0, m = 0, rem = 0;
+            unsigned long long f = 0;
+            const bool rd = valid && off >= 0 && (room ? (uint32_t)off < room : idx < t.log_cap);
+            if (rd) ld_rec(t.log + idx, rh, m, f, rem);
+            if (room == 0) {                                    // run length from its first record
+                if (off == 0) while (rem == 0) ld_rec_cg(t.log + idx, rh, m, f, rem);
+                room = (uint32_t)__shfl_sync(FULLW, rem, r);
+            }
+            const bool in = valid && off >= 0 && (uint32_t)off < room;
+            if (in) while (rem == 0) ld_rec_cg(t.log + idx, rh, m, f, rem);   // published, not yet visible
+            const int nres = leading_ones(__ballot_sync(FULLW, in && rh == h) >> r);
+            if (nres == 0) {                                    // a head always matches itself
+                if (lane == 0) atomicOr(&t.dev->status, B200R_S_INTERNAL);
+                finished = true;
+                break;
+            }
+            pidx = base + (uint32_t)nres - 1;
+            if (r + nres < 32 || (uint32_t)nres == room) have_base = false;     // diverged, or the run ended
+            else { base += (uint32_t)nres; room -= (uint32_t)nres; }            // next window, same run
             // ---- lanes [r, r + nres) hold resolved nodes
             const bool res = off >= 0 && off < nres;
             const bool use = res && (m & a.avail);
@@ -360,47 +368,6 @@ restart:
                 }
             }
             r += nres;
-        }
-        if (finished || r >= nvalid) continue;          // window done (or lookup ended)
-
-        // ---- depth w0 + r is absent, and so is everything below it
-        finished = true;
-        if (MODE == W_LOOKUP) break;
-        const int pos = w0 + r;
-        const uint32_t L = (uint32_t)(C - pos);
-        bool from_block = false;
-        const uint32_t base = warp_alloc(t, wa, L, lane, from_block);
-        if (base == SLOT_NONE) {
-            if (MODE == W_CLAIM)
-                for (int d2 = pos + lane; d2 < C; d2 += 32) a.slots[sp.b0 + d2] = SLOT_NONE;
-            break;
-        }
-        const uint64_t mask0 = MODE == W_INSERT ? bit : 0ULL;
-        const unsigned long long first0 = MODE == W_CLAIM ? mine : 0ULL;
-        if (valid && lane >= r) {
-            const uint32_t x = base + (uint32_t)(lane - r);
-            st_rec(t.log + x, h, mask0, first0);
-            if (MODE == W_CLAIM) a.slots[sp.b0 + d] = x;
-        }
-        for (int d2 = w0 + 32 + lane; d2 < C; d2 += 32) {
-            const uint32_t x = base + (uint32_t)(d2 - pos);
-            st_rec(t.log + x, hs[d2], mask0, first0);
-            if (MODE == W_CLAIM) a.slots[sp.b0 + d2] = x;
-        }
-        const uint64_t hh = __shfl_sync(FULLW, h, r);
-        __syncwarp();
-        int won = 0;
-        if (lane == 0) {
-            __threadfence();                            // records before the head
-            won = head_publish(t.tab, t.tab_log2, hh, (uint64_t)pidx + 1, ((unsigned long long)L << 32) | base) ? 1 : 0;
-        }
-        won = __shfl_sync(FULLW, won, 0);
-        if (!won) {
-            // another request of the batch created this child first: give the records back and
-            // walk again (rare; everything done so far is idempotent)
-            if (from_block) wa.cur -= L;
-            lost = true;
-            goto restart;
         }
     }
     if (lane == 0) {
