@@ -499,7 +499,7 @@ __global__ void k_count_nodes(const Head *__restrict__ tab, const Rec *__restric
     for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < cap;
          s += (int64_t)gridDim.x * blockDim.x) {
         const Head e = tab[s];
-        if (e.pk) mine += log[(uint32_t)e.pk].rem;
+        if (e.pk) mine += (uint32_t)log[(uint32_t)e.pk].rc;
     }
     for (int o = 16; o; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
     if ((threadIdx.x & 31) == 0 && mine) atomicAdd(&dev->num_nodes, mine);
@@ -516,7 +516,7 @@ __global__ void k_dump(const Head *__restrict__ tab, const Rec *__restrict__ log
         const Head e = tab[s];
         if (!e.pk) continue;
         const uint32_t idx = (uint32_t)e.pk;
-        const uint32_t len = (uint32_t)log[idx].rem;
+        const uint32_t len = (uint32_t)log[idx].rc;
         const unsigned long long at = atomicAdd(&dev->dump_count, (unsigned long long)len);
         for (uint32_t j = 0; j < len; j++) {
             if ((int64_t)(at + j) >= max_nodes) break;
@@ -542,7 +542,8 @@ __global__ void k_restore(TrieRef t, const uint64_t *__restrict__ ent, int64_t c
         atomicOr(&t.dev->status, B200R_S_TABLE_FULL);
         return;
     }
-    st_rec(t.log + idx, h, m, 0, rem);
+    st_rec_key(t.log + idx, h, rem);
+    t.log[idx].mask = m;
     atomicMax(&t.dev->log_count, (unsigned long long)idx + 1);
     if ((e1 >> 63) && head_publish(t.tab, t.tab_log2, h, parent_key(parent), idx) != idx)
         atomicOr(&t.dev->status, B200R_S_INTERNAL);

@@ -25,13 +25,20 @@ namespace b200r {
 
 struct __align__(32) Rec {       // one trie node
     uint64_t h;                  // chunk hash of the edge parent -> node
-    uint64_t mask;               // endpoint set
-    unsigned long long first;    // (epoch << 32) | ~request: first request of batch `epoch`
-                                 // that touched the node (merged with atomicMax)
-    uint64_t rem;                // records from this one to the end of its run (>= 1); 0 = the
-                                 // record has not been written (yet): the log starts zeroed and
-                                 // every record is written exactly once, by one 32-byte store
+    uint64_t rc;                 // low 32 bits: records from this one to the end of its run (>= 1);
+                                 // high 32 bits: check word of h (rec_chk)
+    uint64_t mask;               // endpoint set                     } only ever changed
+    unsigned long long first;    // (epoch << 32) | ~request: first   } by atomics
+                                 // request of batch `epoch` that touched the node (atomicMax); 0 = none
 };
+// Publication needs no fence.  The log starts zeroed; a record is written exactly once: {h, rc}
+// by one 16-byte store, while mask and first start at zero and are only ever updated by
+// atomics (the creator's own first-toucher mark included), so nothing a reader does can be
+// overwritten by a store that lands late.  A run becomes reachable when its head entry appears
+// in the table (one 128-bit CAS carrying key and log index); its records may become visible a
+// little later: a reader that finds a record of a published run with rc == 0, or whose check
+// word does not fit its h (the two words of the store seen at different moments), re-reads it
+// past L1 until it is whole.
 
 struct __align__(16) Head {      // hash-table entry: the run that starts at child `h` of `parent`
     uint64_t h;                  // chunk hash of the run's first node
@@ -67,28 +74,32 @@ constexpr unsigned FULLW = 0xffffffffu;
 __device__ __forceinline__ uint32_t parent_key(uint32_t pidx) { return pidx + 2u; }   // ROOT_IDX -> 1
 
 // ------------------------------------------------------------------ memory ops
-// Publication needs no fence.  A run becomes reachable when its head entry appears in the
-// table (one 128-bit CAS carrying key and log index); its records may become visible a
-// little later, so a reader that finds an in-range record still unwritten (rem == 0) re-reads
-// it past L1 until it is there.  Records are immutable in h / rem once written.
+__device__ __forceinline__ uint32_t rec_chk(uint64_t h)
+{
+    return ((uint32_t)h * 0x9E3779B1u) ^ ((uint32_t)(h >> 32) * 0x85EBCA77u) ^ 0x5bd1e995u;
+}
+__device__ __forceinline__ bool rec_whole(uint64_t h, uint64_t rc)
+{
+    return (uint32_t)rc != 0 && (uint32_t)(rc >> 32) == rec_chk(h);
+}
 __device__ __forceinline__ void ld_rec(const Rec *r, uint64_t &h, uint64_t &mask, unsigned long long &first,
-                                       uint64_t &rem)
-{   // one 32-byte load (LDG.256).  L1 may serve it: masks only change in kernels that do not
-    // read them through this path, and a stale `first` only costs a redundant atomicMax.
+                                       uint64_t &rc)
+{   // one 32-byte load (LDG.256).  L1 may serve it: h / rc never change once written, masks only
+    // change in kernels that do not read them through this path, and a stale `first` only
+    // costs a redundant atomicMax.
     asm volatile("ld.global.ca.v4.u64 {%0, %1, %2, %3}, [%4];"
-                 : "=l"(h), "=l"(mask), "=l"(first), "=l"(rem) : "l"(r) : "memory");
+                 : "=l"(h), "=l"(rc), "=l"(mask), "=l"(first) : "l"(r) : "memory");
 }
 __device__ __forceinline__ void ld_rec_cg(const Rec *r, uint64_t &h, uint64_t &mask, unsigned long long &first,
-                                          uint64_t &rem)
+                                          uint64_t &rc)
 {
     asm volatile("ld.global.cg.v4.u64 {%0, %1, %2, %3}, [%4];"
-                 : "=l"(h), "=l"(mask), "=l"(first), "=l"(rem) : "l"(r) : "memory");
+                 : "=l"(h), "=l"(rc), "=l"(mask), "=l"(first) : "l"(r) : "memory");
 }
-__device__ __forceinline__ void st_rec(Rec *r, uint64_t h, uint64_t mask, unsigned long long first,
-                                       uint64_t rem)
-{
-    asm volatile("st.global.v4.u64 [%0], {%1, %2, %3, %4};"
-                 :: "l"(r), "l"(h), "l"(mask), "l"(first), "l"(rem) : "memory");
+__device__ __forceinline__ void st_rec_key(Rec *r, uint64_t h, uint32_t rem)
+{   // the immutable half of a record
+    const uint64_t rc = (uint64_t)rem | ((uint64_t)rec_chk(h) << 32);
+    asm volatile("st.global.v2.u64 [%0], {%1, %2};" :: "l"(r), "l"(h), "l"(rc) : "memory");
 }
 __device__ __forceinline__ void ld_head(const Head *e, uint64_t &a, uint64_t &b)
 {
@@ -98,8 +109,24 @@ __device__ __forceinline__ void ld_head_cg(const Head *e, uint64_t &a, uint64_t 
 {
     asm volatile("ld.global.cg.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(e) : "memory");
 }
+template <bool RELEASE = false>
 __device__ __forceinline__ void cas128(Head *e, uint64_t n1, uint64_t n2, uint64_t &o1, uint64_t &o2)
-{   // compare the entry with (0,0), swap in (n1,n2); returns the previous entry
+{   // compare the entry with (0,0), swap in (n1,n2); returns the previous entry.  RELEASE: every
+    // write that happens-before this thread's CAS is visible to whoever sees the new entry.
+    if (RELEASE) {
+        asm volatile(
+            "{\n\t"
+            ".reg .b128 cmp, nw, old;\n\t"
+            "mov.b128 cmp, {%2, %3};\n\t"
+            "mov.b128 nw, {%4, %5};\n\t"
+            "atom.global.release.gpu.cas.b128 old, [%6], cmp, nw;\n\t"
+            "mov.b128 {%0, %1}, old;\n\t"
+            "}\n"
+            : "=l"(o1), "=l"(o2)
+            : "l"(0ULL), "l"(0ULL), "l"(n1), "l"(n2), "l"(e)
+            : "memory");
+        return;
+    }
     asm volatile(
         "{\n\t"
         ".reg .b128 cmp, nw, old;\n\t"
@@ -142,6 +169,7 @@ __device__ __forceinline__ uint32_t head_find(const Head *tab, int tab_log2, uin
 // Enter the run starting at log index idx under (h, pkey).  Returns idx when this call entered
 // it; the log index of the existing run when that child exists already (someone else created
 // it first); SLOT_NONE if the table is full.
+template <bool RELEASE = false>
 __device__ __forceinline__ uint32_t head_publish(Head *tab, int tab_log2, uint64_t h, uint32_t pkey,
                                                  uint32_t idx)
 {
@@ -153,7 +181,7 @@ __device__ __forceinline__ uint32_t head_publish(Head *tab, int tab_log2, uint64
         uint64_t a, b;
         ld_head(e, a, b);
         if (b == 0) {
-            cas128(e, h, pk, a, b);
+            cas128<RELEASE>(e, h, pk, a, b);
             if (a == 0 && b == 0) return idx;
         }                                       // else (a, b) is what sits there now
         if (a == h && (uint32_t)(b >> 32) == pkey) return (uint32_t)b;
@@ -292,16 +320,23 @@ __device__ __forceinline__ void walk_request(const WalkArgs &a, int i, int lane,
                     const uint32_t nb = warp_alloc(t, wa, L, lane);
                     if (nb == SLOT_NONE) {
                         if (MODE == W_CLAIM)
-                            for (int d2 = pos + lane; d2 < C; d2 += 32) a.slots[sp.b0 + d2] = SLOT_NONE;
+                            for (int d2 = d; d2 < C; d2 += 32)
+                                if (d2 >= pos) a.slots[sp.b0 + d2] = SLOT_NONE;
                         finished = true;
                         break;
                     }
-                    const uint64_t mask0 = MODE == W_INSERT ? bit : 0ULL;
-                    const unsigned long long first0 = MODE == W_CLAIM ? mine : 0ULL;
-                    for (int d2 = pos + lane; d2 < C; d2 += 32) {
+                    // every lane keeps to its own depths d, d + 32, ...: a slot word is only ever
+                    // written by one thread, so a later correction (lost race) lands in order
+                    for (int d2 = d; d2 < C; d2 += 32) {
+                        if (d2 < pos) continue;
                         const uint32_t x = nb + (uint32_t)(d2 - pos);
-                        st_rec(t.log + x, hs[d2], mask0, first0, (uint64_t)(C - d2));
-                        if (MODE == W_CLAIM) a.slots[sp.b0 + d2] = x;
+                        st_rec_key(t.log + x, d2 == d ? h : hs[d2], (uint32_t)(C - d2));
+                        if (MODE == W_CLAIM) {
+                            atomicMax(&t.log[x].first, mine);
+                            a.slots[sp.b0 + d2] = x;
+                        } else {
+                            atomicOr((unsigned long long *)&t.log[x].mask, bit);
+                        }
                     }
                     uint32_t got = 0;
                     if (off == 0) got = head_publish(t.tab, t.tab_log2, h, parent_key(pidx), nb);
@@ -321,21 +356,27 @@ __device__ __forceinline__ void walk_request(const WalkArgs &a, int i, int lane,
             }
             // ---- A
             uint32_t idx = base + (uint32_t)off;
-            uint64_t rh = 0, m = 0, rem = 0;
+            uint64_t rh = 0, m = 0, rc = 0;
             unsigned long long f = 0;
+            const uint32_t room0 = room;
             const bool rd = valid && off >= 0 && (room ? (uint32_t)off < room : idx < t.log_cap);
-            if (rd) ld_rec(t.log + idx, rh, m, f, rem);
+            if (rd) ld_rec(t.log + idx, rh, m, f, rc);
             if (room == 0) {                                    // run length from its first record
-                if (off == 0) while (rem == 0) ld_rec_cg(t.log + idx, rh, m, f, rem);
-                room = (uint32_t)__shfl_sync(FULLW, rem, r);
+                if (off == 0) while (!rec_whole(rh, rc)) ld_rec_cg(t.log + idx, rh, m, f, rc);
+                room = (uint32_t)__shfl_sync(FULLW, rc, r);
             }
             const bool in = valid && off >= 0 && (uint32_t)off < room;
-            if (in) while (rem == 0) ld_rec_cg(t.log + idx, rh, m, f, rem);   // published, not yet visible
+            if (in) while (!rec_whole(rh, rc)) ld_rec_cg(t.log + idx, rh, m, f, rc);   // published, not yet visible
+            const bool fresh = room0 == 0;                      // base came from the table just now
             const int nres = leading_ones(__ballot_sync(FULLW, in && rh == h) >> r);
-            if (nres == 0) {                                    // a head always matches itself
-                if (lane == 0) atomicOr(&t.dev->status, B200R_S_INTERNAL);
-                finished = true;
-                break;
+            if (nres == 0) {
+                if (fresh) {                                    // a head always matches itself
+                    if (lane == 0) atomicOr(&t.dev->status, B200R_S_INTERNAL);
+                    finished = true;
+                    break;
+                }
+                have_base = false;                              // the path leaves the run right here
+                continue;
             }
             pidx = base + (uint32_t)nres - 1;
             if (r + nres < 32 || (uint32_t)nres == room) have_base = false;     // diverged, or the run ended
