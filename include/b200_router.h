@@ -205,6 +205,30 @@ int b200r_prefix_route_stage(b200r_trie *t, int64_t n, int64_t max_chunks, uint3
                              int32_t *d_endpoint, int32_t *d_match_depth,
                              uint64_t *d_matched_mask, void *d_scratch, size_t scratch_bytes,
                              void *stream);
+/* The same three steps -- prep | hash | route -- pipelined over consecutive batches by the
+ * library itself: prep of batch b+2 and hash of batch b+1 run on two streams the pipeline
+ * owns while route of batch b runs on the caller's `stream`; route stages stay in call order,
+ * so results are those of sequential routing.  The caller rotates `depth` scratch buffers
+ * (call i uses buffer i mod depth; the pipeline makes call i+depth wait for call i).
+ * inputs_on_prep_stream = 0: the inputs were produced on `stream` (the prep step waits for
+ * it); 1: they are complete, or were copied on b200r_pipe_prep_stream(), e.g. a host-to-device
+ * copy that should itself overlap the routing of earlier batches.  (The reference routes one
+ * request at a time, request.py:252-257; there is no counterpart.) */
+typedef struct b200r_pipe b200r_pipe;
+int b200r_pipe_create(b200r_trie *t, int32_t depth, b200r_pipe **out);
+int b200r_pipe_destroy(b200r_pipe *p);
+void *b200r_pipe_prep_stream(b200r_pipe *p);
+/* Optional, before copying the next call's inputs on the prep stream into memory that an
+ * earlier call's inputs occupied: makes the prep stream wait until the call that used this
+ * rotation slot `depth` calls ago has finished (it no longer reads its inputs then). */
+int b200r_pipe_begin(b200r_pipe *p);
+/* host-to-device copy of inputs on the prep stream (pinned host memory for a true async copy) */
+int b200r_pipe_copy_h2d(b200r_pipe *p, void *d_dst, const void *h_src, size_t bytes);
+int b200r_pipe_route(b200r_pipe *p, const uint8_t *d_bytes, const int64_t *d_starts,
+                     const int32_t *d_lens, const int32_t *d_nchars, int64_t n, int64_t max_chunks,
+                     uint32_t flags, uint64_t avail_mask, uint64_t seed, uint64_t seq0,
+                     int32_t *d_endpoint, int32_t *d_match_depth, uint64_t *d_matched_mask,
+                     void *d_scratch, size_t scratch_bytes, int32_t inputs_on_prep_stream, void *stream);
 /* The route stage from chunk hashes the caller already holds (CSR exactly as b200r_xxh64_chunks
  * writes it): claim / select / commit, same results as b200r_prefix_route_batch on the prompts
  * those hashes came from.  Used where hashes of several sources are merged before routing
@@ -295,6 +319,10 @@ int b200r_ring_lookup_batch(b200r_ring *r, const uint8_t *d_bytes, const int64_t
  * b200r_launch_count: kernels enqueued by this library
  * since load (process-wide).
  * ---------------------------------------------------------------------- */
+/* tuning switch of the route stage's claim step: 0 = choose per batch (a thread per request
+ * while prompts average at most 64 chunks, a warp per request beyond), 1 = always a thread, 2 =
+ * always a warp; identical results */
+int b200r_set_claim_mode(int mode);
 #define B200R_PROF_SLOTS 13
 int b200r_prof_enable(int on);
 int b200r_prof_read(float *ms_out, long long *count_out, int nslots);

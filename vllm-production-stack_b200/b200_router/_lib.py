@@ -47,6 +47,13 @@ SIGNATURES = {
                                            _sz, _vp]),
     "b200r_prefix_route_hashes": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _u64, _u64, _u64, _vp, _vp, _vp, _vp,
                                             _sz, _vp]),
+    "b200r_pipe_create": (C.c_int, [_vp, _i32, C.POINTER(_vp)]),
+    "b200r_pipe_destroy": (C.c_int, [_vp]),
+    "b200r_pipe_prep_stream": (_vp, [_vp]),
+    "b200r_pipe_begin": (C.c_int, [_vp]),
+    "b200r_pipe_copy_h2d": (C.c_int, [_vp, _vp, _vp, _sz]),
+    "b200r_pipe_route": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _u32, _u64, _u64, _u64, _vp, _vp, _vp,
+                                   _vp, _sz, _i32, _vp]),
     "b200r_pick": (_u32, [_u64, _u64, _u32]),
     "b200r_trie_dump": (C.c_int, [_vp, _vp, _i64, C.POINTER(_i64), C.POINTER(_u64), _vp]),
     "b200r_trie_restore": (C.c_int, [_vp, _vp, _i64, _u64, _vp]),
@@ -55,6 +62,7 @@ SIGNATURES = {
                                   _u32, _vp, _vp, _sz, _vp]),
     "b200r_part_route": (C.c_int, [_vp, _u64, _u64, _vp, _vp, _i32, _i32, _i64, _i64, _u32, _vp, _vp]),
     "b200r_part_finish": (C.c_int, [_vp, _i64, _vp, _i32, _i32, _i64, _i64, _u32, _vp, _vp, _vp, _vp, _vp]),
+    "b200r_set_claim_mode": (C.c_int, [C.c_int]),
     "b200r_prof_enable": (C.c_int, [C.c_int]),
     "b200r_prof_read": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_longlong), C.c_int]),
     "b200r_launch_count": (C.c_longlong, []),

@@ -322,14 +322,24 @@ class RoutePipeline:
         self.trie = trie
         self.depth = depth
         self.device = trie.device
-        self.prep_stream = torch.cuda.Stream(device=self.device)
-        self.hash_stream = torch.cuda.Stream(device=self.device)
+        self._p = C.c_void_p()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().b200r_pipe_create(trie._h, depth, C.byref(self._p)))
         self._scratch = [None] * depth
-        self._done = [None] * depth
-        self._prepped = [torch.cuda.Event() for _ in range(depth)]
-        self._hashed = [torch.cuda.Event() for _ in range(depth)]
+        self._keep = [None] * depth
         self._outs = [None] * (depth + 1)
         self._i = 0
+
+    def close(self):
+        if getattr(self, "_p", None) and self._p.value:
+            _lib.lib().b200r_pipe_destroy(self._p)
+            self._p = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
     def _scratch_for(self, k, nbytes):
         t = self._scratch[k]
@@ -354,57 +364,58 @@ class RoutePipeline:
                                  torch.empty(max(n, 1), dtype=torch.int64, device=self.device))
         return o
 
+    def _copy_on_prep_stream(self, p: PackedPrompts) -> PackedPrompts:
+        L = _lib.lib()
+
+        def mv(t):
+            if t is None:
+                return None
+            d = torch.empty(t.shape, dtype=t.dtype, device=self.device)
+            _lib.check(L.b200r_pipe_copy_h2d(self._p, d.data_ptr(), t.data_ptr(),
+                                             t.numel() * t.element_size()))
+            return d
+        return PackedPrompts(mv(p.bytes), mv(p.starts), mv(p.lens), mv(p.nchars), p.n, p.max_chunks,
+                             p.all_ascii, p.payload_bytes)
+
     def route(self, p: PackedPrompts, avail_mask: int, seed: int, seq0: int, out=None,
               inputs_ready: bool = False):
         """Returns device tensors (endpoint, depth, matched), valid in stream order on
         the caller's current stream.  Unless `out` is given they live in a ring of
-        depth+1 buffers: consume them before depth+1 further batches are submitted."""
+        depth+1 buffers: consume them before depth+1 further batches are submitted.
+        One native call per batch (b200r_pipe_route)."""
         L = _lib.lib()
-        k = self._i % self.depth
-        o = out if out is not None else self._out_for(self._i % (self.depth + 1), p.n)
-        self._i += 1
         n = p.n
-        cur = torch.cuda.current_stream(self.device)
-        ps, hs = self.prep_stream, self.hash_stream
+        if n == 0:
+            e = torch.empty(0, dtype=torch.int32, device=self.device)
+            return e, e.clone(), torch.empty(0, dtype=torch.int64, device=self.device)
+        k = self._i % self.depth
+        o = out if out is not None else self._out_for(self._i % (self.depth + 1), n)
+        self._i += 1
         flags = _lib.F_ALL_ASCII if p.all_ascii else 0
+        sc = self._scratch[k]
         need = L.b200r_prefix_route_scratch_bytes(n, p.max_chunks, flags)
-        sc = self._scratch_for(k, need)
-        on_host = p.bytes.device.type == "cpu"
-        if self._done[k] is not None:
-            ps.wait_event(self._done[k])          # scratch k is free again
-        if not on_host and not inputs_ready:
-            ps.wait_stream(cur)
-        with torch.cuda.device(self.device):
-            with torch.cuda.stream(ps):
-                if on_host:
-                    p = p.to(self.device, non_blocking=True)
-                _lib.check(L.b200r_prefix_hash_stage(
-                    self.trie._h, _ptr(p.bytes), _ptr(p.starts), _ptr(p.lens), _ptr(p.nchars), n,
-                    p.max_chunks, flags | _lib.F_PREP_ONLY, _ptr(sc), sc.numel(),
-                    C.c_void_p(ps.cuda_stream)))
-                self._prepped[k].record(ps)
-            hs.wait_event(self._prepped[k])
-            with torch.cuda.stream(hs):
-                _lib.check(L.b200r_prefix_hash_stage(
-                    self.trie._h, _ptr(p.bytes), _ptr(p.starts), _ptr(p.lens), _ptr(p.nchars), n,
-                    p.max_chunks, flags | _lib.F_PREP_DONE, _ptr(sc), sc.numel(),
-                    C.c_void_p(hs.cuda_stream)))
-                self._hashed[k].record(hs)
-                if on_host:
-                    p.bytes.record_stream(hs)     # allocated on the prep stream, read on this one
-                    p.starts.record_stream(hs)
-                    p.lens.record_stream(hs)
-                    if p.nchars is not None:
-                        p.nchars.record_stream(hs)
-            cur.wait_event(self._hashed[k])
-            ep, depth, matched = o
-            _lib.check(L.b200r_prefix_route_stage(
-                self.trie._h, n, p.max_chunks, flags, avail_mask & M64, seed & M64, seq0 & M64,
-                _ptr(ep), _ptr(depth), _ptr(matched), _ptr(sc), sc.numel(),
-                C.c_void_p(cur.cuda_stream)))
-        done = torch.cuda.Event()
-        done.record(cur)
-        self._done[k] = done
+        if sc is None or sc.numel() < need:
+            sc = self._scratch_for(k, need)
+        on_prep = inputs_ready
+        cur = torch.cuda.current_stream(self.device)
+        if p.bytes.device.type == "cpu":
+            # copy on the prep stream, after the call that used this rotation slot has finished;
+            # its device copy of the inputs is released only now, so the allocator can hand the
+            # memory to this copy without overtaking a kernel that still reads it
+            _lib.check(L.b200r_pipe_begin(self._p))
+            self._keep[k] = None
+            with torch.cuda.device(self.device):
+                p = self._copy_on_prep_stream(p)
+            self._keep[k] = p
+            on_prep = True
+        ep, depth, matched = o
+        rc = L.b200r_pipe_route(self._p, p.bytes.data_ptr(), p.starts.data_ptr(), p.lens.data_ptr(),
+                                None if p.nchars is None else p.nchars.data_ptr(), n, p.max_chunks,
+                                flags, avail_mask & M64, seed & M64, seq0 & M64, ep.data_ptr(),
+                                depth.data_ptr(), matched.data_ptr(), sc.data_ptr(), sc.numel(),
+                                1 if on_prep else 0, cur.cuda_stream)
+        if rc:
+            _lib.check(rc)
         return ep[:n], depth[:n], matched[:n]
 
     def check_status(self, count_nodes: bool = False):

@@ -47,6 +47,7 @@ int cuda_fail(cudaError_t e, const char *what)
 }
 
 // ------------------------------------------------------------- profiling (internal.cuh)
+int g_claim_mode = 0;          // 0 auto, 1 thread per request, 2 warp per request (b200r_set_claim_mode)
 bool g_prof_on = false;
 std::vector<ProfSpan> g_spans;
 long long g_launches = 0;
@@ -735,7 +736,13 @@ int launch_route_core(b200r_trie *t, const RouteCore &rc, cudaStream_t st)
     const int nn = rc.n_dev ? 0 : (int)rc.n;
     const int tblocks = (int)((rc.n + 255) / 256);
     { ProfScope ps__(PK_CLAIM, st); g_launches += 1;
-    k_walk<W_CLAIM><<<walk_grid(rc.n), WARPS_PER_CTA * 32, 0, st>>>(a, nn, rc.n_dev);
+    if (rc.by_thread) {
+        int64_t blocks = (rc.n + 127) / 128;
+        if (blocks > 148 * 16) blocks = 148 * 16;
+        k_claim_thread<<<(int)(blocks < 1 ? 1 : blocks), 128, 0, st>>>(a, nn, rc.n_dev);
+    } else {
+        k_walk<W_CLAIM><<<walk_grid(rc.n), WARPS_PER_CTA * 32, 0, st>>>(a, nn, rc.n_dev);
+    }
     B200R_LAUNCH_CHECK("k_walk<claim>");
     }
     { ProfScope ps__(PK_SELECT, st); g_launches += 1;
@@ -764,6 +771,13 @@ extern "C" {
 int b200r_abi_version(void) { return B200R_ABI_VERSION; }
 const char *b200r_last_error(void) { return g_err; }
 uint32_t b200r_pick(uint64_t seed, uint64_t seq, uint32_t n) { return pick(seed, seq, n); }
+
+int b200r_set_claim_mode(int mode)
+{
+    if (mode < 0 || mode > 2) { set_error("b200r_set_claim_mode: 0 auto, 1 thread, 2 warp"); return B200R_E_INVALID; }
+    g_claim_mode = mode;
+    return B200R_OK;
+}
 
 int b200r_prof_enable(int on)
 {
@@ -1075,6 +1089,8 @@ static int route_from(b200r_trie *t, const uint64_t *hashes, const int32_t *chun
     rc.dpre = (int32_t *)(sc + p.off_dpre);
     rc.cand = (uint64_t *)(sc + p.off_cand);
     rc.endpoint = d_endpoint; rc.depth = d_match_depth; rc.matched = d_matched_mask;
+    // a thread per request while prompts are short on average, a warp per request beyond
+    rc.by_thread = g_claim_mode == 1 || (g_claim_mode == 0 && max_chunks <= n * CLAIM_THREAD_MAX_AVG_CHUNKS);
     return launch_route_core(t, rc, st);
 }
 
@@ -1128,6 +1144,116 @@ int b200r_prefix_route_batch(b200r_trie *t, const uint8_t *d_bytes, const int64_
     if (rc) return rc;
     return b200r_prefix_route_stage(t, n, max_chunks, flags, avail_mask, seed, seq0, d_endpoint,
                                     d_match_depth, d_matched_mask, d_scratch, scratch_bytes, stream);
+}
+
+// ---------------------------------------------------------------------------
+// The three steps of a routed batch (prep | hash | route) pipelined over consecutive batches
+// natively: stream and event handling in Python costs more host time per batch than the GPU
+// needs for the batch.
+struct b200r_pipe {
+    b200r_trie *t;
+    int depth;
+    long long calls;
+    cudaStream_t prep, hash;
+    cudaEvent_t prepped[8], hashed[8], done[8], inputs;
+    bool has_done[8];
+};
+
+int b200r_pipe_create(b200r_trie *t, int32_t depth, b200r_pipe **out)
+{
+    if (!t || !out || depth < 1 || depth > 8) { set_error("b200r_pipe_create: trie, 1 <= depth <= 8"); return B200R_E_INVALID; }
+    b200r_pipe *p = new b200r_pipe();
+    p->t = t; p->depth = depth; p->calls = 0;
+    B200R_CUDA(cudaStreamCreateWithFlags(&p->prep, cudaStreamNonBlocking));
+    B200R_CUDA(cudaStreamCreateWithFlags(&p->hash, cudaStreamNonBlocking));
+    B200R_CUDA(cudaEventCreateWithFlags(&p->inputs, cudaEventDisableTiming));
+    for (int k = 0; k < depth; k++) {
+        B200R_CUDA(cudaEventCreateWithFlags(&p->prepped[k], cudaEventDisableTiming));
+        B200R_CUDA(cudaEventCreateWithFlags(&p->hashed[k], cudaEventDisableTiming));
+        B200R_CUDA(cudaEventCreateWithFlags(&p->done[k], cudaEventDisableTiming));
+        p->has_done[k] = false;
+    }
+    *out = p;
+    return B200R_OK;
+}
+
+int b200r_pipe_destroy(b200r_pipe *p)
+{
+    if (!p) return B200R_OK;
+    cudaStreamSynchronize(p->prep); cudaStreamSynchronize(p->hash);
+    for (int k = 0; k < p->depth; k++) {
+        cudaEventDestroy(p->prepped[k]); cudaEventDestroy(p->hashed[k]); cudaEventDestroy(p->done[k]);
+    }
+    cudaEventDestroy(p->inputs);
+    cudaStreamDestroy(p->prep); cudaStreamDestroy(p->hash);
+    delete p;
+    return B200R_OK;
+}
+
+void *b200r_pipe_prep_stream(b200r_pipe *p) { return p ? (void *)p->prep : nullptr; }
+
+int b200r_pipe_copy_h2d(b200r_pipe *p, void *d_dst, const void *h_src, size_t bytes)
+{
+    if (!p || (bytes && (!d_dst || !h_src))) { set_error("b200r_pipe_copy_h2d: null pointer"); return B200R_E_INVALID; }
+    if (bytes) B200R_CUDA(cudaMemcpyAsync(d_dst, h_src, bytes, cudaMemcpyHostToDevice, p->prep));
+    return B200R_OK;
+}
+
+int b200r_pipe_begin(b200r_pipe *p)
+{
+    if (!p) { set_error("null pipeline"); return B200R_E_INVALID; }
+    const int k = (int)(p->calls % p->depth);
+    if (p->has_done[k]) {
+        B200R_CUDA(cudaStreamWaitEvent(p->prep, p->done[k], 0));
+        p->has_done[k] = false;               // waited for: b200r_pipe_route need not wait again
+    }
+    return B200R_OK;
+}
+
+int b200r_pipe_route(b200r_pipe *p, const uint8_t *d_bytes, const int64_t *d_starts,
+                     const int32_t *d_lens, const int32_t *d_nchars, int64_t n, int64_t max_chunks,
+                     uint32_t flags, uint64_t avail_mask, uint64_t seed, uint64_t seq0,
+                     int32_t *d_endpoint, int32_t *d_match_depth, uint64_t *d_matched_mask,
+                     void *d_scratch, size_t scratch_bytes, int32_t inputs_on_prep_stream, void *stream)
+{
+    if (!p) { set_error("null pipeline"); return B200R_E_INVALID; }
+    b200r_trie *t = p->t;
+    int rc = check_prompt_args(d_bytes, d_starts, d_lens, n, max_chunks, t->chunk_chars);
+    if (rc) return rc;
+    if (n == 0) return B200R_OK;
+    if (!d_endpoint || !d_match_depth || !d_matched_mask) { set_error("null output pointer"); return B200R_E_INVALID; }
+    const Plan pl = make_plan(n, max_chunks, flags, true);
+    if (!d_scratch || scratch_bytes < pl.total) {
+        set_error("scratch too small: need %zu bytes, got %zu", pl.total, scratch_bytes);
+        return B200R_E_SCRATCH;
+    }
+    cudaStream_t cur = (cudaStream_t)stream;
+    const int k = (int)(p->calls % p->depth);
+    p->calls++;
+    uint8_t *sc = (uint8_t *)d_scratch;
+    int32_t *chunk_base = (int32_t *)(sc + pl.off_chunk_base);
+    uint64_t *hashes = (uint64_t *)(sc + pl.off_hashes);
+    if (p->has_done[k]) B200R_CUDA(cudaStreamWaitEvent(p->prep, p->done[k], 0));   // scratch k is free again
+    if (!inputs_on_prep_stream) {
+        B200R_CUDA(cudaEventRecord(p->inputs, cur));
+        B200R_CUDA(cudaStreamWaitEvent(p->prep, p->inputs, 0));
+    }
+    rc = launch_hash(d_bytes, d_starts, d_lens, d_nchars, n, t->chunk_chars, flags, chunk_base, hashes,
+                     max_chunks, sc, pl, t->dev, p->prep, 1);
+    if (rc) return rc;
+    B200R_CUDA(cudaEventRecord(p->prepped[k], p->prep));
+    B200R_CUDA(cudaStreamWaitEvent(p->hash, p->prepped[k], 0));
+    rc = launch_hash(d_bytes, d_starts, d_lens, d_nchars, n, t->chunk_chars, flags, chunk_base, hashes,
+                     max_chunks, sc, pl, t->dev, p->hash, 2);
+    if (rc) return rc;
+    B200R_CUDA(cudaEventRecord(p->hashed[k], p->hash));
+    B200R_CUDA(cudaStreamWaitEvent(cur, p->hashed[k], 0));
+    rc = route_from(t, hashes, chunk_base, n, max_chunks, avail_mask, seed, seq0, d_endpoint,
+                    d_match_depth, d_matched_mask, sc, pl, cur);
+    if (rc) return rc;
+    B200R_CUDA(cudaEventRecord(p->done[k], cur));
+    p->has_done[k] = true;
+    return B200R_OK;
 }
 
 int b200r_trie_dump(b200r_trie *t, uint64_t *d_out, int64_t max_nodes, int64_t *count,

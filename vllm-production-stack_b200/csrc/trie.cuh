@@ -141,9 +141,12 @@ __device__ __forceinline__ void cas128(Head *e, uint64_t n1, uint64_t n2, uint64
 }
 
 __device__ __forceinline__ uint32_t slot_of(uint64_t h, uint32_t pkey, int tab_log2)
-{
-    const uint64_t x = (h ^ ((uint64_t)pkey << 32 | pkey)) * 0x9E3779B97F4A7C15ULL;
-    return (uint32_t)(x >> (64 - tab_log2));
+{   // 32-bit mixing (h is a hash already): three multiplies on the 32-bit pipe
+    uint32_t x = ((uint32_t)h ^ __funnelshift_l((uint32_t)(h >> 32), (uint32_t)(h >> 32), 15)) * 0x9E3779B1u;
+    x += pkey * 0x85EBCA77u;
+    x ^= x >> 15;
+    x *= 0x2C1B3C6Du;
+    return x >> (32 - tab_log2);
 }
 
 // ------------------------------------------------------------------ head table
@@ -151,15 +154,16 @@ __device__ __forceinline__ uint32_t slot_of(uint64_t h, uint32_t pkey, int tab_l
 // An "absent" answer may come from a stale L1 line; callers that act on it (creation) confirm
 // with the CAS in head_publish.  coherent = read past L1 from the start.
 __device__ __forceinline__ uint32_t head_find(const Head *tab, int tab_log2, uint64_t h, uint32_t pkey,
-                                              bool coherent = false)
-{
+                                              bool coherent, uint32_t &eslot)
+{   // eslot: the empty slot the probe sequence ended at when the answer is "absent"
     const uint32_t m = (1u << tab_log2) - 1;
     uint32_t s = slot_of(h, pkey, tab_log2);
+    eslot = SLOT_NONE;
     for (uint32_t probe = 0; probe <= m; probe++) {
         uint64_t a, b;
         if (coherent) ld_head_cg(tab + s, a, b);
         else ld_head(tab + s, a, b);
-        if (b == 0) return SLOT_NONE;                           // empty slot: not there
+        if (b == 0) { eslot = s; return SLOT_NONE; }            // empty slot: not there
         if (a == h && (uint32_t)(b >> 32) == pkey) return (uint32_t)b;
         s = (s + 1) & m;
     }
@@ -275,10 +279,21 @@ __device__ __forceinline__ int leading_ones(unsigned bal)
 //      W_CLAIM / W_INSERT append the rest of the path as ONE run and enter its head in the
 //      table with a 128-bit CAS.  If another request of the batch entered that child first, the
 //      walk simply goes on through the winner's run (the records just written stay unused).
-template <int MODE>
-__device__ __forceinline__ void walk_request(const WalkArgs &a, int i, int lane, WarpAlloc &wa)
+struct Pending {              // a head CAS whose outcome has not been looked at yet
+    int req;                   // request it belongs to, -1 = none
+    int lane;                  // lane that issued it
+    uint64_t oa, ob;           // what the CAS found in the slot ((0,0) = the run is entered)
+};
+
+// DEFER (claim fast path): the CAS that enters a new run goes straight to the empty slot the
+// probe ended at and its result is left in `pend`; the caller looks at it one request later
+// (the round trip overlaps the next request) and walks the request again, without DEFER, if
+// the slot had been taken meanwhile.  Walking a request twice is harmless: every step is
+// idempotent, and the records written the first time simply stay unused.
+template <int MODE, bool DEFER>
+__device__ __forceinline__ void walk_request(const WalkArgs &a, int i, int lane, WarpAlloc &wa,
+                                             const ReqSpan sp, uint64_t h_first, Pending &pend)
 {
-    const ReqSpan sp = req_span(a.chunk_base, i, a.max_chunks);
     const int C = sp.C;
     const uint64_t *hs = a.hashes + sp.b0;
     const TrieRef &t = a.t;
@@ -293,7 +308,7 @@ __device__ __forceinline__ void walk_request(const WalkArgs &a, int i, int lane,
     uint32_t pidx = ROOT_IDX;             // last resolved node
     uint32_t base = 0, room = 0;          // A: candidates start at log[base]; room = records of the
     bool have_base = false;               //    run from base on (0 = not known yet)
-    bool lost = false;                    // lost a creation race: probe the table past L1
+    bool lost = !DEFER && MODE == W_CLAIM;  // second walk of a request: probe the table past L1
     int npre = 0;                         // leading nodes with mask & avail != 0 (lookup depth / claim dpre)
     bool allpre = true;
     uint64_t sel = a.avail;
@@ -303,14 +318,14 @@ __device__ __forceinline__ void walk_request(const WalkArgs &a, int i, int lane,
         const int d = w0 + lane;
         const bool valid = d < C;
         const int nvalid = (C - w0) < 32 ? (C - w0) : 32;
-        const uint64_t h = valid ? hs[d] : 0;
+        const uint64_t h = w0 == 0 ? h_first : (valid ? hs[d] : 0);
         int r = 0;                        // lanes [0, r) of the window are resolved
         while (r < nvalid) {
             const int off = lane - r;
             if (!have_base) {
                 // ---- B
-                uint32_t idx = SLOT_NONE;
-                if (off == 0) idx = head_find(t.tab, t.tab_log2, h, parent_key(pidx), lost);
+                uint32_t idx = SLOT_NONE, eslot = SLOT_NONE;
+                if (off == 0) idx = head_find(t.tab, t.tab_log2, h, parent_key(pidx), lost, eslot);
                 idx = __shfl_sync(FULLW, idx, r);
                 if (idx == SLOT_NONE) {
                     // ---- absent at depth w0 + r, and so is everything below it
@@ -337,6 +352,15 @@ __device__ __forceinline__ void walk_request(const WalkArgs &a, int i, int lane,
                         } else {
                             atomicOr((unsigned long long *)&t.log[x].mask, bit);
                         }
+                    }
+                    if (DEFER) {                    // enter the run at the empty slot; look later
+                        pend.req = i;
+                        pend.lane = r;
+                        pend.oa = 0; pend.ob = 1;   // "taken" unless the CAS below says otherwise
+                        if (off == 0 && eslot != SLOT_NONE)
+                            cas128(t.tab + eslot, h, ((uint64_t)parent_key(pidx) << 32) | nb, pend.oa, pend.ob);
+                        finished = true;
+                        break;
                     }
                     uint32_t got = 0;
                     if (off == 0) got = head_publish(t.tab, t.tab_log2, h, parent_key(pidx), nb);
@@ -423,9 +447,10 @@ __device__ __forceinline__ void walk_request(const WalkArgs &a, int i, int lane,
 }
 
 // One warp per request, persistent grid-stride; the allocation block of each warp slot
-// survives the launch in t.wblk.
+// survives the launch in t.wblk.  The span of the request after next and the chunk hashes of
+// the next one are fetched while the current request is walked.
 template <int MODE>
-__global__ void __launch_bounds__(256, 5)
+__global__ void __launch_bounds__(256, 4)
 k_walk(WalkArgs a, int n, const int32_t *__restrict__ n_dev)
 {
     const int lane = threadIdx.x & 31;
@@ -434,9 +459,142 @@ k_walk(WalkArgs a, int n, const int32_t *__restrict__ n_dev)
     if (n_dev) n = *n_dev;
     WarpAlloc wa = { 0, 0 };
     constexpr bool ALLOC = (MODE == W_CLAIM || MODE == W_INSERT);
+    constexpr bool DEFER = (MODE == W_CLAIM);
     if (ALLOC) { const uint2 v = a.t.wblk[gw]; wa.cur = v.x; wa.end = v.y; }
-    for (int i = gw; i < n; i += nw) walk_request<MODE>(a, i, lane, wa);
+    Pending pend = { -1, 0, 0, 0 }, none = { -1, 0, 0, 0 };
+    ReqSpan sp0 = { 0, 0 }, sp1 = { 0, 0 };
+    uint64_t h0 = 0;
+    if (gw < n) {
+        sp0 = req_span(a.chunk_base, gw, a.max_chunks);
+        if (lane < sp0.C) h0 = a.hashes[sp0.b0 + lane];
+    }
+    if (gw + nw < n) sp1 = req_span(a.chunk_base, gw + nw, a.max_chunks);
+    for (int i = gw; i < n; i += nw) {
+        ReqSpan sp2 = { 0, 0 };
+        if (i + 2 * nw < n) sp2 = req_span(a.chunk_base, i + 2 * nw, a.max_chunks);
+        uint64_t h1 = 0;
+        if (i + nw < n && lane < sp1.C) h1 = a.hashes[sp1.b0 + lane];
+        Pending mine = { -1, 0, 0, 0 };
+        walk_request<MODE, DEFER>(a, i, lane, wa, sp0, h0, mine);
+        if (DEFER) {
+            if (pend.req >= 0 && __ballot_sync(FULLW, lane == pend.lane && (pend.oa | pend.ob))) {
+                // the slot was taken while the CAS was on its way: walk that request again
+                const ReqSpan spr = req_span(a.chunk_base, pend.req, a.max_chunks);
+                walk_request<MODE, false>(a, pend.req, lane, wa, spr,
+                                          lane < spr.C ? a.hashes[spr.b0 + lane] : 0, none);
+            }
+            pend = mine;
+        }
+        sp0 = sp1; sp1 = sp2; h0 = h1;
+    }
+    if (DEFER && pend.req >= 0 && __ballot_sync(FULLW, lane == pend.lane && (pend.oa | pend.ob))) {
+        const ReqSpan spr = req_span(a.chunk_base, pend.req, a.max_chunks);
+        walk_request<MODE, false>(a, pend.req, lane, wa, spr,
+                                  lane < spr.C ? a.hashes[spr.b0 + lane] : 0, none);
+    }
     if (ALLOC && lane == 0) a.t.wblk[gw] = make_uint2(wa.cur, wa.end);
+}
+
+// ------------------------------------------------------------------ claim, one THREAD per request
+// The same walk as walk_request<W_CLAIM>, but a thread per request instead of a warp.  With
+// runs, walking a stored prefix is a short loop over consecutive records that are usually in L1
+// (the shared prefixes of a batch are the hot ones), one table probe per run, and at most one
+// probe that misses; a thread does that in a few hundred instructions, so 32 requests cost a
+// warp about as many issue slots as ONE request costs the warp-per-request kernel.  Accesses
+// are per-thread 32-byte sectors rather than coalesced lines, which is what the records are.
+// Right for batches of short prompts (tens of chunks); the warp kernel is kept for long ones.
+// Log space for the new runs of a warp's 32 requests is taken with one atomic per warp.
+static __global__ void __launch_bounds__(128)
+k_claim_thread(WalkArgs a, int n, const int32_t *__restrict__ n_dev)
+{
+    const TrieRef &t = a.t;
+    const int lane = threadIdx.x & 31;
+    const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int nw = (gridDim.x * blockDim.x) >> 5;
+    if (n_dev) n = *n_dev;
+    for (int wbase = gw * 32; wbase < n; wbase += nw * 32) {
+        const int i = wbase + lane;
+        const bool active = i < n;
+        ReqSpan sp = { 0, 0 };
+        if (active) sp = req_span(a.chunk_base, i, a.max_chunks);
+        const int C = sp.C;
+        const uint64_t *hs = a.hashes + sp.b0;
+        uint32_t *sl = a.slots + sp.b0;
+        const unsigned long long mine = a.tag | (unsigned long long)(~(unsigned)i);
+        int d = 0;                            // depths [0, d) are resolved
+        uint32_t pidx = ROOT_IDX;             // last resolved node
+        int npre = 0;
+        bool allpre = true;
+        uint64_t sel = a.avail;
+        bool todo = active && C > 0;
+        bool coherent = false;
+        for (;;) {
+            uint32_t eslot = SLOT_NONE;
+            uint64_t hd = 0;                  // chunk hash at depth d when the walk stops there
+            // ---- find: follow stored runs as far as they go
+            while (todo && d < C) {
+                uint64_t h = hs[d];
+                const uint32_t idx = head_find(t.tab, t.tab_log2, h, parent_key(pidx), coherent, eslot);
+                if (idx == SLOT_NONE) { hd = h; break; }
+                uint32_t room = 1;
+                uint32_t k = 0;
+                for (;;) {
+                    uint64_t rh, m, rc;
+                    unsigned long long f;
+                    ld_rec(t.log + idx + k, rh, m, f, rc);
+                    while (!rec_whole(rh, rc)) ld_rec_cg(t.log + idx + k, rh, m, f, rc);
+                    if (k == 0) room = (uint32_t)rc;            // the head matches by its key
+                    else if (rh != h) break;                    // the path leaves the run here
+                    if (m & a.avail) {
+                        if (allpre) { npre++; sel = m & a.avail; }
+                    } else {
+                        allpre = false;
+                        sl[d] = idx + k;
+                        if (f < mine) atomicMax(&t.log[idx + k].first, mine);
+                    }
+                    d++; k++;
+                    if (d >= C || k >= room) break;
+                    h = hs[d];
+                }
+                pidx = idx + k - 1;
+            }
+            // ---- create what is missing: one run per request, log space per warp
+            const uint32_t L = (todo && d < C) ? (uint32_t)(C - d) : 0u;
+            uint32_t incl = L;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t v = __shfl_up_sync(FULLW, incl, o);
+                if (lane >= o) incl += v;
+            }
+            const uint32_t total = __shfl_sync(FULLW, incl, 31);
+            unsigned long long wb = 0;
+            if (total && lane == 0) wb = atomicAdd(&t.dev->log_count, (unsigned long long)total);
+            wb = __shfl_sync(FULLW, wb, 0);
+            bool lost = false;
+            if (total && wb + total > (unsigned long long)t.log_cap) {
+                if (lane == 0) atomicOr(&t.dev->status, B200R_S_TABLE_FULL);
+                for (int x = d; L && x < C; x++) sl[x] = SLOT_NONE;
+            } else if (L) {
+                const uint32_t nb = (uint32_t)wb + incl - L;
+                uint64_t oa = 0, ob = 1;
+                if (eslot != SLOT_NONE)         // enter the run at the empty slot the probe ended at
+                    cas128(t.tab + eslot, hd, ((uint64_t)parent_key(pidx) << 32) | nb, oa, ob);
+                for (uint32_t k = 0; k < L; k++) {
+                    st_rec_key(t.log + nb + k, k ? hs[d + k] : hd, L - k);
+                    atomicMax(&t.log[nb + k].first, mine);
+                    sl[d + k] = nb + k;
+                }
+                lost = (oa | ob) != 0;          // the slot was taken meanwhile (rare): walk on from
+            }                                   // depth d with coherent probes; the records stay unused
+            if (!__any_sync(FULLW, lost)) break;
+            todo = lost;
+            coherent = true;
+        }
+        if (active) {
+            a.dpre[i] = npre;
+            a.cand[i] = sel;
+        }
+    }
 }
 
 }  // namespace b200r
