@@ -206,9 +206,10 @@ int b200r_prefix_route_stage(b200r_trie *t, int64_t n, int64_t max_chunks, uint3
                              uint64_t *d_matched_mask, void *d_scratch, size_t scratch_bytes,
                              void *stream);
 /* The same three steps -- prep | hash | route -- pipelined over consecutive batches by the
- * library itself: prep of batch b+2 and hash of batch b+1 run on two streams the pipeline
- * owns while route of batch b runs on the caller's `stream`; route stages stay in call order,
- * so results are those of sequential routing.  The caller rotates `depth` scratch buffers
+ * library itself, on three streams the pipeline owns (prep and route at the highest stream
+ * priority, the SM-filling hashing kernel at the lowest): prep of batch b+2 and hash of batch
+ * b+1 run while route of batch b runs; route stages stay in call order, so results are those
+ * of sequential routing, and the caller's `stream` waits for the call's results.  The caller rotates `depth` scratch buffers
  * (call i uses buffer i mod depth; the pipeline makes call i+depth wait for call i).
  * inputs_on_prep_stream = 0: the inputs were produced on `stream` (the prep step waits for
  * it); 1: they are complete, or were copied on b200r_pipe_prep_stream(), e.g. a host-to-device

@@ -1154,7 +1154,7 @@ struct b200r_pipe {
     b200r_trie *t;
     int depth;
     long long calls;
-    cudaStream_t prep, hash;
+    cudaStream_t prep, hash, route;
     cudaEvent_t prepped[8], hashed[8], done[8], inputs;
     bool has_done[8];
 };
@@ -1164,8 +1164,15 @@ int b200r_pipe_create(b200r_trie *t, int32_t depth, b200r_pipe **out)
     if (!t || !out || depth < 1 || depth > 8) { set_error("b200r_pipe_create: trie, 1 <= depth <= 8"); return B200R_E_INVALID; }
     b200r_pipe *p = new b200r_pipe();
     p->t = t; p->depth = depth; p->calls = 0;
-    B200R_CUDA(cudaStreamCreateWithFlags(&p->prep, cudaStreamNonBlocking));
-    B200R_CUDA(cudaStreamCreateWithFlags(&p->hash, cudaStreamNonBlocking));
+    // The route step (small, latency-bound kernels) and the prep step get the highest stream
+    // priority, the hashing kernel (thousands of CTAs that fill every SM) the lowest: without
+    // it the block scheduler hands out the hashing kernel's CTAs first and the route step of the
+    // batch before only starts when they are nearly through -- the steps would not overlap.
+    int least = 0, greatest = 0;
+    B200R_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+    B200R_CUDA(cudaStreamCreateWithPriority(&p->prep, cudaStreamNonBlocking, greatest));
+    B200R_CUDA(cudaStreamCreateWithPriority(&p->hash, cudaStreamNonBlocking, least));
+    B200R_CUDA(cudaStreamCreateWithPriority(&p->route, cudaStreamNonBlocking, greatest));
     B200R_CUDA(cudaEventCreateWithFlags(&p->inputs, cudaEventDisableTiming));
     for (int k = 0; k < depth; k++) {
         B200R_CUDA(cudaEventCreateWithFlags(&p->prepped[k], cudaEventDisableTiming));
@@ -1180,12 +1187,12 @@ int b200r_pipe_create(b200r_trie *t, int32_t depth, b200r_pipe **out)
 int b200r_pipe_destroy(b200r_pipe *p)
 {
     if (!p) return B200R_OK;
-    cudaStreamSynchronize(p->prep); cudaStreamSynchronize(p->hash);
+    cudaStreamSynchronize(p->prep); cudaStreamSynchronize(p->hash); cudaStreamSynchronize(p->route);
     for (int k = 0; k < p->depth; k++) {
         cudaEventDestroy(p->prepped[k]); cudaEventDestroy(p->hashed[k]); cudaEventDestroy(p->done[k]);
     }
     cudaEventDestroy(p->inputs);
-    cudaStreamDestroy(p->prep); cudaStreamDestroy(p->hash);
+    cudaStreamDestroy(p->prep); cudaStreamDestroy(p->hash); cudaStreamDestroy(p->route);
     delete p;
     return B200R_OK;
 }
@@ -1247,11 +1254,20 @@ int b200r_pipe_route(b200r_pipe *p, const uint8_t *d_bytes, const int64_t *d_sta
                      max_chunks, sc, pl, t->dev, p->hash, 2);
     if (rc) return rc;
     B200R_CUDA(cudaEventRecord(p->hashed[k], p->hash));
-    B200R_CUDA(cudaStreamWaitEvent(cur, p->hashed[k], 0));
+    // the route step runs on the pipeline's own high-priority stream, in call order; the
+    // outputs may have been in use on the caller's stream, and the caller's stream sees them
+    // when the step is done
+    B200R_CUDA(cudaStreamWaitEvent(p->route, p->hashed[k], 0));
+    if (!inputs_on_prep_stream) B200R_CUDA(cudaStreamWaitEvent(p->route, p->inputs, 0));
+    else {
+        B200R_CUDA(cudaEventRecord(p->inputs, cur));
+        B200R_CUDA(cudaStreamWaitEvent(p->route, p->inputs, 0));
+    }
     rc = route_from(t, hashes, chunk_base, n, max_chunks, avail_mask, seed, seq0, d_endpoint,
-                    d_match_depth, d_matched_mask, sc, pl, cur);
+                    d_match_depth, d_matched_mask, sc, pl, p->route);
     if (rc) return rc;
-    B200R_CUDA(cudaEventRecord(p->done[k], cur));
+    B200R_CUDA(cudaEventRecord(p->done[k], p->route));
+    B200R_CUDA(cudaStreamWaitEvent(cur, p->done[k], 0));
     p->has_done[k] = true;
     return B200R_OK;
 }
