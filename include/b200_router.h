@@ -320,9 +320,9 @@ int b200r_ring_lookup_batch(b200r_ring *r, const uint8_t *d_bytes, const int64_t
  * b200r_launch_count: kernels enqueued by this library
  * since load (process-wide).
  * ---------------------------------------------------------------------- */
-/* tuning switch of the route stage's claim step: 0 = choose per batch (a thread per request
- * while prompts average at most 64 chunks, a warp per request beyond), 1 = always a thread, 2 =
- * always a warp; identical results */
+/* tuning switch of the route stage's claim step, i.e. how many lanes walk one request: 0 =
+ * choose per batch from the average number of chunks (one thread up to 64 chunks per prompt, a
+ * warp beyond), 1 = one thread, 2 = a warp, 3 = 16 lanes, 4 = 8 lanes; identical results */
 int b200r_set_claim_mode(int mode);
 #define B200R_PROF_SLOTS 13
 int b200r_prof_enable(int on);

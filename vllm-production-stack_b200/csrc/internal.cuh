@@ -18,7 +18,7 @@ extern bool g_prof_on;
 extern std::vector<ProfSpan> g_spans;
 extern long long g_launches;
 extern int g_claim_mode;
-constexpr int64_t CLAIM_THREAD_MAX_AVG_CHUNKS = 64;
+int claim_kind_for(int64_t n, int64_t chunks);
 
 struct ProfScope {
     bool on; cudaStream_t st; ProfSpan sp;
@@ -77,7 +77,7 @@ struct RouteCore {
     uint32_t *slots; int32_t *leader, *choice, *dpre; uint64_t *cand;
     int32_t *endpoint, *depth; uint64_t *matched;
     const P2PDyn *dyn; const uint32_t *pos; const int32_t *n_dev;
-    bool by_thread;       // claim with a thread per request (short prompts) instead of a warp
+    int claim_kind;       // claim_kind_for()
 };
 int launch_route_core(b200r_trie *t, const RouteCore &rc, cudaStream_t st);
 

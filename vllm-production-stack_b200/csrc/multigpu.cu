@@ -508,7 +508,7 @@ int b200r_part_route(b200r_trie *t, uint64_t avail_mask, uint64_t seed,
     core.dpre = (int32_t *)(sc + p.off_dpre); core.cand = (uint64_t *)(sc + p.off_cand);
     core.endpoint = ep; core.depth = depth; core.matched = matched;
     core.dyn = &dyn->base; core.pos = pos_owned; core.n_dev = n_dev;
-    core.by_thread = g_claim_mode == 1 || (g_claim_mode == 0 && cap <= rcap * CLAIM_THREAD_MAX_AVG_CHUNKS);
+    core.claim_kind = claim_kind_for(rcap, cap);
     rc = launch_route_core(t, core, st);
     if (rc) return rc;
     { ProfScope ps__(PK_PUSH, st); g_launches += 1;

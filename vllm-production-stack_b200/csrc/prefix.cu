@@ -47,7 +47,7 @@ int cuda_fail(cudaError_t e, const char *what)
 }
 
 // ------------------------------------------------------------- profiling (internal.cuh)
-int g_claim_mode = 0;          // 0 auto, 1 thread per request, 2 warp per request (b200r_set_claim_mode)
+int g_claim_mode = 0;          // b200r_set_claim_mode: 0 auto, else claim_kind_for's value
 bool g_prof_on = false;
 std::vector<ProfSpan> g_spans;
 long long g_launches = 0;
@@ -716,9 +716,20 @@ static int next_epoch(b200r_trie *t, cudaStream_t st, unsigned long long *tag)
     return B200R_OK;
 }
 
-static int walk_grid(int64_t n)
+// How the claim step is decomposed: 1 = a thread per request, 2 = a warp, 3 = 16 lanes, 4 = 8
+// lanes (identical results).  Measured on C3 (21.5 chunks per prompt): thread 30 us, 8 lanes 39,
+// 16 lanes 47, warp 49.5 per 64K batch -- short prompts leave most lanes of a wider tile idle
+// while costing its issue slots all the same.  Long prompts (C4: 256 chunks) want the coalesced
+// record reads of the warp.
+int claim_kind_for(int64_t n, int64_t chunks)
 {
-    int64_t b = (n + WARPS_PER_CTA - 1) / WARPS_PER_CTA;
+    if (g_claim_mode) return g_claim_mode;
+    return chunks <= n * 64 ? 1 : 2;
+}
+
+static int walk_grid(int64_t n, int tw = 32)
+{
+    int64_t b = (n * tw + WARPS_PER_CTA * 32 - 1) / (WARPS_PER_CTA * 32);
     if (b > WALK_MAX_CTAS) b = WALK_MAX_CTAS;
     return b < 1 ? 1 : (int)b;
 }
@@ -736,12 +747,16 @@ int launch_route_core(b200r_trie *t, const RouteCore &rc, cudaStream_t st)
     const int nn = rc.n_dev ? 0 : (int)rc.n;
     const int tblocks = (int)((rc.n + 255) / 256);
     { ProfScope ps__(PK_CLAIM, st); g_launches += 1;
-    if (rc.by_thread) {
+    if (rc.claim_kind == 1) {
         int64_t blocks = (rc.n + 127) / 128;
         if (blocks > 148 * 16) blocks = 148 * 16;
         k_claim_thread<<<(int)(blocks < 1 ? 1 : blocks), 128, 0, st>>>(a, nn, rc.n_dev);
+    } else if (rc.claim_kind == 4) {
+        k_walk<W_CLAIM, 8><<<walk_grid(rc.n, 8), WARPS_PER_CTA * 32, 0, st>>>(a, nn, rc.n_dev);
+    } else if (rc.claim_kind == 3) {
+        k_walk<W_CLAIM, 16><<<walk_grid(rc.n, 16), WARPS_PER_CTA * 32, 0, st>>>(a, nn, rc.n_dev);
     } else {
-        k_walk<W_CLAIM><<<walk_grid(rc.n), WARPS_PER_CTA * 32, 0, st>>>(a, nn, rc.n_dev);
+        k_walk<W_CLAIM, 32><<<walk_grid(rc.n), WARPS_PER_CTA * 32, 0, st>>>(a, nn, rc.n_dev);
     }
     B200R_LAUNCH_CHECK("k_walk<claim>");
     }
@@ -774,7 +789,7 @@ uint32_t b200r_pick(uint64_t seed, uint64_t seq, uint32_t n) { return pick(seed,
 
 int b200r_set_claim_mode(int mode)
 {
-    if (mode < 0 || mode > 2) { set_error("b200r_set_claim_mode: 0 auto, 1 thread, 2 warp"); return B200R_E_INVALID; }
+    if (mode < 0 || mode > 4) { set_error("b200r_set_claim_mode: 0 auto, 1 thread, 2 warp, 3 half warp, 4 quarter warp"); return B200R_E_INVALID; }
     g_claim_mode = mode;
     return B200R_OK;
 }
@@ -1019,7 +1034,7 @@ int b200r_trie_lookup_batch(b200r_trie *t, const uint64_t *d_hashes, const int32
     a.hashes = d_hashes; a.chunk_base = d_chunk_base; a.max_chunks = INT64_MAX;
     a.avail = avail_mask; a.depth_out = d_match_depth; a.matched_out = d_matched_mask;
     { ProfScope ps__(PK_LOOKUP, (cudaStream_t)stream); g_launches += 1;
-    k_walk<W_LOOKUP><<<walk_grid(n), WARPS_PER_CTA * 32, 0, (cudaStream_t)stream>>>(a, (int)n, nullptr);
+    k_walk<W_LOOKUP, 32><<<walk_grid(n), WARPS_PER_CTA * 32, 0, (cudaStream_t)stream>>>(a, (int)n, nullptr);
     B200R_LAUNCH_CHECK("k_walk<lookup>");
     }
     return B200R_OK;
@@ -1036,7 +1051,7 @@ int b200r_trie_insert_batch(b200r_trie *t, const uint64_t *d_hashes, const int32
     a.hashes = d_hashes; a.chunk_base = d_chunk_base; a.max_chunks = INT64_MAX;
     a.endpoint = d_endpoint;
     { ProfScope ps__(PK_INSERT, (cudaStream_t)stream); g_launches += 1;
-    k_walk<W_INSERT><<<walk_grid(n), WARPS_PER_CTA * 32, 0, (cudaStream_t)stream>>>(a, (int)n, nullptr);
+    k_walk<W_INSERT, 32><<<walk_grid(n), WARPS_PER_CTA * 32, 0, (cudaStream_t)stream>>>(a, (int)n, nullptr);
     B200R_LAUNCH_CHECK("k_walk<insert>");
     }
     return B200R_OK;
@@ -1090,7 +1105,7 @@ static int route_from(b200r_trie *t, const uint64_t *hashes, const int32_t *chun
     rc.cand = (uint64_t *)(sc + p.off_cand);
     rc.endpoint = d_endpoint; rc.depth = d_match_depth; rc.matched = d_matched_mask;
     // a thread per request while prompts are short on average, a warp per request beyond
-    rc.by_thread = g_claim_mode == 1 || (g_claim_mode == 0 && max_chunks <= n * CLAIM_THREAD_MAX_AVG_CHUNKS);
+    rc.claim_kind = claim_kind_for(n, max_chunks);
     return launch_route_core(t, rc, st);
 }
 

@@ -67,7 +67,7 @@ constexpr uint32_t ROOT_IDX = 0xFFFFFFFFu;      // "log index" of the root (it h
 constexpr uint32_t SLOT_NONE = 0xFFFFFFFFu;
 constexpr uint32_t PREOK_BIT = 0x80000000u;     // slots[]: node usable before the batch
 constexpr uint32_t IDX_MASK = 0x7FFFFFFFu;
-constexpr int NWSLOT = 16384;                   // warp slots with a persistent allocation block
+constexpr int NWSLOT = 65536;                   // tile slots with a persistent allocation block
 constexpr unsigned FULLW = 0xffffffffu;
 #define B200R_S_INTERNAL 8u                     /* latched: inconsistent table (never expected) */
 
@@ -207,9 +207,34 @@ __device__ __forceinline__ uint32_t alloc_block_size(uint32_t log_cap)
     return b > 128u ? 128u : b;
 }
 
-// warp-uniform: every lane passes the same arguments and receives the same result
-__device__ __forceinline__ uint32_t warp_alloc(const TrieRef &t, WarpAlloc &wa, uint32_t L, int lane)
+// A request is walked by a TILE of TW lanes (8, 16 or the whole warp): several short requests
+// share a warp, each tile on its own.  Collectives use the tile's lane mask.
+struct Tile { unsigned mask; int base; int tl; };       // lanes of the tile, first lane, my index
+template <int TW>
+__device__ __forceinline__ Tile make_tile(int lane)
 {
+    Tile g;
+    g.base = lane & ~(TW - 1);
+    g.tl = lane & (TW - 1);
+    g.mask = TW == 32 ? FULLW : (((1u << TW) - 1u) << g.base);
+    return g;
+}
+template <int TW>
+__device__ __forceinline__ unsigned tile_ballot(const Tile &g, bool p)
+{   // bit k = lane k of the tile
+    const unsigned b = __ballot_sync(g.mask, p);
+    return TW == 32 ? b : ((b >> g.base) & ((1u << TW) - 1u));
+}
+template <int TW>
+__device__ __forceinline__ int leading_ones_t(unsigned bal)
+{   // bal has no bits at or above TW
+    return (TW == 32 && bal == FULLW) ? 32 : (__ffs(~bal) - 1);
+}
+
+// tile-uniform: every lane passes the same arguments and receives the same result
+__device__ __forceinline__ uint32_t warp_alloc(const TrieRef &t, WarpAlloc &wa, uint32_t L, const Tile &g)
+{
+    const int lane = g.tl;
     if (L <= wa.end - wa.cur) {
         const uint32_t base = wa.cur;
         wa.cur += L;
@@ -219,7 +244,7 @@ __device__ __forceinline__ uint32_t warp_alloc(const TrieRef &t, WarpAlloc &wa, 
     const uint32_t take = L >= blk ? L : blk;
     unsigned long long b = 0;
     if (lane == 0) b = atomicAdd(&t.dev->log_count, (unsigned long long)take);
-    b = __shfl_sync(FULLW, b, 0);
+    b = __shfl_sync(g.mask, b, g.base);
     if (b + L > (unsigned long long)t.log_cap) {
         if (lane == 0) atomicOr(&t.dev->status, B200R_S_TABLE_FULL);
         return SLOT_NONE;
@@ -290,10 +315,11 @@ struct Pending {              // a head CAS whose outcome has not been looked at
 // (the round trip overlaps the next request) and walks the request again, without DEFER, if
 // the slot had been taken meanwhile.  Walking a request twice is harmless: every step is
 // idempotent, and the records written the first time simply stay unused.
-template <int MODE, bool DEFER>
-__device__ __forceinline__ void walk_request(const WalkArgs &a, int i, int lane, WarpAlloc &wa,
+template <int MODE, bool DEFER, int TW>
+__device__ __forceinline__ void walk_request(const WalkArgs &a, int i, const Tile &g, WarpAlloc &wa,
                                              const ReqSpan sp, uint64_t h_first, Pending &pend)
 {
+    const int lane = g.tl;                // position inside the tile
     const int C = sp.C;
     const uint64_t *hs = a.hashes + sp.b0;
     const TrieRef &t = a.t;
@@ -314,10 +340,10 @@ __device__ __forceinline__ void walk_request(const WalkArgs &a, int i, int lane,
     uint64_t sel = a.avail;
     bool finished = false;
 
-    for (int w0 = 0; w0 < C && !finished; w0 += 32) {
+    for (int w0 = 0; w0 < C && !finished; w0 += TW) {
         const int d = w0 + lane;
         const bool valid = d < C;
-        const int nvalid = (C - w0) < 32 ? (C - w0) : 32;
+        const int nvalid = (C - w0) < TW ? (C - w0) : TW;
         const uint64_t h = w0 == 0 ? h_first : (valid ? hs[d] : 0);
         int r = 0;                        // lanes [0, r) of the window are resolved
         while (r < nvalid) {
@@ -326,23 +352,23 @@ __device__ __forceinline__ void walk_request(const WalkArgs &a, int i, int lane,
                 // ---- B
                 uint32_t idx = SLOT_NONE, eslot = SLOT_NONE;
                 if (off == 0) idx = head_find(t.tab, t.tab_log2, h, parent_key(pidx), lost, eslot);
-                idx = __shfl_sync(FULLW, idx, r);
+                idx = __shfl_sync(g.mask, idx, g.base + r);
                 if (idx == SLOT_NONE) {
                     // ---- absent at depth w0 + r, and so is everything below it
                     if (MODE == W_LOOKUP) { finished = true; break; }
                     const int pos = w0 + r;
                     const uint32_t L = (uint32_t)(C - pos);
-                    const uint32_t nb = warp_alloc(t, wa, L, lane);
+                    const uint32_t nb = warp_alloc(t, wa, L, g);
                     if (nb == SLOT_NONE) {
                         if (MODE == W_CLAIM)
-                            for (int d2 = d; d2 < C; d2 += 32)
+                            for (int d2 = d; d2 < C; d2 += TW)
                                 if (d2 >= pos) a.slots[sp.b0 + d2] = SLOT_NONE;
                         finished = true;
                         break;
                     }
-                    // every lane keeps to its own depths d, d + 32, ...: a slot word is only ever
+                    // every lane keeps to its own depths d, d + TW, ...: a slot word is only ever
                     // written by one thread, so a later correction (lost race) lands in order
-                    for (int d2 = d; d2 < C; d2 += 32) {
+                    for (int d2 = d; d2 < C; d2 += TW) {
                         if (d2 < pos) continue;
                         const uint32_t x = nb + (uint32_t)(d2 - pos);
                         st_rec_key(t.log + x, d2 == d ? h : hs[d2], (uint32_t)(C - d2));
@@ -364,7 +390,7 @@ __device__ __forceinline__ void walk_request(const WalkArgs &a, int i, int lane,
                     }
                     uint32_t got = 0;
                     if (off == 0) got = head_publish(t.tab, t.tab_log2, h, parent_key(pidx), nb);
-                    got = __shfl_sync(FULLW, got, r);
+                    got = __shfl_sync(g.mask, got, g.base + r);
                     if (got == nb) { finished = true; break; }          // the path is complete
                     if (got == SLOT_NONE) {
                         if (lane == 0) atomicOr(&t.dev->status, B200R_S_TABLE_FULL);
@@ -387,12 +413,12 @@ __device__ __forceinline__ void walk_request(const WalkArgs &a, int i, int lane,
             if (rd) ld_rec(t.log + idx, rh, m, f, rc);
             if (room == 0) {                                    // run length from its first record
                 if (off == 0) while (!rec_whole(rh, rc)) ld_rec_cg(t.log + idx, rh, m, f, rc);
-                room = (uint32_t)__shfl_sync(FULLW, rc, r);
+                room = (uint32_t)__shfl_sync(g.mask, rc, g.base + r);
             }
             const bool in = valid && off >= 0 && (uint32_t)off < room;
             if (in) while (!rec_whole(rh, rc)) ld_rec_cg(t.log + idx, rh, m, f, rc);   // published, not yet visible
             const bool fresh = room0 == 0;                      // base came from the table just now
-            const int nres = leading_ones(__ballot_sync(FULLW, in && rh == h) >> r);
+            const int nres = leading_ones_t<TW>(tile_ballot<TW>(g, in && rh == h) >> r);
             if (nres == 0) {
                 if (fresh) {                                    // a head always matches itself
                     if (lane == 0) atomicOr(&t.dev->status, B200R_S_INTERNAL);
@@ -403,7 +429,7 @@ __device__ __forceinline__ void walk_request(const WalkArgs &a, int i, int lane,
                 continue;
             }
             pidx = base + (uint32_t)nres - 1;
-            if (r + nres < 32 || (uint32_t)nres == room) have_base = false;     // diverged, or the run ended
+            if (r + nres < TW || (uint32_t)nres == room) have_base = false;     // diverged, or the run ended
             else { base += (uint32_t)nres; room -= (uint32_t)nres; }            // next window, same run
             // ---- lanes [r, r + nres) hold resolved nodes
             const bool res = off >= 0 && off < nres;
@@ -421,10 +447,10 @@ __device__ __forceinline__ void walk_request(const WalkArgs &a, int i, int lane,
                 if (res && !(m & bit)) atomicOr((unsigned long long *)&t.log[idx].mask, bit);
             }
             if (MODE != W_INSERT && allpre) {
-                const int nok0 = leading_ones(__ballot_sync(FULLW, use) >> r);
+                const int nok0 = leading_ones_t<TW>(tile_ballot<TW>(g, use) >> r);
                 const int nok = nok0 < nres ? nok0 : nres;
                 if (nok > 0) {
-                    sel = __shfl_sync(FULLW, m & a.avail, r + nok - 1);
+                    sel = __shfl_sync(g.mask, m & a.avail, g.base + r + nok - 1);
                     npre += nok;
                 }
                 if (nok < nres) {
@@ -446,53 +472,53 @@ __device__ __forceinline__ void walk_request(const WalkArgs &a, int i, int lane,
     }
 }
 
-// One warp per request, persistent grid-stride; the allocation block of each warp slot
-// survives the launch in t.wblk.  The span of the request after next and the chunk hashes of
-// the next one are fetched while the current request is walked.
-template <int MODE>
+// One tile of TW lanes per request, persistent grid-stride; the allocation block of each tile
+// slot survives the launch in t.wblk.  The span of the request after next and the chunk hashes
+// of the next one are fetched while the current request is walked.
+template <int MODE, int TW>
 __global__ void __launch_bounds__(256, 4)
 k_walk(WalkArgs a, int n, const int32_t *__restrict__ n_dev)
 {
-    const int lane = threadIdx.x & 31;
-    const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int nw = (gridDim.x * blockDim.x) >> 5;
+    const Tile g = make_tile<TW>(threadIdx.x & 31);
+    const int gt = (blockIdx.x * blockDim.x + threadIdx.x) / TW;       // global tile
+    const int nt = (gridDim.x * blockDim.x) / TW;
     if (n_dev) n = *n_dev;
     WarpAlloc wa = { 0, 0 };
     constexpr bool ALLOC = (MODE == W_CLAIM || MODE == W_INSERT);
     constexpr bool DEFER = (MODE == W_CLAIM);
-    if (ALLOC) { const uint2 v = a.t.wblk[gw]; wa.cur = v.x; wa.end = v.y; }
+    if (ALLOC) { const uint2 v = a.t.wblk[gt]; wa.cur = v.x; wa.end = v.y; }
     Pending pend = { -1, 0, 0, 0 }, none = { -1, 0, 0, 0 };
     ReqSpan sp0 = { 0, 0 }, sp1 = { 0, 0 };
     uint64_t h0 = 0;
-    if (gw < n) {
-        sp0 = req_span(a.chunk_base, gw, a.max_chunks);
-        if (lane < sp0.C) h0 = a.hashes[sp0.b0 + lane];
+    if (gt < n) {
+        sp0 = req_span(a.chunk_base, gt, a.max_chunks);
+        if (g.tl < sp0.C) h0 = a.hashes[sp0.b0 + g.tl];
     }
-    if (gw + nw < n) sp1 = req_span(a.chunk_base, gw + nw, a.max_chunks);
-    for (int i = gw; i < n; i += nw) {
+    if (gt + nt < n) sp1 = req_span(a.chunk_base, gt + nt, a.max_chunks);
+    for (int i = gt; i < n; i += nt) {
         ReqSpan sp2 = { 0, 0 };
-        if (i + 2 * nw < n) sp2 = req_span(a.chunk_base, i + 2 * nw, a.max_chunks);
+        if (i + 2 * nt < n) sp2 = req_span(a.chunk_base, i + 2 * nt, a.max_chunks);
         uint64_t h1 = 0;
-        if (i + nw < n && lane < sp1.C) h1 = a.hashes[sp1.b0 + lane];
+        if (i + nt < n && g.tl < sp1.C) h1 = a.hashes[sp1.b0 + g.tl];
         Pending mine = { -1, 0, 0, 0 };
-        walk_request<MODE, DEFER>(a, i, lane, wa, sp0, h0, mine);
+        walk_request<MODE, DEFER, TW>(a, i, g, wa, sp0, h0, mine);
         if (DEFER) {
-            if (pend.req >= 0 && __ballot_sync(FULLW, lane == pend.lane && (pend.oa | pend.ob))) {
+            if (pend.req >= 0 && __ballot_sync(g.mask, g.tl == pend.lane && (pend.oa | pend.ob))) {
                 // the slot was taken while the CAS was on its way: walk that request again
                 const ReqSpan spr = req_span(a.chunk_base, pend.req, a.max_chunks);
-                walk_request<MODE, false>(a, pend.req, lane, wa, spr,
-                                          lane < spr.C ? a.hashes[spr.b0 + lane] : 0, none);
+                walk_request<MODE, false, TW>(a, pend.req, g, wa, spr,
+                                              g.tl < spr.C ? a.hashes[spr.b0 + g.tl] : 0, none);
             }
             pend = mine;
         }
         sp0 = sp1; sp1 = sp2; h0 = h1;
     }
-    if (DEFER && pend.req >= 0 && __ballot_sync(FULLW, lane == pend.lane && (pend.oa | pend.ob))) {
+    if (DEFER && pend.req >= 0 && __ballot_sync(g.mask, g.tl == pend.lane && (pend.oa | pend.ob))) {
         const ReqSpan spr = req_span(a.chunk_base, pend.req, a.max_chunks);
-        walk_request<MODE, false>(a, pend.req, lane, wa, spr,
-                                  lane < spr.C ? a.hashes[spr.b0 + lane] : 0, none);
+        walk_request<MODE, false, TW>(a, pend.req, g, wa, spr,
+                                      g.tl < spr.C ? a.hashes[spr.b0 + g.tl] : 0, none);
     }
-    if (ALLOC && lane == 0) a.t.wblk[gw] = make_uint2(wa.cur, wa.end);
+    if (ALLOC && g.tl == 0) a.t.wblk[gt] = make_uint2(wa.cur, wa.end);
 }
 
 // ------------------------------------------------------------------ claim, one THREAD per request
@@ -536,25 +562,55 @@ k_claim_thread(WalkArgs a, int n, const int32_t *__restrict__ n_dev)
                 uint64_t h = hs[d];
                 const uint32_t idx = head_find(t.tab, t.tab_log2, h, parent_key(pidx), coherent, eslot);
                 if (idx == SLOT_NONE) { hd = h; break; }
-                uint32_t room = 1;
-                uint32_t k = 0;
-                for (;;) {
+                // the head record first: it matches by its key and tells how long the run is
+                uint32_t room, k = 1;
+                {
                     uint64_t rh, m, rc;
                     unsigned long long f;
-                    ld_rec(t.log + idx + k, rh, m, f, rc);
-                    while (!rec_whole(rh, rc)) ld_rec_cg(t.log + idx + k, rh, m, f, rc);
-                    if (k == 0) room = (uint32_t)rc;            // the head matches by its key
-                    else if (rh != h) break;                    // the path leaves the run here
+                    ld_rec(t.log + idx, rh, m, f, rc);
+                    while (!rec_whole(rh, rc)) ld_rec_cg(t.log + idx, rh, m, f, rc);
+                    room = (uint32_t)rc;
                     if (m & a.avail) {
                         if (allpre) { npre++; sel = m & a.avail; }
                     } else {
                         allpre = false;
-                        sl[d] = idx + k;
-                        if (f < mine) atomicMax(&t.log[idx + k].first, mine);
+                        sl[d] = idx;
+                        if (f < mine) atomicMax(&t.log[idx].first, mine);
                     }
-                    d++; k++;
-                    if (d >= C || k >= room) break;
-                    h = hs[d];
+                    d++;
+                }
+                // then the records behind it, four at a time (independent loads in flight)
+                bool left = false;
+                while (!left && d < C && k < room) {
+                    uint64_t rh[4], m[4], rc[4], hh[4];
+                    unsigned long long f[4];
+                    const int nl = min(min((int)(room - k), C - d), 4);
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        rh[j] = 0; m[j] = 0; rc[j] = 0; f[j] = 0; hh[j] = 0;
+                        if (j < nl) {
+                            hh[j] = hs[d + j];
+                            ld_rec(t.log + idx + k + j, rh[j], m[j], f[j], rc[j]);
+                        }
+                    }
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        if (j < nl && !left) {
+                            while (!rec_whole(rh[j], rc[j])) ld_rec_cg(t.log + idx + k + j, rh[j], m[j], f[j], rc[j]);
+                            if (rh[j] != hh[j]) {
+                                left = true;                    // the path leaves the run here
+                            } else {
+                                if (m[j] & a.avail) {
+                                    if (allpre) { npre++; sel = m[j] & a.avail; }
+                                } else {
+                                    allpre = false;
+                                    sl[d] = idx + k;
+                                    if (f[j] < mine) atomicMax(&t.log[idx + k].first, mine);
+                                }
+                                d++; k++;
+                            }
+                        }
+                    }
                 }
                 pidx = idx + k - 1;
             }
@@ -579,10 +635,19 @@ k_claim_thread(WalkArgs a, int n, const int32_t *__restrict__ n_dev)
                 uint64_t oa = 0, ob = 1;
                 if (eslot != SLOT_NONE)         // enter the run at the empty slot the probe ended at
                     cas128(t.tab + eslot, hd, ((uint64_t)parent_key(pidx) << 32) | nb, oa, ob);
-                for (uint32_t k = 0; k < L; k++) {
-                    st_rec_key(t.log + nb + k, k ? hs[d + k] : hd, L - k);
-                    atomicMax(&t.log[nb + k].first, mine);
-                    sl[d + k] = nb + k;
+                for (uint32_t k0 = 0; k0 < L; k0 += 4) {        // chunk hashes four at a time
+                    uint64_t hh[4];
+#pragma unroll
+                    for (int j = 0; j < 4; j++) hh[j] = (k0 + j < L) ? hs[d + k0 + j] : 0;
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        const uint32_t k = k0 + j;
+                        if (k < L) {
+                            st_rec_key(t.log + nb + k, hh[j], L - k);
+                            atomicMax(&t.log[nb + k].first, mine);
+                            sl[d + k] = nb + k;
+                        }
+                    }
                 }
                 lost = (oa | ob) != 0;          // the slot was taken meanwhile (rare): walk on from
             }                                   // depth d with coherent probes; the records stay unused
