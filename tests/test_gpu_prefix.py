@@ -449,6 +449,34 @@ def test_router_micro_batched_concurrent_requests_equal_reference(golden_prefix)
     routers._reset_singletons_for_tests()
 
 
+def test_every_claim_decomposition_agrees_with_the_oracle():
+    """The claim step can walk a request with one thread, 8, 16 or 32 lanes
+    (b200r_set_claim_mode); every choice must equal the oracle -- heavy sharing inside batches
+    (creation races on the same child, long leader chains), prompts longer than a tile and
+    longer than a warp, runs that other requests leave in the middle."""
+    from b200_router import _lib
+    from b200_router.trie import GpuHashTrie
+    bufL, stL, lnL = traces.long_context_batch(n=200, chars=128 * 70 + 3, group=8, shared_frac=0.4, seed=33)
+    tr = traces.SharedPrefixTrace(n_total=12000, batch=4000, n_sys=8, sys_chars=1024,
+                                  suffix_lo=1, suffix_hi=500, seed=77)
+    try:
+        for mode in (1, 2, 3, 4):
+            _lib.check(_lib.lib().b200r_set_claim_mode(mode))
+            for s in range(3):
+                t = GpuHashTrie(cap_log2=17)
+                batches = [((1 << 64) - 1, bufL, stL, lnL)] if s == 0 else []
+                if s == 1:
+                    batches += [((0xFB if b == 1 else 0xFF),) + tr.batch_arrays(b) for b in range(3)]
+                for avail_idx, prompts in traces.sharing_stress(n_batches=4, batch=200, n_endpoints=7,
+                                                                max_depth=6, alphabet=2, seed=300 + s):
+                    buf, starts, lens, _ = traces.pack_strings(prompts)
+                    batches.append((sum(1 << i for i in avail_idx), buf, starts, lens))
+                _route_vs_oracle(t, batches, seed=s)
+                t.close()
+    finally:
+        _lib.check(_lib.lib().b200r_set_claim_mode(0))
+
+
 def test_byte_chunk_mode_reproduces_the_gateway_picker(trie, golden_go):
     """chunk_by="bytes" (+ from_root_endpoints for lookups) against the restated gateway picker
     (tests/golden/go_picker_kat.json; prefix_aware_picker.go:154-213): chunk hashes of UTF-8
