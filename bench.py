@@ -349,7 +349,7 @@ def clear_router(cx, router):
 def route_any(cx, router, p, avail, seq, out=None, ready=True):
     if cx.world == 1:
         return router.route(p, avail, SEED, seq, out=out, inputs_ready=ready)
-    if hasattr(router, "send_stream"):                       # partitioned: pipelined
+    if hasattr(router, "pipelined"):                       # partitioned: pipelined
         return router.route(p, avail, SEED, seq, out=out, inputs_ready=ready)
     return router.route(p, avail, SEED, seq, out=out)
 
@@ -404,7 +404,7 @@ def parity_check(cx, router, seq, per_rank=2048, n_batches=4):
     else:
         dumps = [mine]
     if cx.rank == 0:
-        replicated = W > 1 and not hasattr(router, "send_stream")
+        replicated = W > 1 and not hasattr(router, "pipelined")
         merged = {}
         for d in dumps:
             for path, m in d.items():
@@ -576,7 +576,7 @@ def run_b200(args):
     def submit(b, seq, j):
         if world == 1:
             ep, _, _ = router.route(host[b], avail_mask(b), SEED, seq)
-        elif hasattr(router, "send_stream"):      # host inputs are copied on the send stream
+        elif hasattr(router, "pipelined"):      # host inputs are copied on the send stream
             ep, _, _ = router.route(host[b], avail_mask(b), SEED, seq, out=out)
         else:
             ep, _, _ = router.route(host[b].to(dev, non_blocking=True), avail_mask(b), SEED, seq,

@@ -291,6 +291,25 @@ int b200r_part_finish(b200r_trie *t, int64_t n, void *d_my_base, int32_t world, 
                       int64_t cap, int64_t rcap, uint32_t epoch, void *d_work, int32_t *d_endpoint,
                       int32_t *d_match_depth, uint64_t *d_matched, void *stream);
 
+/* The three phases of one batch in ONE call, pipelined over consecutive batches on two
+ * streams the table owns (send, with the SM-filling hashing kernel, at the lowest stream
+ * priority; route + finish at the highest): the send phase of batch b+1 overlaps route and
+ * finish of batch b, and the caller's `stream` waits for the call's results.  d_scratch must
+ * be one of two buffers used in turn (the send phase of batch b+1 runs while batch b's route
+ * phase no longer needs b's scratch, but b's send phase may still be running).
+ * inputs_on_send_stream = 1: the inputs are complete or were copied with
+ * b200r_part_copy_h2d after b200r_part_begin(t, epoch) (a host-to-device copy that overlaps the
+ * previous batch); 0: they were produced on `stream`. */
+int b200r_part_begin(b200r_trie *t, uint32_t epoch);
+int b200r_part_copy_h2d(b200r_trie *t, void *d_dst, const void *h_src, size_t bytes);
+int b200r_part_step(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
+                    const int32_t *d_lens, const int32_t *d_nchars, int64_t n, int64_t max_chunks,
+                    uint32_t flags, uint64_t avail_mask, uint64_t seed, const uint64_t *d_peer_bases,
+                    void *d_my_base, int32_t world, int32_t rank, int64_t cap, int64_t rcap,
+                    uint32_t epoch, void *d_work, void *d_scratch, size_t scratch_bytes,
+                    int32_t *d_endpoint, int32_t *d_match_depth, uint64_t *d_matched,
+                    int32_t inputs_on_send_stream, void *stream);
+
 /* ------------------------------------------------------------------------
  * a9  uhashring.HashRing (md5 points, bisect_right + wrap), a7 SessionRouter
  *                                                   routing_logic.py:84-103,217

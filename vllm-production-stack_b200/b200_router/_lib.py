@@ -62,6 +62,10 @@ SIGNATURES = {
                                   _u32, _vp, _vp, _sz, _vp]),
     "b200r_part_route": (C.c_int, [_vp, _u64, _u64, _vp, _vp, _i32, _i32, _i64, _i64, _u32, _vp, _vp]),
     "b200r_part_finish": (C.c_int, [_vp, _i64, _vp, _i32, _i32, _i64, _i64, _u32, _vp, _vp, _vp, _vp, _vp]),
+    "b200r_part_begin": (C.c_int, [_vp, _u32]),
+    "b200r_part_copy_h2d": (C.c_int, [_vp, _vp, _vp, _sz]),
+    "b200r_part_step": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _u32, _u64, _u64, _vp, _vp, _i32, _i32,
+                                  _i64, _i64, _u32, _vp, _vp, _sz, _vp, _vp, _vp, _i32, _vp]),
     "b200r_set_claim_mode": (C.c_int, [C.c_int]),
     "b200r_prof_enable": (C.c_int, [C.c_int]),
     "b200r_prof_read": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_longlong), C.c_int]),

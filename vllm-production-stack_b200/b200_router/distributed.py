@@ -180,11 +180,10 @@ class PartitionedPrefixRouter:
         self.work = torch.zeros(work_bytes, dtype=torch.uint8, device=self.device)
         self.epoch = 0
         self._shape = None
-        # two-stream pipeline: the send phase of batch b+1 (hashing, never touches the table)
-        # runs on its own stream while route + finish of batch b run on the caller's stream
-        self.send_stream = torch.cuda.Stream(device=self.device)
-        self._sent = torch.cuda.Event()
-        self._finished = [None, None]              # finish events by batch parity
+        # route() pipelines consecutive batches natively (b200r_part_step); the phase_* methods
+        # run the three phases one by one on the current stream (lock-step tests)
+        self.pipelined = True
+        self._keep = [None, None]                  # device copies of host inputs, by batch parity
 
     @staticmethod
     def capacities(max_requests: int, max_chunks: int):
@@ -233,32 +232,57 @@ class PartitionedPrefixRouter:
 
     def route(self, p: PackedPrompts, avail_mask: int, seed: int, seq0: int = 0, out=None,
               inputs_ready: bool = False):
-        """Pipelined: the send phase runs on a second stream.  It may not start before this
-        rank has finished batch b-1 (then every peer has consumed the buffer set it is about
-        to overwrite) and, unless inputs_ready, before the caller's stream has produced the
-        inputs; route and finish stay on the caller's stream, in batch order."""
+        """One native call per batch (b200r_part_step): the send phase runs on a low-priority
+        stream of the library, route and finish on a high-priority one, and the caller's stream
+        waits for the results.  The send phase of batch b+1 overlaps route + finish of batch b;
+        it may not start before this rank has finished batch b-1 (then every peer has consumed
+        the buffer set it is about to overwrite) and, unless inputs_ready, before the caller's
+        stream has produced the inputs.  Host (pinned) inputs are copied on the send stream."""
         if self.epoch == 0 and seq0 != 0:
             raise _lib.B200RouterError("PartitionedPrefixRouter keeps the sequence number on the "
                                        "device; it starts at 0")
-        cur = torch.cuda.current_stream(self.device)
-        ss = self.send_stream
-        prev = self._finished[(self.epoch + 1) & 1]      # batch b-1 (same parity as b+1)
-        if prev is not None:
-            ss.wait_event(prev)
-        if p.bytes.device != self.device:
-            inputs_ready = True                          # copied on the send stream below
-        if not inputs_ready:
-            ss.wait_stream(cur)
-        with torch.cuda.stream(ss):
-            self.phase_send(p)
-            self._sent.record(ss)
-        cur.wait_event(self._sent)
-        self.phase_route(avail_mask, seed)
-        res = self.phase_finish(out)
-        done = torch.cuda.Event()
-        done.record(cur)
-        self._finished[self.epoch & 1] = done
-        return res
+        L = _lib.lib()
+        self.epoch += 1
+        n = p.n
+        with torch.cuda.device(self.device):
+            if p.bytes.device != self.device:
+                _lib.check(L.b200r_part_begin(self.trie._h, self.epoch))
+                k = self.epoch & 1
+                self._keep[k] = None
+                self._keep[k] = p = self._copy_on_send_stream(p)
+                inputs_ready = True
+            flags = _lib.F_ALL_ASCII if p.all_ascii else 0
+            need = L.b200r_prefix_route_scratch_bytes(n, p.max_chunks, flags)
+            sc = self.trie._scratch_for(need)
+            self._shape = (n,)
+            if out is None:
+                out = (torch.empty(max(n, 1), dtype=torch.int32, device=self.device),
+                       torch.empty(max(n, 1), dtype=torch.int32, device=self.device),
+                       torch.empty(max(n, 1), dtype=torch.int64, device=self.device))
+            ep, depth, matched = out
+            rc = L.b200r_part_step(
+                self.trie._h, p.bytes.data_ptr(), p.starts.data_ptr(), p.lens.data_ptr(),
+                None if p.nchars is None else p.nchars.data_ptr(), n, p.max_chunks, flags,
+                avail_mask & M64, seed & M64, self.peer_bases.data_ptr(), self.symm.data_ptr(),
+                self.world, self.rank, self.cap, self.rcap, self.epoch, self.work.data_ptr(),
+                sc.data_ptr(), sc.numel(), ep.data_ptr(), depth.data_ptr(), matched.data_ptr(),
+                1 if inputs_ready else 0, torch.cuda.current_stream(self.device).cuda_stream)
+            if rc:
+                _lib.check(rc)
+        return ep[:n], depth[:n], matched[:n]
+
+    def _copy_on_send_stream(self, p: PackedPrompts) -> PackedPrompts:
+        L = _lib.lib()
+
+        def mv(t):
+            if t is None:
+                return None
+            d = torch.empty(t.shape, dtype=t.dtype, device=self.device)
+            _lib.check(L.b200r_part_copy_h2d(self.trie._h, d.data_ptr(), t.data_ptr(),
+                                             t.numel() * t.element_size()))
+            return d
+        return PackedPrompts(mv(p.bytes), mv(p.starts), mv(p.lens), mv(p.nchars), p.n, p.max_chunks,
+                             p.all_ascii, p.payload_bytes)
 
     def check_status(self, count_nodes=False):
         s = self.trie.check_status(count_nodes)

@@ -94,4 +94,8 @@ struct b200r_trie {
     uint2 *wblk;
     b200r::TrieDev *dev;
     uint32_t epoch;
+    // streams / events of b200r_part_step (created on first use)
+    cudaStream_t part_send, part_route;
+    cudaEvent_t part_inputs, part_sent, part_finished[2];
+    bool part_ready, part_has_finished[2];
 };

@@ -180,8 +180,10 @@ k_part_place(const int32_t *__restrict__ chunk_base, const uint64_t *__restrict_
         dest_slot[i] = ((uint32_t)o << 24) | (uint32_t)rreq;
         s_c[threadIdx.x] = C;
         s_dst[threadIdx.x] = (uint32_t)(totals[2 * world + 2 * o + 1] + rchunk);
+        // {local index, offset of the request's chunks inside this (source, owner) segment}: the
+        // owner gets its CSR offsets from these, without a scan of its own
         info_stage[totals[2 * world + 2 * o] + rreq] =
-            (unsigned long long)(uint32_t)i | ((unsigned long long)(uint32_t)C << 32);
+            (unsigned long long)(uint32_t)i | ((unsigned long long)(uint32_t)rchunk << 32);
     }
     __syncthreads();
     // chunk hashes -> local staging: each warp copies the runs of its 32 requests (coalesced)
@@ -241,12 +243,12 @@ __global__ void k_part_publish_in(const unsigned long long *__restrict__ peer_ba
 }
 
 // Wait for all sources (every CTA spins on the flags itself: they are local memory), then
-// concatenate what they sent, in rank order.  Block 0 also leaves the batch's bookkeeping in
+// concatenate what they sent, in rank order, as the CSR the route stage works on.  Block 0 also leaves the batch's bookkeeping in
 // `dyn` for the kernels that follow.
 __global__ void __launch_bounds__(256)
 k_part_gather(const uint8_t *__restrict__ my_base, int set, unsigned long long epoch,
               size_t hash_off, size_t info_off, int64_t cap, int64_t rcap, int world,
-              PartDyn *dyn, TrieDev *dev, int32_t *__restrict__ c_owned,
+              PartDyn *dyn, TrieDev *dev, int32_t *__restrict__ chunk_base,
               uint32_t *__restrict__ pos_owned, uint64_t *__restrict__ hashes_owned)
 {
     __shared__ uint32_t s_req[P2P_MAX_WORLD + 1], s_chunk[P2P_MAX_WORLD + 1], s_n[P2P_MAX_WORLD + 1];
@@ -286,9 +288,10 @@ k_part_gather(const uint8_t *__restrict__ my_base, int set, unsigned long long e
         int k = 0;
         while (k + 1 < world && j >= s_req[k + 1]) k++;
         const unsigned long long v = info[(size_t)k * rcap + (j - s_req[k])];
-        c_owned[j] = (int32_t)(v >> 32);
+        chunk_base[j] = (int32_t)(s_chunk[k] + (uint32_t)(v >> 32));
         pos_owned[j] = s_n[k] + (uint32_t)v;
     }
+    if (tid == 0) chunk_base[n_owned] = (int32_t)ch_owned;
     for (int64_t x = tid; x < ch_owned; x += step) {
         int k = 0;
         while (k + 1 < world && x >= s_chunk[k + 1]) k++;
@@ -476,7 +479,6 @@ int b200r_part_route(b200r_trie *t, uint64_t avail_mask, uint64_t seed,
     const int set = (int)(epoch & 1);
     uint8_t *base = (uint8_t *)d_my_base, *wk = (uint8_t *)d_work, *sc = wk + L.w_plan;
     PartDyn *dyn = (PartDyn *)(wk + L.w_dyn);
-    int32_t *c_owned = (int32_t *)(wk + L.w_c_owned);
     uint32_t *pos_owned = (uint32_t *)(wk + L.w_pos_owned);
     int32_t *ep = (int32_t *)(wk + L.w_ep), *depth = (int32_t *)(wk + L.w_depth);
     uint64_t *matched = (uint64_t *)(wk + L.w_matched);
@@ -484,19 +486,14 @@ int b200r_part_route(b200r_trie *t, uint64_t avail_mask, uint64_t seed,
     uint64_t *hashes = (uint64_t *)(sc + p.off_hashes);
     uint32_t *slots = (uint32_t *)(sc + p.off_slots);
     int32_t *leader = (int32_t *)(sc + p.off_leader), *choice = (int32_t *)(sc + p.off_choice);
-    int32_t *block_sums = (int32_t *)(sc + p.off_block_sums);
     const int32_t *n_dev = &dyn->n_owned;
 
     { ProfScope ps__(PK_WAIT, st); g_launches += 1;
     k_part_gather<<<148 * 4, 256, 0, st>>>(base, set, (unsigned long long)epoch,
                                            L.hash_off + (size_t)set * L.hash_set,
                                            L.info_off + (size_t)set * L.info_set, cap, rcap, world, dyn,
-                                           t->dev, c_owned, pos_owned, hashes);
+                                           t->dev, chunk_base, pos_owned, hashes);
     B200R_LAUNCH_CHECK("k_part_gather");
-    }
-    { ProfScope ps__(PK_PREP, st);
-    rc = launch_prep_counts(c_owned, L.n_max, n_dev, block_sums, chunk_base, L.c_max, t->dev, st);
-    if (rc) return rc;
     }
     // grids are estimates (about two shards' worth); the kernels stride over the rest
     RouteCore core = RouteCore();
@@ -539,6 +536,76 @@ int b200r_part_finish(b200r_trie *t, int64_t n, void *d_my_base, int32_t world, 
         L.res_off + (size_t)set * L.res_set, rcap, (int)n, d_endpoint, d_match_depth, d_matched);
     B200R_LAUNCH_CHECK("k_part_scatter");
     }
+    return B200R_OK;
+}
+
+// One call per batch: the three phases with the stream handling done natively (in Python it
+// cost more host time per batch than the GPU needs).  The send phase (hashing: fills every SM)
+// runs on an internal low-priority stream, route + finish on an internal high-priority one; the
+// send of batch b+1 overlaps route + finish of batch b.
+static int part_streams(b200r_trie *t)
+{
+    if (t->part_ready) return B200R_OK;
+    int least = 0, greatest = 0;
+    B200R_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+    B200R_CUDA(cudaStreamCreateWithPriority(&t->part_send, cudaStreamNonBlocking, least));
+    B200R_CUDA(cudaStreamCreateWithPriority(&t->part_route, cudaStreamNonBlocking, greatest));
+    B200R_CUDA(cudaEventCreateWithFlags(&t->part_inputs, cudaEventDisableTiming));
+    B200R_CUDA(cudaEventCreateWithFlags(&t->part_sent, cudaEventDisableTiming));
+    B200R_CUDA(cudaEventCreateWithFlags(&t->part_finished[0], cudaEventDisableTiming));
+    B200R_CUDA(cudaEventCreateWithFlags(&t->part_finished[1], cudaEventDisableTiming));
+    t->part_ready = true;
+    return B200R_OK;
+}
+
+int b200r_part_begin(b200r_trie *t, uint32_t epoch)
+{
+    if (!t) { set_error("null trie"); return B200R_E_INVALID; }
+    int rc = part_streams(t);
+    if (rc) return rc;
+    // the send phase of batch `epoch` overwrites the buffer set batch epoch-2 used and may only
+    // start when this rank has finished batch epoch-1 (then every peer has consumed that set)
+    const int prev = (int)((epoch + 1) & 1);
+    if (t->part_has_finished[prev]) B200R_CUDA(cudaStreamWaitEvent(t->part_send, t->part_finished[prev], 0));
+    return B200R_OK;
+}
+
+int b200r_part_copy_h2d(b200r_trie *t, void *d_dst, const void *h_src, size_t bytes)
+{
+    if (!t || !t->part_ready || (bytes && (!d_dst || !h_src))) { set_error("b200r_part_copy_h2d: bad argument (call b200r_part_begin first)"); return B200R_E_INVALID; }
+    if (bytes) B200R_CUDA(cudaMemcpyAsync(d_dst, h_src, bytes, cudaMemcpyHostToDevice, t->part_send));
+    return B200R_OK;
+}
+
+int b200r_part_step(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
+                    const int32_t *d_lens, const int32_t *d_nchars, int64_t n, int64_t max_chunks,
+                    uint32_t flags, uint64_t avail_mask, uint64_t seed, const uint64_t *d_peer_bases,
+                    void *d_my_base, int32_t world, int32_t rank, int64_t cap, int64_t rcap,
+                    uint32_t epoch, void *d_work, void *d_scratch, size_t scratch_bytes,
+                    int32_t *d_endpoint, int32_t *d_match_depth, uint64_t *d_matched,
+                    int32_t inputs_on_send_stream, void *stream)
+{
+    int rc = b200r_part_begin(t, epoch);
+    if (rc) return rc;
+    cudaStream_t cur = (cudaStream_t)stream;
+    B200R_CUDA(cudaEventRecord(t->part_inputs, cur));
+    if (!inputs_on_send_stream) B200R_CUDA(cudaStreamWaitEvent(t->part_send, t->part_inputs, 0));
+    rc = b200r_part_send(t, d_bytes, d_starts, d_lens, d_nchars, n, max_chunks, flags, d_peer_bases,
+                         world, rank, cap, rcap, epoch, d_work, d_scratch, scratch_bytes, t->part_send);
+    if (rc) return rc;
+    B200R_CUDA(cudaEventRecord(t->part_sent, t->part_send));
+    B200R_CUDA(cudaStreamWaitEvent(t->part_route, t->part_sent, 0));
+    B200R_CUDA(cudaStreamWaitEvent(t->part_route, t->part_inputs, 0));      // the outputs may be in use
+    rc = b200r_part_route(t, avail_mask, seed, d_peer_bases, d_my_base, world, rank, cap, rcap, epoch,
+                          d_work, t->part_route);
+    if (rc) return rc;
+    rc = b200r_part_finish(t, n, d_my_base, world, rank, cap, rcap, epoch, d_work, d_endpoint,
+                           d_match_depth, d_matched, t->part_route);
+    if (rc) return rc;
+    const int me = (int)(epoch & 1);
+    B200R_CUDA(cudaEventRecord(t->part_finished[me], t->part_route));
+    t->part_has_finished[me] = true;
+    B200R_CUDA(cudaStreamWaitEvent(cur, t->part_finished[me], 0));
     return B200R_OK;
 }
 

@@ -411,16 +411,33 @@ select_request(int i, const Rec *__restrict__ log, const int32_t *__restrict__ c
     const ReqSpan sp = req_span(chunk_base, i, max_chunks);
     const uint32_t *sl = slots + sp.b0;
     const int d0 = dpre[i];
+    // "node d was touched by an earlier request of this batch" is a prefix property (whoever
+    // touched a node touched everything above it on the same path, no later): find the last
+    // such depth -- linear for the first few, then by bisection (long prompts: C4 has 256)
+    const uint32_t me = req_off + (uint32_t)i;
+    auto touched = [&](int d, uint32_t &f) -> bool {
+        const uint32_t x = sl[d];
+        if (x == SLOT_NONE) return false;
+        const unsigned long long fv = log[x & IDX_MASK].first;
+        f = ~(uint32_t)fv;
+        return ((fv >> 32) == (tag >> 32)) && f < me;
+    };
     int dstar = d0;
     uint32_t star_first = 0;
-    for (int d = d0; d < sp.C; d++) {
-        const uint32_t x = sl[d];
-        if (x == SLOT_NONE) break;
-        const unsigned long long fv = log[x & IDX_MASK].first;
-        const uint32_t f = ~(uint32_t)fv;
-        if (!(((fv >> 32) == (tag >> 32)) && f < req_off + (uint32_t)i)) break;
-        dstar = d + 1;
-        star_first = f;
+    int lo = d0, probes = 0;
+    while (lo < sp.C && probes < 4) {
+        uint32_t f;
+        if (!touched(lo, f)) break;
+        star_first = f; dstar = ++lo; probes++;
+    }
+    if (probes == 4 && lo < sp.C) {
+        int hi = sp.C;                          // invariant: depths < lo touched, depth hi not
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            uint32_t f;
+            if (touched(mid, f)) { star_first = f; dstar = mid + 1; lo = mid + 1; }
+            else hi = mid;
+        }
     }
     depth_out[i] = dstar;
     if (dstar == d0) {
@@ -934,6 +951,7 @@ int b200r_trie_create(int32_t cap_log2, int32_t chunk_chars, b200r_trie **out)
     t->chunk_chars = chunk_chars;
     t->epoch = 0;
     t->tab = nullptr; t->log = nullptr; t->wblk = nullptr; t->dev = nullptr;
+    t->part_ready = false; t->part_has_finished[0] = t->part_has_finished[1] = false;
     const size_t cap = (size_t)1 << cap_log2;
     cudaError_t e;
     if ((e = cudaMalloc(&t->tab, 2 * cap * sizeof(Head))) != cudaSuccess ||
@@ -954,6 +972,12 @@ int b200r_trie_create(int32_t cap_log2, int32_t chunk_chars, b200r_trie **out)
 int b200r_trie_destroy(b200r_trie *t)
 {
     if (!t) return B200R_OK;
+    if (t->part_ready) {
+        cudaStreamSynchronize(t->part_send); cudaStreamSynchronize(t->part_route);
+        cudaEventDestroy(t->part_inputs); cudaEventDestroy(t->part_sent);
+        cudaEventDestroy(t->part_finished[0]); cudaEventDestroy(t->part_finished[1]);
+        cudaStreamDestroy(t->part_send); cudaStreamDestroy(t->part_route);
+    }
     cudaFree(t->tab); cudaFree(t->log); cudaFree(t->wblk); cudaFree(t->dev);
     delete t;
     return B200R_OK;

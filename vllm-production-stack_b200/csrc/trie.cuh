@@ -560,7 +560,12 @@ k_claim_thread(WalkArgs a, int n, const int32_t *__restrict__ n_dev)
             // ---- find: follow stored runs as far as they go
             while (todo && d < C) {
                 uint64_t h = hs[d];
-                const uint32_t idx = head_find(t.tab, t.tab_log2, h, parent_key(pidx), coherent, eslot);
+                uint32_t idx = head_find(t.tab, t.tab_log2, h, parent_key(pidx), coherent, eslot);
+                // a long stretch is about to be created: look once more, past L1 -- when many
+                // requests meet a new shared prefix at the same moment, most of them then find the
+                // winner's run instead of writing (and wasting) a copy of their own
+                if (idx == SLOT_NONE && !coherent && C - d >= 8)
+                    idx = head_find(t.tab, t.tab_log2, h, parent_key(pidx), true, eslot);
                 if (idx == SLOT_NONE) { hd = h; break; }
                 // the head record first: it matches by its key and tells how long the run is
                 uint32_t room, k = 1;
@@ -585,18 +590,19 @@ k_claim_thread(WalkArgs a, int n, const int32_t *__restrict__ n_dev)
                     uint64_t rh[4], m[4], rc[4], hh[4];
                     unsigned long long f[4];
                     const int nl = min(min((int)(room - k), C - d), 4);
+                    const Rec *grp = t.log + idx + k;           // k moves on below: fix the group's base
 #pragma unroll
                     for (int j = 0; j < 4; j++) {
                         rh[j] = 0; m[j] = 0; rc[j] = 0; f[j] = 0; hh[j] = 0;
                         if (j < nl) {
                             hh[j] = hs[d + j];
-                            ld_rec(t.log + idx + k + j, rh[j], m[j], f[j], rc[j]);
+                            ld_rec(grp + j, rh[j], m[j], f[j], rc[j]);
                         }
                     }
 #pragma unroll
                     for (int j = 0; j < 4; j++) {
                         if (j < nl && !left) {
-                            while (!rec_whole(rh[j], rc[j])) ld_rec_cg(t.log + idx + k + j, rh[j], m[j], f[j], rc[j]);
+                            while (!rec_whole(rh[j], rc[j])) ld_rec_cg(grp + j, rh[j], m[j], f[j], rc[j]);
                             if (rh[j] != hh[j]) {
                                 left = true;                    // the path leaves the run here
                             } else {
