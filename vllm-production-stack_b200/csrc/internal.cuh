@@ -76,7 +76,7 @@ struct RouteCore {
     uint64_t avail, seed, seq0;
     uint32_t *slots; int32_t *leader, *choice, *dpre; uint64_t *cand;
     int32_t *endpoint, *depth; uint64_t *matched;
-    const P2PDyn *dyn; const uint32_t *pos; const int32_t *n_dev;
+    const P2PDyn *dyn; const uint32_t *pos; const uint32_t *idx_of_pos; const int32_t *n_dev;
     int claim_kind;       // claim_kind_for()
 };
 int launch_route_core(b200r_trie *t, const RouteCore &rc, cudaStream_t st);

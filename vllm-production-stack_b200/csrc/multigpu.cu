@@ -81,74 +81,24 @@ __device__ __forceinline__ int part_owner(const uint64_t *hashes, int b, int C, 
 
 constexpr int PART_BLOCK = 256;
 
-// per block of 256 requests: how many requests / chunks go to each owner
-__global__ void __launch_bounds__(PART_BLOCK)
-k_part_count(const int32_t *__restrict__ chunk_base, const uint64_t *__restrict__ hashes, int n,
-             int world, int32_t *__restrict__ blk_cnt)
-{
-    __shared__ int s_cnt[2 * P2P_MAX_WORLD];
-    for (int k = threadIdx.x; k < 2 * world; k += PART_BLOCK) s_cnt[k] = 0;
-    __syncthreads();
-    const int i = blockIdx.x * PART_BLOCK + threadIdx.x;
-    if (i < n) {
-        const int b = chunk_base[i], C = chunk_base[i + 1] - b;
-        const int o = part_owner(hashes, b, C, world);
-        atomicAdd(&s_cnt[2 * o], 1);
-        atomicAdd(&s_cnt[2 * o + 1], C);
-    }
-    __syncthreads();
-    for (int k = threadIdx.x; k < 2 * world; k += PART_BLOCK)
-        blk_cnt[(size_t)blockIdx.x * 2 * world + k] = s_cnt[k];
-}
-
-// exclusive scan over the blocks, per owner and kind (one warp each, 32 blocks per step)
-__global__ void k_part_scan(const int32_t *__restrict__ blk_cnt, int nblk, int world,
-                            int32_t *__restrict__ blk_off, int32_t *__restrict__ totals)
-{
-    const int lane = threadIdx.x & 31;
-    const int nwarps = blockDim.x >> 5;
-    for (int k = threadIdx.x >> 5; k < 2 * world; k += nwarps) {
-        int run = 0;
-        for (int b0 = 0; b0 < nblk; b0 += 32) {
-            const int b = b0 + lane;
-            const int v = b < nblk ? blk_cnt[(size_t)b * 2 * world + k] : 0;
-            int inc = v;
-            for (int sft = 1; sft < 32; sft <<= 1) {
-                const int t = __shfl_up_sync(0xffffffffu, inc, sft);
-                if (lane >= sft) inc += t;
-            }
-            if (b < nblk) blk_off[(size_t)b * 2 * world + k] = run + inc - v;
-            run += __shfl_sync(0xffffffffu, inc, 31);
-        }
-        if (lane == 0) totals[k] = run;
-    }
-    // starts of the per-owner segments in the local staging buffers (even, so that every
-    // segment can be copied with 16-byte vectors): totals[2*world + 2*o] requests, [+1] chunks
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        int r = 0, c = 0;
-        for (int o = 0; o < world; o++) {
-            totals[2 * world + 2 * o] = r; totals[2 * world + 2 * o + 1] = c;
-            r += (totals[2 * o] + 1) & ~1; c += (totals[2 * o + 1] + 1) & ~1;
-        }
-    }
-}
-
-// order-preserving compaction per owner: where does every request (and its run of chunk
-// hashes) go in its owner's buffer?  The {local index, chunk count} words and the hashes
-// are first compacted into LOCAL staging buffers, one contiguous segment per owner, and then
-// shipped by k_part_bulk with full-line 16-byte vector stores: NVLink moves the same bytes
-// several times faster in 128-byte lines than as 8-byte words or ragged ~170-byte runs
-// (measured at 2 GPUs: 47 us per shard for direct scattered peer stores).
+// Where does every request (and its run of chunk hashes) go in its owner's buffer?  Requests
+// need not arrive in order: the owner identifies a request by its GLOBAL position (source
+// offset + local index), which is what "first toucher", leader links and the tie-break counter
+// are expressed in.  So a slot in the (source, owner) segment is simply taken with one packed
+// atomicAdd per warp and owner {requests << 32 | chunks} -- no counting pass, no scan.  The
+// {local index, chunk offset in the segment} words and the hashes are first compacted into
+// LOCAL staging segments (one per owner, fixed capacity) and then shipped by k_part_bulk with
+// full-line 16-byte vector stores: NVLink moves the same bytes several times faster in
+// 128-byte lines than as 8-byte words or ragged ~170-byte runs (measured at 2 GPUs: 47 us per
+// shard for direct scattered peer stores).
 __global__ void __launch_bounds__(PART_BLOCK)
 k_part_place(const int32_t *__restrict__ chunk_base, const uint64_t *__restrict__ hashes, int n,
-             int world, const int32_t *__restrict__ blk_off, const int32_t *__restrict__ totals,
+             int world, unsigned long long *__restrict__ totals, int64_t cap, int64_t rcap,
              unsigned long long *__restrict__ info_stage, uint32_t *__restrict__ dest_slot,
              uint64_t *__restrict__ hash_stage)
 {
-    __shared__ int s_w[PART_BLOCK / 32][2 * P2P_MAX_WORLD];
     __shared__ int s_b[PART_BLOCK], s_c[PART_BLOCK];
-    __shared__ uint32_t s_dst[PART_BLOCK];
+    __shared__ unsigned long long s_dst[PART_BLOCK];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int i = blockIdx.x * PART_BLOCK + threadIdx.x;
     int b = 0, C = 0, o = -1;
@@ -157,33 +107,32 @@ k_part_place(const int32_t *__restrict__ chunk_base, const uint64_t *__restrict_
         C = chunk_base[i + 1] - b;
         o = part_owner(hashes, b, C, world);
     }
-    // rank of this request / its chunks among the warp's earlier requests of the same owner
-    int rreq = 0, rchunk = 0;
+    uint32_t rreq = 0, rchunk = 0;
     for (int d = 0; d < world; d++) {
         const unsigned m = __ballot_sync(0xffffffffu, o == d);
+        if (!m) continue;                                   // warp-uniform
         int v = (o == d) ? C : 0, inc = v;
         for (int sft = 1; sft < 32; sft <<= 1) {
             const int t = __shfl_up_sync(0xffffffffu, inc, sft);
             if (lane >= sft) inc += t;
         }
-        if (o == d) { rreq = __popc(m & ((1u << lane) - 1)); rchunk = inc - v; }
-        if (lane == 31) { s_w[w][2 * d] = __popc(m); s_w[w][2 * d + 1] = inc; }
+        const int tot = __shfl_sync(0xffffffffu, inc, 31);
+        unsigned long long base = 0;
+        if (lane == 0)
+            base = atomicAdd(&totals[d], ((unsigned long long)__popc(m) << 32) | (unsigned long long)(uint32_t)tot);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (o == d) {
+            rreq = (uint32_t)(base >> 32) + (uint32_t)__popc(m & ((1u << lane) - 1));
+            rchunk = (uint32_t)base + (uint32_t)(inc - v);
+        }
     }
-    __syncthreads();
     s_b[threadIdx.x] = b; s_c[threadIdx.x] = 0; s_dst[threadIdx.x] = 0;
     if (o >= 0) {
-        int breq = blk_off[(size_t)blockIdx.x * 2 * world + 2 * o];
-        int bchunk = blk_off[(size_t)blockIdx.x * 2 * world + 2 * o + 1];
-        for (int k = 0; k < w; k++) { breq += s_w[k][2 * o]; bchunk += s_w[k][2 * o + 1]; }
-        rreq += breq;
-        rchunk += bchunk;
-        dest_slot[i] = ((uint32_t)o << 24) | (uint32_t)rreq;
+        dest_slot[i] = ((uint32_t)o << 24) | rreq;
         s_c[threadIdx.x] = C;
-        s_dst[threadIdx.x] = (uint32_t)(totals[2 * world + 2 * o + 1] + rchunk);
-        // {local index, offset of the request's chunks inside this (source, owner) segment}: the
-        // owner gets its CSR offsets from these, without a scan of its own
-        info_stage[totals[2 * world + 2 * o] + rreq] =
-            (unsigned long long)(uint32_t)i | ((unsigned long long)(uint32_t)rchunk << 32);
+        s_dst[threadIdx.x] = (unsigned long long)o * (unsigned long long)cap + rchunk;
+        info_stage[(size_t)o * rcap + rreq] =
+            (unsigned long long)(uint32_t)i | ((unsigned long long)rchunk << 32);
     }
     __syncthreads();
     // chunk hashes -> local staging: each warp copies the runs of its 32 requests (coalesced)
@@ -200,7 +149,7 @@ k_part_place(const int32_t *__restrict__ chunk_base, const uint64_t *__restrict_
 // the last CTA to finish publishes the arrival flags (no separate launch).
 __global__ void __launch_bounds__(256)
 k_part_bulk(const uint64_t *__restrict__ hash_stage, const unsigned long long *__restrict__ info_stage,
-            const int32_t *__restrict__ totals, int world, int my_rank,
+            unsigned long long *__restrict__ totals, int world, int my_rank,
             const unsigned long long *__restrict__ peer_bases, size_t hash_off, size_t info_off,
             int64_t cap, int64_t rcap, unsigned int *ticket, int set, unsigned long long epoch,
             unsigned int n)
@@ -209,50 +158,48 @@ k_part_bulk(const uint64_t *__restrict__ hash_stage, const unsigned long long *_
     const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
     for (int k = 0; k < world; k++) {
         const int o = (my_rank + 1 + k) % world;       // start with the next rank: spread the links
-        const int nreq = totals[2 * o], nchunk = totals[2 * o + 1];
-        const uint4 *hs = (const uint4 *)(hash_stage + totals[2 * world + 2 * o + 1]);
+        const unsigned long long tt = totals[o];
+        const int nreq = (int)(tt >> 32), nchunk = (int)(uint32_t)tt;
+        const uint4 *hs = (const uint4 *)(hash_stage + (size_t)o * cap);
         uint4 *hd = (uint4 *)((uint64_t *)(uintptr_t)(peer_bases[o] + hash_off) + (size_t)my_rank * cap);
         for (int64_t x = tid; x < (nchunk + 1) / 2; x += nthr) hd[x] = hs[x];
-        const uint4 *is = (const uint4 *)(info_stage + totals[2 * world + 2 * o]);
+        const uint4 *is = (const uint4 *)(info_stage + (size_t)o * rcap);
         uint4 *id = (uint4 *)((unsigned long long *)(uintptr_t)(peer_bases[o] + info_off) + (size_t)my_rank * rcap);
         for (int64_t x = tid; x < (nreq + 1) / 2; x += nthr) id[x] = is[x];
     }
     if (last_cta_after_peer_stores(ticket) && (int)threadIdx.x < world) {
         const int d = threadIdx.x;
+        const unsigned long long tt = totals[d];
         PartFlags *f = (PartFlags *)(uintptr_t)peer_bases[d];
         *(volatile unsigned long long *)&f->in_n[set][my_rank] = (epoch << 32) | n;
-        *(volatile unsigned long long *)&f->in_chunk[set][my_rank] = (epoch << 32) | (uint32_t)totals[2 * d + 1];
-        *(volatile unsigned long long *)&f->in_req[set][my_rank] = (epoch << 32) | (uint32_t)totals[2 * d];
+        *(volatile unsigned long long *)&f->in_chunk[set][my_rank] = (epoch << 32) | (uint32_t)tt;
+        *(volatile unsigned long long *)&f->in_req[set][my_rank] = (epoch << 32) | (uint32_t)(tt >> 32);
         __threadfence_system();
+        totals[d] = 0;                                 // every CTA has read it: ready for the next batch
     }
 }
 
 // batch with no request at all on this rank: only the flags
 __global__ void k_part_publish_in(const unsigned long long *__restrict__ peer_bases, int world,
-                                  int my_rank, int set, unsigned long long epoch,
-                                  const int32_t *__restrict__ totals, unsigned int n)
+                                  int my_rank, int set, unsigned long long epoch, unsigned int n)
 {
     const int d = threadIdx.x;
     if (d >= world) return;
     PartFlags *f = (PartFlags *)(uintptr_t)peer_bases[d];
     __threadfence_system();
     *(volatile unsigned long long *)&f->in_n[set][my_rank] = (epoch << 32) | n;
-    *(volatile unsigned long long *)&f->in_chunk[set][my_rank] = (epoch << 32) | (uint32_t)totals[2 * d + 1];
-    *(volatile unsigned long long *)&f->in_req[set][my_rank] = (epoch << 32) | (uint32_t)totals[2 * d];
+    *(volatile unsigned long long *)&f->in_chunk[set][my_rank] = (epoch << 32);
+    *(volatile unsigned long long *)&f->in_req[set][my_rank] = (epoch << 32);
     __threadfence_system();
 }
 
-// Wait for all sources (every CTA spins on the flags itself: they are local memory), then
-// concatenate what they sent, in rank order, as the CSR the route stage works on.  Block 0 also leaves the batch's bookkeeping in
-// `dyn` for the kernels that follow.
-__global__ void __launch_bounds__(256)
-k_part_gather(const uint8_t *__restrict__ my_base, int set, unsigned long long epoch,
-              size_t hash_off, size_t info_off, int64_t cap, int64_t rcap, int world,
-              PartDyn *dyn, TrieDev *dev, int32_t *__restrict__ chunk_base,
-              uint32_t *__restrict__ pos_owned, uint64_t *__restrict__ hashes_owned)
+// Wait for all sources.  ONE small CTA spins on the arrival flags (local memory): a grid of
+// spinning CTAs would hold SM slots that the next batch's send phase needs while the slowest
+// peer is still on its way.  Leaves the batch's bookkeeping in `dyn`.
+__global__ void k_part_wait_meta(const PartFlags *__restrict__ mine, int set, unsigned long long epoch,
+                                 int world, PartDyn *dyn, TrieDev *dev)
 {
-    __shared__ uint32_t s_req[P2P_MAX_WORLD + 1], s_chunk[P2P_MAX_WORLD + 1], s_n[P2P_MAX_WORLD + 1];
-    const PartFlags *mine = (const PartFlags *)my_base;
+    __shared__ uint32_t s_req[P2P_MAX_WORLD], s_chunk[P2P_MAX_WORLD], s_n[P2P_MAX_WORLD];
     const int q = threadIdx.x;
     if (q < world) {
         unsigned long long a = 0, b = 0, c = 0;
@@ -261,22 +208,31 @@ k_part_gather(const uint8_t *__restrict__ my_base, int set, unsigned long long e
                         p2p_spin(&mine->in_n[set][q], epoch, &c);
         if (!ok) atomicOr(&dev->status, B200R_S_PEER_TIMEOUT);
         s_req[q] = ok ? (uint32_t)a : 0; s_chunk[q] = ok ? (uint32_t)b : 0; s_n[q] = ok ? (uint32_t)c : 0;
-        __threadfence();                      // flags before data
     }
     __syncthreads();
-    if (threadIdx.x == 0) {                   // counts -> exclusive bases, in place
+    if (threadIdx.x == 0) {
         uint32_t r = 0, c = 0, o = 0;
         for (int k = 0; k < world; k++) {
-            const uint32_t a = s_req[k], b = s_chunk[k], d = s_n[k];
-            s_req[k] = r; s_chunk[k] = c; s_n[k] = o;
-            r += a; c += b; o += d;
+            dyn->reqbase[k] = r; dyn->chunkbase[k] = c; dyn->off[k] = o;
+            r += s_req[k]; c += s_chunk[k]; o += s_n[k];
         }
-        s_req[world] = r; s_chunk[world] = c; s_n[world] = o;
-        if (blockIdx.x == 0) {
-            for (int k = 0; k <= world; k++) { dyn->reqbase[k] = s_req[k]; dyn->chunkbase[k] = s_chunk[k]; dyn->off[k] = s_n[k]; }
-            dyn->n_owned = (int32_t)r; dyn->c_owned = (int32_t)c;
-            dyn->base.my_off = 0; dyn->base.total_n = o;
-        }
+        dyn->reqbase[world] = r; dyn->chunkbase[world] = c; dyn->off[world] = o;
+        dyn->n_owned = (int32_t)r; dyn->c_owned = (int32_t)c;
+        dyn->base.my_off = 0; dyn->base.total_n = o;
+    }
+    __threadfence_system();
+}
+
+// concatenate what the sources sent, in rank order, as the CSR the route stage works on
+__global__ void __launch_bounds__(256)
+k_part_gather(const uint8_t *__restrict__ my_base, size_t hash_off, size_t info_off, int64_t cap,
+              int64_t rcap, int world, const PartDyn *__restrict__ dyn,
+              int32_t *__restrict__ chunk_base, uint32_t *__restrict__ pos_owned,
+              uint32_t *__restrict__ idx_of_pos, uint64_t *__restrict__ hashes_owned)
+{
+    __shared__ uint32_t s_req[P2P_MAX_WORLD + 1], s_chunk[P2P_MAX_WORLD + 1], s_n[P2P_MAX_WORLD + 1];
+    for (int k = threadIdx.x; k <= world; k += blockDim.x) {
+        s_req[k] = dyn->reqbase[k]; s_chunk[k] = dyn->chunkbase[k]; s_n[k] = dyn->off[k];
     }
     __syncthreads();
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -289,7 +245,9 @@ k_part_gather(const uint8_t *__restrict__ my_base, int set, unsigned long long e
         while (k + 1 < world && j >= s_req[k + 1]) k++;
         const unsigned long long v = info[(size_t)k * rcap + (j - s_req[k])];
         chunk_base[j] = (int32_t)(s_chunk[k] + (uint32_t)(v >> 32));
-        pos_owned[j] = s_n[k] + (uint32_t)v;
+        const uint32_t gp = s_n[k] + (uint32_t)v;       // position in the global (rank-major) batch
+        pos_owned[j] = gp;
+        idx_of_pos[gp] = (uint32_t)j;
     }
     if (tid == 0) chunk_base[n_owned] = (int32_t)ch_owned;
     for (int64_t x = tid; x < ch_owned; x += step) {
@@ -323,22 +281,27 @@ k_part_push_results(PartDyn *dyn, int world, int my_rank,
     }
 }
 
-// wait for all owners' results (every CTA spins on the local flags), then scatter them to
-// request order; block 0 advances the global sequence number to the next batch's request 0
+// wait for all owners' results (one small CTA, see k_part_wait_meta); advances the global
+// sequence number to the next batch's request 0
+__global__ void k_part_wait_res(const PartFlags *__restrict__ mine, int set, unsigned long long epoch,
+                                int world, TrieDev *dev, PartDyn *dyn)
+{
+    const int q = threadIdx.x;
+    if (q < world) {
+        unsigned long long v;
+        if (!p2p_spin(&mine->res[set][q], epoch, &v)) atomicOr(&dev->status, B200R_S_PEER_TIMEOUT);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) dyn->base.seq_base += dyn->base.total_n;   // next batch's request 0
+    __threadfence_system();
+}
+
+// results back to request order
 __global__ void __launch_bounds__(256)
 k_part_scatter(const uint32_t *__restrict__ dest_slot, const uint8_t *__restrict__ my_base,
-               int set, unsigned long long epoch, int world, TrieDev *dev, PartDyn *dyn,
                size_t res_off, int64_t rcap, int n, int32_t *__restrict__ endpoint,
                int32_t *__restrict__ depth, uint64_t *__restrict__ matched)
 {
-    const PartFlags *mine = (const PartFlags *)my_base;
-    if ((int)threadIdx.x < world) {
-        unsigned long long v;
-        if (!p2p_spin(&mine->res[set][threadIdx.x], epoch, &v)) atomicOr(&dev->status, B200R_S_PEER_TIMEOUT);
-        __threadfence();
-    }
-    __syncthreads();
-    if (blockIdx.x == 0 && threadIdx.x == 0) dyn->base.seq_base += dyn->base.total_n;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const uint32_t ds = dest_slot[i];
@@ -356,7 +319,7 @@ extern "C" {
 struct PartLayout {
     size_t symm_total, hash_off, info_off, res_off, hash_set, info_set, res_set;
     // local work buffer
-    size_t work_total, w_dyn, w_blk_cnt, w_blk_off, w_totals, w_dest_slot, w_req_dst, w_hash_stage, w_info_stage, w_c_owned, w_pos_owned,
+    size_t work_total, w_dyn, w_totals, w_dest_slot, w_hash_stage, w_info_stage, w_pos_owned, w_idx_of_pos,
         w_ep, w_depth, w_matched, w_plan;
     int64_t n_max, c_max;
     int nblk_max;
@@ -377,15 +340,12 @@ static PartLayout part_layout(int world, int64_t cap, int64_t rcap)
     L.nblk_max = (int)((rcap + PART_BLOCK - 1) / PART_BLOCK);
     size_t o = 0;
     L.w_dyn = o;       o += align_up(sizeof(PartDyn));
-    L.w_blk_cnt = o;   o += align_up((size_t)L.nblk_max * 2 * world * 4);
-    L.w_blk_off = o;   o += align_up((size_t)L.nblk_max * 2 * world * 4);
-    L.w_totals = o;    o += align_up((size_t)4 * world * 4);
+    L.w_totals = o;    o += align_up((size_t)world * 8);
     L.w_dest_slot = o; o += 2 * align_up((size_t)rcap * 4);     // one per batch parity
-    L.w_req_dst = o;   o += align_up((size_t)rcap * 4);
-    L.w_hash_stage = o; o += align_up((size_t)(cap + 2 * world + 2) * 8);
-    L.w_info_stage = o; o += align_up((size_t)(rcap + 2 * world + 2) * 8);
-    L.w_c_owned = o;   o += align_up((size_t)L.n_max * 4);
+    L.w_hash_stage = o; o += align_up((size_t)world * (cap + 2) * 8);   // one fixed segment per owner
+    L.w_info_stage = o; o += align_up((size_t)world * (rcap + 2) * 8);
     L.w_pos_owned = o; o += align_up((size_t)L.n_max * 4);
+    L.w_idx_of_pos = o; o += align_up((size_t)L.n_max * 4);
     L.w_ep = o;        o += align_up((size_t)L.n_max * 4);
     L.w_depth = o;     o += align_up((size_t)L.n_max * 4);
     L.w_matched = o;   o += align_up((size_t)L.n_max * 8);
@@ -432,22 +392,17 @@ int b200r_part_send(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_star
     uint8_t *sc = (uint8_t *)d_scratch, *wk = (uint8_t *)d_work;
     const int32_t *chunk_base = (const int32_t *)(sc + p.off_chunk_base);
     const uint64_t *hashes = (const uint64_t *)(sc + p.off_hashes);
-    int32_t *blk_cnt = (int32_t *)(wk + L.w_blk_cnt), *blk_off = (int32_t *)(wk + L.w_blk_off);
-    int32_t *totals = (int32_t *)(wk + L.w_totals);
+    unsigned long long *totals = (unsigned long long *)(wk + L.w_totals);
     const int set = (int)(epoch & 1);
     const int nblk = (int)((n + PART_BLOCK - 1) / PART_BLOCK);
     PartDyn *dyn = (PartDyn *)(wk + L.w_dyn);
     ProfScope ps__(PK_PUSH, st);
     if (nblk > 0) {
-        g_launches += 4;
-        k_part_count<<<nblk, PART_BLOCK, 0, st>>>(chunk_base, hashes, (int)n, world, blk_cnt);
-        B200R_LAUNCH_CHECK("k_part_count");
-        k_part_scan<<<1, 1024, 0, st>>>(blk_cnt, nblk, world, blk_off, totals);
-        B200R_LAUNCH_CHECK("k_part_scan");
+        g_launches += 2;
         uint32_t *dest_slot = (uint32_t *)(wk + L.w_dest_slot + (size_t)set * align_up((size_t)rcap * 4));
         uint64_t *hash_stage = (uint64_t *)(wk + L.w_hash_stage);
         unsigned long long *info_stage = (unsigned long long *)(wk + L.w_info_stage);
-        k_part_place<<<nblk, PART_BLOCK, 0, st>>>(chunk_base, hashes, (int)n, world, blk_off, totals,
+        k_part_place<<<nblk, PART_BLOCK, 0, st>>>(chunk_base, hashes, (int)n, world, totals, cap, rcap,
                                                   info_stage, dest_slot, hash_stage);
         B200R_LAUNCH_CHECK("k_part_place");
         k_part_bulk<<<148 * 2, 256, 0, st>>>(hash_stage, info_stage, totals, world, rank,
@@ -457,10 +412,9 @@ int b200r_part_send(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_star
                                              &dyn->ticket_bulk, set, (unsigned long long)epoch, (unsigned)n);
         B200R_LAUNCH_CHECK("k_part_bulk");
     } else {
-        B200R_CUDA(cudaMemsetAsync(totals, 0, (size_t)4 * world * 4, st));
         g_launches += 1;
         k_part_publish_in<<<1, P2P_MAX_WORLD, 0, st>>>((const unsigned long long *)d_peer_bases, world, rank,
-                                                       set, epoch, totals, (unsigned)n);
+                                                       set, epoch, (unsigned)n);
         B200R_LAUNCH_CHECK("k_part_publish_in");
     }
     return B200R_OK;
@@ -489,10 +443,14 @@ int b200r_part_route(b200r_trie *t, uint64_t avail_mask, uint64_t seed,
     const int32_t *n_dev = &dyn->n_owned;
 
     { ProfScope ps__(PK_WAIT, st); g_launches += 1;
-    k_part_gather<<<148 * 4, 256, 0, st>>>(base, set, (unsigned long long)epoch,
-                                           L.hash_off + (size_t)set * L.hash_set,
+    k_part_wait_meta<<<1, P2P_MAX_WORLD, 0, st>>>((const PartFlags *)base, set, (unsigned long long)epoch,
+                                                  world, dyn, t->dev);
+    B200R_LAUNCH_CHECK("k_part_wait_meta");
+    }
+    { ProfScope ps__(PK_PREP, st); g_launches += 1;
+    k_part_gather<<<148 * 4, 256, 0, st>>>(base, L.hash_off + (size_t)set * L.hash_set,
                                            L.info_off + (size_t)set * L.info_set, cap, rcap, world, dyn,
-                                           t->dev, chunk_base, pos_owned, hashes);
+                                           chunk_base, pos_owned, (uint32_t *)(wk + L.w_idx_of_pos), hashes);
     B200R_LAUNCH_CHECK("k_part_gather");
     }
     // grids are estimates (about two shards' worth); the kernels stride over the rest
@@ -505,6 +463,7 @@ int b200r_part_route(b200r_trie *t, uint64_t avail_mask, uint64_t seed,
     core.dpre = (int32_t *)(sc + p.off_dpre); core.cand = (uint64_t *)(sc + p.off_cand);
     core.endpoint = ep; core.depth = depth; core.matched = matched;
     core.dyn = &dyn->base; core.pos = pos_owned; core.n_dev = n_dev;
+    core.idx_of_pos = (const uint32_t *)(wk + L.w_idx_of_pos);
     core.claim_kind = claim_kind_for(rcap, cap);
     rc = launch_route_core(t, core, st);
     if (rc) return rc;
@@ -529,12 +488,17 @@ int b200r_part_finish(b200r_trie *t, int64_t n, void *d_my_base, int32_t world, 
     const PartLayout L = part_layout(world, cap, rcap);
     const int set = (int)(epoch & 1);
     uint8_t *base = (uint8_t *)d_my_base, *wk = (uint8_t *)d_work;
-    { ProfScope ps__(PK_RESOLVE, st); g_launches += 1;
-    k_part_scatter<<<(int)((n + 255) / 256) > 0 ? (int)((n + 255) / 256) : 1, 256, 0, st>>>(
-        (const uint32_t *)(wk + L.w_dest_slot + (size_t)set * align_up((size_t)rcap * 4)), base, set,
-        (unsigned long long)epoch, world, t->dev, (PartDyn *)(wk + L.w_dyn),
-        L.res_off + (size_t)set * L.res_set, rcap, (int)n, d_endpoint, d_match_depth, d_matched);
-    B200R_LAUNCH_CHECK("k_part_scatter");
+    { ProfScope ps__(PK_WAIT, st); g_launches += 1;
+    k_part_wait_res<<<1, P2P_MAX_WORLD, 0, st>>>((const PartFlags *)base, set, (unsigned long long)epoch,
+                                                 world, t->dev, (PartDyn *)(wk + L.w_dyn));
+    B200R_LAUNCH_CHECK("k_part_wait_res");
+    }
+    if (n > 0) {
+        ProfScope ps__(PK_RESOLVE, st); g_launches += 1;
+        k_part_scatter<<<(int)((n + 255) / 256), 256, 0, st>>>(
+            (const uint32_t *)(wk + L.w_dest_slot + (size_t)set * align_up((size_t)rcap * 4)), base,
+            L.res_off + (size_t)set * L.res_set, rcap, (int)n, d_endpoint, d_match_depth, d_matched);
+        B200R_LAUNCH_CHECK("k_part_scatter");
     }
     return B200R_OK;
 }
@@ -563,9 +527,11 @@ int b200r_part_begin(b200r_trie *t, uint32_t epoch)
     if (!t) { set_error("null trie"); return B200R_E_INVALID; }
     int rc = part_streams(t);
     if (rc) return rc;
-    // the send phase of batch `epoch` overwrites the buffer set batch epoch-2 used and may only
-    // start when this rank has finished batch epoch-1 (then every peer has consumed that set)
-    const int prev = (int)((epoch + 1) & 1);
+    // the send phase of batch `epoch` overwrites the buffer set that batch epoch-2 used: it may
+    // start once this rank has finished batch epoch-2 (every owner has then pushed its results
+    // for that batch, i.e. has consumed what all sources sent it); the event of that parity
+    // still belongs to batch epoch-2 here
+    const int prev = (int)(epoch & 1);
     if (t->part_has_finished[prev]) B200R_CUDA(cudaStreamWaitEvent(t->part_send, t->part_finished[prev], 0));
     return B200R_OK;
 }

@@ -414,7 +414,7 @@ select_request(int i, const Rec *__restrict__ log, const int32_t *__restrict__ c
     // "node d was touched by an earlier request of this batch" is a prefix property (whoever
     // touched a node touched everything above it on the same path, no later): find the last
     // such depth -- linear for the first few, then by bisection (long prompts: C4 has 256)
-    const uint32_t me = req_off + (uint32_t)i;
+    const uint32_t me = pos ? pos[i] : req_off + (uint32_t)i;
     auto touched = [&](int d, uint32_t &f) -> bool {
         const uint32_t x = sl[d];
         if (x == SLOT_NONE) return false;
@@ -479,10 +479,12 @@ commit_request(int i, Rec *__restrict__ log, TrieDev *dev, const int32_t *__rest
                int64_t max_chunks, const uint32_t *__restrict__ slots,
                const int32_t *__restrict__ leader, const int32_t *__restrict__ choice,
                const int32_t *__restrict__ depth, int32_t *__restrict__ endpoint,
-               uint64_t *__restrict__ matched_out)
+               uint64_t *__restrict__ matched_out, const uint32_t *__restrict__ idx_of_pos)
 {
+    // leaders are global positions; idx_of_pos (partitioned multi-GPU path, where requests sit
+    // in arrival order, not in global order) maps them back to local indices
     int j = i, l;
-    while ((l = leader[j]) >= 0) j = l;          // chains strictly decrease in index
+    while ((l = leader[j]) >= 0) j = idx_of_pos ? (int)idx_of_pos[l] : l;   // positions strictly decrease
     const int e = choice[j];
     endpoint[i] = e;
     if (j != i) matched_out[i] = (e >= 0) ? (1ULL << e) : 0;
@@ -501,12 +503,12 @@ k_commit(Rec *__restrict__ log, TrieDev *dev, const int32_t *__restrict__ chunk_
          int64_t max_chunks, const uint32_t *__restrict__ slots, const int32_t *__restrict__ leader,
          const int32_t *__restrict__ choice, const int32_t *__restrict__ depth,
          int32_t *__restrict__ endpoint, uint64_t *__restrict__ matched_out,
-         const int32_t *__restrict__ n_dev)
+         const int32_t *__restrict__ n_dev, const uint32_t *__restrict__ idx_of_pos)
 {
     if (n_dev) n = *n_dev;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
         commit_request(i, log, dev, chunk_base, max_chunks, slots, leader, choice, depth, endpoint,
-                       matched_out);
+                       matched_out, idx_of_pos);
 }
 
 // ------------------------------------------------------------ dump / restore / sweeps
@@ -761,6 +763,7 @@ int launch_route_core(b200r_trie *t, const RouteCore &rc, cudaStream_t st)
     a.t = trie_ref(t);
     a.hashes = rc.hashes; a.chunk_base = rc.chunk_base; a.max_chunks = rc.max_chunks;
     a.avail = rc.avail; a.tag = tag; a.slots = rc.slots; a.dpre = rc.dpre; a.cand = rc.cand;
+    a.pos = rc.pos;
     const int nn = rc.n_dev ? 0 : (int)rc.n;
     const int tblocks = (int)((rc.n + 255) / 256);
     { ProfScope ps__(PK_CLAIM, st); g_launches += 1;
@@ -785,7 +788,8 @@ int launch_route_core(b200r_trie *t, const RouteCore &rc, cudaStream_t st)
     }
     { ProfScope ps__(PK_COMMIT, st); g_launches += 1;
     k_commit<<<tblocks, 256, 0, st>>>(t->log, t->dev, rc.chunk_base, nn, rc.max_chunks, rc.slots,
-                                     rc.leader, rc.choice, rc.depth, rc.endpoint, rc.matched, rc.n_dev);
+                                     rc.leader, rc.choice, rc.depth, rc.endpoint, rc.matched, rc.n_dev,
+                                     rc.idx_of_pos);
     B200R_LAUNCH_CHECK("k_commit");
     }
     return B200R_OK;

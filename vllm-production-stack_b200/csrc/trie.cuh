@@ -286,6 +286,8 @@ struct WalkArgs {
     int32_t *depth_out;           // lookup
     uint64_t *matched_out;        // lookup
     const int32_t *endpoint;      // insert
+    const uint32_t *pos;          // claim: global position of request i (NULL: i itself) -- the
+                                  // index that "first toucher" marks are expressed in
 };
 
 __device__ __forceinline__ int leading_ones(unsigned bal)
@@ -330,7 +332,7 @@ __device__ __forceinline__ void walk_request(const WalkArgs &a, int i, const Til
         bit = 1ULL << e;
         if (lane == 0 && !(t.dev->root_mask & bit)) atomicOr((unsigned long long *)&t.dev->root_mask, bit);
     }
-    const unsigned long long mine = a.tag | (unsigned long long)(~(unsigned)i);
+    const unsigned long long mine = a.tag | (unsigned long long)(~(a.pos ? a.pos[i] : (unsigned)i));
     uint32_t pidx = ROOT_IDX;             // last resolved node
     uint32_t base = 0, room = 0;          // A: candidates start at log[base]; room = records of the
     bool have_base = false;               //    run from base on (0 = not known yet)
@@ -546,7 +548,7 @@ k_claim_thread(WalkArgs a, int n, const int32_t *__restrict__ n_dev)
         const int C = sp.C;
         const uint64_t *hs = a.hashes + sp.b0;
         uint32_t *sl = a.slots + sp.b0;
-        const unsigned long long mine = a.tag | (unsigned long long)(~(unsigned)i);
+        const unsigned long long mine = a.tag | (unsigned long long)(~(a.pos ? a.pos[i] : (unsigned)i));
         int d = 0;                            // depths [0, d) are resolved
         uint32_t pidx = ROOT_IDX;             // last resolved node
         int npre = 0;
