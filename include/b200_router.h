@@ -291,13 +291,15 @@ int b200r_part_finish(b200r_trie *t, int64_t n, void *d_my_base, int32_t world, 
                       int64_t cap, int64_t rcap, uint32_t epoch, void *d_work, int32_t *d_endpoint,
                       int32_t *d_match_depth, uint64_t *d_matched, void *stream);
 
-/* The three phases of one batch in ONE call, pipelined over consecutive batches on two
- * streams the table owns (send, with the SM-filling hashing kernel, at the lowest stream
- * priority; route + finish at the highest): the send phase of batch b+1 overlaps route and
- * finish of batch b, and the caller's `stream` waits for the call's results.  d_scratch must
- * be one of two buffers used in turn (the send phase of batch b+1 runs while batch b's route
- * phase no longer needs b's scratch, but b's send phase may still be running).
- * inputs_on_send_stream = 1: the inputs are complete or were copied with
+/* The three phases of one batch in ONE call, pipelined over consecutive batches on four
+ * streams the table owns: prep (input copies, per-request counting + scan), send (the
+ * SM-filling hashing kernel, placement and shipment; lowest stream priority), route (wait for
+ * the sources, gather, claim, select, commit) and return (push results, wait for the owners,
+ * scatter); prep, route and return run at the highest priority.  Send of batch
+ * b+1 overlaps route and return of batch b; route of batch b+1 follows the commit of batch b.
+ * The caller's `stream` waits for the call's results.  d_scratch must be one of TWO buffers
+ * used in turn by batch parity (the prep of batch b+1 runs while batch b is being hashed).
+ * inputs_on_prep_stream = 1: the inputs are complete or were copied with
  * b200r_part_copy_h2d after b200r_part_begin(t, epoch) (a host-to-device copy that overlaps the
  * previous batch); 0: they were produced on `stream`. */
 int b200r_part_begin(b200r_trie *t, uint32_t epoch);
@@ -308,7 +310,7 @@ int b200r_part_step(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_star
                     void *d_my_base, int32_t world, int32_t rank, int64_t cap, int64_t rcap,
                     uint32_t epoch, void *d_work, void *d_scratch, size_t scratch_bytes,
                     int32_t *d_endpoint, int32_t *d_match_depth, uint64_t *d_matched,
-                    int32_t inputs_on_send_stream, void *stream);
+                    int32_t inputs_on_prep_stream, void *stream);
 
 /* ------------------------------------------------------------------------
  * a9  uhashring.HashRing (md5 points, bisect_right + wrap), a7 SessionRouter

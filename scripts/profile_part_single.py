@@ -1,0 +1,35 @@
+"""The partitioned exchange with world = 1 on ONE GPU (every request is owned by this rank):
+all of its kernels run -- place, bulk, wait, gather, claim, select, commit, push, wait,
+scatter -- so that a launch list (ncu) shows each one alone.  Usage:
+    python scripts/profile_part_single.py [batches] [batch]"""
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "vllm-production-stack_b200"))
+import torch  # noqa: E402
+from b200_router import traces  # noqa: E402
+from b200_router.distributed import PartitionedPrefixRouter  # noqa: E402
+from b200_router.packing import pack_arrays  # noqa: E402
+
+nb = int(sys.argv[1]) if len(sys.argv) > 1 else 6
+batch = int(sys.argv[2]) if len(sys.argv) > 2 else 65536
+dev = torch.device("cuda:0")
+tr = traces.SharedPrefixTrace(n_total=nb * batch, batch=batch, n_sys=64, sys_chars=2048,
+                              suffix_lo=256, suffix_hi=1024, seed=1234)
+packs = [pack_arrays(*tr.batch_arrays(b), pin=False).to(dev) for b in range(nb)]
+mr, mc = max(p.n for p in packs), max(p.max_chunks for p in packs)
+nbytes = PartitionedPrefixRouter.symm_bytes_for(1, mr, mc)
+buf = torch.zeros(nbytes, dtype=torch.uint8, device=dev)
+r = PartitionedPrefixRouter(cap_log2=24, device=dev, max_requests=mr, max_chunks=mc,
+                            _sim={"world": 1, "rank": 0, "buffers": [buf]})
+out = (torch.empty(mr, dtype=torch.int32, device=dev), torch.empty(mr, dtype=torch.int32, device=dev),
+       torch.empty(mr, dtype=torch.int64, device=dev))
+torch.cuda.synchronize()
+t0 = time.perf_counter()
+for p in packs:
+    r.route(p, 0xFF, 7, out=out, inputs_ready=True)
+torch.cuda.synchronize()
+print("batches %d x %d: %.3f ms/batch (first batches build the table)" %
+      (nb, batch, (time.perf_counter() - t0) * 1e3 / nb), r.check_status())

@@ -184,6 +184,8 @@ class PartitionedPrefixRouter:
         # run the three phases one by one on the current stream (lock-step tests)
         self.pipelined = True
         self._keep = [None, None]                  # device copies of host inputs, by batch parity
+        self._sc = [None, None]                    # hash-stage scratch, by batch parity
+        self._retired = []                         # outgrown scratch buffers (may still be in use)
 
     @staticmethod
     def capacities(max_requests: int, max_chunks: int):
@@ -232,12 +234,13 @@ class PartitionedPrefixRouter:
 
     def route(self, p: PackedPrompts, avail_mask: int, seed: int, seq0: int = 0, out=None,
               inputs_ready: bool = False):
-        """One native call per batch (b200r_part_step): the send phase runs on a low-priority
-        stream of the library, route and finish on a high-priority one, and the caller's stream
-        waits for the results.  The send phase of batch b+1 overlaps route + finish of batch b;
-        it may not start before this rank has finished batch b-1 (then every peer has consumed
-        the buffer set it is about to overwrite) and, unless inputs_ready, before the caller's
-        stream has produced the inputs.  Host (pinned) inputs are copied on the send stream."""
+        """One native call per batch (b200r_part_step): prep, send (hashing + shipment), route and
+        return run on four streams of the library and the caller's stream waits for the results.
+        Send of batch b+1 overlaps route + return of batch b, the route chain of batch b+1 starts
+        right behind the commit of batch b.  The send may not start before this rank has finished
+        batch b-1 (then every peer has consumed the buffer set it is about to overwrite) and,
+        unless inputs_ready, before the caller's stream has produced the inputs.  Host (pinned)
+        inputs are copied on the prep stream."""
         if self.epoch == 0 and seq0 != 0:
             raise _lib.B200RouterError("PartitionedPrefixRouter keeps the sequence number on the "
                                        "device; it starts at 0")
@@ -249,11 +252,11 @@ class PartitionedPrefixRouter:
                 _lib.check(L.b200r_part_begin(self.trie._h, self.epoch))
                 k = self.epoch & 1
                 self._keep[k] = None
-                self._keep[k] = p = self._copy_on_send_stream(p)
+                self._keep[k] = p = self._copy_on_prep_stream(p)
                 inputs_ready = True
             flags = _lib.F_ALL_ASCII if p.all_ascii else 0
             need = L.b200r_prefix_route_scratch_bytes(n, p.max_chunks, flags)
-            sc = self.trie._scratch_for(need)
+            sc = self._step_scratch(need)
             self._shape = (n,)
             if out is None:
                 out = (torch.empty(max(n, 1), dtype=torch.int32, device=self.device),
@@ -271,7 +274,18 @@ class PartitionedPrefixRouter:
                 _lib.check(rc)
         return ep[:n], depth[:n], matched[:n]
 
-    def _copy_on_send_stream(self, p: PackedPrompts) -> PackedPrompts:
+    def _step_scratch(self, nbytes: int) -> torch.Tensor:
+        # two buffers in turn: the prep of batch b+1 runs next to the hashing of batch b
+        k = self.epoch & 1
+        sc = self._sc[k]
+        if sc is None or sc.numel() < nbytes:
+            if sc is not None:
+                self._retired.append(sc)
+            sc = self._sc[k] = torch.empty(int(nbytes * 1.25) + 4096, dtype=torch.uint8,
+                                           device=self.device)
+        return sc
+
+    def _copy_on_prep_stream(self, p: PackedPrompts) -> PackedPrompts:
         L = _lib.lib()
 
         def mv(t):

@@ -95,7 +95,7 @@ struct b200r_trie {
     b200r::TrieDev *dev;
     uint32_t epoch;
     // streams / events of b200r_part_step (created on first use)
-    cudaStream_t part_send, part_route;
-    cudaEvent_t part_inputs, part_sent, part_finished[2];
+    cudaStream_t part_send, part_route, part_prep, part_ret;
+    cudaEvent_t part_inputs, part_prepped, part_routed, part_sent[2], part_finished[2];
     bool part_ready, part_has_finished[2];
 };

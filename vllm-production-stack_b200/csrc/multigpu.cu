@@ -97,7 +97,7 @@ k_part_place(const int32_t *__restrict__ chunk_base, const uint64_t *__restrict_
              unsigned long long *__restrict__ info_stage, uint32_t *__restrict__ dest_slot,
              uint64_t *__restrict__ hash_stage)
 {
-    __shared__ int s_b[PART_BLOCK], s_c[PART_BLOCK];
+    __shared__ int s_ex[PART_BLOCK / 32][32];
     __shared__ unsigned long long s_dst[PART_BLOCK];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int i = blockIdx.x * PART_BLOCK + threadIdx.x;
@@ -126,21 +126,61 @@ k_part_place(const int32_t *__restrict__ chunk_base, const uint64_t *__restrict_
             rchunk = (uint32_t)base + (uint32_t)(inc - v);
         }
     }
-    s_b[threadIdx.x] = b; s_c[threadIdx.x] = 0; s_dst[threadIdx.x] = 0;
+    // chunk hashes -> local staging.  The 32 requests of a warp are consecutive in the batch, so
+    // their hashes are ONE contiguous source range: the warp copies it flat (every lane busy,
+    // four loads in flight) and looks the destination up by request (search over 32 prefixes).
+    int ex = C;
+    for (int sft = 1; sft < 32; sft <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, ex, sft);
+        if (lane >= sft) ex += t;
+    }
+    const int T = __shfl_sync(0xffffffffu, ex, 31);
+    ex -= C;
+    s_ex[w][lane] = ex;
+    s_dst[threadIdx.x] = 0;
     if (o >= 0) {
         dest_slot[i] = ((uint32_t)o << 24) | rreq;
-        s_c[threadIdx.x] = C;
-        s_dst[threadIdx.x] = (unsigned long long)o * (unsigned long long)cap + rchunk;
+        s_dst[threadIdx.x] = (unsigned long long)o * (unsigned long long)cap + rchunk - (unsigned)ex;
         info_stage[(size_t)o * rcap + rreq] =
             (unsigned long long)(uint32_t)i | ((unsigned long long)rchunk << 32);
     }
-    __syncthreads();
-    // chunk hashes -> local staging: each warp copies the runs of its 32 requests (coalesced)
-    for (int k = 0; k < 32; k++) {
-        const int t = w * 32 + k;
-        const int cb = s_b[t], cc = s_c[t];
-        uint64_t *dst = hash_stage + s_dst[t];
-        for (int c = lane; c < cc; c += 32) dst[c] = hashes[cb + c];
+    const int cb0 = __shfl_sync(0xffffffffu, b, 0);          // lane 0's request exists if any does
+    __syncwarp();
+    const uint64_t *src = hashes + cb0;
+    const int *pex = s_ex[w];
+    const unsigned long long *pdst = s_dst + w * 32;
+    for (int j0 = 0; j0 < T; j0 += 128) {
+        uint64_t v[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int j = j0 + u * 32 + lane;
+            v[u] = j < T ? __ldcs(src + j) : 0;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int j = j0 + u * 32 + lane;
+            if (j >= T) continue;
+            int r = 0;                                       // largest r with ex[r] <= j
+#pragma unroll
+            for (int sft = 16; sft; sft >>= 1)
+                if (pex[r + sft] <= j) r += sft;
+            hash_stage[pdst[r] + (unsigned)j] = v[u];
+        }
+    }
+}
+
+// grid-strided copy of 16-byte vectors, four loads in flight per thread
+__device__ __forceinline__ void copy_vec4(uint4 *__restrict__ dst, const uint4 *__restrict__ src,
+                                          int64_t cnt, int64_t tid, int64_t nthr)
+{
+    for (int64_t x0 = tid; x0 < cnt; x0 += 4 * nthr) {
+        uint4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+            if (x0 + u * nthr < cnt) v[u] = __ldcs(src + x0 + u * nthr);
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+            if (x0 + u * nthr < cnt) dst[x0 + u * nthr] = v[u];
     }
 }
 
@@ -162,10 +202,10 @@ k_part_bulk(const uint64_t *__restrict__ hash_stage, const unsigned long long *_
         const int nreq = (int)(tt >> 32), nchunk = (int)(uint32_t)tt;
         const uint4 *hs = (const uint4 *)(hash_stage + (size_t)o * cap);
         uint4 *hd = (uint4 *)((uint64_t *)(uintptr_t)(peer_bases[o] + hash_off) + (size_t)my_rank * cap);
-        for (int64_t x = tid; x < (nchunk + 1) / 2; x += nthr) hd[x] = hs[x];
+        copy_vec4(hd, hs, (nchunk + 1) / 2, tid, nthr);
         const uint4 *is = (const uint4 *)(info_stage + (size_t)o * rcap);
         uint4 *id = (uint4 *)((unsigned long long *)(uintptr_t)(peer_bases[o] + info_off) + (size_t)my_rank * rcap);
-        for (int64_t x = tid; x < (nreq + 1) / 2; x += nthr) id[x] = is[x];
+        copy_vec4(id, is, (nreq + 1) / 2, tid, nthr);
     }
     if (last_cta_after_peer_stores(ticket) && (int)threadIdx.x < world) {
         const int d = threadIdx.x;
@@ -197,7 +237,7 @@ __global__ void k_part_publish_in(const unsigned long long *__restrict__ peer_ba
 // spinning CTAs would hold SM slots that the next batch's send phase needs while the slowest
 // peer is still on its way.  Leaves the batch's bookkeeping in `dyn`.
 __global__ void k_part_wait_meta(const PartFlags *__restrict__ mine, int set, unsigned long long epoch,
-                                 int world, PartDyn *dyn, TrieDev *dev)
+                                 int world, PartDyn *dyn, const PartDyn *prev, TrieDev *dev)
 {
     __shared__ uint32_t s_req[P2P_MAX_WORLD], s_chunk[P2P_MAX_WORLD], s_n[P2P_MAX_WORLD];
     const int q = threadIdx.x;
@@ -219,8 +259,10 @@ __global__ void k_part_wait_meta(const PartFlags *__restrict__ mine, int set, un
         dyn->reqbase[world] = r; dyn->chunkbase[world] = c; dyn->off[world] = o;
         dyn->n_owned = (int32_t)r; dyn->c_owned = (int32_t)c;
         dyn->base.my_off = 0; dyn->base.total_n = o;
+        // global sequence number of this batch's request 0: the previous batch's, plus its size
+        dyn->base.seq_base = prev->base.seq_base + prev->base.total_n;
     }
-    __threadfence_system();
+    // no fence: what the sources wrote before their flags is read by LATER launches only
 }
 
 // concatenate what the sources sent, in rank order, as the CSR the route stage works on
@@ -281,19 +323,15 @@ k_part_push_results(PartDyn *dyn, int world, int my_rank,
     }
 }
 
-// wait for all owners' results (one small CTA, see k_part_wait_meta); advances the global
-// sequence number to the next batch's request 0
+// wait for all owners' results (one small CTA, see k_part_wait_meta)
 __global__ void k_part_wait_res(const PartFlags *__restrict__ mine, int set, unsigned long long epoch,
-                                int world, TrieDev *dev, PartDyn *dyn)
+                                int world, TrieDev *dev)
 {
     const int q = threadIdx.x;
     if (q < world) {
         unsigned long long v;
         if (!p2p_spin(&mine->res[set][q], epoch, &v)) atomicOr(&dev->status, B200R_S_PEER_TIMEOUT);
     }
-    __syncthreads();
-    if (threadIdx.x == 0) dyn->base.seq_base += dyn->base.total_n;   // next batch's request 0
-    __threadfence_system();
 }
 
 // results back to request order
@@ -339,19 +377,24 @@ static PartLayout part_layout(int world, int64_t cap, int64_t rcap)
     L.c_max = (int64_t)world * cap;
     L.nblk_max = (int)((rcap + PART_BLOCK - 1) / PART_BLOCK);
     size_t o = 0;
-    L.w_dyn = o;       o += align_up(sizeof(PartDyn));
+    L.w_dyn = o;       o += 2 * align_up(sizeof(PartDyn));          // one per batch parity
     L.w_totals = o;    o += align_up((size_t)world * 8);
     L.w_dest_slot = o; o += 2 * align_up((size_t)rcap * 4);     // one per batch parity
     L.w_hash_stage = o; o += align_up((size_t)world * (cap + 2) * 8);   // one fixed segment per owner
     L.w_info_stage = o; o += align_up((size_t)world * (rcap + 2) * 8);
     L.w_pos_owned = o; o += align_up((size_t)L.n_max * 4);
     L.w_idx_of_pos = o; o += align_up((size_t)L.n_max * 4);
-    L.w_ep = o;        o += align_up((size_t)L.n_max * 4);
-    L.w_depth = o;     o += align_up((size_t)L.n_max * 4);
-    L.w_matched = o;   o += align_up((size_t)L.n_max * 8);
+    L.w_ep = o;        o += 2 * align_up((size_t)L.n_max * 4);      // results: one per batch parity
+    L.w_depth = o;     o += 2 * align_up((size_t)L.n_max * 4);
+    L.w_matched = o;   o += 2 * align_up((size_t)L.n_max * 8);
     L.w_plan = o;      o += make_plan(L.n_max, L.c_max, B200R_F_ALL_ASCII, true).total;
     L.work_total = o + 256;
     return L;
+}
+
+static inline PartDyn *part_dyn(uint8_t *wk, const PartLayout &L, int set)
+{
+    return (PartDyn *)(wk + L.w_dyn + (size_t)set * align_up(sizeof(PartDyn)));
 }
 
 static int part_check(int world, int rank, int64_t cap, int64_t rcap, const void *a, const void *b)
@@ -374,19 +417,30 @@ int b200r_part_layout(int32_t world, int64_t cap, int64_t rcap, size_t out[2])
     return B200R_OK;
 }
 
-int b200r_part_send(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
-                    const int32_t *d_lens, const int32_t *d_nchars, int64_t n, int64_t max_chunks,
-                    uint32_t flags, const uint64_t *d_peer_bases, int32_t world, int32_t rank,
-                    int64_t cap, int64_t rcap, uint32_t epoch, void *d_work, void *d_scratch,
-                    size_t scratch_bytes, void *stream)
+// Send phase.  With a prep stream, the per-request counting + scan of the hash stage runs there
+// (it is a chain of small kernels; next to the previous batch's hashing kernel instead of after
+// it) and `st` picks up at the hashing kernel.
+static int part_send_impl(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
+                          const int32_t *d_lens, const int32_t *d_nchars, int64_t n, int64_t max_chunks,
+                          uint32_t flags, const uint64_t *d_peer_bases, int32_t world, int32_t rank,
+                          int64_t cap, int64_t rcap, uint32_t epoch, void *d_work, void *d_scratch,
+                          size_t scratch_bytes, cudaStream_t prep_st, cudaEvent_t prepped, cudaStream_t st)
 {
     int rc = part_check(world, rank, cap, rcap, d_peer_bases, d_work);
     if (rc) return rc;
     if (max_chunks > cap || n > rcap) { set_error("partitioned routing: batch (n=%lld, max_chunks=%lld) exceeds the exchange capacity (rcap=%lld, cap=%lld)", (long long)n, (long long)max_chunks, (long long)rcap, (long long)cap); return B200R_E_INVALID; }
+    if (prep_st != st) {
+        rc = b200r_prefix_hash_stage(t, d_bytes, d_starts, d_lens, d_nchars, n, max_chunks,
+                                     flags | B200R_F_PREP_ONLY, d_scratch, scratch_bytes, prep_st);
+        if (rc) return rc;
+        B200R_CUDA(cudaEventRecord(prepped, prep_st));
+        B200R_CUDA(cudaStreamWaitEvent(st, prepped, 0));
+        flags |= B200R_F_PREP_DONE;
+    }
     rc = b200r_prefix_hash_stage(t, d_bytes, d_starts, d_lens, d_nchars, n, max_chunks, flags,
-                                 d_scratch, scratch_bytes, stream);
+                                 d_scratch, scratch_bytes, st);
     if (rc) return rc;
-    cudaStream_t st = (cudaStream_t)stream;
+    flags &= ~(uint32_t)(B200R_F_PREP_ONLY | B200R_F_PREP_DONE);
     const PartLayout L = part_layout(world, cap, rcap);
     const Plan p = make_plan(n, max_chunks, flags, true);
     uint8_t *sc = (uint8_t *)d_scratch, *wk = (uint8_t *)d_work;
@@ -395,7 +449,7 @@ int b200r_part_send(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_star
     unsigned long long *totals = (unsigned long long *)(wk + L.w_totals);
     const int set = (int)(epoch & 1);
     const int nblk = (int)((n + PART_BLOCK - 1) / PART_BLOCK);
-    PartDyn *dyn = (PartDyn *)(wk + L.w_dyn);
+    PartDyn *dyn = part_dyn(wk, L, set);
     ProfScope ps__(PK_PUSH, st);
     if (nblk > 0) {
         g_launches += 2;
@@ -420,22 +474,50 @@ int b200r_part_send(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_star
     return B200R_OK;
 }
 
+int b200r_part_send(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
+                    const int32_t *d_lens, const int32_t *d_nchars, int64_t n, int64_t max_chunks,
+                    uint32_t flags, const uint64_t *d_peer_bases, int32_t world, int32_t rank,
+                    int64_t cap, int64_t rcap, uint32_t epoch, void *d_work, void *d_scratch,
+                    size_t scratch_bytes, void *stream)
+{
+    return part_send_impl(t, d_bytes, d_starts, d_lens, d_nchars, n, max_chunks, flags, d_peer_bases,
+                          world, rank, cap, rcap, epoch, d_work, d_scratch, scratch_bytes,
+                          (cudaStream_t)stream, nullptr, (cudaStream_t)stream);
+}
+
+// Owner side: wait for every source's send, build the CSR of the owned requests, route them
+// (st_route); push each source's results back (st_ret, after `routed`).  One stream for both
+// when st_ret == st_route.
+static int part_route_impl(b200r_trie *t, uint64_t avail_mask, uint64_t seed,
+                           const uint64_t *d_peer_bases, void *d_my_base, int32_t world, int32_t rank,
+                           int64_t cap, int64_t rcap, uint32_t epoch, void *d_work,
+                           cudaStream_t st, cudaStream_t st_ret, cudaEvent_t routed);
+
 int b200r_part_route(b200r_trie *t, uint64_t avail_mask, uint64_t seed,
                      const uint64_t *d_peer_bases, void *d_my_base, int32_t world, int32_t rank,
                      int64_t cap, int64_t rcap, uint32_t epoch, void *d_work, void *stream)
 {
+    return part_route_impl(t, avail_mask, seed, d_peer_bases, d_my_base, world, rank, cap, rcap, epoch,
+                           d_work, (cudaStream_t)stream, (cudaStream_t)stream, nullptr);
+}
+
+static int part_route_impl(b200r_trie *t, uint64_t avail_mask, uint64_t seed,
+                           const uint64_t *d_peer_bases, void *d_my_base, int32_t world, int32_t rank,
+                           int64_t cap, int64_t rcap, uint32_t epoch, void *d_work,
+                           cudaStream_t st, cudaStream_t st_ret, cudaEvent_t routed)
+{
     int rc = part_check(world, rank, cap, rcap, d_peer_bases, d_work);
     if (rc) return rc;
     if (!t || !d_my_base) { set_error("b200r_part_route: null pointer"); return B200R_E_INVALID; }
-    cudaStream_t st = (cudaStream_t)stream;
     const PartLayout L = part_layout(world, cap, rcap);
     const Plan p = make_plan(L.n_max, L.c_max, B200R_F_ALL_ASCII, true);
     const int set = (int)(epoch & 1);
     uint8_t *base = (uint8_t *)d_my_base, *wk = (uint8_t *)d_work, *sc = wk + L.w_plan;
-    PartDyn *dyn = (PartDyn *)(wk + L.w_dyn);
+    PartDyn *dyn = part_dyn(wk, L, set);
     uint32_t *pos_owned = (uint32_t *)(wk + L.w_pos_owned);
-    int32_t *ep = (int32_t *)(wk + L.w_ep), *depth = (int32_t *)(wk + L.w_depth);
-    uint64_t *matched = (uint64_t *)(wk + L.w_matched);
+    int32_t *ep = (int32_t *)(wk + L.w_ep + (size_t)set * align_up((size_t)L.n_max * 4));
+    int32_t *depth = (int32_t *)(wk + L.w_depth + (size_t)set * align_up((size_t)L.n_max * 4));
+    uint64_t *matched = (uint64_t *)(wk + L.w_matched + (size_t)set * align_up((size_t)L.n_max * 8));
     int32_t *chunk_base = (int32_t *)(sc + p.off_chunk_base);
     uint64_t *hashes = (uint64_t *)(sc + p.off_hashes);
     uint32_t *slots = (uint32_t *)(sc + p.off_slots);
@@ -444,7 +526,7 @@ int b200r_part_route(b200r_trie *t, uint64_t avail_mask, uint64_t seed,
 
     { ProfScope ps__(PK_WAIT, st); g_launches += 1;
     k_part_wait_meta<<<1, P2P_MAX_WORLD, 0, st>>>((const PartFlags *)base, set, (unsigned long long)epoch,
-                                                  world, dyn, t->dev);
+                                                  world, dyn, part_dyn(wk, L, set ^ 1), t->dev);
     B200R_LAUNCH_CHECK("k_part_wait_meta");
     }
     { ProfScope ps__(PK_PREP, st); g_launches += 1;
@@ -467,8 +549,12 @@ int b200r_part_route(b200r_trie *t, uint64_t avail_mask, uint64_t seed,
     core.claim_kind = claim_kind_for(rcap, cap);
     rc = launch_route_core(t, core, st);
     if (rc) return rc;
-    { ProfScope ps__(PK_PUSH, st); g_launches += 1;
-    k_part_push_results<<<148 * 2, 256, 0, st>>>(dyn, world, rank, ep, depth, matched,
+    if (st_ret != st) {
+        B200R_CUDA(cudaEventRecord(routed, st));
+        B200R_CUDA(cudaStreamWaitEvent(st_ret, routed, 0));
+    }
+    { ProfScope ps__(PK_PUSH, st_ret); g_launches += 1;
+    k_part_push_results<<<148 * 2, 256, 0, st_ret>>>(dyn, world, rank, ep, depth, matched,
                                                  (const unsigned long long *)d_peer_bases,
                                                  L.res_off + (size_t)set * L.res_set, rcap, set,
                                                  (unsigned long long)epoch);
@@ -490,7 +576,7 @@ int b200r_part_finish(b200r_trie *t, int64_t n, void *d_my_base, int32_t world, 
     uint8_t *base = (uint8_t *)d_my_base, *wk = (uint8_t *)d_work;
     { ProfScope ps__(PK_WAIT, st); g_launches += 1;
     k_part_wait_res<<<1, P2P_MAX_WORLD, 0, st>>>((const PartFlags *)base, set, (unsigned long long)epoch,
-                                                 world, t->dev, (PartDyn *)(wk + L.w_dyn));
+                                                 world, t->dev);
     B200R_LAUNCH_CHECK("k_part_wait_res");
     }
     if (n > 0) {
@@ -504,9 +590,15 @@ int b200r_part_finish(b200r_trie *t, int64_t n, void *d_my_base, int32_t world, 
 }
 
 // One call per batch: the three phases with the stream handling done natively (in Python it
-// cost more host time per batch than the GPU needs).  The send phase (hashing: fills every SM)
-// runs on an internal low-priority stream, route + finish on an internal high-priority one; the
-// send of batch b+1 overlaps route + finish of batch b.
+// cost more host time per batch than the GPU needs).  Four internal streams:
+//   prep  (high)  H2D copies of the inputs, per-request counting + scan of batch b
+//   send  (low)   hashing kernel (fills every SM), placement, shipment to the owners
+//   route (high)  wait for the sources, gather, claim, select, commit
+//   ret   (high)  push results to the sources, wait for the owners' results, scatter
+// so the route chain of batch b+1 starts right behind the commit of batch b, and the send of
+// batch b+1 overlaps both.  `d_scratch` alternates between two buffers by batch parity (the
+// caller passes the one of this batch); dyn blocks, result buffers and exchange buffer sets
+// alternate the same way.
 static int part_streams(b200r_trie *t)
 {
     if (t->part_ready) return B200R_OK;
@@ -514,10 +606,11 @@ static int part_streams(b200r_trie *t)
     B200R_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
     B200R_CUDA(cudaStreamCreateWithPriority(&t->part_send, cudaStreamNonBlocking, least));
     B200R_CUDA(cudaStreamCreateWithPriority(&t->part_route, cudaStreamNonBlocking, greatest));
-    B200R_CUDA(cudaEventCreateWithFlags(&t->part_inputs, cudaEventDisableTiming));
-    B200R_CUDA(cudaEventCreateWithFlags(&t->part_sent, cudaEventDisableTiming));
-    B200R_CUDA(cudaEventCreateWithFlags(&t->part_finished[0], cudaEventDisableTiming));
-    B200R_CUDA(cudaEventCreateWithFlags(&t->part_finished[1], cudaEventDisableTiming));
+    B200R_CUDA(cudaStreamCreateWithPriority(&t->part_prep, cudaStreamNonBlocking, greatest));
+    B200R_CUDA(cudaStreamCreateWithPriority(&t->part_ret, cudaStreamNonBlocking, greatest));
+    cudaEvent_t *evs[] = { &t->part_inputs, &t->part_prepped, &t->part_routed, &t->part_sent[0],
+                           &t->part_sent[1], &t->part_finished[0], &t->part_finished[1] };
+    for (cudaEvent_t *e : evs) B200R_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
     t->part_ready = true;
     return B200R_OK;
 }
@@ -527,19 +620,23 @@ int b200r_part_begin(b200r_trie *t, uint32_t epoch)
     if (!t) { set_error("null trie"); return B200R_E_INVALID; }
     int rc = part_streams(t);
     if (rc) return rc;
-    // the send phase of batch `epoch` overwrites the buffer set that batch epoch-2 used: it may
-    // start once this rank has finished batch epoch-2 (every owner has then pushed its results
-    // for that batch, i.e. has consumed what all sources sent it); the event of that parity
-    // still belongs to batch epoch-2 here
-    const int prev = (int)(epoch & 1);
-    if (t->part_has_finished[prev]) B200R_CUDA(cudaStreamWaitEvent(t->part_send, t->part_finished[prev], 0));
+    // Batch `epoch` reuses what batch epoch-2 used (the events of that parity still belong to
+    // batch epoch-2 here).  Its send phase overwrites that exchange buffer set: it may start
+    // once this rank has finished batch epoch-2 (every owner has then pushed its results for
+    // that batch, i.e. has consumed what all sources sent it).  Its prep writes the scratch
+    // buffer of that parity: after the send of batch epoch-2 has read it.
+    const int par = (int)(epoch & 1);
+    if (t->part_has_finished[par]) {
+        B200R_CUDA(cudaStreamWaitEvent(t->part_send, t->part_finished[par], 0));
+        B200R_CUDA(cudaStreamWaitEvent(t->part_prep, t->part_sent[par], 0));
+    }
     return B200R_OK;
 }
 
 int b200r_part_copy_h2d(b200r_trie *t, void *d_dst, const void *h_src, size_t bytes)
 {
     if (!t || !t->part_ready || (bytes && (!d_dst || !h_src))) { set_error("b200r_part_copy_h2d: bad argument (call b200r_part_begin first)"); return B200R_E_INVALID; }
-    if (bytes) B200R_CUDA(cudaMemcpyAsync(d_dst, h_src, bytes, cudaMemcpyHostToDevice, t->part_send));
+    if (bytes) B200R_CUDA(cudaMemcpyAsync(d_dst, h_src, bytes, cudaMemcpyHostToDevice, t->part_prep));
     return B200R_OK;
 }
 
@@ -549,27 +646,31 @@ int b200r_part_step(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_star
                     void *d_my_base, int32_t world, int32_t rank, int64_t cap, int64_t rcap,
                     uint32_t epoch, void *d_work, void *d_scratch, size_t scratch_bytes,
                     int32_t *d_endpoint, int32_t *d_match_depth, uint64_t *d_matched,
-                    int32_t inputs_on_send_stream, void *stream)
+                    int32_t inputs_on_prep_stream, void *stream)
 {
     int rc = b200r_part_begin(t, epoch);
     if (rc) return rc;
     cudaStream_t cur = (cudaStream_t)stream;
-    B200R_CUDA(cudaEventRecord(t->part_inputs, cur));
-    if (!inputs_on_send_stream) B200R_CUDA(cudaStreamWaitEvent(t->part_send, t->part_inputs, 0));
-    rc = b200r_part_send(t, d_bytes, d_starts, d_lens, d_nchars, n, max_chunks, flags, d_peer_bases,
-                         world, rank, cap, rcap, epoch, d_work, d_scratch, scratch_bytes, t->part_send);
-    if (rc) return rc;
-    B200R_CUDA(cudaEventRecord(t->part_sent, t->part_send));
-    B200R_CUDA(cudaStreamWaitEvent(t->part_route, t->part_sent, 0));
-    B200R_CUDA(cudaStreamWaitEvent(t->part_route, t->part_inputs, 0));      // the outputs may be in use
-    rc = b200r_part_route(t, avail_mask, seed, d_peer_bases, d_my_base, world, rank, cap, rcap, epoch,
-                          d_work, t->part_route);
-    if (rc) return rc;
-    rc = b200r_part_finish(t, n, d_my_base, world, rank, cap, rcap, epoch, d_work, d_endpoint,
-                           d_match_depth, d_matched, t->part_route);
-    if (rc) return rc;
     const int me = (int)(epoch & 1);
-    B200R_CUDA(cudaEventRecord(t->part_finished[me], t->part_route));
+    B200R_CUDA(cudaEventRecord(t->part_inputs, cur));
+    if (!inputs_on_prep_stream) B200R_CUDA(cudaStreamWaitEvent(t->part_prep, t->part_inputs, 0));
+    rc = part_send_impl(t, d_bytes, d_starts, d_lens, d_nchars, n, max_chunks, flags, d_peer_bases,
+                        world, rank, cap, rcap, epoch, d_work, d_scratch, scratch_bytes,
+                        t->part_prep, t->part_prepped, t->part_send);
+    if (rc) return rc;
+    B200R_CUDA(cudaEventRecord(t->part_sent[me], t->part_send));
+    B200R_CUDA(cudaStreamWaitEvent(t->part_route, t->part_sent[me], 0));
+    // the route stage's dyn block and result buffers of this parity: free once batch epoch-2
+    // has been returned
+    if (t->part_has_finished[me]) B200R_CUDA(cudaStreamWaitEvent(t->part_route, t->part_finished[me], 0));
+    rc = part_route_impl(t, avail_mask, seed, d_peer_bases, d_my_base, world, rank, cap, rcap, epoch,
+                         d_work, t->part_route, t->part_ret, t->part_routed);
+    if (rc) return rc;
+    B200R_CUDA(cudaStreamWaitEvent(t->part_ret, t->part_inputs, 0));        // the outputs may be in use
+    rc = b200r_part_finish(t, n, d_my_base, world, rank, cap, rcap, epoch, d_work, d_endpoint,
+                           d_match_depth, d_matched, t->part_ret);
+    if (rc) return rc;
+    B200R_CUDA(cudaEventRecord(t->part_finished[me], t->part_ret));
     t->part_has_finished[me] = true;
     B200R_CUDA(cudaStreamWaitEvent(cur, t->part_finished[me], 0));
     return B200R_OK;

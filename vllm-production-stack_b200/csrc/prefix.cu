@@ -977,10 +977,12 @@ int b200r_trie_destroy(b200r_trie *t)
 {
     if (!t) return B200R_OK;
     if (t->part_ready) {
-        cudaStreamSynchronize(t->part_send); cudaStreamSynchronize(t->part_route);
-        cudaEventDestroy(t->part_inputs); cudaEventDestroy(t->part_sent);
-        cudaEventDestroy(t->part_finished[0]); cudaEventDestroy(t->part_finished[1]);
-        cudaStreamDestroy(t->part_send); cudaStreamDestroy(t->part_route);
+        cudaStream_t sts[] = { t->part_prep, t->part_send, t->part_route, t->part_ret };
+        for (cudaStream_t s : sts) cudaStreamSynchronize(s);
+        cudaEvent_t evs[] = { t->part_inputs, t->part_prepped, t->part_routed, t->part_sent[0],
+                              t->part_sent[1], t->part_finished[0], t->part_finished[1] };
+        for (cudaEvent_t e : evs) cudaEventDestroy(e);
+        for (cudaStream_t s : sts) cudaStreamDestroy(s);
     }
     cudaFree(t->tab); cudaFree(t->log); cudaFree(t->wblk); cudaFree(t->dev);
     delete t;
