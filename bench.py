@@ -943,6 +943,17 @@ def latency_line(cx, args):
     lat = np.array(asyncio.run(serial(prompts[64:1088]))) * 1e6
     out["one_at_a_time"] = {"p50_us": float(np.percentile(lat, 50)), "p99_us": float(np.percentile(lat, 99)),
                             "decisions_per_s": 1e6 / float(lat.mean()), "requests": len(lat)}
+    # the same through the batch kernels (a batch of one: six launches, two copies) -- what the
+    # latency path (b200r_prefix_route_one: one launch, prompt read from pinned host memory)
+    # replaces
+    lat1 = []
+    for p in prompts[1088:1600]:
+        t0 = time.perf_counter()
+        r.route_batch(eps, [p])
+        lat1.append(time.perf_counter() - t0)
+    lat1 = np.array(lat1[64:]) * 1e6
+    out["one_at_a_time_as_batch_of_one"] = {"p50_us": float(np.percentile(lat1, 50)),
+                                            "p99_us": float(np.percentile(lat1, 99))}
     routers._reset_singletons_for_tests()
     conc = {}
     for c in (8, 64, 512, 4096):

@@ -262,6 +262,19 @@ int b200r_trie_dump(b200r_trie *t, uint64_t *d_out, int64_t max_nodes, int64_t *
 int b200r_trie_restore(b200r_trie *t, const uint64_t *d_entries, int64_t count,
                        uint64_t root_mask, void *stream);
 
+/* Latency path: a5 for ONE request with HOST buffers in and out -- one launch (the prompt is
+ * read from a pinned staging buffer of the table straight into shared memory, hashed, walked,
+ * the endpoint drawn and inserted) and one stream synchronisation; same results as a batch of
+ * one.  Returns 0 = routed; 1 = not taken (prompt not pure ASCII, longer than 16384 chunks, or
+ * a chunk size that is not a multiple of 16): route it as a batch of one instead.  `status`
+ * receives the latched B200R_S_* bits.  The staging buffer and ~200 KB of device scratch are
+ * allocated on the table's first call (not a no-allocation entry point).
+ * Replaces PrefixAwareRouter.route_request for a lone request (routing_logic.py:363-423). */
+int b200r_prefix_route_one(b200r_trie *t, const uint8_t *h_prompt, int64_t len_bytes,
+                           uint64_t avail_mask, uint64_t seed, uint64_t seq, int32_t *endpoint,
+                           int32_t *match_depth, uint64_t *matched_mask, uint32_t *status,
+                           void *stream);
+
 /* ------------------------------------------------------------------------
  * Multi-GPU with a PARTITIONED table (scalable variant; no counterpart in the
  * reference).  A request's whole path hangs under its first chunk, so the

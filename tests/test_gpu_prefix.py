@@ -272,6 +272,83 @@ def test_route_from_hashes_and_on_a_restored_table_vs_oracle():
     t2.close()
 
 
+def test_latency_path_one_request_per_launch(golden_prefix):
+    """b200r_prefix_route_one (one launch per request, host bytes in, host result out) equals
+    the unmodified reference on every golden trace -- decisions, lookup results, final trie;
+    prompts it does not take (non-ASCII) go through the batch path in between."""
+    from b200_router.trie import GpuHashTrie
+    taken = 0
+    for tr in golden_prefix["traces"]:
+        t = GpuHashTrie(cap_log2=14)
+        seq, dec, looks = 0, [], []
+        for b in tr["batches"]:
+            avail = sum(1 << i for i in b["avail"])
+            for item in b["prompts"]:
+                p = prefix_ref.flatten_prompt(tr["json_inputs"][item]) if tr["json_inputs"] is not None else item
+                r = t.route_one(p.encode("utf-8"), avail, tr["seed"], seq)
+                if r is None:
+                    assert not p.isascii(), tr["name"]
+                    ep, depth, matched = t.route(pack_prompts([p]), avail, tr["seed"], seq)
+                    r = (int(ep.cpu()[0]), int(depth.cpu()[0]), int(u64(matched)[0]), 0)
+                else:
+                    assert p.isascii() and r[3] == 0
+                    taken += 1
+                seq += 1
+                dec.append(r[0])
+                looks.append([r[1], bits(r[2])])
+        assert dec == tr["decisions"], tr["name"]
+        if tr["lookups"] is not None:
+            assert looks == tr["lookups"], tr["name"]
+        assert trie_as_sorted_list(t.dump()) == tr["trie"], tr["name"]
+        t.close()
+    assert taken > 100
+
+
+def test_latency_path_between_batches_vs_oracle():
+    """Lone requests (latency path) interleaved with batches on one table, against the C
+    oracle: long prompts (several staging passes), an empty prompt, availability churn."""
+    from b200_router.trie import GpuHashTrie
+    tr = traces.SharedPrefixTrace(n_total=3000, batch=1000, n_sys=6, sys_chars=1024,
+                                  suffix_lo=1, suffix_hi=500, seed=77)
+    bufL, stL, lnL = traces.long_context_batch(n=12, chars=128 * 300 + 5, group=4, shared_frac=0.6, seed=5)
+    orc = coracle.TrieOracle()
+    t = GpuHashTrie(cap_log2=17)
+    seq = 0
+
+    def one(buf, start, ln, avail):
+        nonlocal seq
+        raw = bytes(buf[start:start + ln])
+        r = t.route_one(raw, avail, 9, seq)
+        assert r is not None
+        oep, odepth, omatched = orc.route_batch(np.frombuffer(raw, dtype=np.uint8) if ln else np.zeros(16, np.uint8),
+                                                np.zeros(1, np.int64), np.array([ln], np.int32), avail, 9, seq)
+        seq += 1
+        assert (r[0], r[1], r[2]) == (int(oep[0]), int(odepth[0]), int(omatched[0]))
+
+    def batch(buf, starts, lens, avail):
+        nonlocal seq
+        ep, depth, matched = t.route(pack_arrays(buf, starts, lens, pin=False), avail, 9, seq)
+        oep, odepth, omatched = orc.route_batch(buf, starts, lens, avail, 9, seq)
+        seq += len(starts)
+        assert (ep.cpu().numpy() == oep).all() and (depth.cpu().numpy() == odepth).all()
+        assert (u64(matched) == omatched).all()
+
+    b0, b1, b2 = (tr.batch_arrays(k) for k in range(3))
+    for i in range(40):                                # cold table: lone requests create the runs
+        one(b0[0], int(b0[1][i]), int(b0[2][i]), 0xFF)
+    batch(*b1, 0xFF)
+    for i in range(12):                                # 301 chunks each: two staging passes
+        one(bufL, int(stL[i]), int(lnL[i]), 0xFF if i % 3 else 0x0F)
+    one(b0[0], 0, 0, 0xFF)                             # empty prompt
+    for i in range(40, 200):
+        one(b0[0], int(b0[1][i]), int(b0[2][i]), 0xF7 if i % 5 == 0 else 0xFF)
+    batch(*b2, 0xFF)
+    batch(bufL, stL, lnL, 0xFF)
+    t.check_status()
+    assert t.dump() == orc.dump()
+    t.close()
+
+
 def test_batch_epoch_wraps_without_losing_the_table():
     """The per-node first-toucher words are tagged with a 32-bit batch epoch.  When it runs out
     the library sweeps those words and restarts the count; learned prefixes stay

@@ -47,6 +47,9 @@ SIGNATURES = {
                                            _sz, _vp]),
     "b200r_prefix_route_hashes": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _u64, _u64, _u64, _vp, _vp, _vp, _vp,
                                             _sz, _vp]),
+    "b200r_prefix_route_one": (C.c_int, [_vp, C.c_char_p, _i64, _u64, _u64, _u64, C.POINTER(C.c_int32),
+                                         C.POINTER(C.c_int32), C.POINTER(C.c_uint64),
+                                         C.POINTER(C.c_uint32), _vp]),
     "b200r_pipe_create": (C.c_int, [_vp, _i32, C.POINTER(_vp)]),
     "b200r_pipe_destroy": (C.c_int, [_vp]),
     "b200r_pipe_prep_stream": (_vp, [_vp]),

@@ -277,6 +277,21 @@ class PrefixAwareRouter(_RefPrefix):
         prompt = extract_prompt_parts(request_json)
         if self.batcher is not None:
             return await self.batcher.route(endpoints, prompt)
+        return self.route_one(endpoints, prompt)
+
+    def route_one(self, endpoints, prompt) -> str:
+        """One request, now: the latency path (one kernel launch, b200r_prefix_route_one) when
+        the prompt is ASCII, else a batch of one.  Same decision either way."""
+        text = prompt if isinstance(prompt, str) else "\n".join(prompt)
+        if text.isascii():
+            r = self.hashtrie.route_one(text.encode("ascii"), self.registry.mask(endpoints),
+                                        self.seed, self.seq)
+            if r is not None:
+                self.seq += 1
+                self.hashtrie.raise_for_status(r[3])
+                if r[0] < 0:
+                    raise IndexError("Cannot choose from an empty sequence")   # random.choice([])
+                return self.registry.urls[r[0]]
         return self.route_batch(endpoints, [prompt])[0]
 
     # ---- checkpoint (the reference has none: its trie dies with the process)

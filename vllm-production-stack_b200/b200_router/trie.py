@@ -198,6 +198,21 @@ class GpuHashTrie:
                 _stream()))
         return ep[:n], depth[:n], matched[:n]
 
+    # ------------------------------------------------- a5 for one request (latency path)
+    def route_one(self, prompt: bytes, avail_mask: int, seed: int, seq: int):
+        """b200r_prefix_route_one: one launch and one synchronisation for ONE request given as
+        host bytes.  Returns (endpoint, depth, matched mask, latched status bits), or None when
+        the latency path does not take the prompt (not ASCII, too long): use route()."""
+        ep, depth, matched, st = C.c_int32(), C.c_int32(), C.c_uint64(), C.c_uint32()
+        with torch.cuda.device(self.device):
+            rc = _lib.lib().b200r_prefix_route_one(
+                self._h, prompt, len(prompt), avail_mask & M64, seed & M64, seq & M64,
+                C.byref(ep), C.byref(depth), C.byref(matched), C.byref(st), _stream())
+        if rc == 1:
+            return None
+        _lib.check(rc)
+        return ep.value, depth.value, matched.value, st.value
+
     # --------------------------------------------------------------- dump etc
     def dump_raw(self):
         """(entries uint64[count,4], root_mask); an entry is {log index | records left in its run

@@ -98,4 +98,6 @@ struct b200r_trie {
     cudaStream_t part_send, part_route, part_prep, part_ret;
     cudaEvent_t part_inputs, part_prepped, part_routed, part_sent[2], part_finished[2];
     bool part_ready, part_has_finished[2];
+    // latency path (b200r_prefix_route_one; allocated on first use)
+    uint8_t *one_host, *one_host_dev, *one_dev;
 };

@@ -511,6 +511,111 @@ k_commit(Rec *__restrict__ log, TrieDev *dev, const int32_t *__restrict__ chunk_
                        matched_out, idx_of_pos);
 }
 
+
+// =========================================================================
+// Latency path: ONE request per launch (live traffic arrives one request at a time and a
+// batch of one through the batch kernels costs six launches and two copies).  One CTA:
+//   1. the prompt is read straight from the caller's pinned host buffer into shared memory
+//      (16-byte loads, all in flight at once: one PCIe round trip), hashed from there, a
+//      thread per chunk;
+//   2. warp 0 walks the trie with the batch path's own walker (claim mode, 32 lanes);
+//   3. a lone request is a root by definition: draw from the candidates of the deepest node
+//      usable before the call, OR the endpoint bit into everything below, write the result to
+//      the caller's (host-mapped) result block.
+// ASCII prompts only (code points = bytes); anything else is reported back untouched and the
+// caller takes the batch path.
+// =========================================================================
+constexpr int ONE_PASS = 32768;        // prompt bytes staged per pass
+constexpr int ONE_MAX_CHUNKS = 16384;  // scratch capacity of the latency path
+constexpr uint32_t ONE_DONE = 0x80000000u, ONE_NONASCII = 0x40000000u;
+struct OneResult { int32_t endpoint, depth; uint64_t matched; uint32_t status, pad[3]; };
+
+__device__ __forceinline__ uint64_t xxh64_words(const uint8_t *p, int len)
+{   // p 8-byte aligned (shared memory)
+    const uint8_t *end = p + len;
+    uint64_t h;
+    if (len >= 32) {
+        uint64_t v1 = XP1 + XP2, v2 = XP2, v3 = 0, v4 = 0 - XP1;
+        const uint8_t *lim = end - 32;
+        do {
+            const uint4 a = *(const uint4 *)p, b = *(const uint4 *)(p + 16);
+            v1 = xround(v1, u64_of(a.x, a.y));
+            v2 = xround(v2, u64_of(a.z, a.w));
+            v3 = xround(v3, u64_of(b.x, b.y));
+            v4 = xround(v4, u64_of(b.z, b.w));
+            p += 32;
+        } while (p <= lim);
+        h = rotl<1>(v1) + rotl<7>(v2) + rotl<12>(v3) + rotl<18>(v4);
+        h = xmerge(h, v1); h = xmerge(h, v2); h = xmerge(h, v3); h = xmerge(h, v4);
+    } else {
+        h = XP5;
+    }
+    h += (uint64_t)len;
+    while (p + 8 <= end) { h ^= xround(0, *(const uint64_t *)p); h = mulc<XP1>(rotl<27>(h)) + XP4; p += 8; }
+    if (p + 4 <= end) { h ^= mulc<XP1>((uint64_t)(*(const uint32_t *)p)); h = mulc<XP2>(rotl<23>(h)) + XP3; p += 4; }
+    while (p < end) { h ^= mulc<XP5>((uint64_t)(*p)); h = mulc<XP1>(rotl<11>(h)); p++; }
+    return xavalanche(h);
+}
+
+__global__ void __launch_bounds__(256)
+k_route_one(WalkArgs a, TrieDev *dev, const uint8_t *__restrict__ prompt, int len, int cc,
+            uint64_t seed, uint64_t seq, int32_t *chunk_base, uint64_t *hashes, OneResult *out)
+{
+    __shared__ __align__(16) uint8_t s_buf[ONE_PASS];
+    __shared__ unsigned s_hi;
+    const int C = (len + cc - 1) / cc;
+    const int pass = (ONE_PASS / cc) * cc;             // whole chunks per pass; cc % 16 == 0
+    if (threadIdx.x == 0) s_hi = 0;
+    unsigned hi = 0;
+    for (int base = 0; base < len; base += pass) {
+        const int m = min(pass, len - base);
+        __syncthreads();
+#pragma unroll 4
+        for (int x = threadIdx.x; x * 16 < m; x += blockDim.x) {
+            const uint4 v = *(const uint4 *)(prompt + base + x * 16);
+            ((uint4 *)s_buf)[x] = v;
+            hi |= (v.x | v.y | v.z | v.w) & 0x80808080u;
+        }
+        __syncthreads();
+        for (int c = threadIdx.x; c * cc < m; c += blockDim.x)
+            hashes[base / cc + c] = xxh64_words(s_buf + c * cc, min(cc, m - c * cc));
+    }
+    if (hi) atomicOr(&s_hi, 1u);
+    if (threadIdx.x == 0) { chunk_base[0] = 0; chunk_base[1] = C; }
+    __syncthreads();
+    if (threadIdx.x >= 32) return;
+    const int lane = threadIdx.x;
+    if (s_hi) {                                         // not ASCII: nothing touched
+        if (lane == 0) { out->endpoint = -1; out->depth = 0; out->matched = 0; __threadfence_system(); out->status = ONE_DONE | ONE_NONASCII; }
+        return;
+    }
+    const Tile g = make_tile<32>(lane);
+    WarpAlloc wa;
+    { const uint2 v = a.t.wblk[NWSLOT - 1]; wa.cur = v.x; wa.end = v.y; }
+    ReqSpan sp; sp.b0 = 0; sp.C = C;
+    Pending none = { -1, 0, 0, 0 };
+    walk_request<W_CLAIM, false, 32>(a, 0, g, wa, sp, lane < C ? __ldcg(hashes + lane) : 0, none);
+    if (lane == 0) a.t.wblk[NWSLOT - 1] = make_uint2(wa.cur, wa.end);
+    __syncwarp();
+    const int dpre = __ldcg(a.dpre);
+    const uint64_t cand = __ldcg(a.cand);
+    const int cnt = __popcll(cand);
+    const int e = cnt ? nth_set_bit(cand, pick(seed, seq, (uint32_t)cnt)) : -1;
+    if (e >= 0) {
+        const uint64_t bit = 1ULL << e;
+        if (lane == 0 && !(dev->root_mask & bit)) atomicOr((unsigned long long *)&dev->root_mask, bit);
+        for (int d = dpre + lane; d < C; d += 32) {
+            const uint32_t x = __ldcg(a.slots + d);
+            if (x != SLOT_NONE) atomicOr((unsigned long long *)&a.t.log[x & IDX_MASK].mask, bit);
+        }
+    }
+    if (lane == 0) {
+        out->endpoint = e; out->depth = dpre; out->matched = cand;
+        __threadfence_system();
+        out->status = ONE_DONE | (dev->status & 0xFFFFu);
+    }
+}
+
 // ------------------------------------------------------------ dump / restore / sweeps
 __global__ void k_count_nodes(const Head *__restrict__ tab, const Rec *__restrict__ log, int64_t cap,
                               TrieDev *dev)
@@ -956,6 +1061,7 @@ int b200r_trie_create(int32_t cap_log2, int32_t chunk_chars, b200r_trie **out)
     t->epoch = 0;
     t->tab = nullptr; t->log = nullptr; t->wblk = nullptr; t->dev = nullptr;
     t->part_ready = false; t->part_has_finished[0] = t->part_has_finished[1] = false;
+    t->one_host = t->one_host_dev = t->one_dev = nullptr;
     const size_t cap = (size_t)1 << cap_log2;
     cudaError_t e;
     if ((e = cudaMalloc(&t->tab, 2 * cap * sizeof(Head))) != cudaSuccess ||
@@ -984,6 +1090,7 @@ int b200r_trie_destroy(b200r_trie *t)
         for (cudaEvent_t e : evs) cudaEventDestroy(e);
         for (cudaStream_t s : sts) cudaStreamDestroy(s);
     }
+    if (t->one_host) { cudaDeviceSynchronize(); cudaFreeHost(t->one_host); cudaFree(t->one_dev); }
     cudaFree(t->tab); cudaFree(t->log); cudaFree(t->wblk); cudaFree(t->dev);
     delete t;
     return B200R_OK;
@@ -1176,6 +1283,61 @@ int b200r_prefix_route_hashes(b200r_trie *t, const uint64_t *d_hashes, const int
     return route_from(t, d_hashes, d_chunk_base, n, max_chunks, avail_mask, seed, seq0, d_endpoint,
                       d_match_depth, d_matched_mask, (uint8_t *)d_scratch, p, (cudaStream_t)stream);
 }
+
+// a5 for ONE request with host buffers in and out (see k_route_one).  Synchronous: one launch
+// and one stream synchronisation.  Returns 0 = routed, 1 = not taken (prompt not ASCII, longer
+// than the path's staging buffer, or chunk size not a multiple of 16): route it as a batch of
+// one.  The staging buffer (pinned, host-mapped) and 200 KB of device scratch are allocated on
+// the table's first call.
+int b200r_prefix_route_one(b200r_trie *t, const uint8_t *h_prompt, int64_t len_bytes,
+                           uint64_t avail_mask, uint64_t seed, uint64_t seq, int32_t *endpoint,
+                           int32_t *match_depth, uint64_t *matched_mask, uint32_t *status,
+                           void *stream)
+{
+    if (!t || len_bytes < 0 || (len_bytes && !h_prompt) || !endpoint) { set_error("b200r_prefix_route_one: bad argument"); return B200R_E_INVALID; }
+    const int cc = t->chunk_chars;
+    if ((cc & 15) || cc > ONE_PASS || len_bytes > (int64_t)ONE_MAX_CHUNKS * cc) return 1;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (!t->one_host) {
+        const size_t hb = (size_t)ONE_MAX_CHUNKS * cc + 256;
+        B200R_CUDA(cudaHostAlloc((void **)&t->one_host, hb, cudaHostAllocMapped));
+        B200R_CUDA(cudaHostGetDevicePointer((void **)&t->one_host_dev, t->one_host, 0));
+        const size_t db = (size_t)ONE_MAX_CHUNKS * 12 + 256;
+        cudaError_t e = cudaMalloc((void **)&t->one_dev, db);
+        if (e != cudaSuccess) { cudaFreeHost(t->one_host); t->one_host = nullptr; set_error("b200r_prefix_route_one: %s", cudaGetErrorString(e)); return B200R_E_NOMEM; }
+    }
+    // layout: host = [result block 64 B | prompt]; device = [hashes | slots | chunk_base, dpre, cand]
+    OneResult *res = (OneResult *)t->one_host;
+    uint8_t *stage = t->one_host + 64;
+    memcpy(stage, h_prompt, (size_t)len_bytes);
+    memset(stage + len_bytes, 0, 16);
+    res->status = 0;
+    unsigned long long tag;
+    int rc = next_epoch(t, st, &tag);
+    if (rc) return rc;
+    uint64_t *hashes = (uint64_t *)t->one_dev;
+    uint32_t *slots = (uint32_t *)(t->one_dev + (size_t)ONE_MAX_CHUNKS * 8);
+    uint8_t *tail = t->one_dev + (size_t)ONE_MAX_CHUNKS * 12;
+    WalkArgs a = WalkArgs();
+    a.t = trie_ref(t);
+    a.hashes = hashes; a.chunk_base = (int32_t *)tail; a.max_chunks = ONE_MAX_CHUNKS;
+    a.avail = avail_mask; a.tag = tag; a.slots = slots;
+    a.dpre = (int32_t *)(tail + 8); a.cand = (uint64_t *)(tail + 16);
+    g_launches += 1;
+    k_route_one<<<1, 256, 0, st>>>(a, t->dev, t->one_host_dev + 64, (int)len_bytes, cc, seed, seq,
+                                   (int32_t *)tail, hashes, (OneResult *)t->one_host_dev);
+    B200R_LAUNCH_CHECK("k_route_one");
+    B200R_CUDA(cudaStreamSynchronize(st));
+    const uint32_t s = *(volatile uint32_t *)&res->status;
+    if (!(s & ONE_DONE)) { set_error("b200r_prefix_route_one: the kernel left no result"); return B200R_E_CUDA; }
+    if (s & ONE_NONASCII) return 1;
+    *endpoint = res->endpoint;
+    if (match_depth) *match_depth = res->depth;
+    if (matched_mask) *matched_mask = res->matched;
+    if (status) *status = s & 0xFFFFu;
+    return B200R_OK;
+}
+
 
 int b200r_prefix_route_batch(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
                              const int32_t *d_lens, const int32_t *d_nchars, int64_t n,
