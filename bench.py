@@ -538,7 +538,9 @@ def run_b200(args):
     core = {k: prof[k] for k in ("prep", "hash", "claim", "select", "commit") if prof[k][1]}
     dom = max(core, key=lambda k: core[k][0])
     dom_ms, dom_n = core[dom]
-    kernel_name = {"prep": "k_prep_scan", "hash": "k_hash_chunks", "claim": "k_walk<claim>",
+    from b200_router.trie import claim_kernel_name
+    kernel_name = {"prep": "k_prep_scan", "hash": "k_hash_chunks",
+                   "claim": claim_kernel_name(args.batch, my_chunks // max(K, 1)),
                    "select": "k_select", "commit": "k_commit"}[dom]
     achieved = algo[dom] / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else 0.0
     traffic, traffic_commit = load_ncu_traffic(kernel_name)

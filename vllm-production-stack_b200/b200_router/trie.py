@@ -24,6 +24,12 @@ def _stream():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+def claim_kernel_name(n: int, chunks: int) -> str:
+    """The kernel the automatic claim decomposition picks for a batch of n requests with
+    `chunks` chunks in total (csrc/prefix.cu: claim_kind_for)."""
+    return "k_claim_thread" if chunks <= n * 64 else "k_walk<claim>"
+
+
 class GpuHashTrie:
     """Open-addressing table of trie nodes on one GPU.
 
