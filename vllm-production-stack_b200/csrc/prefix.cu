@@ -512,6 +512,40 @@ k_commit(Rec *__restrict__ log, TrieDev *dev, const int32_t *__restrict__ chunk_
 }
 
 
+// The same with a warp per request, lanes over depths: long prompts (C4: 256 chunks, half of
+// them new) make the thread version a chain of a hundred dependent atomics.
+__global__ void __launch_bounds__(256)
+k_commit_warp(Rec *__restrict__ log, TrieDev *dev, const int32_t *__restrict__ chunk_base, int n,
+              int64_t max_chunks, const uint32_t *__restrict__ slots, const int32_t *__restrict__ leader,
+              const int32_t *__restrict__ choice, const int32_t *__restrict__ depth,
+              int32_t *__restrict__ endpoint, uint64_t *__restrict__ matched_out,
+              const int32_t *__restrict__ n_dev, const uint32_t *__restrict__ idx_of_pos)
+{
+    if (n_dev) n = *n_dev;
+    const int lane = threadIdx.x & 31;
+    const int w0 = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = (gridDim.x * blockDim.x) >> 5;
+    for (int i = w0; i < n; i += nw) {
+        int e = -1;
+        if (lane == 0) {
+            int j = i, l;
+            while ((l = leader[j]) >= 0) j = idx_of_pos ? (int)idx_of_pos[l] : l;
+            e = choice[j];
+            endpoint[i] = e;
+            if (j != i) matched_out[i] = (e >= 0) ? (1ULL << e) : 0;
+            if (e >= 0 && !(dev->root_mask & (1ULL << e)))
+                atomicOr((unsigned long long *)&dev->root_mask, 1ULL << e);
+        }
+        e = __shfl_sync(0xffffffffu, e, 0);
+        if (e < 0) continue;
+        const uint64_t bit = 1ULL << e;
+        const ReqSpan sp = req_span(chunk_base, i, max_chunks);
+        for (int d = depth[i] + lane; d < sp.C; d += 32) {
+            const uint32_t x = slots[sp.b0 + d];
+            if (x != SLOT_NONE) atomicOr((unsigned long long *)&log[x & IDX_MASK].mask, bit);
+        }
+    }
+}
+
 // =========================================================================
 // Latency path: ONE request per launch (live traffic arrives one request at a time and a
 // batch of one through the batch kernels costs six launches and two copies).  One CTA:
@@ -892,9 +926,14 @@ int launch_route_core(b200r_trie *t, const RouteCore &rc, cudaStream_t st)
     B200R_LAUNCH_CHECK("k_select");
     }
     { ProfScope ps__(PK_COMMIT, st); g_launches += 1;
-    k_commit<<<tblocks, 256, 0, st>>>(t->log, t->dev, rc.chunk_base, nn, rc.max_chunks, rc.slots,
-                                     rc.leader, rc.choice, rc.depth, rc.endpoint, rc.matched, rc.n_dev,
-                                     rc.idx_of_pos);
+    if (rc.claim_kind == 1)
+        k_commit<<<tblocks, 256, 0, st>>>(t->log, t->dev, rc.chunk_base, nn, rc.max_chunks, rc.slots,
+                                         rc.leader, rc.choice, rc.depth, rc.endpoint, rc.matched, rc.n_dev,
+                                         rc.idx_of_pos);
+    else
+        k_commit_warp<<<walk_grid(rc.n), 256, 0, st>>>(t->log, t->dev, rc.chunk_base, nn, rc.max_chunks,
+                                                       rc.slots, rc.leader, rc.choice, rc.depth, rc.endpoint,
+                                                       rc.matched, rc.n_dev, rc.idx_of_pos);
     B200R_LAUNCH_CHECK("k_commit");
     }
     return B200R_OK;
