@@ -358,6 +358,12 @@ int b200r_ring_lookup_batch(b200r_ring *r, const uint8_t *d_bytes, const int64_t
  * choose per batch from the average number of chunks (one thread up to 64 chunks per prompt, a
  * warp beyond), 1 = one thread, 2 = a warp, 3 = 16 lanes, 4 = 8 lanes; identical results */
 int b200r_set_claim_mode(int mode);
+
+/* Partitioned multi-GPU send phase: 0 (default) = for ASCII batches the hashing kernel stores the
+ * chunk hashes straight into the owners' buffers (placement done by the prep kernel); 1 = always
+ * hash into local CSR order, compact per owner and ship (the path non-ASCII batches take).  Same
+ * results; for tests and comparison. */
+int b200r_set_part_staged(int on);
 #define B200R_PROF_SLOTS 13
 int b200r_prof_enable(int on);
 int b200r_prof_read(float *ms_out, long long *count_out, int nslots);

@@ -191,3 +191,16 @@ def test_partitioned_lockstep_shared_prefix_and_empty_shard():
             shards[1] = traces.pack_strings([])[:3]
         batches.append((avail, shards))
     _check_partitioned_lockstep(world, batches, seed=14)
+
+
+def test_partitioned_lockstep_with_the_staged_send_path():
+    """ASCII batches normally have their hashes stored straight into the owners' buffers by the
+    hashing kernel; b200r_set_part_staged(1) forces the compaction + shipment kernels that
+    non-ASCII batches take.  Same decisions and tables either way."""
+    from b200_router import _lib
+    _lib.check(_lib.lib().b200r_set_part_staged(1))
+    try:
+        test_partitioned_lockstep_shared_prefix_and_empty_shard()
+        test_partitioned_lockstep_heavy_sharing()
+    finally:
+        _lib.check(_lib.lib().b200r_set_part_staged(0))

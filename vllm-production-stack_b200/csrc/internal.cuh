@@ -18,6 +18,7 @@ extern bool g_prof_on;
 extern std::vector<ProfSpan> g_spans;
 extern long long g_launches;
 extern int g_claim_mode;
+extern int g_part_staged;      // b200r_set_part_staged: 1 = always compact + ship (test / comparison)
 int claim_kind_for(int64_t n, int64_t chunks);
 
 struct ProfScope {
@@ -49,6 +50,28 @@ struct P2PDyn {
 
 static inline size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
+// Partitioned multi-GPU path, send side: the prep kernel also decides where every request goes
+// (owner = mix(first chunk hash) % world, slot in the (source, owner) segment taken with one
+// packed atomicAdd {requests << 32 | chunks} per warp and owner), writes the request's info
+// word straight into the owner's inbound buffer and leaves, per request, the ADDRESS of its
+// first chunk hash in that buffer -- where the hashing kernel then stores the hashes (plain
+// stores over NVLink peer memory; no staging copy, no shipment kernel).  world == 0: off.
+struct PartPlace {
+    int world, my_rank;
+    unsigned long long *totals;             // [world]
+    long long cap, rcap;
+    const unsigned long long *peer_bases;   // [world]
+    size_t hash_off, info_off;              // of this batch's buffer set
+    uint32_t *dest_slot;                    // [n] owner << 24 | slot
+    unsigned long long *out_ptr;            // [n]
+};
+
+__host__ __device__ inline int part_owner_of(uint64_t h0, int world)
+{
+    const uint64_t x = h0 * 0x9E3779B97F4A7C15ULL;
+    return (int)((x >> 33) % (uint64_t)world);
+}
+
 struct Plan {           // carve-up of the caller's scratch buffer
     size_t off_tile_first, off_block_sums, off_nchars, off_chunk_off, off_chunk_base, off_hashes,
         off_slots, off_leader, off_choice, off_dpre, off_cand, total;
@@ -62,7 +85,8 @@ int check_prompt_args(const void *bytes, const void *starts, const void *lens, i
 int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const int32_t *d_lens,
                 const int32_t *d_nchars, int64_t n, int32_t cc, uint32_t flags,
                 int32_t *d_chunk_base, uint64_t *d_hashes, int64_t max_chunks, uint8_t *scratch,
-                const Plan &p, TrieDev *dev, cudaStream_t st, int phase = 0);
+                const Plan &p, TrieDev *dev, cudaStream_t st, int phase = 0,
+                const PartPlace *pp = nullptr);
 
 // CSR of given per-request chunk counts; the count of requests is known only on the device
 int launch_prep_counts(const int32_t *d_counts, int64_t n_max, const int32_t *n_dev,

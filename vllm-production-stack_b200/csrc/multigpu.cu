@@ -75,8 +75,7 @@ __device__ __forceinline__ bool last_cta_after_peer_stores(unsigned int *ticket)
 __device__ __forceinline__ int part_owner(const uint64_t *hashes, int b, int C, int world)
 {
     if (C == 0) return 0;                     // empty prompt: touches only a root
-    uint64_t x = hashes[b] * 0x9E3779B97F4A7C15ULL;
-    return (int)((x >> 33) % (uint64_t)world);
+    return part_owner_of(hashes[b], world);
 }
 
 constexpr int PART_BLOCK = 256;
@@ -219,18 +218,24 @@ k_part_bulk(const uint64_t *__restrict__ hash_stage, const unsigned long long *_
     }
 }
 
-// batch with no request at all on this rank: only the flags
+// Arrival flags for every owner.  Runs behind the kernels that stored into the owners' buffers
+// (stream order: their stores are complete when this starts).  `totals` = the packed
+// {requests << 32 | chunks} per owner that the placement left (NULL: an empty batch); reset
+// here for the batch after next.
 __global__ void k_part_publish_in(const unsigned long long *__restrict__ peer_bases, int world,
-                                  int my_rank, int set, unsigned long long epoch, unsigned int n)
+                                  int my_rank, int set, unsigned long long epoch, unsigned int n,
+                                  unsigned long long *__restrict__ totals)
 {
     const int d = threadIdx.x;
     if (d >= world) return;
+    const unsigned long long tt = totals ? totals[d] : 0ULL;
     PartFlags *f = (PartFlags *)(uintptr_t)peer_bases[d];
     __threadfence_system();
     *(volatile unsigned long long *)&f->in_n[set][my_rank] = (epoch << 32) | n;
-    *(volatile unsigned long long *)&f->in_chunk[set][my_rank] = (epoch << 32);
-    *(volatile unsigned long long *)&f->in_req[set][my_rank] = (epoch << 32);
+    *(volatile unsigned long long *)&f->in_chunk[set][my_rank] = (epoch << 32) | (uint32_t)tt;
+    *(volatile unsigned long long *)&f->in_req[set][my_rank] = (epoch << 32) | (uint32_t)(tt >> 32);
     __threadfence_system();
+    if (totals) totals[d] = 0;
 }
 
 // Wait for all sources.  ONE small CTA spins on the arrival flags (local memory): a grid of
@@ -357,7 +362,7 @@ extern "C" {
 struct PartLayout {
     size_t symm_total, hash_off, info_off, res_off, hash_set, info_set, res_set;
     // local work buffer
-    size_t work_total, w_dyn, w_totals, w_dest_slot, w_hash_stage, w_info_stage, w_pos_owned, w_idx_of_pos,
+    size_t work_total, w_dyn, w_totals, w_out_ptr, w_dest_slot, w_hash_stage, w_info_stage, w_pos_owned, w_idx_of_pos,
         w_ep, w_depth, w_matched, w_plan;
     int64_t n_max, c_max;
     int nblk_max;
@@ -378,7 +383,8 @@ static PartLayout part_layout(int world, int64_t cap, int64_t rcap)
     L.nblk_max = (int)((rcap + PART_BLOCK - 1) / PART_BLOCK);
     size_t o = 0;
     L.w_dyn = o;       o += 2 * align_up(sizeof(PartDyn));          // one per batch parity
-    L.w_totals = o;    o += align_up((size_t)world * 8);
+    L.w_totals = o;    o += 2 * align_up((size_t)world * 8);               // one per batch parity
+    L.w_out_ptr = o;   o += 2 * align_up((size_t)rcap * 8);
     L.w_dest_slot = o; o += 2 * align_up((size_t)rcap * 4);     // one per batch parity
     L.w_hash_stage = o; o += align_up((size_t)world * (cap + 2) * 8);   // one fixed segment per owner
     L.w_info_stage = o; o += align_up((size_t)world * (rcap + 2) * 8);
@@ -420,6 +426,12 @@ int b200r_part_layout(int32_t world, int64_t cap, int64_t rcap, size_t out[2])
 // Send phase.  With a prep stream, the per-request counting + scan of the hash stage runs there
 // (it is a chain of small kernels; next to the previous batch's hashing kernel instead of after
 // it) and `st` picks up at the hashing kernel.
+//   ASCII batches (the rule): the prep kernel places the requests (PartPlace) and the hashing
+//   kernel stores every chunk hash straight into the owner's inbound buffer over NVLink peer
+//   memory -- the hashing is fused with the dispatch; a one-CTA kernel behind it publishes the
+//   arrival flags.  No copy of the hashes is made on the sending side.
+//   Other batches: hashes in CSR order, then k_part_place (compaction into per-owner staging
+//   segments) and k_part_bulk (shipment).
 static int part_send_impl(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_starts,
                           const int32_t *d_lens, const int32_t *d_nchars, int64_t n, int64_t max_chunks,
                           uint32_t flags, const uint64_t *d_peer_bases, int32_t world, int32_t rank,
@@ -428,32 +440,49 @@ static int part_send_impl(b200r_trie *t, const uint8_t *d_bytes, const int64_t *
 {
     int rc = part_check(world, rank, cap, rcap, d_peer_bases, d_work);
     if (rc) return rc;
+    if (!t) { set_error("null trie"); return B200R_E_INVALID; }
     if (max_chunks > cap || n > rcap) { set_error("partitioned routing: batch (n=%lld, max_chunks=%lld) exceeds the exchange capacity (rcap=%lld, cap=%lld)", (long long)n, (long long)max_chunks, (long long)rcap, (long long)cap); return B200R_E_INVALID; }
-    if (prep_st != st) {
-        rc = b200r_prefix_hash_stage(t, d_bytes, d_starts, d_lens, d_nchars, n, max_chunks,
-                                     flags | B200R_F_PREP_ONLY, d_scratch, scratch_bytes, prep_st);
-        if (rc) return rc;
-        B200R_CUDA(cudaEventRecord(prepped, prep_st));
-        B200R_CUDA(cudaStreamWaitEvent(st, prepped, 0));
-        flags |= B200R_F_PREP_DONE;
-    }
-    rc = b200r_prefix_hash_stage(t, d_bytes, d_starts, d_lens, d_nchars, n, max_chunks, flags,
-                                 d_scratch, scratch_bytes, st);
-    if (rc) return rc;
     flags &= ~(uint32_t)(B200R_F_PREP_ONLY | B200R_F_PREP_DONE);
     const PartLayout L = part_layout(world, cap, rcap);
     const Plan p = make_plan(n, max_chunks, flags, true);
     uint8_t *sc = (uint8_t *)d_scratch, *wk = (uint8_t *)d_work;
-    const int32_t *chunk_base = (const int32_t *)(sc + p.off_chunk_base);
-    const uint64_t *hashes = (const uint64_t *)(sc + p.off_hashes);
-    unsigned long long *totals = (unsigned long long *)(wk + L.w_totals);
     const int set = (int)(epoch & 1);
-    const int nblk = (int)((n + PART_BLOCK - 1) / PART_BLOCK);
+    unsigned long long *totals = (unsigned long long *)(wk + L.w_totals + (size_t)set * align_up((size_t)world * 8));
+    uint32_t *dest_slot = (uint32_t *)(wk + L.w_dest_slot + (size_t)set * align_up((size_t)rcap * 4));
+    const bool direct = (flags & B200R_F_ALL_ASCII) && n > 0 && !g_part_staged;
+    if (n > 0) {
+        rc = check_prompt_args(d_bytes, d_starts, d_lens, n, max_chunks, t->chunk_chars);
+        if (rc) return rc;
+        if (!d_scratch || scratch_bytes < p.total) { set_error("scratch too small: need %zu bytes, got %zu", p.total, scratch_bytes); return B200R_E_SCRATCH; }
+        PartPlace pp = PartPlace();
+        if (direct) {
+            pp.world = world; pp.my_rank = rank; pp.totals = totals; pp.cap = cap; pp.rcap = rcap;
+            pp.peer_bases = (const unsigned long long *)d_peer_bases;
+            pp.hash_off = L.hash_off + (size_t)set * L.hash_set;
+            pp.info_off = L.info_off + (size_t)set * L.info_set;
+            pp.dest_slot = dest_slot;
+            pp.out_ptr = (unsigned long long *)(wk + L.w_out_ptr + (size_t)set * align_up((size_t)rcap * 8));
+        }
+        int32_t *cb = (int32_t *)(sc + p.off_chunk_base);
+        uint64_t *hs = (uint64_t *)(sc + p.off_hashes);
+        rc = launch_hash(d_bytes, d_starts, d_lens, d_nchars, n, t->chunk_chars, flags, cb, hs, max_chunks,
+                         sc, p, t->dev, prep_st, 1, direct ? &pp : nullptr);
+        if (rc) return rc;
+        if (prep_st != st) {
+            B200R_CUDA(cudaEventRecord(prepped, prep_st));
+            B200R_CUDA(cudaStreamWaitEvent(st, prepped, 0));
+        }
+        rc = launch_hash(d_bytes, d_starts, d_lens, d_nchars, n, t->chunk_chars, flags, cb, hs, max_chunks,
+                         sc, p, t->dev, st, 2, direct ? &pp : nullptr);
+        if (rc) return rc;
+    }
     PartDyn *dyn = part_dyn(wk, L, set);
     ProfScope ps__(PK_PUSH, st);
-    if (nblk > 0) {
+    if (n > 0 && !direct) {
+        const int32_t *chunk_base = (const int32_t *)(sc + p.off_chunk_base);
+        const uint64_t *hashes = (const uint64_t *)(sc + p.off_hashes);
+        const int nblk = (int)((n + PART_BLOCK - 1) / PART_BLOCK);
         g_launches += 2;
-        uint32_t *dest_slot = (uint32_t *)(wk + L.w_dest_slot + (size_t)set * align_up((size_t)rcap * 4));
         uint64_t *hash_stage = (uint64_t *)(wk + L.w_hash_stage);
         unsigned long long *info_stage = (unsigned long long *)(wk + L.w_info_stage);
         k_part_place<<<nblk, PART_BLOCK, 0, st>>>(chunk_base, hashes, (int)n, world, totals, cap, rcap,
@@ -468,7 +497,7 @@ static int part_send_impl(b200r_trie *t, const uint8_t *d_bytes, const int64_t *
     } else {
         g_launches += 1;
         k_part_publish_in<<<1, P2P_MAX_WORLD, 0, st>>>((const unsigned long long *)d_peer_bases, world, rank,
-                                                       set, epoch, (unsigned)n);
+                                                       set, epoch, (unsigned)n, n > 0 ? totals : nullptr);
         B200R_LAUNCH_CHECK("k_part_publish_in");
     }
     return B200R_OK;
@@ -628,6 +657,7 @@ int b200r_part_begin(b200r_trie *t, uint32_t epoch)
     const int par = (int)(epoch & 1);
     if (t->part_has_finished[par]) {
         B200R_CUDA(cudaStreamWaitEvent(t->part_send, t->part_finished[par], 0));
+        B200R_CUDA(cudaStreamWaitEvent(t->part_prep, t->part_finished[par], 0));   // it stores into that set too
         B200R_CUDA(cudaStreamWaitEvent(t->part_prep, t->part_sent[par], 0));
     }
     return B200R_OK;

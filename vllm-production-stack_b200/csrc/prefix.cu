@@ -48,6 +48,7 @@ int cuda_fail(cudaError_t e, const char *what)
 
 // ------------------------------------------------------------- profiling (internal.cuh)
 int g_claim_mode = 0;          // b200r_set_claim_mode: 0 auto, else claim_kind_for's value
+int g_part_staged = 0;
 bool g_prof_on = false;
 std::vector<ProfSpan> g_spans;
 long long g_launches = 0;
@@ -95,7 +96,7 @@ k_prep_scan(const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars
             const int32_t *__restrict__ block_sums, int32_t *__restrict__ chunk_base,
             int32_t *__restrict__ tile_first, int64_t max_chunks, TrieDev *dev,
             const uint8_t *__restrict__ bytes, const int64_t *__restrict__ starts,
-            uint64_t *__restrict__ hashes, const int32_t *__restrict__ n_dev)
+            uint64_t *__restrict__ hashes, const int32_t *__restrict__ n_dev, const PartPlace pp)
 {
     __shared__ int s_red[32];
     __shared__ int s_wsum[32];
@@ -122,6 +123,8 @@ k_prep_scan(const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars
     int wbase = 0;
     for (int k = 0; k < w; k++) wbase += s_wsum[k];
     const int base = offset + wbase + inc - c;      // exclusive prefix
+    bool have_tail = false;                         // ragged last chunk hashed here
+    uint64_t tailh = 0;
     if (i < n) {
         chunk_base[i] = base;
         if (i == n - 1) {
@@ -145,6 +148,7 @@ k_prep_scan(const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars
                 const uint8_t *q = bytes + starts[i];
                 if ((((uintptr_t)q) & 15) == 0) {
                     const uint8_t *tp = q + (ln - tail);
+                    have_tail = true;
                     if (tail < 128 && (((uintptr_t)tp) & 15) == 0) {
                         // fetch the whole tail with independent 16-byte loads first (one DRAM
                         // round trip instead of one per stripe), then hash it out of registers
@@ -156,13 +160,78 @@ k_prep_scan(const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars
                             wv[2 * u] = u64_of(q.x, q.y);
                             wv[2 * u + 1] = u64_of(q.z, q.w);
                         }
-                        hashes[gl] = b200r_th::xxh64_tail_words(wv, tail);
+                        tailh = b200r_th::xxh64_tail_words(wv, tail);
                     } else {
-                        hashes[gl] = xxh64_global(tp, tail);
+                        tailh = xxh64_global(tp, tail);
                     }
+                    if (!pp.world) hashes[gl] = tailh;
                 }
             }
         }
+    }
+    if (!pp.world) return;
+    // ---- partitioned multi-GPU: place the request in its owner's inbound buffer (PartPlace)
+    const int lane_ = tid & 31;
+    int o = -1;
+    if (i < n) {
+        if (c == 0) o = 0;                          // empty prompt: touches only a root
+        else {
+            uint64_t h0;
+            const int ln = lens[i];
+            if (c == 1 && have_tail) h0 = tailh;
+            else {
+                const uint8_t *q = bytes + starts[i];
+                const int l0 = ln < cc ? ln : cc;
+                if (l0 == 128 && (((uintptr_t)q) & 15) == 0) {
+                    uint64_t v1 = XP1 + XP2, v2 = XP2, v3 = 0, v4 = 0 - XP1;
+                    uint4 qa[8];
+#pragma unroll
+                    for (int u = 0; u < 8; u++) qa[u] = __ldg((const uint4 *)q + u);
+#pragma unroll
+                    for (int u = 0; u < 4; u++) {
+                        v1 = xround(v1, u64_of(qa[2 * u].x, qa[2 * u].y));
+                        v2 = xround(v2, u64_of(qa[2 * u].z, qa[2 * u].w));
+                        v3 = xround(v3, u64_of(qa[2 * u + 1].x, qa[2 * u + 1].y));
+                        v4 = xround(v4, u64_of(qa[2 * u + 1].z, qa[2 * u + 1].w));
+                    }
+                    uint64_t h = rotl<1>(v1) + rotl<7>(v2) + rotl<12>(v3) + rotl<18>(v4);
+                    h = xmerge(h, v1); h = xmerge(h, v2); h = xmerge(h, v3); h = xmerge(h, v4);
+                    h0 = xavalanche(h + 128);
+                } else {
+                    h0 = xxh64_global(q, l0);
+                }
+            }
+            o = part_owner_of(h0, pp.world);
+        }
+    }
+    uint32_t rreq = 0, rchunk = 0;
+    for (int d = 0; d < pp.world; d++) {
+        const unsigned m = __ballot_sync(0xffffffffu, o == d);
+        if (!m) continue;                                   // warp-uniform
+        const int v = (o == d) ? c : 0;
+        int inc2 = v;
+        for (int sft = 1; sft < 32; sft <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc2, sft);
+            if (lane_ >= sft) inc2 += t;
+        }
+        const int tot = __shfl_sync(0xffffffffu, inc2, 31);
+        unsigned long long bs = 0;
+        if (lane_ == 0)
+            bs = atomicAdd(&pp.totals[d], ((unsigned long long)__popc(m) << 32) | (unsigned long long)(uint32_t)tot);
+        bs = __shfl_sync(0xffffffffu, bs, 0);
+        if (o == d) {
+            rreq = (uint32_t)(bs >> 32) + (uint32_t)__popc(m & ((1u << lane_) - 1));
+            rchunk = (uint32_t)bs + (uint32_t)(inc2 - v);
+        }
+    }
+    if (o >= 0) {
+        pp.dest_slot[i] = ((uint32_t)o << 24) | rreq;
+        const unsigned long long pb = pp.peer_bases[o];
+        ((unsigned long long *)(uintptr_t)(pb + pp.info_off))[(size_t)pp.my_rank * pp.rcap + rreq] =
+            (unsigned long long)(uint32_t)i | ((unsigned long long)rchunk << 32);
+        const unsigned long long op = pb + pp.hash_off + ((size_t)pp.my_rank * pp.cap + rchunk) * 8;
+        pp.out_ptr[i] = op;
+        if (have_tail) ((uint64_t *)(uintptr_t)op)[c - 1] = tailh;
     }
 }
 
@@ -285,15 +354,17 @@ __device__ __forceinline__ uint64_t xxh64_row128(uint32_t row, int sw)
 constexpr int WTILE = 32;                 // chunks per warp tile
 constexpr int HASH_WARPS = 8;             // warps per CTA
 
-struct ReqRec { int b, b1, ln, nc; long long st; };
+struct ReqRec { int b, b1, ln, nc; long long st; unsigned long long op; };
 
 __global__ void __launch_bounds__(HASH_WARPS * 32, 6)
 k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ starts,
               const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars,
               const int32_t *__restrict__ chunk_base, const int32_t *__restrict__ tile_first,
               const int32_t *__restrict__ chunk_off, int n, int cc, int64_t max_chunks,
-              uint64_t *__restrict__ hashes)
+              uint64_t *__restrict__ hashes, const unsigned long long *__restrict__ out_ptr)
 {
+    // out_ptr (partitioned multi-GPU path, see PartPlace): per request, where its hashes go --
+    // an address in the owning GPU's inbound buffer; else they go to hashes[] (CSR order)
     __shared__ __align__(1024) uint8_t s_tile[HASH_WARPS * WTILE * 128];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int64_t tile = (int64_t)blockIdx.x * HASH_WARPS + w;
@@ -303,15 +374,16 @@ k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ sta
     if (G0 >= total) return;                                   // whole warp
 
     // ---- map: which request owns each of the 32 chunks?
-    ReqRec mine = { 0, 0, 0, 0, 0 };      // record of the request that owns this lane's chunk
+    ReqRec mine = { 0, 0, 0, 0, 0, 0 };   // record of the request that owns this lane's chunk
     const int r0 = tile_first[tile];
     for (int jb = 0;; jb += 32) {
         const int r = r0 + jb + lane;
-        ReqRec q = { 0, 0, 0, 0, 0 };
+        ReqRec q = { 0, 0, 0, 0, 0, 0 };
         bool live = false;
         if (r < n) {
             q.b = chunk_base[r]; q.b1 = chunk_base[r + 1];
             q.st = starts[r]; q.ln = lens[r];
+            if (out_ptr) q.op = out_ptr[r];
             q.nc = nchars ? nchars[r] : q.ln;
             live = (int64_t)q.b < G0 + WTILE;
         }
@@ -330,7 +402,8 @@ k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ sta
         const int tb = __shfl_sync(0xffffffffu, q.b, src), tb1 = __shfl_sync(0xffffffffu, q.b1, src);
         const int tln = __shfl_sync(0xffffffffu, q.ln, src), tnc = __shfl_sync(0xffffffffu, q.nc, src);
         const long long tst = __shfl_sync(0xffffffffu, q.st, src);
-        if (below) { mine.b = tb; mine.b1 = tb1; mine.ln = tln; mine.nc = tnc; mine.st = tst; }
+        const unsigned long long top = out_ptr ? __shfl_sync(0xffffffffu, q.op, src) : 0ULL;
+        if (below) { mine.b = tb; mine.b1 = tb1; mine.ln = tln; mine.nc = tnc; mine.st = tst; mine.op = top; }
         // more requests can start inside the tile only if the last lane's request ends inside it
         const int last_b1 = __shfl_sync(0xffffffffu, q.b1, 31);
         const bool last_live = __shfl_sync(0xffffffffu, (int)live, 31);
@@ -382,7 +455,10 @@ k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ sta
     __syncwarp();
     if (kind == 1) h = xxh64_row128(wrow + lane * 128, lane & 7);
     else if (kind == 3) h = xxh64_global(p, clen);
-    if (kind) hashes[g] = h;
+    if (kind) {
+        if (out_ptr) ((uint64_t *)(uintptr_t)mine.op)[g - mine.b] = h;
+        else hashes[g] = h;
+    }
 }
 
 // =========================================================================
@@ -779,8 +855,11 @@ int check_prompt_args(const void *bytes, const void *starts, const void *lens, i
 int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const int32_t *d_lens,
                 const int32_t *d_nchars, int64_t n, int32_t cc, uint32_t flags,
                 int32_t *d_chunk_base, uint64_t *d_hashes, int64_t max_chunks,
-                uint8_t *scratch, const Plan &p, TrieDev *dev, cudaStream_t st, int phase)
+                uint8_t *scratch, const Plan &p, TrieDev *dev, cudaStream_t st, int phase,
+                const PartPlace *pp)
 {
+    PartPlace place = PartPlace();          // world == 0: off
+    if (pp) place = *pp;
     // phase 0: everything; 1: all but the chunk-hashing kernel (the "prep" part: code-point
     // counts, CSR, tile map, UTF-8 chunk offsets, ragged tails); 2: the chunk-hashing kernel only
     int32_t *tile_first = (int32_t *)(scratch + p.off_tile_first);
@@ -811,7 +890,8 @@ int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const int32_t *
     }
     { ProfScope ps__(PK_PREP, st); g_launches += 1;
     k_prep_scan<<<nblk, PREP_BLOCK, 0, st>>>(d_lens, d_nchars, (int)n, cc, block_sums, d_chunk_base,
-                                             tile_first, max_chunks, dev, d_bytes, d_starts, d_hashes, nullptr);
+                                             tile_first, max_chunks, dev, d_bytes, d_starts, d_hashes, nullptr,
+                                             place);
     B200R_LAUNCH_CHECK("k_prep_scan");
     }
     if (!ascii) {
@@ -827,7 +907,7 @@ int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const int32_t *
         ProfScope ps__(PK_HASH, st); g_launches += 1;
         k_hash_chunks<<<ntiles, HASH_WARPS * 32, 0, st>>>(
             d_bytes, d_starts, d_lens, d_nchars, d_chunk_base, tile_first, chunk_off, (int)n, cc,
-            max_chunks, d_hashes);
+            max_chunks, d_hashes, pp ? pp->out_ptr : nullptr);
         B200R_LAUNCH_CHECK("k_hash_chunks");
     }
     return B200R_OK;
@@ -842,7 +922,7 @@ int launch_prep_counts(const int32_t *d_counts, int64_t n_max, const int32_t *n_
     k_prep_sums<<<nblk, PREP_BLOCK, 0, st>>>(d_counts, nullptr, (int)n_max, 1, block_sums, n_dev);
     B200R_LAUNCH_CHECK("k_prep_sums(counts)");
     k_prep_scan<<<nblk, PREP_BLOCK, 0, st>>>(d_counts, nullptr, (int)n_max, 1, block_sums, chunk_base,
-                                             nullptr, c_max, dev, nullptr, nullptr, nullptr, n_dev);
+                                             nullptr, c_max, dev, nullptr, nullptr, nullptr, n_dev, PartPlace());
     B200R_LAUNCH_CHECK("k_prep_scan(counts)");
     return B200R_OK;
 }
@@ -956,6 +1036,12 @@ int b200r_set_claim_mode(int mode)
 {
     if (mode < 0 || mode > 4) { set_error("b200r_set_claim_mode: 0 auto, 1 thread, 2 warp, 3 half warp, 4 quarter warp"); return B200R_E_INVALID; }
     g_claim_mode = mode;
+    return B200R_OK;
+}
+
+int b200r_set_part_staged(int on)
+{
+    g_part_staged = on != 0;
     return B200R_OK;
 }
 
