@@ -96,7 +96,8 @@ int launch_prep_counts(const int32_t *d_counts, int64_t n_max, const int32_t *n_
 // claim -> select -> commit over chunk hashes already in memory.  `n` sizes the grids; when the
 // real count lives on the device (n_dev) it is an estimate and the kernels stride.
 struct RouteCore {
-    const uint64_t *hashes; const int32_t *chunk_base; int64_t n; int64_t max_chunks;
+    const uint64_t *hashes; const int32_t *chunk_base; const int32_t *chunk_end;  // NULL = CSR
+    int64_t n; int64_t max_chunks;
     uint64_t avail, seed, seq0;
     uint32_t *slots; int32_t *leader, *choice, *dpre; uint64_t *cand;
     int32_t *endpoint, *depth; uint64_t *matched;

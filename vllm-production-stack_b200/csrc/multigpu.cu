@@ -270,12 +270,15 @@ __global__ void k_part_wait_meta(const PartFlags *__restrict__ mine, int set, un
     // no fence: what the sources wrote before their flags is read by LATER launches only
 }
 
-// concatenate what the sources sent, in rank order, as the CSR the route stage works on
+// The requests this rank owns, in rank order of their sources: where each one's chunk hashes
+// lie in the inbound buffer (they are routed from there; no copy), its global position, and the
+// inverse map.  A request's run ends where the next slot of its (source, owner) segment begins
+// (slots and chunk offsets were handed out together, so both are monotone within a segment).
 __global__ void __launch_bounds__(256)
-k_part_gather(const uint8_t *__restrict__ my_base, size_t hash_off, size_t info_off, int64_t cap,
-              int64_t rcap, int world, const PartDyn *__restrict__ dyn,
-              int32_t *__restrict__ chunk_base, uint32_t *__restrict__ pos_owned,
-              uint32_t *__restrict__ idx_of_pos, uint64_t *__restrict__ hashes_owned)
+k_part_gather(const uint8_t *__restrict__ my_base, size_t info_off, int64_t cap, int64_t rcap,
+              int world, const PartDyn *__restrict__ dyn, int32_t *__restrict__ chunk_base,
+              int32_t *__restrict__ chunk_end, uint32_t *__restrict__ pos_owned,
+              uint32_t *__restrict__ idx_of_pos)
 {
     __shared__ uint32_t s_req[P2P_MAX_WORLD + 1], s_chunk[P2P_MAX_WORLD + 1], s_n[P2P_MAX_WORLD + 1];
     for (int k = threadIdx.x; k <= world; k += blockDim.x) {
@@ -285,22 +288,20 @@ k_part_gather(const uint8_t *__restrict__ my_base, size_t hash_off, size_t info_
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t step = (int64_t)gridDim.x * blockDim.x;
     const unsigned long long *info = (const unsigned long long *)(my_base + info_off);
-    const uint64_t *hin = (const uint64_t *)(my_base + hash_off);
-    const int64_t n_owned = s_req[world], ch_owned = s_chunk[world];
+    const int64_t n_owned = s_req[world];
     for (int64_t j = tid; j < n_owned; j += step) {
         int k = 0;
         while (k + 1 < world && j >= s_req[k + 1]) k++;
-        const unsigned long long v = info[(size_t)k * rcap + (j - s_req[k])];
-        chunk_base[j] = (int32_t)(s_chunk[k] + (uint32_t)(v >> 32));
+        const uint32_t r = (uint32_t)(j - s_req[k]), nreq = s_req[k + 1] - s_req[k];
+        const unsigned long long v = info[(size_t)k * rcap + r];
+        const uint32_t seg = (uint32_t)(v >> 32);
+        const uint32_t nxt = (r + 1 < nreq) ? (uint32_t)(info[(size_t)k * rcap + r + 1] >> 32)
+                                            : s_chunk[k + 1] - s_chunk[k];
+        chunk_base[j] = (int32_t)((uint32_t)k * (uint32_t)cap + seg);
+        chunk_end[j] = (int32_t)((uint32_t)k * (uint32_t)cap + nxt);
         const uint32_t gp = s_n[k] + (uint32_t)v;       // position in the global (rank-major) batch
         pos_owned[j] = gp;
         idx_of_pos[gp] = (uint32_t)j;
-    }
-    if (tid == 0) chunk_base[n_owned] = (int32_t)ch_owned;
-    for (int64_t x = tid; x < ch_owned; x += step) {
-        int k = 0;
-        while (k + 1 < world && x >= s_chunk[k + 1]) k++;
-        hashes_owned[x] = hin[(size_t)k * cap + (x - s_chunk[k])];
     }
 }
 
@@ -362,7 +363,7 @@ extern "C" {
 struct PartLayout {
     size_t symm_total, hash_off, info_off, res_off, hash_set, info_set, res_set;
     // local work buffer
-    size_t work_total, w_dyn, w_totals, w_out_ptr, w_dest_slot, w_hash_stage, w_info_stage, w_pos_owned, w_idx_of_pos,
+    size_t work_total, w_dyn, w_totals, w_out_ptr, w_dest_slot, w_hash_stage, w_info_stage, w_chunk_end, w_pos_owned, w_idx_of_pos,
         w_ep, w_depth, w_matched, w_plan;
     int64_t n_max, c_max;
     int nblk_max;
@@ -388,6 +389,7 @@ static PartLayout part_layout(int world, int64_t cap, int64_t rcap)
     L.w_dest_slot = o; o += 2 * align_up((size_t)rcap * 4);     // one per batch parity
     L.w_hash_stage = o; o += align_up((size_t)world * (cap + 2) * 8);   // one fixed segment per owner
     L.w_info_stage = o; o += align_up((size_t)world * (rcap + 2) * 8);
+    L.w_chunk_end = o; o += align_up((size_t)L.n_max * 4);
     L.w_pos_owned = o; o += align_up((size_t)L.n_max * 4);
     L.w_idx_of_pos = o; o += align_up((size_t)L.n_max * 4);
     L.w_ep = o;        o += 2 * align_up((size_t)L.n_max * 4);      // results: one per batch parity
@@ -548,7 +550,6 @@ static int part_route_impl(b200r_trie *t, uint64_t avail_mask, uint64_t seed,
     int32_t *depth = (int32_t *)(wk + L.w_depth + (size_t)set * align_up((size_t)L.n_max * 4));
     uint64_t *matched = (uint64_t *)(wk + L.w_matched + (size_t)set * align_up((size_t)L.n_max * 8));
     int32_t *chunk_base = (int32_t *)(sc + p.off_chunk_base);
-    uint64_t *hashes = (uint64_t *)(sc + p.off_hashes);
     uint32_t *slots = (uint32_t *)(sc + p.off_slots);
     int32_t *leader = (int32_t *)(sc + p.off_leader), *choice = (int32_t *)(sc + p.off_choice);
     const int32_t *n_dev = &dyn->n_owned;
@@ -558,15 +559,17 @@ static int part_route_impl(b200r_trie *t, uint64_t avail_mask, uint64_t seed,
                                                   world, dyn, part_dyn(wk, L, set ^ 1), t->dev);
     B200R_LAUNCH_CHECK("k_part_wait_meta");
     }
+    int32_t *chunk_end = (int32_t *)(wk + L.w_chunk_end);
     { ProfScope ps__(PK_PREP, st); g_launches += 1;
-    k_part_gather<<<148 * 4, 256, 0, st>>>(base, L.hash_off + (size_t)set * L.hash_set,
-                                           L.info_off + (size_t)set * L.info_set, cap, rcap, world, dyn,
-                                           chunk_base, pos_owned, (uint32_t *)(wk + L.w_idx_of_pos), hashes);
+    k_part_gather<<<148, 256, 0, st>>>(base, L.info_off + (size_t)set * L.info_set, cap, rcap, world, dyn,
+                                       chunk_base, chunk_end, pos_owned, (uint32_t *)(wk + L.w_idx_of_pos));
     B200R_LAUNCH_CHECK("k_part_gather");
     }
     // grids are estimates (about two shards' worth); the kernels stride over the rest
     RouteCore core = RouteCore();
-    core.hashes = hashes; core.chunk_base = chunk_base;
+    // the hashes are routed from where the sources stored them (inbound buffer of this set)
+    core.hashes = (const uint64_t *)(base + L.hash_off + (size_t)set * L.hash_set);
+    core.chunk_base = chunk_base; core.chunk_end = chunk_end;
     core.n = 2 * rcap < L.n_max ? 2 * rcap : L.n_max;
     core.max_chunks = L.c_max;
     core.avail = avail_mask; core.seed = seed; core.seq0 = 0;

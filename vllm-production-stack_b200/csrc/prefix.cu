@@ -478,13 +478,13 @@ k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ sta
 // the node first.  The walk starts at dpre[i]: everything above is PREOK.
 __device__ __forceinline__ void
 select_request(int i, const Rec *__restrict__ log, const int32_t *__restrict__ chunk_base,
-               int64_t max_chunks, const uint32_t *__restrict__ slots,
+               const int32_t *__restrict__ chunk_end, int64_t max_chunks, const uint32_t *__restrict__ slots,
                const int32_t *__restrict__ dpre, const uint64_t *__restrict__ cand_in,
                unsigned long long tag, uint64_t seed, uint64_t seq0, int32_t *__restrict__ leader,
                int32_t *__restrict__ choice, int32_t *__restrict__ depth_out,
                uint64_t *__restrict__ matched_out, uint32_t req_off, const uint32_t *__restrict__ pos)
 {
-    const ReqSpan sp = req_span(chunk_base, i, max_chunks);
+    const ReqSpan sp = req_span(chunk_base, chunk_end, i, max_chunks);
     const uint32_t *sl = slots + sp.b0;
     const int d0 = dpre[i];
     // "node d was touched by an earlier request of this batch" is a prefix property (whoever
@@ -529,7 +529,8 @@ select_request(int i, const Rec *__restrict__ log, const int32_t *__restrict__ c
 }
 
 __global__ void __launch_bounds__(256)
-k_select(const Rec *__restrict__ log, const int32_t *__restrict__ chunk_base, int n, int64_t max_chunks,
+k_select(const Rec *__restrict__ log, const int32_t *__restrict__ chunk_base,
+         const int32_t *__restrict__ chunk_end, int n, int64_t max_chunks,
          const uint32_t *__restrict__ slots, const int32_t *__restrict__ dpre,
          const uint64_t *__restrict__ cand, unsigned long long tag, uint64_t seed,
          uint64_t seq0, int32_t *__restrict__ leader, int32_t *__restrict__ choice,
@@ -543,7 +544,7 @@ k_select(const Rec *__restrict__ log, const int32_t *__restrict__ chunk_base, in
     if (n_dev) n = *n_dev;
     if (dyn) { req_off = dyn->my_off; seq0 = dyn->seq_base; }
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-        select_request(i, log, chunk_base, max_chunks, slots, dpre, cand, tag, seed, seq0, leader,
+        select_request(i, log, chunk_base, chunk_end, max_chunks, slots, dpre, cand, tag, seed, seq0, leader,
                        choice, depth_out, matched_out, req_off, pos);
 }
 
@@ -552,7 +553,7 @@ k_select(const Rec *__restrict__ log, const int32_t *__restrict__ chunk_base, in
 // nodes it was the first to touch, so no other request writes them.
 __device__ __forceinline__ void
 commit_request(int i, Rec *__restrict__ log, TrieDev *dev, const int32_t *__restrict__ chunk_base,
-               int64_t max_chunks, const uint32_t *__restrict__ slots,
+               const int32_t *__restrict__ chunk_end, int64_t max_chunks, const uint32_t *__restrict__ slots,
                const int32_t *__restrict__ leader, const int32_t *__restrict__ choice,
                const int32_t *__restrict__ depth, int32_t *__restrict__ endpoint,
                uint64_t *__restrict__ matched_out, const uint32_t *__restrict__ idx_of_pos)
@@ -567,7 +568,7 @@ commit_request(int i, Rec *__restrict__ log, TrieDev *dev, const int32_t *__rest
     if (e < 0) return;
     const uint64_t bit = 1ULL << e;
     if (!(dev->root_mask & bit)) atomicOr((unsigned long long *)&dev->root_mask, bit);
-    const ReqSpan sp = req_span(chunk_base, i, max_chunks);
+    const ReqSpan sp = req_span(chunk_base, chunk_end, i, max_chunks);
     for (int d = depth[i]; d < sp.C; d++) {
         const uint32_t x = slots[sp.b0 + d];
         if (x != SLOT_NONE) atomicOr((unsigned long long *)&log[x & IDX_MASK].mask, bit);
@@ -575,15 +576,15 @@ commit_request(int i, Rec *__restrict__ log, TrieDev *dev, const int32_t *__rest
 }
 
 __global__ void __launch_bounds__(256)
-k_commit(Rec *__restrict__ log, TrieDev *dev, const int32_t *__restrict__ chunk_base, int n,
-         int64_t max_chunks, const uint32_t *__restrict__ slots, const int32_t *__restrict__ leader,
+k_commit(Rec *__restrict__ log, TrieDev *dev, const int32_t *__restrict__ chunk_base,
+         const int32_t *__restrict__ chunk_end, int n, int64_t max_chunks, const uint32_t *__restrict__ slots, const int32_t *__restrict__ leader,
          const int32_t *__restrict__ choice, const int32_t *__restrict__ depth,
          int32_t *__restrict__ endpoint, uint64_t *__restrict__ matched_out,
          const int32_t *__restrict__ n_dev, const uint32_t *__restrict__ idx_of_pos)
 {
     if (n_dev) n = *n_dev;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-        commit_request(i, log, dev, chunk_base, max_chunks, slots, leader, choice, depth, endpoint,
+        commit_request(i, log, dev, chunk_base, chunk_end, max_chunks, slots, leader, choice, depth, endpoint,
                        matched_out, idx_of_pos);
 }
 
@@ -591,8 +592,8 @@ k_commit(Rec *__restrict__ log, TrieDev *dev, const int32_t *__restrict__ chunk_
 // The same with a warp per request, lanes over depths: long prompts (C4: 256 chunks, half of
 // them new) make the thread version a chain of a hundred dependent atomics.
 __global__ void __launch_bounds__(256)
-k_commit_warp(Rec *__restrict__ log, TrieDev *dev, const int32_t *__restrict__ chunk_base, int n,
-              int64_t max_chunks, const uint32_t *__restrict__ slots, const int32_t *__restrict__ leader,
+k_commit_warp(Rec *__restrict__ log, TrieDev *dev, const int32_t *__restrict__ chunk_base,
+              const int32_t *__restrict__ chunk_end, int n, int64_t max_chunks, const uint32_t *__restrict__ slots, const int32_t *__restrict__ leader,
               const int32_t *__restrict__ choice, const int32_t *__restrict__ depth,
               int32_t *__restrict__ endpoint, uint64_t *__restrict__ matched_out,
               const int32_t *__restrict__ n_dev, const uint32_t *__restrict__ idx_of_pos)
@@ -614,7 +615,7 @@ k_commit_warp(Rec *__restrict__ log, TrieDev *dev, const int32_t *__restrict__ c
         e = __shfl_sync(0xffffffffu, e, 0);
         if (e < 0) continue;
         const uint64_t bit = 1ULL << e;
-        const ReqSpan sp = req_span(chunk_base, i, max_chunks);
+        const ReqSpan sp = req_span(chunk_base, chunk_end, i, max_chunks);
         for (int d = depth[i] + lane; d < sp.C; d += 32) {
             const uint32_t x = slots[sp.b0 + d];
             if (x != SLOT_NONE) atomicOr((unsigned long long *)&log[x & IDX_MASK].mask, bit);
@@ -980,7 +981,8 @@ int launch_route_core(b200r_trie *t, const RouteCore &rc, cudaStream_t st)
     if (rc0) return rc0;
     WalkArgs a = WalkArgs();
     a.t = trie_ref(t);
-    a.hashes = rc.hashes; a.chunk_base = rc.chunk_base; a.max_chunks = rc.max_chunks;
+    a.hashes = rc.hashes; a.chunk_base = rc.chunk_base; a.chunk_end = rc.chunk_end;
+    a.max_chunks = rc.max_chunks;
     a.avail = rc.avail; a.tag = tag; a.slots = rc.slots; a.dpre = rc.dpre; a.cand = rc.cand;
     a.pos = rc.pos;
     const int nn = rc.n_dev ? 0 : (int)rc.n;
@@ -1000,18 +1002,18 @@ int launch_route_core(b200r_trie *t, const RouteCore &rc, cudaStream_t st)
     B200R_LAUNCH_CHECK("k_walk<claim>");
     }
     { ProfScope ps__(PK_SELECT, st); g_launches += 1;
-    k_select<<<tblocks, 256, 0, st>>>(t->log, rc.chunk_base, nn, rc.max_chunks, rc.slots, rc.dpre,
+    k_select<<<tblocks, 256, 0, st>>>(t->log, rc.chunk_base, rc.chunk_end, nn, rc.max_chunks, rc.slots, rc.dpre,
                                      rc.cand, tag, rc.seed, rc.seq0, rc.leader, rc.choice,
                                      rc.depth, rc.matched, 0u, rc.dyn, rc.pos, rc.n_dev);
     B200R_LAUNCH_CHECK("k_select");
     }
     { ProfScope ps__(PK_COMMIT, st); g_launches += 1;
     if (rc.claim_kind == 1)
-        k_commit<<<tblocks, 256, 0, st>>>(t->log, t->dev, rc.chunk_base, nn, rc.max_chunks, rc.slots,
+        k_commit<<<tblocks, 256, 0, st>>>(t->log, t->dev, rc.chunk_base, rc.chunk_end, nn, rc.max_chunks, rc.slots,
                                          rc.leader, rc.choice, rc.depth, rc.endpoint, rc.matched, rc.n_dev,
                                          rc.idx_of_pos);
     else
-        k_commit_warp<<<walk_grid(rc.n), 256, 0, st>>>(t->log, t->dev, rc.chunk_base, nn, rc.max_chunks,
+        k_commit_warp<<<walk_grid(rc.n), 256, 0, st>>>(t->log, t->dev, rc.chunk_base, rc.chunk_end, nn, rc.max_chunks,
                                                        rc.slots, rc.leader, rc.choice, rc.depth, rc.endpoint,
                                                        rc.matched, rc.n_dev, rc.idx_of_pos);
     B200R_LAUNCH_CHECK("k_commit");

@@ -261,11 +261,14 @@ __device__ __forceinline__ uint32_t warp_alloc(const TrieRef &t, WarpAlloc &wa, 
 // ------------------------------------------------------------------ request walk
 struct ReqSpan { int b0, C; };
 
-__device__ __forceinline__ ReqSpan req_span(const int32_t *chunk_base, int i, int64_t max_chunks)
+// chunk_end == NULL: plain CSR (request i ends where i + 1 begins); else the requests' hash
+// runs are not adjacent (partitioned multi-GPU path: they lie where the sources stored them)
+__device__ __forceinline__ ReqSpan req_span(const int32_t *chunk_base, const int32_t *chunk_end, int i,
+                                            int64_t max_chunks)
 {
     ReqSpan s;
     s.b0 = chunk_base[i];
-    int64_t e = chunk_base[i + 1];
+    int64_t e = chunk_end ? chunk_end[i] : chunk_base[i + 1];
     if (e > max_chunks) e = max_chunks;
     s.C = (e > s.b0) ? (int)(e - s.b0) : 0;
     return s;
@@ -277,6 +280,7 @@ struct WalkArgs {
     TrieRef t;
     const uint64_t *hashes;
     const int32_t *chunk_base;
+    const int32_t *chunk_end;     // NULL = CSR (see req_span)
     int64_t max_chunks;
     uint64_t avail;               // lookup / claim
     unsigned long long tag;       // claim: epoch << 32
@@ -493,13 +497,13 @@ k_walk(WalkArgs a, int n, const int32_t *__restrict__ n_dev)
     ReqSpan sp0 = { 0, 0 }, sp1 = { 0, 0 };
     uint64_t h0 = 0;
     if (gt < n) {
-        sp0 = req_span(a.chunk_base, gt, a.max_chunks);
+        sp0 = req_span(a.chunk_base, a.chunk_end, gt, a.max_chunks);
         if (g.tl < sp0.C) h0 = a.hashes[sp0.b0 + g.tl];
     }
-    if (gt + nt < n) sp1 = req_span(a.chunk_base, gt + nt, a.max_chunks);
+    if (gt + nt < n) sp1 = req_span(a.chunk_base, a.chunk_end, gt + nt, a.max_chunks);
     for (int i = gt; i < n; i += nt) {
         ReqSpan sp2 = { 0, 0 };
-        if (i + 2 * nt < n) sp2 = req_span(a.chunk_base, i + 2 * nt, a.max_chunks);
+        if (i + 2 * nt < n) sp2 = req_span(a.chunk_base, a.chunk_end, i + 2 * nt, a.max_chunks);
         uint64_t h1 = 0;
         if (i + nt < n && g.tl < sp1.C) h1 = a.hashes[sp1.b0 + g.tl];
         Pending mine = { -1, 0, 0, 0 };
@@ -507,7 +511,7 @@ k_walk(WalkArgs a, int n, const int32_t *__restrict__ n_dev)
         if (DEFER) {
             if (pend.req >= 0 && __ballot_sync(g.mask, g.tl == pend.lane && (pend.oa | pend.ob))) {
                 // the slot was taken while the CAS was on its way: walk that request again
-                const ReqSpan spr = req_span(a.chunk_base, pend.req, a.max_chunks);
+                const ReqSpan spr = req_span(a.chunk_base, a.chunk_end, pend.req, a.max_chunks);
                 walk_request<MODE, false, TW>(a, pend.req, g, wa, spr,
                                               g.tl < spr.C ? a.hashes[spr.b0 + g.tl] : 0, none);
             }
@@ -516,7 +520,7 @@ k_walk(WalkArgs a, int n, const int32_t *__restrict__ n_dev)
         sp0 = sp1; sp1 = sp2; h0 = h1;
     }
     if (DEFER && pend.req >= 0 && __ballot_sync(g.mask, g.tl == pend.lane && (pend.oa | pend.ob))) {
-        const ReqSpan spr = req_span(a.chunk_base, pend.req, a.max_chunks);
+        const ReqSpan spr = req_span(a.chunk_base, a.chunk_end, pend.req, a.max_chunks);
         walk_request<MODE, false, TW>(a, pend.req, g, wa, spr,
                                       g.tl < spr.C ? a.hashes[spr.b0 + g.tl] : 0, none);
     }
@@ -544,7 +548,7 @@ k_claim_thread(WalkArgs a, int n, const int32_t *__restrict__ n_dev)
         const int i = wbase + lane;
         const bool active = i < n;
         ReqSpan sp = { 0, 0 };
-        if (active) sp = req_span(a.chunk_base, i, a.max_chunks);
+        if (active) sp = req_span(a.chunk_base, a.chunk_end, i, a.max_chunks);
         const int C = sp.C;
         const uint64_t *hs = a.hashes + sp.b0;
         uint32_t *sl = a.slots + sp.b0;
