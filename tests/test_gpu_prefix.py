@@ -500,7 +500,37 @@ def test_checkpoint_save_load(tmp_path):
     b = t2.route(p, 0x15, 9, 300)
     assert all(torch.equal(x, y) for x, y in zip(a, b))
     assert t2.dump() == t.dump()
-    t.close(); t2.close()
+    bare = str(tmp_path / "checkpoint_without_suffix")          # np.savez would append ".npz"
+    t.save(bare)
+    t3 = GpuHashTrie.load(bare)
+    assert t3.dump() == t.dump()
+    t.close(); t2.close(); t3.close()
+
+
+def test_router_checkpoint_keeps_registry_and_counter(tmp_path):
+    """PrefixAwareRouter.save/load: the urls behind the mask bits, the chunking mode and the
+    tie-break counter travel with the table, so a reloaded router continues like the original."""
+    from b200_router import routers
+
+    class Ep:
+        def __init__(self, url):
+            self.url = url
+    eps = [Ep(u) for u in traces.endpoint_urls(5)]
+    _, prompts = traces.sharing_stress(n_batches=1, batch=200, max_depth=5, seed=5)[0]
+    routers._reset_singletons_for_tests()
+    r = routers.PrefixAwareRouter(cap_log2=13, seed=3)
+    first = r.route_batch(eps[::-1], prompts[:100])             # bits assigned in reverse url order
+    path = str(tmp_path / "router_state")
+    r.save(path)
+    want = r.route_batch(eps, prompts[100:])
+    one = r.route_one(eps, prompts[0])
+    routers._reset_singletons_for_tests()
+    r2 = routers.PrefixAwareRouter(cap_log2=13, seed=99)
+    r2.load(path)
+    assert r2.route_batch(eps, prompts[100:]) == want
+    assert r2.route_one(eps, prompts[0]) == one
+    assert set(first) <= {e.url for e in eps}
+    routers._reset_singletons_for_tests()
 
 
 def test_router_micro_batched_concurrent_requests_equal_reference(golden_prefix):

@@ -354,8 +354,9 @@ __device__ __forceinline__ uint64_t xxh64_row128(uint32_t row, int sw)
 constexpr int WTILE = 32;                 // chunks per warp tile
 constexpr int HASH_WARPS = 8;             // warps per CTA
 
-struct ReqRec { int b, b1, ln, nc; long long st; unsigned long long op; };
+struct ReqRec { int b, b1, ln, nc; long long st; int r; };
 
+template <bool DIRECT>
 __global__ void __launch_bounds__(HASH_WARPS * 32, 6)
 k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ starts,
               const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars,
@@ -383,8 +384,8 @@ k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ sta
         if (r < n) {
             q.b = chunk_base[r]; q.b1 = chunk_base[r + 1];
             q.st = starts[r]; q.ln = lens[r];
-            if (out_ptr) q.op = out_ptr[r];
-            q.nc = nchars ? nchars[r] : q.ln;
+            q.r = r;
+            q.nc = (!DIRECT && nchars) ? nchars[r] : q.ln;       // DIRECT batches are ASCII
             live = (int64_t)q.b < G0 + WTILE;
         }
         const bool nonempty = live && q.b1 > q.b;
@@ -400,10 +401,11 @@ k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ sta
             src = (ne == (0xffffffffu >> (32 - __popc(ne)))) ? k : (int)__fns(ne, 0, k + 1);
         }
         const int tb = __shfl_sync(0xffffffffu, q.b, src), tb1 = __shfl_sync(0xffffffffu, q.b1, src);
-        const int tln = __shfl_sync(0xffffffffu, q.ln, src), tnc = __shfl_sync(0xffffffffu, q.nc, src);
+        const int tln = __shfl_sync(0xffffffffu, q.ln, src);
+        const int tnc = DIRECT ? tln : __shfl_sync(0xffffffffu, q.nc, src);
         const long long tst = __shfl_sync(0xffffffffu, q.st, src);
-        const unsigned long long top = out_ptr ? __shfl_sync(0xffffffffu, q.op, src) : 0ULL;
-        if (below) { mine.b = tb; mine.b1 = tb1; mine.ln = tln; mine.nc = tnc; mine.st = tst; mine.op = top; }
+        const int tr = DIRECT ? __shfl_sync(0xffffffffu, q.r, src) : 0;
+        if (below) { mine.b = tb; mine.b1 = tb1; mine.ln = tln; mine.nc = tnc; mine.st = tst; mine.r = tr; }
         // more requests can start inside the tile only if the last lane's request ends inside it
         const int last_b1 = __shfl_sync(0xffffffffu, q.b1, 31);
         const bool last_live = __shfl_sync(0xffffffffu, (int)live, 31);
@@ -415,10 +417,12 @@ k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ sta
     const bool valid = g < total;
     const uint8_t *p = nullptr;
     int clen = 0, kind = 0;               // 0 none / done elsewhere, 1 full staged, 3 generic
+    uint64_t *dst = nullptr;              // DIRECT: where this chunk's hash goes (owner's buffer)
     if (valid) {
         const int d = (int)(g - mine.b);  // depth of the chunk inside its request (0-based)
+        if (DIRECT) dst = (uint64_t *)(uintptr_t)out_ptr[mine.r] + d;
         int off;
-        if (mine.nc == mine.ln) {                        // ASCII: chunk = cc bytes
+        if (DIRECT || mine.nc == mine.ln) {              // ASCII: chunk = cc bytes
             off = d * cc;
             clen = min(cc, mine.ln - off);
         } else {                                         // code-point boundaries (k_utf8_bounds)
@@ -428,7 +432,7 @@ k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ sta
         }
         p = bytes + mine.st + off;
         const bool aligned = (((uintptr_t)p & 15) == 0);
-        const bool tail_done_by_prep = (mine.nc == mine.ln) && g + 1 == (int64_t)mine.b1 &&
+        const bool tail_done_by_prep = (DIRECT || mine.nc == mine.ln) && g + 1 == (int64_t)mine.b1 &&
                                        clen < cc && ((((uintptr_t)bytes + mine.st) & 15) == 0);
         kind = tail_done_by_prep ? 0 : ((aligned && clen == 128) ? 1 : 3);
     }
@@ -456,7 +460,7 @@ k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ sta
     if (kind == 1) h = xxh64_row128(wrow + lane * 128, lane & 7);
     else if (kind == 3) h = xxh64_global(p, clen);
     if (kind) {
-        if (out_ptr) ((uint64_t *)(uintptr_t)mine.op)[g - mine.b] = h;
+        if (DIRECT) *dst = h;
         else hashes[g] = h;
     }
 }
@@ -906,9 +910,14 @@ int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const int32_t *
     const int ntiles = (int)((max_chunks + HASH_WARPS * WTILE - 1) / (HASH_WARPS * WTILE));
     if (ntiles > 0 && phase != 1) {
         ProfScope ps__(PK_HASH, st); g_launches += 1;
-        k_hash_chunks<<<ntiles, HASH_WARPS * 32, 0, st>>>(
-            d_bytes, d_starts, d_lens, d_nchars, d_chunk_base, tile_first, chunk_off, (int)n, cc,
-            max_chunks, d_hashes, pp ? pp->out_ptr : nullptr);
+        if (pp)
+            k_hash_chunks<true><<<ntiles, HASH_WARPS * 32, 0, st>>>(
+                d_bytes, d_starts, d_lens, d_nchars, d_chunk_base, tile_first, chunk_off, (int)n, cc,
+                max_chunks, d_hashes, pp->out_ptr);
+        else
+            k_hash_chunks<false><<<ntiles, HASH_WARPS * 32, 0, st>>>(
+                d_bytes, d_starts, d_lens, d_nchars, d_chunk_base, tile_first, chunk_off, (int)n, cc,
+                max_chunks, d_hashes, nullptr);
         B200R_LAUNCH_CHECK("k_hash_chunks");
     }
     return B200R_OK;
