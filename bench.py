@@ -776,7 +776,7 @@ def session_line(cx, args, K=None, W=None):
             "ring_rebuild_ms": rebuild_ms, "cpu_baseline": cpu, "gpu_launches": K}
 
 
-def mrqa_line(cx, args, router, seq, users=5000, rounds=10):
+def mrqa_line(cx, args, router, seq, users=5000, rounds=10, label="C5"):
     """configs[4]: replay of a benchmarks/multi-round-qa style trace (users x rounds, every
     round carries the whole chat history) through the GPU router, one global batch per round
     (users split over the ranks), vs the Python restatement of the reference on a sample."""
@@ -836,9 +836,9 @@ def mrqa_line(cx, args, router, seq, users=5000, rounds=10):
     return {"metric": METRIC, "value": n / (ms * 1e-3), "unit": UNIT, "n_gpus": W, "steps": rounds,
             "warmup": max(args.warmup, 1), "ms_per_step": ms / rounds, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-            "config": {"workload": "C5: multi-round-QA replay, %d users x %d rounds, 4 endpoints, one "
+            "config": {"workload": "%s: multi-round-QA replay, %d users x %d rounds, 4 endpoints, one "
                                    "global batch per round, prompts %.1f KB on average" %
-                                   (nu, rounds, payload / n / 1e3)},
+                                   (label, nu, rounds, payload / n / 1e3)},
             "clocks": clocks, "prompt_gbs": payload / (ms * 1e-3) / 1e9,
             "prompt_frac_of_hbm": payload / (ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
             "e2e": {"value": n / e2e_s, "unit": UNIT,
@@ -1010,8 +1010,13 @@ def run_extras(cx, args, router, seq):
     try:
         if cx.world == 1 and cx.rank == 0:
             ex["session"] = session_line(cx, args, K=10, W=3)
+        # configs[0] (the reference's own CPU-runnable case: 10K multi-round-QA prompts, 4
+        # endpoints), configs[4] (the larger replay), configs[3] (32K-char prompts, 64 endpoints,
+        # shared-fraction sweep, exchange bytes and time at N > 1)
+        if cx.world == 1:
+            ex["c1"], seq = mrqa_line(cx, args, router, seq, users=1000, rounds=10, label="C1")
         ex["mrqa"], seq = mrqa_line(cx, args, router, seq)
-        ex["c4"], seq = c4_line(cx, args, router, seq, fracs=(0.5,), steps=3)
+        ex["c4"], seq = c4_line(cx, args, router, seq, fracs=(0.0, 0.5, 0.94), steps=3)
         if cx.world == 1 and cx.rank == 0:
             ex["latency"] = latency_line(cx, args)
     except Exception as exc:                               # extras never take the headline down
