@@ -1000,6 +1000,32 @@ def latency_line(cx, args):
         per = out["reference_port_one_at_a_time"]["decisions_per_s"]
         out["break_even_concurrency"] = next((int(c) for c in ("8", "64", "512", "4096")
                                               if conc[c] > per), None)
+    # device side of the operating point between one request and the 64K headline: one routed
+    # batch of n C3-shaped prompts, inputs resident, through the three-stream pipeline
+    from b200_router.packing import pack_arrays
+    from b200_router.trie import GpuHashTrie, RoutePipeline
+    torch = cx.torch
+    sweep = {}
+    for nreq in (16, 256, 4096, 32768):
+        trs = traces.SharedPrefixTrace(n_total=24 * nreq, batch=nreq, n_sys=64, sys_chars=SYS_CHARS,
+                                       suffix_lo=SUFFIX[0], suffix_hi=SUFFIX[1], seed=SEED + 11)
+        packs = [pack_arrays(*trs.batch_arrays(b), pin=False).to(cx.dev, non_blocking=False) for b in range(24)]
+        pipe = RoutePipeline(GpuHashTrie(cap_log2=22, device=cx.dev), depth=3)
+        pipe.reserve(nreq, max(p.max_chunks for p in packs))
+        for b in range(8):
+            pipe.route(packs[b], (1 << N_ENDPOINTS) - 1, SEED, b * nreq, inputs_ready=True)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for b in range(8, 24):
+            pipe.route(packs[b], (1 << N_ENDPOINTS) - 1, SEED, b * nreq, inputs_ready=True)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / 16
+        sweep[str(nreq)] = {"us_per_batch": ms * 1e3, "decisions_per_s": nreq / (ms * 1e-3)}
+        pipe.close()
+        pipe.trie.close()
+    out["device_batch_sweep"] = sweep
     out["config"] = {"workload": "C3-shaped prompts (2048-char shared system prompt + 256-1024-char "
                                  "suffix), 8 endpoints, Python str in, url out"}
     return out

@@ -1493,6 +1493,8 @@ int b200r_prefix_route_batch(b200r_trie *t, const uint8_t *d_bytes, const int64_
 // The three steps of a routed batch (prep | hash | route) pipelined over consecutive batches
 // natively: stream and event handling in Python costs more host time per batch than the GPU
 // needs for the batch.
+constexpr int64_t PIPE_SERIAL_MAX = 4096;   // batches up to this size skip the stream pipeline
+
 struct b200r_pipe {
     b200r_trie *t;
     int depth;
@@ -1583,6 +1585,27 @@ int b200r_pipe_route(b200r_pipe *p, const uint8_t *d_bytes, const int64_t *d_sta
     uint8_t *sc = (uint8_t *)d_scratch;
     int32_t *chunk_base = (int32_t *)(sc + pl.off_chunk_base);
     uint64_t *hashes = (uint64_t *)(sc + pl.off_hashes);
+    if (n <= PIPE_SERIAL_MAX) {
+        // Small batch: the GPU needs less time for it than the host needs to hand it to three
+        // streams (a dozen event calls), so all six kernels go to the route stream in order.
+        // Scratch k: every earlier user's stages precede its route step, which is on this stream.
+        if (inputs_on_prep_stream) {                   // the copies were put on the prep stream
+            B200R_CUDA(cudaEventRecord(p->prepped[k], p->prep));
+            B200R_CUDA(cudaStreamWaitEvent(p->route, p->prepped[k], 0));
+        }
+        B200R_CUDA(cudaEventRecord(p->inputs, cur));   // inputs produced / outputs last used there
+        B200R_CUDA(cudaStreamWaitEvent(p->route, p->inputs, 0));
+        rc = launch_hash(d_bytes, d_starts, d_lens, d_nchars, n, t->chunk_chars, flags, chunk_base, hashes,
+                         max_chunks, sc, pl, t->dev, p->route, 0);
+        if (rc) return rc;
+        rc = route_from(t, hashes, chunk_base, n, max_chunks, avail_mask, seed, seq0, d_endpoint,
+                        d_match_depth, d_matched_mask, sc, pl, p->route);
+        if (rc) return rc;
+        B200R_CUDA(cudaEventRecord(p->done[k], p->route));
+        B200R_CUDA(cudaStreamWaitEvent(cur, p->done[k], 0));
+        p->has_done[k] = true;
+        return B200R_OK;
+    }
     if (p->has_done[k]) B200R_CUDA(cudaStreamWaitEvent(p->prep, p->done[k], 0));   // scratch k is free again
     if (!inputs_on_prep_stream) {
         B200R_CUDA(cudaEventRecord(p->inputs, cur));
