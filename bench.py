@@ -616,19 +616,21 @@ def run_b200(args):
     e2e_strings = None
     if rank == 0 and world == 1 and not args.no_cpu:
         from b200_router.packing import PackArena, PackPipeline
-        ns = min(4, nb)
+        ns = min(8, nb)
         strs = [prompts_of(*tr.batch_arrays(b), args.batch) for b in range(ns)]
-        pp = PackPipeline(arena=PackArena(slots=5), workers=2)     # packs 2 batches ahead
+        workers = int(os.environ.get("BENCH_PACK_WORKERS", "3"))
+        ahead = workers
+        pp = PackPipeline(arena=PackArena(slots=ahead + 3), workers=workers)   # packs `ahead` batches ahead
         for rep in range(3):                      # reps 0-1 touch every arena slot (pinned allocation)
             torch.cuda.synchronize()
             t0 = time.perf_counter()
             prev = None
-            for k in range(min(2, ns)):
+            for k in range(min(ahead, ns)):
                 pp.submit(strs[k])
             for k in range(ns):
                 pk = pp.next()
-                if k + 2 < ns:
-                    pp.submit(strs[k + 2])
+                if k + ahead < ns:
+                    pp.submit(strs[k + ahead])
                 ep, _, _ = router.route(pk, avail_mask(W), SEED, seq)
                 seq += args.batch
                 res_host[k % 3][:ep.numel()].copy_(ep, non_blocking=True)
@@ -640,8 +642,9 @@ def run_b200(args):
             str_s = time.perf_counter() - t0
         pp.close()
         e2e_strings = {"value": ns * args.batch / str_s, "unit": UNIT, "ms_per_step": str_s / ns * 1e3,
-                       "note": "input = list of Python str per step; native packer on 2 worker threads "
-                               "(copy phase without the GIL, %d cpus) + H2D + route + D2H" % os.cpu_count()}
+                       "note": "input = list of Python str per step; native packer on %d worker threads "
+                               "(copy phase without the GIL, %d cpus) + H2D + route + D2H" %
+                               (workers, os.cpu_count())}
         del strs
 
     # ---- CPU baseline (rank 0, N=1 only): the Python port on the first requests of timed
