@@ -204,3 +204,42 @@ def test_partitioned_lockstep_with_the_staged_send_path():
         test_partitioned_lockstep_heavy_sharing()
     finally:
         _lib.check(_lib.lib().b200r_set_part_staged(0))
+
+
+def test_partitioned_lockstep_utf8_and_unaligned_prompts():
+    """Non-ASCII batches take the staged send path (chunk boundaries come from the code-point
+    scan); ASCII prompts packed without alignment have their first chunk hashed by the generic
+    path of the placing prep kernel.  Both against the oracle, next to ordinary batches."""
+    import random
+    world = 2
+
+    def tight_arrays(ps):                     # CSR-tight: unaligned starts
+        blobs = [p.encode("ascii") for p in ps]
+        lens = np.array([len(b) for b in blobs], dtype=np.int32)
+        starts = np.zeros(len(blobs), dtype=np.int64)
+        starts[1:] = np.cumsum(lens[:-1])
+        return np.frombuffer(b"".join(blobs) + b"\0" * 16, dtype=np.uint8).copy(), starts, lens
+
+    rng = random.Random(5)
+    heads = ["systémé prompt " * 20, "Ünïcödé ✓ header " * 17, "plain ascii header " * 15]
+
+    def prompts(k, ascii_only):
+        out = []
+        for _ in range(k):
+            h = heads[2] if ascii_only else rng.choice(heads)
+            tail = "".join(rng.choice("abcdé✓xyz" if not ascii_only else "abcdxyz") for _ in range(rng.randint(0, 400)))
+            out.append(h + tail)
+        return out
+
+    batches = []
+    for g in range(5):
+        shards = []
+        for r in range(world):
+            if g % 2 == 0:
+                ps = prompts(150, ascii_only=False)
+                shards.append(traces.pack_strings(ps))                  # (buf, starts, lens, nchars)
+            else:
+                ps = prompts(150, ascii_only=True)
+                shards.append(tight_arrays(ps) if r == 0 else traces.pack_strings(ps)[:3])
+        batches.append((0x3F if g != 2 else 0x2F, shards))
+    _check_partitioned_lockstep(world, batches, seed=21)
