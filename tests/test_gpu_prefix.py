@@ -396,7 +396,7 @@ def test_retire_endpoints_clears_their_bits_everywhere():
 
 
 def test_route_long_prompts_many_blocks_vs_oracle():
-    """Prompts of more than 32 chunks (several warp iterations, carried path key)."""
+    """Prompts of more than 32 chunks (several windows of the warp walker, runs spanning windows)."""
     from b200_router.trie import GpuHashTrie
     buf, starts, lens = traces.long_context_batch(n=96, chars=128 * 70 + 5, group=8,
                                                   shared_frac=0.6, seed=5)

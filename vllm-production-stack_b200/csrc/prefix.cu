@@ -11,11 +11,16 @@
 //                [k_count_chars, k_utf8_bounds   only for batches that are not pure ASCII]
 //                k_hash_chunks               XXH64 of every chunk, one thread per chunk,
 //                                            bytes staged by cp.async into swizzled smem
-//   route stage  k_walk<W_CLAIM>  one warp per request walks the trie (trie.cuh): runs of
-//                                 the node log are compared 32 depths at a time, missing
-//                                 paths are appended as one run; "first toucher" atomicMax
-//                k_select         per request: deepest usable node, root draw or leader
-//                k_commit         resolve leader chains, OR the endpoint into new nodes
+//   route stage  claim     k_claim_thread (a thread per request; short prompts) or
+//                          k_walk<W_CLAIM> (8/16/32 lanes per request; long prompts), trie.cuh:
+//                          stored runs of the node log are followed, missing paths appended as
+//                          one run, "first toucher" atomicMax on nodes not usable before
+//                k_select  per request: deepest usable node (bisection), root draw or leader
+//                k_commit  resolve leader chains, OR the endpoint into the nodes below the
+//                          match depth (k_commit_warp for long prompts)
+// Around them: the three-stream batch pipeline (b200r_pipe_*), the one-request latency path
+// (k_route_one), status / dump / restore / sweeps, and the C ABI.  The partitioned multi-GPU
+// path is multigpu.cu; its send side hooks into k_prep_scan (PartPlace) and k_hash_chunks<true>.
 #include <cstdarg>
 #include <mutex>
 #include <algorithm>
