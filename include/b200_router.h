@@ -310,8 +310,9 @@ int b200r_part_finish(b200r_trie *t, int64_t n, void *d_my_base, int32_t world, 
  * the sources, gather, claim, select, commit) and return (push results, wait for the owners,
  * scatter); prep, route and return run at the highest priority.  Send of batch
  * b+1 overlaps route and return of batch b; route of batch b+1 follows the commit of batch b.
- * The caller's `stream` waits for the call's results.  d_scratch must be one of TWO buffers
- * used in turn by batch parity (the prep of batch b+1 runs while batch b is being hashed).
+ * The caller's `stream` waits for the call's results.  d_scratch must be one of THREE buffers
+ * used in turn (batch b: buffer b % 3, like the exchange's buffer sets; the prep of batch b+1
+ * runs while batch b is being hashed).
  * inputs_on_prep_stream = 1: the inputs are complete or were copied with
  * b200r_part_copy_h2d after b200r_part_begin(t, epoch) (a host-to-device copy that overlaps the
  * previous batch); 0: they were produced on `stream`. */

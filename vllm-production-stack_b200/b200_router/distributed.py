@@ -131,6 +131,9 @@ class ShardedPrefixRouter:
         return self.ops.dump()
 
 
+PART_SETS = 3        # buffer sets of the partitioned exchange (csrc/internal.cuh)
+
+
 class PartitionedPrefixRouter:
     """Multi-GPU routing with a PARTITIONED table -- the variant that weak-scales.
 
@@ -183,8 +186,8 @@ class PartitionedPrefixRouter:
         # route() pipelines consecutive batches natively (b200r_part_step); the phase_* methods
         # run the three phases one by one on the current stream (lock-step tests)
         self.pipelined = True
-        self._keep = [None, None]                  # device copies of host inputs, by batch parity
-        self._sc = [None, None]                    # hash-stage scratch, by batch parity
+        self._keep = [None] * PART_SETS            # device copies of host inputs, by buffer set
+        self._sc = [None] * PART_SETS              # hash-stage scratch, by buffer set
         self._retired = []                         # outgrown scratch buffers (may still be in use)
 
     @staticmethod
@@ -250,7 +253,7 @@ class PartitionedPrefixRouter:
         with torch.cuda.device(self.device):
             if p.bytes.device != self.device:
                 _lib.check(L.b200r_part_begin(self.trie._h, self.epoch))
-                k = self.epoch & 1
+                k = self.epoch % PART_SETS
                 self._keep[k] = None
                 self._keep[k] = p = self._copy_on_prep_stream(p)
                 inputs_ready = True
@@ -275,8 +278,8 @@ class PartitionedPrefixRouter:
         return ep[:n], depth[:n], matched[:n]
 
     def _step_scratch(self, nbytes: int) -> torch.Tensor:
-        # two buffers in turn: the prep of batch b+1 runs next to the hashing of batch b
-        k = self.epoch & 1
+        # one buffer per set in turn: the prep of batch b+1 runs next to the hashing of batch b
+        k = self.epoch % PART_SETS
         sc = self._sc[k]
         if sc is None or sc.numel() < nbytes:
             if sc is not None:

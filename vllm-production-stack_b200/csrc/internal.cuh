@@ -43,6 +43,8 @@ constexpr int WALK_MAX_CTAS = 148 * 8; // persistent grid of the walk kernels (<
 
 // Device-resident bookkeeping of the partitioned multi-GPU path (read by k_select).
 constexpr int P2P_MAX_WORLD = 64;
+constexpr int PART_SETS = 3;       // buffer sets of the partitioned exchange: batch b uses set b % 3
+                                   // and may start once batch b - 3 has been returned
 struct P2PDyn {
     unsigned long long seq_base;     // global sequence number of the next batch's request 0
     uint32_t my_off, total_n;        // position of this shard / size of the current global batch
@@ -121,8 +123,8 @@ struct b200r_trie {
     uint32_t epoch;
     // streams / events of b200r_part_step (created on first use)
     cudaStream_t part_send, part_route, part_prep, part_ret;
-    cudaEvent_t part_inputs, part_prepped, part_routed, part_sent[2], part_finished[2];
-    bool part_ready, part_has_finished[2];
+    cudaEvent_t part_inputs, part_prepped, part_routed, part_sent[b200r::PART_SETS], part_finished[b200r::PART_SETS];
+    bool part_ready, part_has_finished[b200r::PART_SETS];
     // latency path (b200r_prefix_route_one; allocated on first use)
     uint8_t *one_host, *one_host_dev, *one_dev;
 };

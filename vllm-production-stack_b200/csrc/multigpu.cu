@@ -43,10 +43,10 @@ __device__ __forceinline__ bool p2p_spin(const volatile unsigned long long *flag
 // Per-GPU work no longer grows with the number of GPUs.
 // =========================================================================
 struct PartFlags {
-    unsigned long long in_req[2][P2P_MAX_WORLD], in_chunk[2][P2P_MAX_WORLD], in_n[2][P2P_MAX_WORLD],
-        res[2][P2P_MAX_WORLD];
+    unsigned long long in_req[PART_SETS][P2P_MAX_WORLD], in_chunk[PART_SETS][P2P_MAX_WORLD],
+        in_n[PART_SETS][P2P_MAX_WORLD], res[PART_SETS][P2P_MAX_WORLD];
 };
-static_assert(sizeof(PartFlags) <= 4096, "flag block");
+static_assert(sizeof(PartFlags) <= 8192, "flag block");
 struct PartRes { int32_t ep, depth; uint64_t matched; };
 struct PartDyn {
     P2PDyn base;                              // seq_base, total_n (my_off stays 0)
@@ -372,29 +372,29 @@ struct PartLayout {
 static PartLayout part_layout(int world, int64_t cap, int64_t rcap)
 {
     PartLayout L;
-    L.hash_off = 4096;
+    L.hash_off = 8192;                                  // the flag block comes first
     L.hash_set = (size_t)world * cap * 8;
-    L.info_off = L.hash_off + 2 * L.hash_set;
+    L.info_off = L.hash_off + PART_SETS * L.hash_set;
     L.info_set = (size_t)world * rcap * 8;
-    L.res_off = L.info_off + 2 * L.info_set;
+    L.res_off = L.info_off + PART_SETS * L.info_set;
     L.res_set = (size_t)world * rcap * sizeof(PartRes);
-    L.symm_total = align_up(L.res_off + 2 * L.res_set);
+    L.symm_total = align_up(L.res_off + PART_SETS * L.res_set);
     L.n_max = (int64_t)world * rcap;
     L.c_max = (int64_t)world * cap;
     L.nblk_max = (int)((rcap + PART_BLOCK - 1) / PART_BLOCK);
     size_t o = 0;
-    L.w_dyn = o;       o += 2 * align_up(sizeof(PartDyn));          // one per batch parity
-    L.w_totals = o;    o += 2 * align_up((size_t)world * 8);               // one per batch parity
-    L.w_out_ptr = o;   o += 2 * align_up((size_t)rcap * 8);
-    L.w_dest_slot = o; o += 2 * align_up((size_t)rcap * 4);     // one per batch parity
+    L.w_dyn = o;       o += PART_SETS * align_up(sizeof(PartDyn));          // one per buffer set
+    L.w_totals = o;    o += PART_SETS * align_up((size_t)world * 8);               // one per buffer set
+    L.w_out_ptr = o;   o += PART_SETS * align_up((size_t)rcap * 8);
+    L.w_dest_slot = o; o += PART_SETS * align_up((size_t)rcap * 4);     // one per buffer set
     L.w_hash_stage = o; o += align_up((size_t)world * (cap + 2) * 8);   // one fixed segment per owner
     L.w_info_stage = o; o += align_up((size_t)world * (rcap + 2) * 8);
     L.w_chunk_end = o; o += align_up((size_t)L.n_max * 4);
     L.w_pos_owned = o; o += align_up((size_t)L.n_max * 4);
     L.w_idx_of_pos = o; o += align_up((size_t)L.n_max * 4);
-    L.w_ep = o;        o += 2 * align_up((size_t)L.n_max * 4);      // results: one per batch parity
-    L.w_depth = o;     o += 2 * align_up((size_t)L.n_max * 4);
-    L.w_matched = o;   o += 2 * align_up((size_t)L.n_max * 8);
+    L.w_ep = o;        o += PART_SETS * align_up((size_t)L.n_max * 4);      // results: one per buffer set
+    L.w_depth = o;     o += PART_SETS * align_up((size_t)L.n_max * 4);
+    L.w_matched = o;   o += PART_SETS * align_up((size_t)L.n_max * 8);
     L.w_plan = o;      o += make_plan(L.n_max, L.c_max, B200R_F_ALL_ASCII, true).total;
     L.work_total = o + 256;
     return L;
@@ -448,7 +448,7 @@ static int part_send_impl(b200r_trie *t, const uint8_t *d_bytes, const int64_t *
     const PartLayout L = part_layout(world, cap, rcap);
     const Plan p = make_plan(n, max_chunks, flags, true);
     uint8_t *sc = (uint8_t *)d_scratch, *wk = (uint8_t *)d_work;
-    const int set = (int)(epoch & 1);
+    const int set = (int)(epoch % PART_SETS);
     unsigned long long *totals = (unsigned long long *)(wk + L.w_totals + (size_t)set * align_up((size_t)world * 8));
     uint32_t *dest_slot = (uint32_t *)(wk + L.w_dest_slot + (size_t)set * align_up((size_t)rcap * 4));
     const bool direct = (flags & B200R_F_ALL_ASCII) && n > 0 && !g_part_staged;
@@ -542,7 +542,7 @@ static int part_route_impl(b200r_trie *t, uint64_t avail_mask, uint64_t seed,
     if (!t || !d_my_base) { set_error("b200r_part_route: null pointer"); return B200R_E_INVALID; }
     const PartLayout L = part_layout(world, cap, rcap);
     const Plan p = make_plan(L.n_max, L.c_max, B200R_F_ALL_ASCII, true);
-    const int set = (int)(epoch & 1);
+    const int set = (int)(epoch % PART_SETS);
     uint8_t *base = (uint8_t *)d_my_base, *wk = (uint8_t *)d_work, *sc = wk + L.w_plan;
     PartDyn *dyn = part_dyn(wk, L, set);
     uint32_t *pos_owned = (uint32_t *)(wk + L.w_pos_owned);
@@ -556,7 +556,7 @@ static int part_route_impl(b200r_trie *t, uint64_t avail_mask, uint64_t seed,
 
     { ProfScope ps__(PK_WAIT, st); g_launches += 1;
     k_part_wait_meta<<<1, P2P_MAX_WORLD, 0, st>>>((const PartFlags *)base, set, (unsigned long long)epoch,
-                                                  world, dyn, part_dyn(wk, L, set ^ 1), t->dev);
+                                                  world, dyn, part_dyn(wk, L, (set + PART_SETS - 1) % PART_SETS), t->dev);
     B200R_LAUNCH_CHECK("k_part_wait_meta");
     }
     int32_t *chunk_end = (int32_t *)(wk + L.w_chunk_end);
@@ -604,7 +604,7 @@ int b200r_part_finish(b200r_trie *t, int64_t n, void *d_my_base, int32_t world, 
     if (!t || (n > 0 && (!d_endpoint || !d_match_depth || !d_matched))) { set_error("b200r_part_finish: null pointer"); return B200R_E_INVALID; }
     cudaStream_t st = (cudaStream_t)stream;
     const PartLayout L = part_layout(world, cap, rcap);
-    const int set = (int)(epoch & 1);
+    const int set = (int)(epoch % PART_SETS);
     uint8_t *base = (uint8_t *)d_my_base, *wk = (uint8_t *)d_work;
     { ProfScope ps__(PK_WAIT, st); g_launches += 1;
     k_part_wait_res<<<1, P2P_MAX_WORLD, 0, st>>>((const PartFlags *)base, set, (unsigned long long)epoch,
@@ -640,9 +640,12 @@ static int part_streams(b200r_trie *t)
     B200R_CUDA(cudaStreamCreateWithPriority(&t->part_route, cudaStreamNonBlocking, greatest));
     B200R_CUDA(cudaStreamCreateWithPriority(&t->part_prep, cudaStreamNonBlocking, greatest));
     B200R_CUDA(cudaStreamCreateWithPriority(&t->part_ret, cudaStreamNonBlocking, greatest));
-    cudaEvent_t *evs[] = { &t->part_inputs, &t->part_prepped, &t->part_routed, &t->part_sent[0],
-                           &t->part_sent[1], &t->part_finished[0], &t->part_finished[1] };
+    cudaEvent_t *evs[] = { &t->part_inputs, &t->part_prepped, &t->part_routed };
     for (cudaEvent_t *e : evs) B200R_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+    for (int k = 0; k < PART_SETS; k++) {
+        B200R_CUDA(cudaEventCreateWithFlags(&t->part_sent[k], cudaEventDisableTiming));
+        B200R_CUDA(cudaEventCreateWithFlags(&t->part_finished[k], cudaEventDisableTiming));
+    }
     t->part_ready = true;
     return B200R_OK;
 }
@@ -652,12 +655,12 @@ int b200r_part_begin(b200r_trie *t, uint32_t epoch)
     if (!t) { set_error("null trie"); return B200R_E_INVALID; }
     int rc = part_streams(t);
     if (rc) return rc;
-    // Batch `epoch` reuses what batch epoch-2 used (the events of that parity still belong to
-    // batch epoch-2 here).  Its send phase overwrites that exchange buffer set: it may start
-    // once this rank has finished batch epoch-2 (every owner has then pushed its results for
+    // Batch `epoch` reuses what batch epoch-3 used (PART_SETS buffer sets; the events of that set
+    // still belong to batch epoch-3 here).  Its send phase overwrites that exchange buffer set: it may start
+    // once this rank has finished batch epoch-3 (every owner has then pushed its results for
     // that batch, i.e. has consumed what all sources sent it).  Its prep writes the scratch
-    // buffer of that parity: after the send of batch epoch-2 has read it.
-    const int par = (int)(epoch & 1);
+    // buffer of that set: after the send of batch epoch-3 has read it.
+    const int par = (int)(epoch % PART_SETS);
     if (t->part_has_finished[par]) {
         B200R_CUDA(cudaStreamWaitEvent(t->part_send, t->part_finished[par], 0));
         B200R_CUDA(cudaStreamWaitEvent(t->part_prep, t->part_finished[par], 0));   // it stores into that set too
@@ -684,7 +687,7 @@ int b200r_part_step(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_star
     int rc = b200r_part_begin(t, epoch);
     if (rc) return rc;
     cudaStream_t cur = (cudaStream_t)stream;
-    const int me = (int)(epoch & 1);
+    const int me = (int)(epoch % PART_SETS);
     B200R_CUDA(cudaEventRecord(t->part_inputs, cur));
     if (!inputs_on_prep_stream) B200R_CUDA(cudaStreamWaitEvent(t->part_prep, t->part_inputs, 0));
     rc = part_send_impl(t, d_bytes, d_starts, d_lens, d_nchars, n, max_chunks, flags, d_peer_bases,
@@ -693,7 +696,7 @@ int b200r_part_step(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_star
     if (rc) return rc;
     B200R_CUDA(cudaEventRecord(t->part_sent[me], t->part_send));
     B200R_CUDA(cudaStreamWaitEvent(t->part_route, t->part_sent[me], 0));
-    // the route stage's dyn block and result buffers of this parity: free once batch epoch-2
+    // the route stage's dyn block and result buffers of this parity: free once batch epoch-3
     // has been returned
     if (t->part_has_finished[me]) B200R_CUDA(cudaStreamWaitEvent(t->part_route, t->part_finished[me], 0));
     rc = part_route_impl(t, avail_mask, seed, d_peer_bases, d_my_base, world, rank, cap, rcap, epoch,

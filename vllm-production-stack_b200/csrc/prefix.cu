@@ -1201,7 +1201,8 @@ int b200r_trie_create(int32_t cap_log2, int32_t chunk_chars, b200r_trie **out)
     t->chunk_chars = chunk_chars;
     t->epoch = 0;
     t->tab = nullptr; t->log = nullptr; t->wblk = nullptr; t->dev = nullptr;
-    t->part_ready = false; t->part_has_finished[0] = t->part_has_finished[1] = false;
+    t->part_ready = false;
+    for (int k = 0; k < PART_SETS; k++) t->part_has_finished[k] = false;
     t->one_host = t->one_host_dev = t->one_dev = nullptr;
     const size_t cap = (size_t)1 << cap_log2;
     cudaError_t e;
@@ -1226,9 +1227,9 @@ int b200r_trie_destroy(b200r_trie *t)
     if (t->part_ready) {
         cudaStream_t sts[] = { t->part_prep, t->part_send, t->part_route, t->part_ret };
         for (cudaStream_t s : sts) cudaStreamSynchronize(s);
-        cudaEvent_t evs[] = { t->part_inputs, t->part_prepped, t->part_routed, t->part_sent[0],
-                              t->part_sent[1], t->part_finished[0], t->part_finished[1] };
+        cudaEvent_t evs[] = { t->part_inputs, t->part_prepped, t->part_routed };
         for (cudaEvent_t e : evs) cudaEventDestroy(e);
+        for (int k = 0; k < PART_SETS; k++) { cudaEventDestroy(t->part_sent[k]); cudaEventDestroy(t->part_finished[k]); }
         for (cudaStream_t s : sts) cudaStreamDestroy(s);
     }
     if (t->one_host) { cudaDeviceSynchronize(); cudaFreeHost(t->one_host); cudaFree(t->one_dev); }
