@@ -661,11 +661,11 @@ int b200r_part_begin(b200r_trie *t, uint32_t epoch)
     // that batch, i.e. has consumed what all sources sent it).  Its prep writes the scratch
     // buffer of that set: after the send of batch epoch-3 has read it.
     const int par = (int)(epoch % PART_SETS);
-    if (t->part_has_finished[par]) {
-        B200R_CUDA(cudaStreamWaitEvent(t->part_send, t->part_finished[par], 0));
-        B200R_CUDA(cudaStreamWaitEvent(t->part_prep, t->part_finished[par], 0));   // it stores into that set too
-        B200R_CUDA(cudaStreamWaitEvent(t->part_prep, t->part_sent[par], 0));
-    }
+    // One wait does it: the prep stream stores into that set first, the send stream follows the
+    // prep stream (prepped event), and "returned" implies that the send of that batch had been
+    // consumed by every owner, i.e. had read its scratch.
+    if (t->part_has_finished[par])
+        B200R_CUDA(cudaStreamWaitEvent(t->part_prep, t->part_finished[par], 0));
     return B200R_OK;
 }
 
@@ -696,9 +696,8 @@ int b200r_part_step(b200r_trie *t, const uint8_t *d_bytes, const int64_t *d_star
     if (rc) return rc;
     B200R_CUDA(cudaEventRecord(t->part_sent[me], t->part_send));
     B200R_CUDA(cudaStreamWaitEvent(t->part_route, t->part_sent[me], 0));
-    // the route stage's dyn block and result buffers of this parity: free once batch epoch-3
-    // has been returned
-    if (t->part_has_finished[me]) B200R_CUDA(cudaStreamWaitEvent(t->part_route, t->part_finished[me], 0));
+    // (the route stage's dyn block and result buffers of this set are free: the send waited for
+    // batch epoch-3 to be returned)
     rc = part_route_impl(t, avail_mask, seed, d_peer_bases, d_my_base, world, rank, cap, rcap, epoch,
                          d_work, t->part_route, t->part_ret, t->part_routed);
     if (rc) return rc;
