@@ -628,9 +628,9 @@ int b200r_part_finish(b200r_trie *t, int64_t n, void *d_my_base, int32_t world, 
 //   route (high)  wait for the sources, gather, claim, select, commit
 //   ret   (high)  push results to the sources, wait for the owners' results, scatter
 // so the route chain of batch b+1 starts right behind the commit of batch b, and the send of
-// batch b+1 overlaps both.  `d_scratch` alternates between two buffers by batch parity (the
+// batch b+1 overlaps both.  `d_scratch` alternates between PART_SETS buffers, batch b: b % PART_SETS (the
 // caller passes the one of this batch); dyn blocks, result buffers and exchange buffer sets
-// alternate the same way.
+// rotate the same way.
 static int part_streams(b200r_trie *t)
 {
     if (t->part_ready) return B200R_OK;
