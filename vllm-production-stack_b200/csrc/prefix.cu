@@ -361,7 +361,10 @@ constexpr int HASH_WARPS = 8;             // warps per CTA
 
 struct ReqRec { int b, b1, ln, nc; long long st; int r; };
 
-template <bool DIRECT>
+// ASCII: the batch is declared pure ASCII (code points = bytes): no nchars, no chunk_off, and a
+// request's last chunk is recognised by its byte range alone.  Chunk indices are 32-bit by
+// construction (chunk_base is int32).
+template <bool DIRECT, bool ASCII>
 __global__ void __launch_bounds__(HASH_WARPS * 32, 6)
 k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ starts,
               const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars,
@@ -373,10 +376,10 @@ k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ sta
     // an address in the owning GPU's inbound buffer; else they go to hashes[] (CSR order)
     __shared__ __align__(1024) uint8_t s_tile[HASH_WARPS * WTILE * 128];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const int64_t tile = (int64_t)blockIdx.x * HASH_WARPS + w;
-    const int64_t G0 = tile * WTILE;
-    int64_t total = chunk_base[n];
-    if (total > max_chunks) total = max_chunks;
+    const int tile = blockIdx.x * HASH_WARPS + w;
+    const int G0 = tile * WTILE;
+    int total = chunk_base[n];
+    if ((int64_t)total > max_chunks) total = (int)max_chunks;
     if (G0 >= total) return;                                   // whole warp
 
     // ---- map: which request owns each of the 32 chunks?
@@ -390,11 +393,11 @@ k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ sta
             q.b = chunk_base[r]; q.b1 = chunk_base[r + 1];
             q.st = starts[r]; q.ln = lens[r];
             q.r = r;
-            q.nc = (!DIRECT && nchars) ? nchars[r] : q.ln;       // DIRECT batches are ASCII
-            live = (int64_t)q.b < G0 + WTILE;
+            q.nc = (!ASCII && nchars) ? nchars[r] : q.ln;
+            live = q.b < G0 + WTILE;
         }
         const bool nonempty = live && q.b1 > q.b;
-        const int pos = (int64_t)q.b > G0 ? (int)(q.b - G0) : 0;
+        const int pos = q.b > G0 ? q.b - G0 : 0;
         const unsigned heads = __reduce_or_sync(0xffffffffu, nonempty ? (1u << pos) : 0u);
         const unsigned ne = __ballot_sync(0xffffffffu, nonempty);
         const unsigned below = heads & (0xffffffffu >> (31 - lane));   // heads at positions <= lane
@@ -405,47 +408,53 @@ k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ sta
             const int k = __popc(heads & ((1u << hp) - 1));            // its rank among non-empty ones
             src = (ne == (0xffffffffu >> (32 - __popc(ne)))) ? k : (int)__fns(ne, 0, k + 1);
         }
-        const int tb = __shfl_sync(0xffffffffu, q.b, src), tb1 = __shfl_sync(0xffffffffu, q.b1, src);
+        const int tb = __shfl_sync(0xffffffffu, q.b, src);
+        const int tb1 = ASCII ? 0 : __shfl_sync(0xffffffffu, q.b1, src);
         const int tln = __shfl_sync(0xffffffffu, q.ln, src);
-        const int tnc = DIRECT ? tln : __shfl_sync(0xffffffffu, q.nc, src);
+        const int tnc = ASCII ? tln : __shfl_sync(0xffffffffu, q.nc, src);
         const long long tst = __shfl_sync(0xffffffffu, q.st, src);
         const int tr = DIRECT ? __shfl_sync(0xffffffffu, q.r, src) : 0;
         if (below) { mine.b = tb; mine.b1 = tb1; mine.ln = tln; mine.nc = tnc; mine.st = tst; mine.r = tr; }
         // more requests can start inside the tile only if the last lane's request ends inside it
         const int last_b1 = __shfl_sync(0xffffffffu, q.b1, 31);
         const bool last_live = __shfl_sync(0xffffffffu, (int)live, 31);
-        if (!(last_live && (int64_t)last_b1 < G0 + WTILE && r0 + jb + 32 < n)) break;
+        if (!(last_live && last_b1 < G0 + WTILE && r0 + jb + 32 < n)) break;
     }
 
     // ---- chunk descriptor
-    const int64_t g = G0 + lane;
+    const int g = G0 + lane;
     const bool valid = g < total;
     const uint8_t *p = nullptr;
     int clen = 0, kind = 0;               // 0 none / done elsewhere, 1 full staged, 3 generic
     uint64_t *dst = nullptr;              // DIRECT: where this chunk's hash goes (owner's buffer)
     if (valid) {
-        const int d = (int)(g - mine.b);  // depth of the chunk inside its request (0-based)
+        const int d = g - mine.b;         // depth of the chunk inside its request (0-based)
         if (DIRECT) dst = (uint64_t *)(uintptr_t)out_ptr[mine.r] + d;
         int off;
-        if (DIRECT || mine.nc == mine.ln) {              // ASCII: chunk = cc bytes
+        bool last_ragged;                 // the request's ragged last chunk (ASCII requests only)
+        if (ASCII || mine.nc == mine.ln) {               // ASCII: chunk = cc bytes
             off = d * cc;
             clen = min(cc, mine.ln - off);
+            last_ragged = clen < cc;                     // only the last chunk can be short
         } else {                                         // code-point boundaries (k_utf8_bounds)
             off = chunk_off[g];
-            const int end = (g + 1 < (int64_t)mine.b1 && g + 1 < max_chunks) ? chunk_off[g + 1] : mine.ln;
+            const int end = (g + 1 < mine.b1 && (int64_t)g + 1 < max_chunks) ? chunk_off[g + 1] : mine.ln;
             clen = end - off;
+            last_ragged = false;
         }
         p = bytes + mine.st + off;
         const bool aligned = (((uintptr_t)p & 15) == 0);
-        const bool tail_done_by_prep = (DIRECT || mine.nc == mine.ln) && g + 1 == (int64_t)mine.b1 &&
-                                       clen < cc && ((((uintptr_t)bytes + mine.st) & 15) == 0);
+        const bool tail_done_by_prep = last_ragged && ((((uintptr_t)bytes + mine.st) & 15) == 0);
         kind = tail_done_by_prep ? 0 : ((aligned && clen == 128) ? 1 : 3);
     }
 
     // ---- stage this warp's full chunks, then hash
     uint64_t h = 0;
     const uint32_t wrow = (uint32_t)__cvta_generic_to_shared(s_tile) + (uint32_t)(w * WTILE) * 128;
-    const unsigned long long my_src = kind == 1 ? (unsigned long long)(uintptr_t)p : 0ULL;
+    // staged chunks are 16-byte aligned: lanes exchange them as 32-bit offsets (in 16-byte
+    // units, +1; 0 = not staged) from the buffer's aligned base
+    const uintptr_t base16 = (uintptr_t)bytes & ~(uintptr_t)15;
+    const uint32_t my_src = kind == 1 ? (uint32_t)(((uintptr_t)p - base16) >> 4) + 1u : 0u;
     // lane copies unit u of chunk c = 4k + sub; (c & 7) = sub ^ 4(k&1), so the swizzled
     // destination is one of two per-lane bases plus k * 512
     const int u = lane & 7, sub = lane >> 3;
@@ -453,12 +462,12 @@ k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ sta
     uint32_t d_even = wrow + sub * 128 + ((u ^ sub) << 4);
     asm volatile("" : "+r"(d_even));
     const uint32_t d_odd = d_even ^ 64u;
+    const uint8_t *ubase = (const uint8_t *)base16 + (u << 4) - 16;
 #pragma unroll
     for (int k = 0; k < 8; k++) {
-        const unsigned long long src = __shfl_sync(0xffffffffu, my_src, 4 * k + sub);
+        const uint32_t src = __shfl_sync(0xffffffffu, my_src, 4 * k + sub);
         if (src)
-            cp_async16_stream(((k & 1) ? d_odd : d_even) + k * 512,
-                              (const uint8_t *)(uintptr_t)src + (u << 4), pol);
+            cp_async16_stream(((k & 1) ? d_odd : d_even) + k * 512, ubase + ((size_t)src << 4), pol);
     }
     cp_async_wait_all();
     __syncwarp();
@@ -915,14 +924,13 @@ int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const int32_t *
     const int ntiles = (int)((max_chunks + HASH_WARPS * WTILE - 1) / (HASH_WARPS * WTILE));
     if (ntiles > 0 && phase != 1) {
         ProfScope ps__(PK_HASH, st); g_launches += 1;
-        if (pp)
-            k_hash_chunks<true><<<ntiles, HASH_WARPS * 32, 0, st>>>(
-                d_bytes, d_starts, d_lens, d_nchars, d_chunk_base, tile_first, chunk_off, (int)n, cc,
-                max_chunks, d_hashes, pp->out_ptr);
-        else
-            k_hash_chunks<false><<<ntiles, HASH_WARPS * 32, 0, st>>>(
-                d_bytes, d_starts, d_lens, d_nchars, d_chunk_base, tile_first, chunk_off, (int)n, cc,
-                max_chunks, d_hashes, nullptr);
+        const unsigned long long *op = pp ? pp->out_ptr : nullptr;
+#define B200R_HASH_ARGS d_bytes, d_starts, d_lens, d_nchars, d_chunk_base, tile_first, chunk_off, (int)n, cc, \
+                        max_chunks, d_hashes, op
+        if (pp)            k_hash_chunks<true, true><<<ntiles, HASH_WARPS * 32, 0, st>>>(B200R_HASH_ARGS);
+        else if (ascii)    k_hash_chunks<false, true><<<ntiles, HASH_WARPS * 32, 0, st>>>(B200R_HASH_ARGS);
+        else               k_hash_chunks<false, false><<<ntiles, HASH_WARPS * 32, 0, st>>>(B200R_HASH_ARGS);
+#undef B200R_HASH_ARGS
         B200R_LAUNCH_CHECK("k_hash_chunks");
     }
     return B200R_OK;
