@@ -437,6 +437,8 @@ def run_b200(args):
     world, rank, dev = cx.world, cx.rank, cx.dev
     W, K, R = args.warmup, args.steps, max(args.passes, 1)
     nb = W + K
+    if os.environ.get("BENCH_HASH_MODE"):
+        _lib.check(_lib.lib().b200r_set_hash_mode(int(os.environ["BENCH_HASH_MODE"])))
     if os.environ.get("BENCH_CLAIM_MODE"):      # tuning experiments only (see include/b200_router.h)
         _lib.check(_lib.lib().b200r_set_claim_mode(int(os.environ["BENCH_CLAIM_MODE"])))
 

@@ -365,6 +365,10 @@ int b200r_set_claim_mode(int mode);
  * hash into local CSR order, compact per owner and ship (the path non-ASCII batches take).  Same
  * results; for tests and comparison. */
 int b200r_set_part_staged(int on);
+
+/* Chunk-hashing kernel: 0 = persistent warps that stage tile t+2 while hashing tile t
+ * (k_hash_stream), 1 = one 32-chunk tile per warp (k_hash_chunks).  Same results. */
+int b200r_set_hash_mode(int mode);
 #define B200R_PROF_SLOTS 13
 int b200r_prof_enable(int on);
 int b200r_prof_read(float *ms_out, long long *count_out, int nslots);

@@ -28,6 +28,16 @@ def pytest_sessionstart(session):
         print("conftest: could not build the libraries: %r" % (e,))
 
 
+@pytest.fixture(autouse=True, scope="session")
+def _hash_mode_from_env():
+    """B200R_TEST_HASH_MODE=0|1 runs the whole GPU suite with that chunk-hashing kernel."""
+    mode = os.environ.get("B200R_TEST_HASH_MODE")
+    if mode is not None:
+        from b200_router import _lib
+        _lib.check(_lib.lib().b200r_set_hash_mode(int(mode)))
+    yield
+
+
 def pytest_collection_modifyitems(config, items):
     # Without a device the gpu-marked tests cannot run; the driver selects them
     # with -m gpu on the B200 box and with -m "not gpu" here.

@@ -70,6 +70,7 @@ SIGNATURES = {
     "b200r_part_step": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _u32, _u64, _u64, _vp, _vp, _i32, _i32,
                                   _i64, _i64, _u32, _vp, _vp, _sz, _vp, _vp, _vp, _i32, _vp]),
     "b200r_set_part_staged": (C.c_int, [C.c_int]),
+    "b200r_set_hash_mode": (C.c_int, [C.c_int]),
     "b200r_set_claim_mode": (C.c_int, [C.c_int]),
     "b200r_prof_enable": (C.c_int, [C.c_int]),
     "b200r_prof_read": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_longlong), C.c_int]),

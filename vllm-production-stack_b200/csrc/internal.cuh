@@ -18,6 +18,7 @@ extern bool g_prof_on;
 extern std::vector<ProfSpan> g_spans;
 extern long long g_launches;
 extern int g_claim_mode;
+extern int g_hash_mode;
 extern int g_part_staged;      // b200r_set_part_staged: 1 = always compact + ship (test / comparison)
 int claim_kind_for(int64_t n, int64_t chunks);
 

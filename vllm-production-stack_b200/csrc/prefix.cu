@@ -54,6 +54,7 @@ int cuda_fail(cudaError_t e, const char *what)
 // ------------------------------------------------------------- profiling (internal.cuh)
 int g_claim_mode = 0;          // b200r_set_claim_mode: 0 auto, else claim_kind_for's value
 int g_part_staged = 0;
+int g_hash_mode = 1;           // b200r_set_hash_mode: 0 = persistent streaming kernel, 1 = one tile per warp
 bool g_prof_on = false;
 std::vector<ProfSpan> g_spans;
 long long g_launches = 0;
@@ -476,6 +477,179 @@ k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ sta
     if (kind) {
         if (DIRECT) *dst = h;
         else hashes[g] = h;
+    }
+}
+
+// ---------------------------------------------------------------------------
+// k_hash_stream: the same work as k_hash_chunks with every warp as a PERSISTENT worker that
+// keeps loads in flight all the time.  k_hash_chunks' warps live for one tile -- map (two
+// dependent L2 round trips), stage, wait, hash -- so the loads of a warp are in flight for
+// about a sixth of its life, and of 192 KB of staging memory per SM only ~32 KB carry data on
+// average.  Here a warp owns two 4 KB buffers and walks tiles gw, gw + NW, gw + 2 NW, ...:
+//     iteration for tile t:   issue the record loads of tile t+2 (its first request is known
+//                             from a load issued one iteration earlier)
+//                             wait for the staged bytes of tile t, hash, store
+//                             finish the map of tile t+2 and stage it into the buffer just
+//                             freed (tile t+1 has been in flight all along)
+// so every dependent load has a whole hashing phase to arrive and one to two buffers per warp
+// are always being filled.  3 CTAs x 8 warps per SM.
+// ---------------------------------------------------------------------------
+constexpr int HS_WARPS = 8, HS_CTAS_PER_SM = 3;
+constexpr int HS_SMEM = HS_WARPS * 2 * WTILE * 128;          // 64 KB, dynamic
+
+struct HsDesc { const uint8_t *p; uint64_t *dst; int clen, kind; };
+
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait_group() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
+template <bool DIRECT, bool ASCII>
+__global__ void __launch_bounds__(HS_WARPS * 32, HS_CTAS_PER_SM)
+k_hash_stream(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ starts,
+              const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars,
+              const int32_t *__restrict__ chunk_base, const int32_t *__restrict__ tile_first,
+              const int32_t *__restrict__ chunk_off, int n, int cc, int64_t max_chunks,
+              uint64_t *__restrict__ hashes, const unsigned long long *__restrict__ out_ptr)
+{
+    extern __shared__ __align__(1024) uint8_t hs_smem[];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int gw = blockIdx.x * HS_WARPS + w, NW = gridDim.x * HS_WARPS;
+    int total = chunk_base[n];
+    if ((int64_t)total > max_chunks) total = (int)max_chunks;
+    const int ntiles = (total + WTILE - 1) / WTILE;
+    if (gw >= ntiles) return;                                  // whole warp
+    const uint32_t buf_base = (uint32_t)__cvta_generic_to_shared(hs_smem) + (uint32_t)w * (2 * WTILE * 128);
+    uint32_t buf = buf_base;                                   // buffer of the tile hashed next
+    const uintptr_t base16 = (uintptr_t)bytes & ~(uintptr_t)15;
+    const int u = lane & 7, sub = lane >> 3;
+    const uint64_t pol = l2_evict_first_policy();
+    const uint8_t *ubase = (const uint8_t *)base16 + (u << 4) - 16;
+
+    // B: the records of the first 32 requests a tile can touch (independent loads)
+    auto load_recs = [&](int tile, int r0, bool &live) -> ReqRec {
+        const int r = r0 + lane;
+        ReqRec q = { 0, 0, 0, 0, 0, 0 };
+        live = false;
+        if (r < n) {
+            q.b = chunk_base[r]; q.b1 = chunk_base[r + 1];
+            q.st = starts[r]; q.ln = lens[r];
+            q.r = r;
+            q.nc = (!ASCII && nchars) ? nchars[r] : q.ln;
+            live = q.b < tile * WTILE + WTILE;
+        }
+        return q;
+    };
+    // C: finish the map (each chunk lane pulls the record of its request), describe the chunk
+    auto describe = [&](int tile, int r0, ReqRec q, bool live) -> HsDesc {
+        const int G0 = tile * WTILE;
+        ReqRec mine = { 0, 0, 0, 0, 0, 0 };
+        for (int jb = 0;; jb += 32) {
+            if (jb) q = load_recs(tile, r0 + jb, live);        // short requests: more than 32 per tile
+            const bool nonempty = live && q.b1 > q.b;
+            const int pos = q.b > G0 ? q.b - G0 : 0;
+            const unsigned heads = __reduce_or_sync(0xffffffffu, nonempty ? (1u << pos) : 0u);
+            const unsigned ne = __ballot_sync(0xffffffffu, nonempty);
+            const unsigned below = heads & (0xffffffffu >> (31 - lane));
+            int src = 0;
+            if (below) {
+                const int hp = 31 - __clz(below);
+                const int k = __popc(heads & ((1u << hp) - 1));
+                src = (ne == (0xffffffffu >> (32 - __popc(ne)))) ? k : (int)__fns(ne, 0, k + 1);
+            }
+            const int tb = __shfl_sync(0xffffffffu, q.b, src);
+            const int tb1 = ASCII ? 0 : __shfl_sync(0xffffffffu, q.b1, src);
+            const int tln = __shfl_sync(0xffffffffu, q.ln, src);
+            const int tnc = ASCII ? tln : __shfl_sync(0xffffffffu, q.nc, src);
+            const long long tst = __shfl_sync(0xffffffffu, q.st, src);
+            const int tr = DIRECT ? __shfl_sync(0xffffffffu, q.r, src) : 0;
+            if (below) { mine.b = tb; mine.b1 = tb1; mine.ln = tln; mine.nc = tnc; mine.st = tst; mine.r = tr; }
+            const int last_b1 = __shfl_sync(0xffffffffu, q.b1, 31);
+            const bool last_live = __shfl_sync(0xffffffffu, (int)live, 31);
+            if (!(last_live && last_b1 < G0 + WTILE && r0 + jb + 32 < n)) break;
+        }
+        HsDesc d = { nullptr, nullptr, 0, 0 };
+        const int g = G0 + lane;
+        if (g < total) {
+            const int dep = g - mine.b;
+            d.dst = DIRECT ? (uint64_t *)(uintptr_t)out_ptr[mine.r] + dep : hashes + g;
+            int off;
+            bool last_ragged;
+            if (ASCII || mine.nc == mine.ln) {
+                off = dep * cc;
+                d.clen = min(cc, mine.ln - off);
+                last_ragged = d.clen < cc;
+            } else {
+                off = chunk_off[g];
+                const int end = (g + 1 < mine.b1 && (int64_t)g + 1 < max_chunks) ? chunk_off[g + 1] : mine.ln;
+                d.clen = end - off;
+                last_ragged = false;
+            }
+            d.p = bytes + mine.st + off;
+            const bool aligned = (((uintptr_t)d.p & 15) == 0);
+            const bool tail_done_by_prep = last_ragged && ((((uintptr_t)bytes + mine.st) & 15) == 0);
+            d.kind = tail_done_by_prep ? 0 : ((aligned && d.clen == 128) ? 1 : 3);
+        }
+        return d;
+    };
+    // stage the tile's full chunks into `b` (one commit group per tile, empty or not)
+    auto stage = [&](const HsDesc &d, uint32_t b) {
+        const uint32_t my_src = d.kind == 1 ? (uint32_t)(((uintptr_t)d.p - base16) >> 4) + 1u : 0u;
+        uint32_t d_even = b + sub * 128 + ((u ^ sub) << 4);
+        const uint32_t d_odd = d_even ^ 64u;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const uint32_t src = __shfl_sync(0xffffffffu, my_src, 4 * k + sub);
+            if (src)
+                cp_async16_stream(((k & 1) ? d_odd : d_even) + k * 512, ubase + ((size_t)src << 4), pol);
+        }
+        cp_async_commit();
+    };
+    auto hash_tile = [&](const HsDesc &d, uint32_t b) {
+        uint64_t h = 0;
+        if (d.kind == 1) h = xxh64_row128(b + lane * 128, lane & 7);
+        else if (d.kind == 3) h = xxh64_global(d.p, d.clen);
+        if (d.kind) *d.dst = h;
+    };
+
+    // ---- prologue: tiles t and t + NW staged, first request of t + 2 NW on its way
+    int t = gw;
+    bool live;
+    HsDesc d0, d1 = { nullptr, nullptr, 0, 0 };
+    {
+        const int r0 = tile_first[t];
+        const bool h1 = t + NW < ntiles;
+        const int r1 = h1 ? tile_first[t + NW] : 0;
+        ReqRec q = load_recs(t, r0, live);
+        d0 = describe(t, r0, q, live);
+        stage(d0, buf);
+        if (h1) {
+            q = load_recs(t + NW, r1, live);
+            d1 = describe(t + NW, r1, q, live);
+            stage(d1, buf_base + WTILE * 128);
+        }
+    }
+    bool has1 = t + NW < ntiles;
+    int r0_next = (t + 2 * NW < ntiles) ? tile_first[t + 2 * NW] : 0;
+    for (;;) {
+        const bool has2 = t + 2 * NW < ntiles;
+        ReqRec q2 = { 0, 0, 0, 0, 0, 0 };
+        bool live2 = false;
+        if (has2) q2 = load_recs(t + 2 * NW, r0_next, live2);
+        const int r0_next3 = (t + 3 * NW < ntiles) ? tile_first[t + 3 * NW] : 0;
+        if (has1) cp_async_wait_group<1>(); else cp_async_wait_group<0>();
+        __syncwarp();
+        hash_tile(d0, buf);
+        __syncwarp();                                         // the buffer is free again
+        HsDesc d2 = { nullptr, nullptr, 0, 0 };
+        if (has2) {
+            d2 = describe(t + 2 * NW, r0_next, q2, live2);
+            stage(d2, buf);
+        }
+        if (!has1) break;
+        d0 = d1; d1 = d2; has1 = has2;
+        t += NW;
+        buf = (buf == buf_base) ? buf_base + WTILE * 128 : buf_base;
+        r0_next = r0_next3;
     }
 }
 
@@ -927,9 +1101,23 @@ int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const int32_t *
         const unsigned long long *op = pp ? pp->out_ptr : nullptr;
 #define B200R_HASH_ARGS d_bytes, d_starts, d_lens, d_nchars, d_chunk_base, tile_first, chunk_off, (int)n, cc, \
                         max_chunks, d_hashes, op
-        if (pp)            k_hash_chunks<true, true><<<ntiles, HASH_WARPS * 32, 0, st>>>(B200R_HASH_ARGS);
-        else if (ascii)    k_hash_chunks<false, true><<<ntiles, HASH_WARPS * 32, 0, st>>>(B200R_HASH_ARGS);
-        else               k_hash_chunks<false, false><<<ntiles, HASH_WARPS * 32, 0, st>>>(B200R_HASH_ARGS);
+        if (g_hash_mode == 1) {
+            if (pp)            k_hash_chunks<true, true><<<ntiles, HASH_WARPS * 32, 0, st>>>(B200R_HASH_ARGS);
+            else if (ascii)    k_hash_chunks<false, true><<<ntiles, HASH_WARPS * 32, 0, st>>>(B200R_HASH_ARGS);
+            else               k_hash_chunks<false, false><<<ntiles, HASH_WARPS * 32, 0, st>>>(B200R_HASH_ARGS);
+        } else {
+            static bool attr_set = false;
+            if (!attr_set) {
+                B200R_CUDA(cudaFuncSetAttribute(k_hash_stream<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, HS_SMEM));
+                B200R_CUDA(cudaFuncSetAttribute(k_hash_stream<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, HS_SMEM));
+                B200R_CUDA(cudaFuncSetAttribute(k_hash_stream<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, HS_SMEM));
+                attr_set = true;
+            }
+            int grid = ntiles < 148 * HS_CTAS_PER_SM ? ntiles : 148 * HS_CTAS_PER_SM;
+            if (pp)            k_hash_stream<true, true><<<grid, HS_WARPS * 32, HS_SMEM, st>>>(B200R_HASH_ARGS);
+            else if (ascii)    k_hash_stream<false, true><<<grid, HS_WARPS * 32, HS_SMEM, st>>>(B200R_HASH_ARGS);
+            else               k_hash_stream<false, false><<<grid, HS_WARPS * 32, HS_SMEM, st>>>(B200R_HASH_ARGS);
+        }
 #undef B200R_HASH_ARGS
         B200R_LAUNCH_CHECK("k_hash_chunks");
     }
@@ -1060,6 +1248,13 @@ int b200r_set_claim_mode(int mode)
 {
     if (mode < 0 || mode > 4) { set_error("b200r_set_claim_mode: 0 auto, 1 thread, 2 warp, 3 half warp, 4 quarter warp"); return B200R_E_INVALID; }
     g_claim_mode = mode;
+    return B200R_OK;
+}
+
+int b200r_set_hash_mode(int mode)
+{
+    if (mode < 0 || mode > 1) { set_error("b200r_set_hash_mode: 0 streaming, 1 one tile per warp"); return B200R_E_INVALID; }
+    g_hash_mode = mode;
     return B200R_OK;
 }
 
