@@ -345,8 +345,8 @@ __device__ __forceinline__ uint64_t xxh64_row128(uint32_t row, int sw)
 // ---------------------------------------------------------------------------
 // k_hash_chunks: one thread per chunk, and every WARP is an independent worker
 // on its own tile of 32 consecutive chunks -- no block-wide barrier anywhere, so
-// the 48 resident warps of an SM (6 CTAs x 8 warps, 4 KB of staging each) are
-// 48 independent latency chains and ~190 KB of prompt bytes stay in flight.
+// the 40 resident warps of an SM (5 CTAs x 8 warps, 4 KB of staging each) are
+// 40 independent latency chains and ~160 KB of prompt bytes stay in flight.
 //   map     tile -> requests with two rounds of independent global loads:
 //           tile_first[tile], then lane j fetches everything about request
 //           r0 + j; head positions are combined with a warp OR-reduction and
@@ -359,6 +359,12 @@ __device__ __forceinline__ uint64_t xxh64_row128(uint32_t row, int sw)
 // Unaligned or multi-byte-UTF-8 chunks take the generic global-memory routine.
 constexpr int WTILE = 32;                 // chunks per warp tile
 constexpr int HASH_WARPS = 8;             // warps per CTA
+// CTAs per SM the hashing kernel is compiled for.  Six fit (40 registers), and alone the kernel
+// is as fast with six as with five; but six fill the register file, and the route stage's
+// kernels of the previous batch -- short, latency-bound, on a higher-priority stream -- then
+// wait for hashing CTAs to retire before they can start.  With five (48 registers) they find
+// room at once: the pipelined step went 74 -> 67 us with the hashing kernel itself unchanged.
+constexpr int HASH_CTAS_PER_SM = 5;
 
 struct ReqRec { int b, b1, ln, nc; long long st; int r; };
 
@@ -366,7 +372,7 @@ struct ReqRec { int b, b1, ln, nc; long long st; int r; };
 // request's last chunk is recognised by its byte range alone.  Chunk indices are 32-bit by
 // construction (chunk_base is int32).
 template <bool DIRECT, bool ASCII>
-__global__ void __launch_bounds__(HASH_WARPS * 32, 6)
+__global__ void __launch_bounds__(HASH_WARPS * 32, HASH_CTAS_PER_SM)
 k_hash_chunks(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ starts,
               const int32_t *__restrict__ lens, const int32_t *__restrict__ nchars,
               const int32_t *__restrict__ chunk_base, const int32_t *__restrict__ tile_first,
@@ -1724,7 +1730,8 @@ int b200r_pipe_create(b200r_trie *t, int32_t depth, b200r_pipe **out)
     // batch before only starts when they are nearly through -- the steps would not overlap.
     int least = 0, greatest = 0;
     B200R_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
-    B200R_CUDA(cudaStreamCreateWithPriority(&p->prep, cudaStreamNonBlocking, greatest));
+    // route steps first; prep and hashing of the following batches fill in behind them
+    B200R_CUDA(cudaStreamCreateWithPriority(&p->prep, cudaStreamNonBlocking, least));
     B200R_CUDA(cudaStreamCreateWithPriority(&p->hash, cudaStreamNonBlocking, least));
     B200R_CUDA(cudaStreamCreateWithPriority(&p->route, cudaStreamNonBlocking, greatest));
     B200R_CUDA(cudaEventCreateWithFlags(&p->inputs, cudaEventDisableTiming));
