@@ -538,12 +538,15 @@ def run_b200(args):
     kern_ms = {k: v[0] / K for k, v in prof.items() if v[1]}
     prof_total = sum(v[0] for v in prof.values())
     core = {k: prof[k] for k in ("prep", "hash", "claim", "select", "commit") if prof[k][1]}
+    if "commit" not in core:                  # select + commit ran as one kernel (k_select_commit)
+        algo["select"] += algo["commit"]
     dom = max(core, key=lambda k: core[k][0])
     dom_ms, dom_n = core[dom]
     from b200_router.trie import claim_kernel_name
     kernel_name = {"prep": "k_prep_scan", "hash": "k_hash_chunks",
                    "claim": claim_kernel_name(args.batch, my_chunks // max(K, 1)),
-                   "select": "k_select", "commit": "k_commit"}[dom]
+                   "select": "k_select_commit" if "commit" not in core else "k_select",
+                   "commit": "k_commit"}[dom]
     achieved = algo[dom] / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else 0.0
     traffic, traffic_commit = load_ncu_traffic(kernel_name)
     per_kernel = {k: {"ms_per_step": core[k][0] / K,

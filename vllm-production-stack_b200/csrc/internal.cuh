@@ -77,7 +77,7 @@ __host__ __device__ inline int part_owner_of(uint64_t h0, int world)
 
 struct Plan {           // carve-up of the caller's scratch buffer
     size_t off_tile_first, off_block_sums, off_nchars, off_chunk_off, off_chunk_base, off_hashes,
-        off_slots, off_leader, off_choice, off_dpre, off_cand, total;
+        off_slots, off_leader, off_choice, off_dpre, off_cand, off_res, total;
 };
 Plan make_plan(int64_t n, int64_t max_chunks, uint32_t flags, bool routing);
 
@@ -105,6 +105,8 @@ struct RouteCore {
     uint32_t *slots; int32_t *leader, *choice, *dpre; uint64_t *cand;
     int32_t *endpoint, *depth; uint64_t *matched;
     const P2PDyn *dyn; const uint32_t *pos; const uint32_t *idx_of_pos; const int32_t *n_dev;
+    unsigned long long *res;   // per request, tagged {root, endpoint | leader}: the fused select + commit
+                               // kernel resolves leader chains through it (NULL: two kernels)
     int claim_kind;       // claim_kind_for()
 };
 int launch_route_core(b200r_trie *t, const RouteCore &rc, cudaStream_t st);

@@ -54,6 +54,7 @@ int cuda_fail(cudaError_t e, const char *what)
 // ------------------------------------------------------------- profiling (internal.cuh)
 int g_claim_mode = 0;          // b200r_set_claim_mode: 0 auto, else claim_kind_for's value
 int g_part_staged = 0;
+int g_fuse_sc = getenv("B200R_NO_FUSED_COMMIT") ? 0 : 1;   // select + commit in one launch where possible
 int g_hash_mode = 1;           // b200r_set_hash_mode: 0 = persistent streaming kernel, 1 = one tile per warp
 bool g_prof_on = false;
 std::vector<ProfSpan> g_spans;
@@ -787,6 +788,59 @@ k_commit(Rec *__restrict__ log, TrieDev *dev, const int32_t *__restrict__ chunk_
 }
 
 
+// select + commit in ONE launch (single GPU, short prompts): a request publishes, in one tagged
+// 64-bit word, either its endpoint (roots) or the position of its leader (followers); followers
+// then chase their chain through those words, waiting for words that are not there yet.  Leaders
+// have strictly smaller positions, i.e. live in the same or an earlier CTA, and nobody waits
+// before it has published, so the waits always end.  Saves a launch and a ramp on the route
+// step's dependent chain.
+__global__ void __launch_bounds__(256)
+k_select_commit(Rec *__restrict__ log, TrieDev *dev, const int32_t *__restrict__ chunk_base,
+                int n, int64_t max_chunks, const uint32_t *__restrict__ slots,
+                const int32_t *__restrict__ dpre, const uint64_t *__restrict__ cand,
+                unsigned long long tag, uint64_t seed, uint64_t seq0, int32_t *__restrict__ leader,
+                int32_t *__restrict__ choice, int32_t *__restrict__ depth_out,
+                uint64_t *__restrict__ matched_out, int32_t *__restrict__ endpoint,
+                unsigned long long *res)
+{
+    constexpr unsigned long long ROOT = 1ULL << 31;
+    for (int base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {
+        const int i = base + threadIdx.x;
+        const bool active = i < n;
+        int l = -1, ch = -1;
+        if (active) {
+            select_request(i, log, chunk_base, nullptr, max_chunks, slots, dpre, cand, tag, seed, seq0, leader,
+                           choice, depth_out, matched_out, 0u, nullptr);
+            l = leader[i]; ch = choice[i];
+            const unsigned long long wv = tag | (l < 0 ? (ROOT | (unsigned long long)(unsigned)(ch + 1))
+                                                      : (unsigned long long)(unsigned)l);
+            *(volatile unsigned long long *)&res[i] = wv;
+        }
+        __syncwarp();
+        if (!active) continue;
+        int e = ch;
+        if (l >= 0) {
+            int j = l;
+            for (;;) {
+                unsigned long long v;
+                do { v = *(volatile unsigned long long *)&res[j]; } while ((v >> 32) != (tag >> 32));
+                if (v & ROOT) { e = (int)(v & 0xFFu) - 1; break; }
+                j = (int)(v & 0x7FFFFFFFu);
+            }
+            matched_out[i] = (e >= 0) ? (1ULL << e) : 0;
+        }
+        endpoint[i] = e;
+        if (e < 0) continue;
+        const uint64_t bit = 1ULL << e;
+        if (!(dev->root_mask & bit)) atomicOr((unsigned long long *)&dev->root_mask, bit);
+        const ReqSpan sp = req_span(chunk_base, nullptr, i, max_chunks);
+        for (int d = depth_out[i]; d < sp.C; d++) {
+            const uint32_t x = slots[sp.b0 + d];
+            if (x != SLOT_NONE) atomicOr((unsigned long long *)&log[x & IDX_MASK].mask, bit);
+        }
+    }
+}
+
 // The same with a warp per request, lanes over depths: long prompts (C4: 256 chunks, half of
 // them new) make the thread version a chain of a hundred dependent atomics.
 __global__ void __launch_bounds__(256)
@@ -1031,6 +1085,7 @@ Plan make_plan(int64_t n, int64_t max_chunks, uint32_t flags, bool routing)
     p.off_choice = o;     o += routing ? align_up((n + 1) * 4) : 0;
     p.off_dpre = o;       o += routing ? align_up((n + 1) * 4) : 0;
     p.off_cand = o;       o += routing ? align_up((n + 1) * 8) : 0;
+    p.off_res = o;        o += routing ? align_up((n + 1) * 8) : 0;
     p.total = o + 256;
     return p;
 }
@@ -1201,6 +1256,9 @@ int launch_route_core(b200r_trie *t, const RouteCore &rc, cudaStream_t st)
     a.max_chunks = rc.max_chunks;
     a.avail = rc.avail; a.tag = tag; a.slots = rc.slots; a.dpre = rc.dpre; a.cand = rc.cand;
     a.pos = rc.pos;
+    const bool fused_sc = rc.res && !rc.pos && !rc.idx_of_pos && !rc.dyn && !rc.n_dev && !rc.chunk_end &&
+                          rc.claim_kind == 1 && g_fuse_sc;
+    a.res = fused_sc ? rc.res : nullptr;
     const int nn = rc.n_dev ? 0 : (int)rc.n;
     const int tblocks = (int)((rc.n + 255) / 256);
     { ProfScope ps__(PK_CLAIM, st); g_launches += 1;
@@ -1216,6 +1274,14 @@ int launch_route_core(b200r_trie *t, const RouteCore &rc, cudaStream_t st)
         k_walk<W_CLAIM, 32><<<walk_grid(rc.n), WARPS_PER_CTA * 32, 0, st>>>(a, nn, rc.n_dev);
     }
     B200R_LAUNCH_CHECK("k_walk<claim>");
+    }
+    if (fused_sc) {
+        ProfScope ps__(PK_SELECT, st); g_launches += 1;
+        k_select_commit<<<tblocks, 256, 0, st>>>(t->log, t->dev, rc.chunk_base, nn, rc.max_chunks, rc.slots, rc.dpre,
+                                                rc.cand, tag, rc.seed, rc.seq0, rc.leader, rc.choice, rc.depth,
+                                                rc.matched, rc.endpoint, rc.res);
+        B200R_LAUNCH_CHECK("k_select_commit");
+        return B200R_OK;
     }
     { ProfScope ps__(PK_SELECT, st); g_launches += 1;
     k_select<<<tblocks, 256, 0, st>>>(t->log, rc.chunk_base, rc.chunk_end, nn, rc.max_chunks, rc.slots, rc.dpre,
@@ -1591,6 +1657,7 @@ static int route_from(b200r_trie *t, const uint64_t *hashes, const int32_t *chun
     rc.choice = (int32_t *)(sc + p.off_choice);
     rc.dpre = (int32_t *)(sc + p.off_dpre);
     rc.cand = (uint64_t *)(sc + p.off_cand);
+    rc.res = (unsigned long long *)(sc + p.off_res);
     rc.endpoint = d_endpoint; rc.depth = d_match_depth; rc.matched = d_matched_mask;
     // a thread per request while prompts are short on average, a warp per request beyond
     rc.claim_kind = claim_kind_for(n, max_chunks);

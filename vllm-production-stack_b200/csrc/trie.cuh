@@ -290,6 +290,8 @@ struct WalkArgs {
     int32_t *depth_out;           // lookup
     uint64_t *matched_out;        // lookup
     const int32_t *endpoint;      // insert
+    unsigned long long *res;      // claim (thread kernel): per-request word of the fused select +
+                                  // commit kernel, zeroed here (scratch may hold another table's words)
     const uint32_t *pos;          // claim: global position of request i (NULL: i itself) -- the
                                   // index that "first toucher" marks are expressed in
 };
@@ -549,6 +551,7 @@ k_claim_thread(WalkArgs a, int n, const int32_t *__restrict__ n_dev)
         const bool active = i < n;
         ReqSpan sp = { 0, 0 };
         if (active) sp = req_span(a.chunk_base, a.chunk_end, i, a.max_chunks);
+        if (active && a.res) a.res[i] = 0;
         const int C = sp.C;
         const uint64_t *hs = a.hashes + sp.b0;
         uint32_t *sl = a.slots + sp.b0;
