@@ -91,11 +91,6 @@ int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const int32_t *
                 const Plan &p, TrieDev *dev, cudaStream_t st, int phase = 0,
                 const PartPlace *pp = nullptr);
 
-// CSR of given per-request chunk counts; the count of requests is known only on the device
-int launch_prep_counts(const int32_t *d_counts, int64_t n_max, const int32_t *n_dev,
-                       int32_t *block_sums, int32_t *chunk_base, int64_t c_max, TrieDev *dev,
-                       cudaStream_t st);
-
 // claim -> select -> commit over chunk hashes already in memory.  `n` sizes the grids; when the
 // real count lives on the device (n_dev) it is an estimate and the kernels stride.
 struct RouteCore {

@@ -1185,20 +1185,6 @@ int launch_hash(const uint8_t *d_bytes, const int64_t *d_starts, const int32_t *
     return B200R_OK;
 }
 
-int launch_prep_counts(const int32_t *d_counts, int64_t n_max, const int32_t *n_dev,
-                       int32_t *block_sums, int32_t *chunk_base, int64_t c_max, TrieDev *dev,
-                       cudaStream_t st)
-{
-    const int nblk = (int)((n_max + PREP_BLOCK - 1) / PREP_BLOCK);
-    g_launches += 2;
-    k_prep_sums<<<nblk, PREP_BLOCK, 0, st>>>(d_counts, nullptr, (int)n_max, 1, block_sums, n_dev);
-    B200R_LAUNCH_CHECK("k_prep_sums(counts)");
-    k_prep_scan<<<nblk, PREP_BLOCK, 0, st>>>(d_counts, nullptr, (int)n_max, 1, block_sums, chunk_base,
-                                             nullptr, c_max, dev, nullptr, nullptr, nullptr, n_dev, PartPlace());
-    B200R_LAUNCH_CHECK("k_prep_scan(counts)");
-    return B200R_OK;
-}
-
 TrieRef trie_ref(const b200r_trie *t)
 {
     TrieRef r;
