@@ -189,6 +189,8 @@ class PartitionedPrefixRouter:
         self._keep = [None] * PART_SETS            # device copies of host inputs, by buffer set
         self._sc = [None] * PART_SETS              # hash-stage scratch, by buffer set
         self._retired = []                         # outgrown scratch buffers (may still be in use)
+        self._sc_lim = [None] * PART_SETS          # (n, max_chunks, flags) each scratch buffer is good for
+        self._const_ptrs = None
 
     @staticmethod
     def capacities(max_requests: int, max_chunks: int):
@@ -250,7 +252,14 @@ class PartitionedPrefixRouter:
         L = _lib.lib()
         self.epoch += 1
         n = p.n
-        with torch.cuda.device(self.device):
+        # the wrapper is on the critical path of every batch (the step is bound by host time):
+        # constant pointers are cached, the device is switched only when it is not current
+        dev_idx = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        switch = torch.cuda.current_device() != dev_idx
+        if switch:
+            prev_dev = torch.cuda.current_device()
+            torch.cuda.set_device(dev_idx)
+        try:
             if p.bytes.device != self.device:
                 _lib.check(L.b200r_part_begin(self.trie._h, self.epoch))
                 k = self.epoch % PART_SETS
@@ -258,24 +267,43 @@ class PartitionedPrefixRouter:
                 self._keep[k] = p = self._copy_on_prep_stream(p)
                 inputs_ready = True
             flags = _lib.F_ALL_ASCII if p.all_ascii else 0
-            need = L.b200r_prefix_route_scratch_bytes(n, p.max_chunks, flags)
-            sc = self._step_scratch(need)
+            sc = self._step_scratch_for(n, p.max_chunks, flags)
             self._shape = (n,)
             if out is None:
                 out = (torch.empty(max(n, 1), dtype=torch.int32, device=self.device),
                        torch.empty(max(n, 1), dtype=torch.int32, device=self.device),
                        torch.empty(max(n, 1), dtype=torch.int64, device=self.device))
             ep, depth, matched = out
+            c = self._const_ptrs
+            if c is None:
+                c = self._const_ptrs = (self.trie._h, self.peer_bases.data_ptr(), self.symm.data_ptr(),
+                                        self.work.data_ptr())
             rc = L.b200r_part_step(
-                self.trie._h, p.bytes.data_ptr(), p.starts.data_ptr(), p.lens.data_ptr(),
+                c[0], p.bytes.data_ptr(), p.starts.data_ptr(), p.lens.data_ptr(),
                 None if p.nchars is None else p.nchars.data_ptr(), n, p.max_chunks, flags,
-                avail_mask & M64, seed & M64, self.peer_bases.data_ptr(), self.symm.data_ptr(),
-                self.world, self.rank, self.cap, self.rcap, self.epoch, self.work.data_ptr(),
+                avail_mask & M64, seed & M64, c[1], c[2],
+                self.world, self.rank, self.cap, self.rcap, self.epoch, c[3],
                 sc.data_ptr(), sc.numel(), ep.data_ptr(), depth.data_ptr(), matched.data_ptr(),
-                1 if inputs_ready else 0, torch.cuda.current_stream(self.device).cuda_stream)
+                1 if inputs_ready else 0, torch.cuda.current_stream().cuda_stream)
             if rc:
                 _lib.check(rc)
+        finally:
+            if switch:
+                torch.cuda.set_device(prev_dev)
+        if ep.shape[0] == n:                      # a tensor slice costs microseconds
+            return ep, depth, matched
         return ep[:n], depth[:n], matched[:n]
+
+    def _step_scratch_for(self, n: int, max_chunks: int, flags: int) -> torch.Tensor:
+        # the size is monotone in n and max_chunks: ask the library only when either grew
+        k = self.epoch % PART_SETS
+        lim = self._sc_lim[k]
+        if lim is not None and n <= lim[0] and max_chunks <= lim[1] and flags == lim[2]:
+            return self._sc[k]
+        need = _lib.lib().b200r_prefix_route_scratch_bytes(n, max_chunks, flags)
+        sc = self._step_scratch(need)
+        self._sc_lim[k] = (n, max_chunks, flags)
+        return sc
 
     def _step_scratch(self, nbytes: int) -> torch.Tensor:
         # one buffer per set in turn: the prep of batch b+1 runs next to the hashing of batch b
